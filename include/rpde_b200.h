@@ -1,0 +1,154 @@
+/* rpde_b200.h -- C ABI of the B200-native spectral-convolution path of resolution-pde.
+ *
+ * One shared library (librpde_b200.so), plain pointers and sizes, no torch types.  Every entry point
+ * enqueues work on the given CUDA stream and returns immediately: 0 on success, a negative RPDE_E_* code
+ * otherwise (text via rpde_last_error(), thread-local).  The library never allocates, frees or retains
+ * device memory: the caller owns inputs, outputs and workspaces (sizes from the *_workspace_bytes
+ * queries) and keeps them alive until the stream work has completed.  All tensors are contiguous fp32
+ * in the documented layout; complex tensors are interleaved (re, im) pairs.  The calls are re-entrant,
+ * hold no global mutable state, never synchronise and are CUDA-graph capturable.
+ *
+ * Each entry point replaces a piece of the reference's PyTorch operator path (file:line cited per
+ * function; paths are relative to the reference repository root).
+ */
+#ifndef RPDE_B200_H
+#define RPDE_B200_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* rpde_stream_t; /* a cudaStream_t */
+
+enum {
+  RPDE_OK = 0,
+  RPDE_E_INVALID = -1,     /* bad argument / unsupported shape */
+  RPDE_E_WORKSPACE = -2,   /* workspace too small */
+  RPDE_E_CUDA = -3,        /* CUDA launch error (text in rpde_last_error) */
+  RPDE_E_MODES = -4        /* more modes requested than the spectrum holds (reference raises RuntimeError) */
+};
+enum { RPDE_ACT_NONE = 0, RPDE_ACT_GELU = 1, RPDE_ACT_RELU = 2 };
+enum { RPDE_MIX_FULL = 0, RPDE_MIX_LOWPASS = 1 };
+/* DFT table kinds (rpde_dft_table) */
+enum { RPDE_DFT_R2C_ANALYSIS = 0, RPDE_DFT_C2R_SYNTHESIS = 1, RPDE_DFT_C2C_ANALYSIS_ROWS = 2, RPDE_DFT_C2C_SYNTHESIS_ROWS = 3 };
+/* precision of the contraction engine */
+enum { RPDE_PREC_FP32 = 0, RPDE_PREC_3XTF32 = 1, RPDE_PREC_TF32 = 2 };
+
+int rpde_version(void);
+const char* rpde_last_error(void);
+/* Selects the contraction engine for aligned shapes (per thread). FP32 = CUDA-core FMA everywhere. */
+int rpde_set_precision(int prec);
+int rpde_get_precision(void);
+
+/* Twiddle / truncated-DFT tables, generated on the device in fp64 and rounded once to fp32.
+ * Replaces the cuFFT/pocketfft plans behind torch.fft.rfft/irfft/rfft2/irfft2
+ * (models/spectral_convolution.py:41,54,82,97,165,198,265,284,289,308).
+ *   kind 0: out[k][2][n]   analysis, scale s          kind 1: out[n][k][2]   synthesis (c_k weights), scale s
+ *   kind 2: out[j][2][2][n] C2C analysis of rows [0,m1) U [n-m1,n)   kind 3: out[n][2][j][2] its inverse  */
+int rpde_dft_table(float* out, int kind, int n, int k, int m1, double scale, rpde_stream_t stream);
+
+/* ---- FNO SpectralConv1d (models/spectral_convolution.py:24-55), channels-first (B,I,N) -> (B,O,N) --------
+ * w: complex64 (I,O,modes) interleaved.  fa: kind-0 table [modes][2][N] scale 1, fs: kind-1 table scale 1/N.
+ * y = act(spectral(x) + (beta ? y : 0)); z (optional) receives the pre-activation.  spec (B*2I*modes floats)
+ * receives the retained spectrum for the backward pass.  modes > N/2+1 -> RPDE_E_MODES. */
+size_t rpde_spectral1d_workspace_bytes(int B, int I, int O, int N, int modes);
+int rpde_spectral1d_fwd(const float* x, const float* w, const float* fa, const float* fs, float* spec, float* y,
+                        float* z, int B, int I, int O, int N, int modes, int beta, int act, void* ws,
+                        size_t ws_bytes, rpde_stream_t stream);
+/* dx (+)= adjoint wrt x ; dw (complex64 (I,O,modes)) = gradient wrt w.  dx may be NULL. */
+int rpde_spectral1d_bwd(const float* dy, const float* w, const float* fa, const float* fs, const float* spec,
+                        float* dx, int dx_accumulate, float* dw, int B, int I, int O, int N, int modes, void* ws,
+                        size_t ws_bytes, rpde_stream_t stream);
+
+/* ---- FNO SpectralConv2d (models/spectral_convolution.py:61-98), (B,I,H,W) -> (B,O,H,W) ---------------------
+ * w1, w2: complex64 (I,O,m1,m2).  fa_y/fs_y: kind 0/1 tables for axis W with k = m2 (scales 1, 1/W);
+ * gf/gi: kind 2/3 tables for axis H with j = 2*m1 (scales 1, 1/H).  spec: (2*m1*m2*B*2I floats). */
+size_t rpde_spectral2d_workspace_bytes(int B, int I, int O, int H, int W, int m1, int m2);
+int rpde_spectral2d_fwd(const float* x, const float* w1, const float* w2, const float* fa_y, const float* fs_y,
+                        const float* gf, const float* gi, float* spec, float* y, float* z, int B, int I, int O,
+                        int H, int W, int m1, int m2, int beta, int act, void* ws, size_t ws_bytes,
+                        rpde_stream_t stream);
+int rpde_spectral2d_bwd(const float* dy, const float* w1, const float* w2, const float* fa_y, const float* fs_y,
+                        const float* gf, const float* gi, const float* spec, float* dx, int dx_accumulate,
+                        float* dw1, float* dw2, int B, int I, int O, int H, int W, int m1, int m2, void* ws,
+                        size_t ws_bytes, rpde_stream_t stream);
+
+/* ---- F-FNO factorised spectral pass along one axis (models/spectral_convolution.py:159-204, 256-318) -------
+ * x is channels-last, viewed as [outer][n][rest][C]; the transform runs along n, the complex channel mixing
+ * over C with w = fourier_weight (C,C,w_modes,2) restricted to its first k = min(n_modes, n/2+1) modes.
+ * y (+)= irfft(mix(rfft(x)[:k])) ; spec ([outer][k][2][rest][C]) is kept for the backward pass.
+ * 1-D layer: outer=B, rest=1.  2-D layer: y-pass outer=B*M, n=N, rest=1; x-pass outer=B, n=M, rest=N with
+ * accumulate=1 (the reference's xx + xy, spectral_convolution.py:313). */
+size_t rpde_ffno_axis_workspace_bytes(long long outer, int n, long long rest, int C, int k);
+int rpde_ffno_axis_fwd(const float* x, const float* w, const float* fa, const float* fs, float* spec, float* y,
+                       int accumulate, long long outer, int n, long long rest, int C, int k, int w_modes, int mix,
+                       void* ws, size_t ws_bytes, rpde_stream_t stream);
+/* dx (+)= ... ; dw (C,C,w_modes,2) (+)= ... (modes >= k receive exactly zero).  dw may be NULL (low-pass). */
+int rpde_ffno_axis_bwd(const float* dy, const float* w, const float* fa, const float* fs, const float* spec,
+                       float* dx, int dx_accumulate, float* dw, int dw_accumulate, long long outer, int n,
+                       long long rest, int C, int k, int w_modes, int mix, void* ws, size_t ws_bytes,
+                       rpde_stream_t stream);
+
+/* ---- channels-last Linear with fused bias / activation (models/custom_layer.py:49-68 FeedForward layers,
+ * ffno.py:55,75,160,179 in_proj/out_proj).  y[T,out] = act(x[T,in] W^T + b); z (optional) = pre-activation.
+ * y_cf_spatial > 0: y is written channels-first (T/S, out, S) (ffno.py:123, 235 final permute). */
+int rpde_linear_fwd(const float* x, const float* w, const float* bias, float* y, float* z, long long T, int in,
+                    int out, int act, long long y_cf_spatial, rpde_stream_t stream);
+/* dx (+)= (dy W) * act'(zprev)   (zprev/dact describe the activation that produced this layer's input) */
+int rpde_linear_bwd_input(const float* dy, const float* w, const float* zprev, int dact, float* dx, int accumulate,
+                          long long T, int in, int out, long long dy_cf_spatial, rpde_stream_t stream);
+/* dw[out,in] = dy^T x ; db[out] = column sums of dy (db may be NULL) */
+int rpde_linear_bwd_params(const float* dy, const float* x, float* dw, float* db, long long T, int in, int out,
+                           long long dy_cf_spatial, rpde_stream_t stream);
+
+/* ---- channels-first 1x1 convolution (models/fno.py:30,93 lifting; fno_blocks.py:29,38-39,67,76-77) ----------
+ * y[b,o,s] = act(sum_i w[o,i] x[b,i,s] + bias[o] + (beta ? y : 0)) */
+int rpde_conv1x1_fwd(const float* x, const float* w, const float* bias, float* y, float* z, int B, int I, int O,
+                     long long S, int act, int beta, rpde_stream_t stream);
+int rpde_conv1x1_bwd_input(const float* dy, const float* w, const float* zprev, int dact, float* dx, int accumulate,
+                           int B, int I, int O, long long S, rpde_stream_t stream);
+int rpde_conv1x1_bwd_params(const float* dy, const float* x, float* dw, float* db, int B, int I, int O,
+                            long long S, rpde_stream_t stream);
+
+/* out = dy * act'(z)   (backward of the FNO block activation, fno_blocks.py:33,71) */
+int rpde_act_bwd(const float* dy, const float* z, float* out, long long n, int act, rpde_stream_t stream);
+/* out = (res ? res : 0) + act(x)   (FSpectralConv1d activation + FFNO1D residual, spectral_convolution.py:155; ffno.py:118) */
+int rpde_act_fwd(const float* x, const float* res, float* out, long long n, int act, rpde_stream_t stream);
+
+/* ---- LayerNorm over the last dim with optional residual (custom_layer.py:61-62; ffno.py:118,230) ----------
+ * y = (res ? res : 0) + LN(x) * gamma + beta ; mean/rstd (T floats each, optional) kept for backward. */
+int rpde_layernorm_fwd(const float* x, const float* res, const float* gamma, const float* beta, float* y,
+                       float* mean, float* rstd, long long T, int C, float eps, rpde_stream_t stream);
+int rpde_layernorm_bwd(const float* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
+                       float* dx, float* dgamma, float* dbeta, long long T, int C, rpde_stream_t stream);
+
+/* ---- weight-normed Linear weights (custom_layer.py:70-108, legacy weight_norm dim=0) ------------------- */
+int rpde_weight_norm_fwd(const float* v, const float* g, float* w, float* norms, int out, int in,
+                         rpde_stream_t stream);
+int rpde_weight_norm_bwd(const float* dw, const float* v, const float* g, const float* norms, float* dv, float* dg,
+                         int out, int in, rpde_stream_t stream);
+
+/* ---- coordinate-grid concatenation (fno.py:56-68,131-141; ffno.py:98-109,210-222) ------------------------
+ * x (B,Cin,S0,S1) channels-first -> out with G = (g0?1:0)+(g1?1:0) extra channels, channels-first or -last. */
+int rpde_concat_grid_fwd(const float* x, const float* g0, const float* g1, float* out, int B, int Cin, int S0,
+                         int S1, int channels_last, rpde_stream_t stream);
+int rpde_concat_grid_bwd(const float* dout, float* dx, int B, int Cin, int S0, int S1, int G, int channels_last,
+                         rpde_stream_t stream);
+
+/* ---- RelativeL2Loss (utils/loss.py:31-59).  acc: 2*B floats scratch kept for backward; per_sample: B floats;
+ * loss: 1 float (reduce_mode 1 = mean, 2 = sum, 0 = none -> only per_sample is written). */
+int rpde_rel_l2_fwd(const float* x, const float* y, float* acc, float* per_sample, float* loss, int B, long long S,
+                    int reduce_mode, rpde_stream_t stream);
+int rpde_rel_l2_bwd(const float* x, const float* y, const float* acc, const float* gout, float* dx, int B,
+                    long long S, int reduce_mode, rpde_stream_t stream);
+
+/* ---- raw contraction (test hook): C[M,N] = A[M,K] B[K,N], row-major, through the selected engine -------- */
+int rpde_matmul(const float* a, const float* b, float* c, int M, int N, int K, int trans_a, int trans_b,
+                rpde_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RPDE_B200_H */

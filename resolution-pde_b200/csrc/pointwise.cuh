@@ -1,0 +1,407 @@
+// Non-contraction kernels of the spectral path: DFT tables, spectral-weight packing, LayerNorm,
+// relative-L2 loss, grid concatenation, weight-norm and bias-gradient reductions.
+#pragma once
+#include "common.cuh"
+
+namespace rpde {
+
+// ----------------------------------------------------------------------------------------------
+// DFT tables, generated in fp64 with exact integer phase reduction (k*n mod N) and sincospi.
+// kind 0: R2C analysis   out[K][2][N]       row (k,0) = s*cos(2 pi k n/N), row (k,1) = -s*sin
+// kind 1: C2R synthesis  out[N][K][2]       col (k,0) = c_k*s*cos,         col (k,1) = -c_k*s*sin
+//         c_k = 1 for k = 0 and for the Nyquist bin (N even, k = N/2), else 2; the sine entries of
+//         those two bins are exactly zero, which reproduces irfft's "imaginary part ignored" rule.
+// kind 2: C2C analysis over selected rows   out[J][2][2][N]  (j,ro) x (ri,n); f(j) = j (j < m1) or N-2*m1+j
+// kind 3: C2C synthesis over selected rows  out[N][2][J][2]  (n,ro) x (j,ri), scaled by s; columns of the
+//         first block whose row index is overwritten by the second block (2*m1 > N) are zero.
+// ----------------------------------------------------------------------------------------------
+__global__ void dft_table_kernel(float* __restrict__ out, int kind, int N, int K, int m1, double s) {
+  const long long total = (kind <= 1) ? 2LL * K * N : 4LL * K * N;
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
+       e += (long long)gridDim.x * blockDim.x) {
+    if (kind == 0) {
+      const int n = (int)(e % N);
+      const int ri = (int)((e / N) & 1);
+      const int k = (int)(e / (2LL * N));
+      const long long r = ((long long)k * n) % N;
+      double sn, cs;
+      sincospi(2.0 * (double)r / (double)N, &sn, &cs);
+      out[e] = (float)(ri == 0 ? s * cs : -s * sn);
+    } else if (kind == 1) {
+      const int ri = (int)(e & 1);
+      const int k = (int)((e >> 1) % K);
+      const int n = (int)(e / (2LL * K));
+      const long long r = ((long long)k * n) % N;
+      double sn, cs;
+      sincospi(2.0 * (double)r / (double)N, &sn, &cs);
+      const bool edge = (k == 0) || (2 * k == N);
+      const double c = edge ? 1.0 : 2.0;
+      out[e] = (float)(ri == 0 ? c * s * cs : (edge ? 0.0 : -c * s * sn));
+    } else if (kind == 2) {
+      // e = ((j*2 + ro)*2 + ri)*N + n
+      const int n = (int)(e % N);
+      const int ri = (int)((e / N) & 1);
+      const int ro = (int)((e / (2LL * N)) & 1);
+      const int j = (int)(e / (4LL * N));
+      const int f = j < m1 ? j : N - 2 * m1 + j;
+      const long long r = ((long long)f * n) % N;
+      double sn, cs;
+      sincospi(2.0 * (double)r / (double)N, &sn, &cs);
+      // Yr = sum Xr cos + Xi sin ; Yi = sum -Xr sin + Xi cos
+      double v = (ro == 0) ? (ri == 0 ? cs : sn) : (ri == 0 ? -sn : cs);
+      out[e] = (float)(s * v);
+    } else {
+      // e = ((n*2 + ro)*K + j)*2 + ri
+      const int ri = (int)(e & 1);
+      const int j = (int)((e >> 1) % K);
+      const int ro = (int)((e / (2LL * K)) & 1);
+      const int n = (int)(e / (4LL * K));
+      const int f = j < m1 ? j : N - 2 * m1 + j;
+      const bool dropped = (j < m1) && (f >= N - m1);  // overwritten by the second block
+      const long long r = ((long long)f * n) % N;
+      double sn, cs;
+      sincospi(2.0 * (double)r / (double)N, &sn, &cs);
+      // Zr = sum Or cos - Oi sin ; Zi = sum Or sin + Oi cos
+      double v = (ro == 0) ? (ri == 0 ? cs : -sn) : (ri == 0 ? sn : cs);
+      out[e] = dropped ? 0.f : (float)(s * v);
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------------------------
+// Spectral weights.  Parameter layout (I, O, modes, 2) fp32 == view_as_real of complex (I, O, modes).
+// Packed layout per retained mode: Wp[mode][(ri,i)][(ro,o)] = [[Wr, Wi], [-Wi, Wr]], so the complex
+// channel mixing is one real (rows x 2I)(2I x 2O) product per mode.
+// ----------------------------------------------------------------------------------------------
+__global__ void pack_weights_kernel(const float* __restrict__ w, float* __restrict__ wp, int I, int O,
+                                    int modes, int keep, int sub, int sub_keep) {
+  // modes = sub_total * ... : a mode index is (a, b) with b < sub (sub = modes2 for 2-D weights, 1 otherwise);
+  // we keep a < keep and b < sub_keep.  Packed mode index = a * sub_keep + b.
+  const long long total = (long long)keep * sub_keep * 2 * I * 2 * O;
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
+       e += (long long)gridDim.x * blockDim.x) {
+    const int o = (int)(e % O);
+    const int ro = (int)((e / O) & 1);
+    const int i = (int)((e / (2LL * O)) % I);
+    const int ri = (int)((e / (2LL * O * I)) & 1);
+    const long long md = e / (4LL * O * I);
+    const int b = (int)(md % sub_keep), a = (int)(md / sub_keep);
+    const long long src = (((long long)i * O + o) * modes + (long long)a * sub + b) * 2;
+    const float wr = w[src], wi = w[src + 1];
+    wp[e] = (ri == ro) ? wr : (ri == 0 ? wi : -wi);
+  }
+}
+
+// dW[i,o,mode,{re,im}] (+)= unpack(P), zero for modes that were not retained.
+__global__ void unpack_wgrad_kernel(const float* __restrict__ P, float* __restrict__ dw, int I, int O,
+                                    int modes, int keep, int sub, int sub_keep, int accumulate) {
+  const long long total = (long long)I * O * modes;
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
+       e += (long long)gridDim.x * blockDim.x) {
+    const int md = (int)(e % modes);
+    const int o = (int)((e / modes) % O);
+    const int i = (int)(e / ((long long)modes * O));
+    const int a = md / sub, b = md % sub;
+    float gr = 0.f, gi = 0.f;
+    if (a < keep && b < sub_keep) {
+      const long long base = ((long long)a * sub_keep + b) * 4LL * I * O;
+      const long long r0 = base + ((long long)i) * 2 * O;        // row (0,i)
+      const long long r1 = base + ((long long)(I + i)) * 2 * O;  // row (1,i)
+      gr = P[r0 + o] + P[r1 + O + o];
+      gi = P[r0 + O + o] - P[r1 + o];
+    }
+    if (accumulate) {
+      dw[2 * e] += gr;
+      dw[2 * e + 1] += gi;
+    } else {
+      dw[2 * e] = gr;
+      dw[2 * e + 1] = gi;
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------------------------
+// LayerNorm over the last dim (eps inside the sqrt, biased variance), optional residual:
+//   y = res + (x - mean) * rstd * gamma + beta.          One warp per row.
+// ----------------------------------------------------------------------------------------------
+__global__ void layernorm_fwd_kernel(const float* __restrict__ x, const float* __restrict__ res,
+                                     const float* __restrict__ gamma, const float* __restrict__ beta,
+                                     float* __restrict__ y, float* __restrict__ mean, float* __restrict__ rstd,
+                                     long long T, int C, float eps) {
+  const int lane = threadIdx.x & 31;
+  const long long row = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  if (row >= T) return;
+  const float* xr = x + row * C;
+  float s = 0.f;
+  for (int c = lane; c < C; c += 32) s += xr[c];
+  const float mu = warp_sum(s) / (float)C;
+  float v = 0.f;
+  for (int c = lane; c < C; c += 32) {
+    const float d = xr[c] - mu;
+    v += d * d;
+  }
+  const float rs = rsqrtf(warp_sum(v) / (float)C + eps);
+  if (lane == 0 && mean) {
+    mean[row] = mu;
+    rstd[row] = rs;
+  }
+  for (int c = lane; c < C; c += 32) {
+    float o = (xr[c] - mu) * rs * gamma[c] + beta[c];
+    if (res) o += res[row * C + c];
+    y[row * C + c] = o;
+  }
+}
+
+// dx = rstd * (g - mean(g) - xhat * mean(g * xhat)),  g = dy * gamma;  dgamma += dy * xhat;  dbeta += dy.
+// Block = 8 warps, each warp walks rows; per-block partial dgamma/dbeta in shared memory (C <= 1024).
+__global__ void layernorm_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ x,
+                                     const float* __restrict__ gamma, const float* __restrict__ mean,
+                                     const float* __restrict__ rstd, float* __restrict__ dx,
+                                     float* __restrict__ dgamma, float* __restrict__ dbeta, long long T, int C,
+                                     int rows_per_block) {
+  extern __shared__ float sm[];  // [2][C]
+  float* sg = sm;
+  float* sb = sm + C;
+  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) sm[c] = 0.f;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const long long r0 = (long long)blockIdx.x * rows_per_block;
+  const long long r1 = min(T, r0 + rows_per_block);
+  for (long long row = r0 + warp; row < r1; row += nw) {
+    const float mu = mean[row], rs = rstd[row];
+    const float* xr = x + row * C;
+    const float* gr = dy + row * C;
+    float s1 = 0.f, s2 = 0.f;
+    for (int c = lane; c < C; c += 32) {
+      const float xh = (xr[c] - mu) * rs, g = gr[c] * gamma[c];
+      s1 += g;
+      s2 += g * xh;
+    }
+    s1 = warp_sum(s1) / (float)C;
+    s2 = warp_sum(s2) / (float)C;
+    for (int c = lane; c < C; c += 32) {
+      const float xh = (xr[c] - mu) * rs, d = gr[c];
+      dx[row * C + c] = rs * (d * gamma[c] - s1 - xh * s2);
+      atomicAdd(&sg[c], d * xh);
+      atomicAdd(&sb[c], d);
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    atomicAdd(&dgamma[c], sg[c]);
+    atomicAdd(&dbeta[c], sb[c]);
+  }
+}
+
+// ----------------------------------------------------------------------------------------------
+// out[c] += sum over (o, i) of X[o][c][i]      (bias gradients: channels-last inner = 1, channels-first inner = S)
+// ----------------------------------------------------------------------------------------------
+__global__ void reduce_channels_kernel(const float* __restrict__ X, float* __restrict__ out, long long outer, int C,
+                                       long long inner, long long chunk) {
+  // grid.x over chunks of the flattened (outer*inner) range, grid.y over blocks of 32 channels when inner == 1
+  if (inner == 1) {
+    // threads: x = channel within 32-block (coalesced), y = row lane
+    const int c = blockIdx.y * 32 + (threadIdx.x & 31);
+    const int rl = threadIdx.x >> 5, nr = blockDim.x >> 5;
+    const long long r0 = blockIdx.x * chunk, r1 = min(outer, r0 + chunk);
+    float s = 0.f;
+    if (c < C)
+      for (long long r = r0 + rl; r < r1; r += nr) s += X[r * C + c];
+    __shared__ float red[8][33];
+    red[rl][threadIdx.x & 31] = s;
+    __syncthreads();
+    if (rl == 0 && c < C) {
+      float tsum = 0.f;
+      for (int k = 0; k < nr; ++k) tsum += red[k][threadIdx.x & 31];
+      atomicAdd(&out[c], tsum);
+    }
+  } else {
+    // one channel per blockIdx.y, reduce over (outer, inner) chunk
+    const int c = blockIdx.y;
+    const long long total = outer * inner;
+    const long long e0 = blockIdx.x * chunk, e1 = min(total, e0 + chunk);
+    float s = 0.f;
+    for (long long e = e0 + threadIdx.x; e < e1; e += blockDim.x) {
+      const long long o = e / inner, i = e - o * inner;
+      s += X[(o * C + c) * inner + i];
+    }
+    s = warp_sum(s);
+    __shared__ float red[8];
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float tsum = 0.f;
+      for (int k = 0; k < (int)(blockDim.x >> 5); ++k) tsum += red[k];
+      atomicAdd(&out[c], tsum);
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------------------------
+// Relative L2 loss (utils/loss.py:31-59): per sample ||x-y|| / (||y|| + 1e-8), then mean / sum / none.
+// acc[b] = {sum (x-y)^2, sum y^2}  (zero-filled by the caller)
+// ----------------------------------------------------------------------------------------------
+__global__ void rel_l2_partial_kernel(const float* __restrict__ x, const float* __restrict__ y,
+                                      float* __restrict__ acc, long long S, long long chunk) {
+  const int b = blockIdx.y;
+  const long long e0 = blockIdx.x * chunk, e1 = min(S, e0 + chunk);
+  const float* xb = x + (long long)b * S;
+  const float* yb = y + (long long)b * S;
+  float d2 = 0.f, y2 = 0.f;
+  for (long long e = e0 + threadIdx.x; e < e1; e += blockDim.x) {
+    const float yv = yb[e], d = xb[e] - yv;
+    d2 = fmaf(d, d, d2);
+    y2 = fmaf(yv, yv, y2);
+  }
+  d2 = warp_sum(d2);
+  y2 = warp_sum(y2);
+  __shared__ float r1[8], r2[8];
+  if ((threadIdx.x & 31) == 0) {
+    r1[threadIdx.x >> 5] = d2;
+    r2[threadIdx.x >> 5] = y2;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = 0.f, c = 0.f;
+    for (int k = 0; k < (int)(blockDim.x >> 5); ++k) {
+      a += r1[k];
+      c += r2[k];
+    }
+    atomicAdd(&acc[2 * b], a);
+    atomicAdd(&acc[2 * b + 1], c);
+  }
+}
+
+// per_sample[b] = sqrt(d2)/(sqrt(y2)+eps); loss[0] = mean / sum (reduce_mode 1 mean, 2 sum, 0 none)
+__global__ void rel_l2_finalize_kernel(const float* __restrict__ acc, float* __restrict__ per_sample,
+                                       float* __restrict__ loss, int Bn, int reduce_mode) {
+  __shared__ float red[32];
+  float s = 0.f;
+  for (int b = threadIdx.x; b < Bn; b += blockDim.x) {
+    const float r = sqrtf(acc[2 * b]) / (sqrtf(acc[2 * b + 1]) + 1e-8f);
+    per_sample[b] = r;
+    s += r;
+  }
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0 && reduce_mode) {
+    float tsum = 0.f;
+    for (int k = 0; k < (int)((blockDim.x + 31) >> 5); ++k) tsum += red[k];
+    loss[0] = reduce_mode == 1 ? tsum / (float)Bn : tsum;
+  }
+}
+
+// dx[b,:] = g_b / (||d_b|| * (||y_b|| + eps)) * (x - y);  g_b = gout[0]*w (mean/sum) or gout[b] (none)
+__global__ void rel_l2_bwd_kernel(const float* __restrict__ x, const float* __restrict__ y,
+                                  const float* __restrict__ acc, const float* __restrict__ gout,
+                                  float* __restrict__ dx, long long S, int Bn, int reduce_mode) {
+  const int b = blockIdx.y;
+  const float dn = sqrtf(acc[2 * b]), yn = sqrtf(acc[2 * b + 1]);
+  float g = reduce_mode ? gout[0] : gout[b];
+  if (reduce_mode == 1) g /= (float)Bn;
+  const float sc = dn > 0.f ? g / (dn * (yn + 1e-8f)) : 0.f;
+  const float* xb = x + (long long)b * S;
+  const float* yb = y + (long long)b * S;
+  float* db = dx + (long long)b * S;
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < S; e += (long long)gridDim.x * blockDim.x)
+    db[e] = sc * (xb[e] - yb[e]);
+}
+
+// ----------------------------------------------------------------------------------------------
+// Grid concatenation: out = cat(x, grid...) along channels.  x is channels-first (B, Cin, S0[, S1]);
+// out is channels-first (B, Cin+G, S0, S1) or channels-last (B, S0, S1, Cin+G).  g0 indexes S0, g1 indexes S1.
+// ----------------------------------------------------------------------------------------------
+__global__ void concat_grid_kernel(const float* __restrict__ x, const float* __restrict__ g0,
+                                   const float* __restrict__ g1, float* __restrict__ out, int Bn, int Cin, int S0,
+                                   int S1, int G, int channels_last) {
+  const int Ct = Cin + G;
+  const long long total = (long long)Bn * Ct * S0 * S1;
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
+       e += (long long)gridDim.x * blockDim.x) {
+    int b, c, s0, s1;
+    if (channels_last) {
+      c = (int)(e % Ct);
+      s1 = (int)((e / Ct) % S1);
+      s0 = (int)((e / ((long long)Ct * S1)) % S0);
+      b = (int)(e / ((long long)Ct * S1 * S0));
+    } else {
+      s1 = (int)(e % S1);
+      s0 = (int)((e / S1) % S0);
+      c = (int)((e / ((long long)S1 * S0)) % Ct);
+      b = (int)(e / ((long long)S1 * S0 * Ct));
+    }
+    float v;
+    if (c < Cin) v = x[(((long long)b * Cin + c) * S0 + s0) * S1 + s1];
+    else if (c == Cin) v = g0[s0];
+    else v = g1[s1];
+    out[e] = v;
+  }
+}
+__global__ void concat_grid_bwd_kernel(const float* __restrict__ dout, float* __restrict__ dx, int Bn, int Cin,
+                                       int S0, int S1, int G, int channels_last) {
+  const int Ct = Cin + G;
+  const long long total = (long long)Bn * Cin * S0 * S1;
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
+       e += (long long)gridDim.x * blockDim.x) {
+    const int s1 = (int)(e % S1);
+    const int s0 = (int)((e / S1) % S0);
+    const int c = (int)((e / ((long long)S1 * S0)) % Cin);
+    const int b = (int)(e / ((long long)S1 * S0 * Cin));
+    const long long src = channels_last ? ((((long long)b * S0 + s0) * S1 + s1) * Ct + c)
+                                        : ((((long long)b * Ct + c) * S0 + s0) * S1 + s1);
+    dx[e] = dout[src];
+  }
+}
+
+// ----------------------------------------------------------------------------------------------
+// Weight norm (legacy torch.nn.utils.weight_norm, dim=0): w[o,:] = g[o] * v[o,:] / ||v[o,:]||.
+// ----------------------------------------------------------------------------------------------
+__global__ void weight_norm_fwd_kernel(const float* __restrict__ v, const float* __restrict__ g,
+                                       float* __restrict__ w, float* __restrict__ norms, int O, int I) {
+  const int lane = threadIdx.x & 31;
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (row >= O) return;
+  float s = 0.f;
+  for (int i = lane; i < I; i += 32) s = fmaf(v[row * I + i], v[row * I + i], s);
+  const float nrm = sqrtf(warp_sum(s));
+  if (lane == 0) norms[row] = nrm;
+  const float sc = g[row] / nrm;
+  for (int i = lane; i < I; i += 32) w[row * I + i] = v[row * I + i] * sc;
+}
+// dg[o] = sum_i dw*v / ||v||;  dv = g/||v|| * (dw - v * (dw.v)/||v||^2)
+__global__ void weight_norm_bwd_kernel(const float* __restrict__ dw, const float* __restrict__ v,
+                                       const float* __restrict__ g, const float* __restrict__ norms,
+                                       float* __restrict__ dv, float* __restrict__ dg, int O, int I) {
+  const int lane = threadIdx.x & 31;
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (row >= O) return;
+  float s = 0.f;
+  for (int i = lane; i < I; i += 32) s = fmaf(dw[row * I + i], v[row * I + i], s);
+  s = warp_sum(s);
+  const float nrm = norms[row];
+  if (lane == 0) dg[row] = s / nrm;
+  const float sc = g[row] / nrm, proj = s / (nrm * nrm);
+  for (int i = lane; i < I; i += 32) dv[row * I + i] = sc * (dw[row * I + i] - v[row * I + i] * proj);
+}
+
+// elementwise helpers
+__global__ void dact_mul_kernel(const float* __restrict__ dy, const float* __restrict__ z, float* __restrict__ out,
+                                long long n, int act) {
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x)
+    out[e] = dy[e] * dact_f(act, z[e]);
+}
+__global__ void act_kernel(const float* __restrict__ x, const float* __restrict__ res, float* __restrict__ out,
+                           long long n, int act) {
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x)
+    out[e] = (res ? res[e] : 0.f) + act_f(act, x[e]);
+}
+
+static inline unsigned grid_for(long long n, int threads = 256, int cap = 148 * 16) {
+  long long g = (n + threads - 1) / threads;
+  if (g < 1) g = 1;
+  if (g > cap) g = cap;
+  return (unsigned)g;
+}
+
+}  // namespace rpde

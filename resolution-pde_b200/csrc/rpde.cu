@@ -1,0 +1,765 @@
+// C ABI of the B200-native spectral path (see include/rpde_b200.h for the contract).
+// Host-side operator orchestration: every operator is a short sequence of descriptor-driven
+// contractions (gemm_*.cuh) and pointwise kernels (pointwise.cuh) enqueued on the caller's stream.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/rpde_b200.h"
+#include "common.cuh"
+#include "gemm_simt.cuh"
+#include "pointwise.cuh"
+#ifdef RPDE_WITH_TC
+#include "gemm_tc.cuh"
+#endif
+
+using namespace rpde;
+
+static thread_local char g_err[512] = "";
+static thread_local int g_prec = RPDE_PREC_FP32;
+
+static int fail(int code, const char* fmt, const char* a = "") {
+  snprintf(g_err, sizeof(g_err), fmt, a);
+  return code;
+}
+#define RPDE_CUDA(expr)                                                        \
+  do {                                                                         \
+    cudaError_t _e = (expr);                                                   \
+    if (_e != cudaSuccess) return fail(RPDE_E_CUDA, "CUDA error: %s", cudaGetErrorString(_e)); \
+  } while (0)
+#define RPDE_LAUNCH_CHECK() RPDE_CUDA(cudaGetLastError())
+
+static cudaError_t gemm(const GemmP& p, cudaStream_t s) {
+#ifdef RPDE_WITH_TC
+  if (g_prec != RPDE_PREC_FP32 && gemm_tc_supported(p)) return gemm_tc_launch(p, g_prec, s);
+#endif
+  return gemm_simt_launch(p, s);
+}
+
+static inline size_t align_up(size_t v) { return (v + 255) & ~(size_t)255; }
+struct Carver {
+  char* base;
+  size_t off, cap;
+  float* take(size_t floats) {
+    float* p = reinterpret_cast<float*>(base + off);
+    off += align_up(floats * sizeof(float));
+    return p;
+  }
+};
+
+extern "C" {
+
+int rpde_version(void) { return 100; }
+const char* rpde_last_error(void) { return g_err; }
+int rpde_set_precision(int prec) {
+  if (prec < 0 || prec > 2) return fail(RPDE_E_INVALID, "rpde_set_precision: unknown precision%s");
+#ifndef RPDE_WITH_TC
+  if (prec != RPDE_PREC_FP32) return fail(RPDE_E_INVALID, "rpde_set_precision: library built without the tensor-core engine%s");
+#endif
+  g_prec = prec;
+  return RPDE_OK;
+}
+int rpde_get_precision(void) { return g_prec; }
+
+// ------------------------------------------------------------------------------------------------
+int rpde_dft_table(float* out, int kind, int n, int k, int m1, double scale, rpde_stream_t stream) {
+  if (!out || n <= 0 || k <= 0 || kind < 0 || kind > 3) return fail(RPDE_E_INVALID, "rpde_dft_table: bad arguments%s");
+  cudaStream_t s = (cudaStream_t)stream;
+  const long long total = (kind <= 1 ? 2LL : 4LL) * k * n;
+  dft_table_kernel<<<grid_for(total), 256, 0, s>>>(out, kind, n, k, m1, scale);
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+
+static int pack_w(const float* w, float* wp, int I, int O, int modes, int keep, int sub, int sub_keep, cudaStream_t s) {
+  const long long total = (long long)keep * sub_keep * 4 * I * O;
+  pack_weights_kernel<<<grid_for(total), 256, 0, s>>>(w, wp, I, O, modes, keep, sub, sub_keep);
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+static int unpack_g(const float* P, float* dw, int I, int O, int modes, int keep, int sub, int sub_keep, int acc,
+                    cudaStream_t s) {
+  const long long total = (long long)I * O * modes;
+  unpack_wgrad_kernel<<<grid_for(total), 256, 0, s>>>(P, dw, I, O, modes, keep, sub, sub_keep, acc);
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// FNO SpectralConv1d
+// ------------------------------------------------------------------------------------------------
+size_t rpde_spectral1d_workspace_bytes(int B, int I, int O, int N, int modes) {
+  (void)N;
+  const size_t K = modes;
+  size_t f = 0;
+  f += align_up(K * 4 * I * O * 4);       // packed weights
+  f += align_up(K * B * 2 * O * 4);       // mixed spectrum / its gradient
+  f += align_up(K * B * 2 * I * 4);       // gradient of the input spectrum
+  f += align_up(K * 4 * I * O * 4);       // packed weight gradient
+  return f;
+}
+
+int rpde_spectral1d_fwd(const float* x, const float* w, const float* fa, const float* fs, float* spec, float* y,
+                        float* z, int B, int I, int O, int N, int modes, int beta, int act, void* ws,
+                        size_t ws_bytes, rpde_stream_t stream) {
+  if (!x || !w || !fa || !fs || !spec || !y || B <= 0 || I <= 0 || O <= 0 || N <= 0 || modes <= 0)
+    return fail(RPDE_E_INVALID, "rpde_spectral1d_fwd: bad arguments%s");
+  if (modes > N / 2 + 1) return fail(RPDE_E_MODES, "SpectralConv1d: modes1 exceeds N//2+1%s");
+  if (!ws || ws_bytes < rpde_spectral1d_workspace_bytes(B, I, O, N, modes))
+    return fail(RPDE_E_WORKSPACE, "rpde_spectral1d_fwd: workspace too small%s");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int K = modes;
+  Carver cv{(char*)ws, 0, ws_bytes};
+  float* wp = cv.take((size_t)K * 4 * I * O);
+  float* om = cv.take((size_t)K * B * 2 * O);
+  int rc = pack_w(w, wp, I, O, modes, K, 1, 1, s);
+  if (rc) return rc;
+  // 1. analysis: spec[k][b][(ri,i)] = sum_n x[(b,i)][n] fa[(k,ri)][n]
+  GemmP g = gemm_default();
+  g.A = x; g.B = fa; g.C = spec;
+  g.M = B * I; g.N = 2 * K; g.K = N;
+  g.a = MatDesc{lin(0), lin(N), lin(1)};
+  g.b = MatDesc{lin(0), lin(1), lin(N)};
+  g.c = MatDesc{lin(0), two(I, 2LL * I, 1), two(2, (long long)B * 2 * I, I)};
+  RPDE_CUDA(gemm(g, s));
+  // 2. mixing per mode: om[k][b][(ro,o)] = spec[k][b][:] wp[k]
+  g = gemm_default();
+  g.A = spec; g.B = wp; g.C = om;
+  g.batch = K; g.M = B; g.N = 2 * O; g.K = 2 * I;
+  g.a = MatDesc{lin((long long)B * 2 * I), lin(2 * I), lin(1)};
+  g.b = MatDesc{lin(4LL * I * O), lin(2 * O), lin(1)};
+  g.c = MatDesc{lin((long long)B * 2 * O), lin(2 * O), lin(1)};
+  RPDE_CUDA(gemm(g, s));
+  // 3. synthesis: y[(b,o)][n] = sum_(ro,k) om[k][b][(ro,o)] fs[n][(k,ro)]
+  g = gemm_default();
+  g.A = om; g.B = fs; g.C = y;
+  g.M = B * O; g.N = N; g.K = 2 * K;
+  g.a = MatDesc{lin(0), two(O, 2LL * O, 1), two(K, O, (long long)B * 2 * O)};
+  g.b = MatDesc{lin(0), two(K, 1, 2), lin(2 * K)};
+  g.c = MatDesc{lin(0), lin(N), lin(1)};
+  g.beta = beta; g.act = act; g.Z = z;
+  RPDE_CUDA(gemm(g, s));
+  return RPDE_OK;
+}
+
+int rpde_spectral1d_bwd(const float* dy, const float* w, const float* fa, const float* fs, const float* spec,
+                        float* dx, int dx_accumulate, float* dw, int B, int I, int O, int N, int modes, void* ws,
+                        size_t ws_bytes, rpde_stream_t stream) {
+  if (!dy || !w || !fa || !fs || !spec || B <= 0 || I <= 0 || O <= 0 || N <= 0 || modes <= 0)
+    return fail(RPDE_E_INVALID, "rpde_spectral1d_bwd: bad arguments%s");
+  if (modes > N / 2 + 1) return fail(RPDE_E_MODES, "SpectralConv1d: modes1 exceeds N//2+1%s");
+  if (!ws || ws_bytes < rpde_spectral1d_workspace_bytes(B, I, O, N, modes))
+    return fail(RPDE_E_WORKSPACE, "rpde_spectral1d_bwd: workspace too small%s");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int K = modes;
+  Carver cv{(char*)ws, 0, ws_bytes};
+  float* wp = cv.take((size_t)K * 4 * I * O);
+  float* dom = cv.take((size_t)K * B * 2 * O);
+  float* dsp = cv.take((size_t)K * B * 2 * I);
+  float* P = cv.take((size_t)K * 4 * I * O);
+  int rc = pack_w(w, wp, I, O, modes, K, 1, 1, s);
+  if (rc) return rc;
+  // 3'. dom[k][b][(ro,o)] = sum_n dy[(b,o)][n] fs[n][(k,ro)]
+  GemmP g = gemm_default();
+  g.A = dy; g.B = fs; g.C = dom;
+  g.M = B * O; g.N = 2 * K; g.K = N;
+  g.a = MatDesc{lin(0), lin(N), lin(1)};
+  g.b = MatDesc{lin(0), lin(2 * K), lin(1)};
+  g.c = MatDesc{lin(0), two(O, 2LL * O, 1), two(2, (long long)B * 2 * O, O)};
+  RPDE_CUDA(gemm(g, s));
+  if (dw) {
+    // dWp[k] = spec[k]^T dom[k]
+    RPDE_CUDA(cudaMemsetAsync(P, 0, (size_t)K * 4 * I * O * sizeof(float), s));
+    g = gemm_default();
+    g.A = spec; g.B = dom; g.C = P;
+    g.batch = K; g.M = 2 * I; g.N = 2 * O; g.K = B;
+    g.a = MatDesc{lin((long long)B * 2 * I), lin(1), lin(2 * I)};
+    g.b = MatDesc{lin((long long)B * 2 * O), lin(2 * O), lin(1)};
+    g.c = MatDesc{lin(4LL * I * O), lin(2 * O), lin(1)};
+    g.splitk = 0;
+    RPDE_CUDA(gemm(g, s));
+    rc = unpack_g(P, dw, I, O, modes, K, 1, 1, 0, s);
+    if (rc) return rc;
+  }
+  if (dx) {
+    // 2'. dsp[k] = dom[k] wp[k]^T
+    g = gemm_default();
+    g.A = dom; g.B = wp; g.C = dsp;
+    g.batch = K; g.M = B; g.N = 2 * I; g.K = 2 * O;
+    g.a = MatDesc{lin((long long)B * 2 * O), lin(2 * O), lin(1)};
+    g.b = MatDesc{lin(4LL * I * O), lin(1), lin(2 * O)};
+    g.c = MatDesc{lin((long long)B * 2 * I), lin(2 * I), lin(1)};
+    RPDE_CUDA(gemm(g, s));
+    // 1'. dx[(b,i)][n] (+)= sum_(ri,k) dsp[k][b][(ri,i)] fa[(k,ri)][n]
+    g = gemm_default();
+    g.A = dsp; g.B = fa; g.C = dx;
+    g.M = B * I; g.N = N; g.K = 2 * K;
+    g.a = MatDesc{lin(0), two(I, 2LL * I, 1), two(K, I, (long long)B * 2 * I)};
+    g.b = MatDesc{lin(0), two(K, N, 2LL * N), lin(1)};
+    g.c = MatDesc{lin(0), lin(N), lin(1)};
+    g.beta = dx_accumulate;
+    RPDE_CUDA(gemm(g, s));
+  }
+  return RPDE_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// FNO SpectralConv2d: separable truncated transform  (W: R2C keep m2) x (H: C2C keep rows [0,m1) U [H-m1,H))
+// ------------------------------------------------------------------------------------------------
+size_t rpde_spectral2d_workspace_bytes(int B, int I, int O, int H, int W, int m1, int m2) {
+  (void)W;
+  const size_t J = 2 * (size_t)m1, Ky = m2, C = (size_t)(I > O ? I : O);
+  size_t f = 0;
+  f += align_up(J * Ky * 4 * I * O * 4);        // packed weights
+  f += align_up((size_t)B * C * 2 * H * Ky * 4); // half-transformed planes S1 / Z
+  f += align_up(J * Ky * B * 2 * C * 4);        // mixed spectrum or its gradient
+  f += align_up(J * Ky * B * 2 * C * 4);        // gradient of the input spectrum
+  f += align_up(J * Ky * 4 * I * O * 4);        // packed weight gradient
+  return f;
+}
+
+int rpde_spectral2d_fwd(const float* x, const float* w1, const float* w2, const float* fa_y, const float* fs_y,
+                        const float* gf, const float* gi, float* spec, float* y, float* z, int B, int I, int O,
+                        int H, int W, int m1, int m2, int beta, int act, void* ws, size_t ws_bytes,
+                        rpde_stream_t stream) {
+  if (!x || !w1 || !w2 || !fa_y || !fs_y || !gf || !gi || !spec || !y || B <= 0 || I <= 0 || O <= 0 || H <= 0 ||
+      W <= 0 || m1 <= 0 || m2 <= 0)
+    return fail(RPDE_E_INVALID, "rpde_spectral2d_fwd: bad arguments%s");
+  if (m2 > W / 2 + 1 || m1 > H) return fail(RPDE_E_MODES, "SpectralConv2d: modes exceed the available spectrum%s");
+  if (!ws || ws_bytes < rpde_spectral2d_workspace_bytes(B, I, O, H, W, m1, m2))
+    return fail(RPDE_E_WORKSPACE, "rpde_spectral2d_fwd: workspace too small%s");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int J = 2 * m1, Ky = m2;
+  const size_t Cm = (size_t)(I > O ? I : O);
+  Carver cv{(char*)ws, 0, ws_bytes};
+  float* wp = cv.take((size_t)J * Ky * 4 * I * O);
+  float* pl = cv.take((size_t)B * Cm * 2 * H * Ky);
+  float* om = cv.take((size_t)J * Ky * B * 2 * Cm);
+  int rc = pack_w(w1, wp, I, O, m1 * m2, m1, m2, m2, s);
+  if (rc) return rc;
+  rc = pack_w(w2, wp + (size_t)m1 * Ky * 4 * I * O, I, O, m1 * m2, m1, m2, m2, s);
+  if (rc) return rc;
+  const long long HK = (long long)H * Ky;
+  // 1. y-analysis: pl[(b,i)][ri][h][ky] = sum_w x[(b,i,h)][w] fa_y[(ky,ri)][w]
+  GemmP g = gemm_default();
+  g.A = x; g.B = fa_y; g.C = pl;
+  g.M = B * I * H; g.N = 2 * Ky; g.K = W;
+  g.a = MatDesc{lin(0), lin(W), lin(1)};
+  g.b = MatDesc{lin(0), lin(1), lin(W)};
+  g.c = MatDesc{lin(0), two(H, 2 * HK, Ky), two(2, 1, HK)};
+  RPDE_CUDA(gemm(g, s));
+  // 2. x-analysis: spec[j][ky][b][ro][i] = sum_(ri,h) gf[(j,ro)][(ri,h)] pl[(b,i)][ri][h][ky]
+  g = gemm_default();
+  g.A = gf; g.B = pl; g.C = spec;
+  g.batch = B * I; g.M = 2 * J; g.N = Ky; g.K = 2 * H;
+  g.a = MatDesc{lin(0), lin(2 * H), lin(1)};
+  g.b = MatDesc{lin(2 * HK), lin(Ky), lin(1)};
+  g.c = MatDesc{two(I, 2LL * I, 1), two(2, (long long)Ky * B * 2 * I, I), lin((long long)B * 2 * I)};
+  RPDE_CUDA(gemm(g, s));
+  // 3. mixing per retained mode
+  g = gemm_default();
+  g.A = spec; g.B = wp; g.C = om;
+  g.batch = J * Ky; g.M = B; g.N = 2 * O; g.K = 2 * I;
+  g.a = MatDesc{lin((long long)B * 2 * I), lin(2 * I), lin(1)};
+  g.b = MatDesc{lin(4LL * I * O), lin(2 * O), lin(1)};
+  g.c = MatDesc{lin((long long)B * 2 * O), lin(2 * O), lin(1)};
+  RPDE_CUDA(gemm(g, s));
+  // 4. x-synthesis: pl[(b,o)][ro][h][ky] = sum_(j,ri) gi[(h,ro)][(j,ri)] om[j][ky][b][ri][o]
+  g = gemm_default();
+  g.A = gi; g.B = om; g.C = pl;
+  g.batch = B * O; g.M = 2 * H; g.N = Ky; g.K = 2 * J;
+  g.a = MatDesc{lin(0), lin(2 * J), lin(1)};
+  g.b = MatDesc{two(O, 2LL * O, 1), two(2, (long long)Ky * B * 2 * O, O), lin((long long)B * 2 * O)};
+  g.c = MatDesc{lin(2 * HK), two(2, Ky, HK), lin(1)};
+  RPDE_CUDA(gemm(g, s));
+  // 5. y-synthesis: y[(b,o,h)][w] = sum_(ri,ky) pl[(b,o)][ri][h][ky] fs_y[w][(ky,ri)]
+  g = gemm_default();
+  g.A = pl; g.B = fs_y; g.C = y;
+  g.M = B * O * H; g.N = W; g.K = 2 * Ky;
+  g.a = MatDesc{lin(0), two(H, 2 * HK, Ky), two(Ky, HK, 1)};
+  g.b = MatDesc{lin(0), two(Ky, 1, 2), lin(2 * Ky)};
+  g.c = MatDesc{lin(0), lin(W), lin(1)};
+  g.beta = beta; g.act = act; g.Z = z;
+  RPDE_CUDA(gemm(g, s));
+  return RPDE_OK;
+}
+
+int rpde_spectral2d_bwd(const float* dy, const float* w1, const float* w2, const float* fa_y, const float* fs_y,
+                        const float* gf, const float* gi, const float* spec, float* dx, int dx_accumulate,
+                        float* dw1, float* dw2, int B, int I, int O, int H, int W, int m1, int m2, void* ws,
+                        size_t ws_bytes, rpde_stream_t stream) {
+  if (!dy || !w1 || !w2 || !fa_y || !fs_y || !gf || !gi || !spec || B <= 0 || I <= 0 || O <= 0 || H <= 0 ||
+      W <= 0 || m1 <= 0 || m2 <= 0)
+    return fail(RPDE_E_INVALID, "rpde_spectral2d_bwd: bad arguments%s");
+  if (m2 > W / 2 + 1 || m1 > H) return fail(RPDE_E_MODES, "SpectralConv2d: modes exceed the available spectrum%s");
+  if (!ws || ws_bytes < rpde_spectral2d_workspace_bytes(B, I, O, H, W, m1, m2))
+    return fail(RPDE_E_WORKSPACE, "rpde_spectral2d_bwd: workspace too small%s");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int J = 2 * m1, Ky = m2;
+  const size_t Cm = (size_t)(I > O ? I : O);
+  Carver cv{(char*)ws, 0, ws_bytes};
+  float* wp = cv.take((size_t)J * Ky * 4 * I * O);
+  float* pl = cv.take((size_t)B * Cm * 2 * H * Ky);
+  float* dom = cv.take((size_t)J * Ky * B * 2 * Cm);
+  float* dsp = cv.take((size_t)J * Ky * B * 2 * Cm);
+  float* P = cv.take((size_t)J * Ky * 4 * I * O);
+  int rc = pack_w(w1, wp, I, O, m1 * m2, m1, m2, m2, s);
+  if (rc) return rc;
+  rc = pack_w(w2, wp + (size_t)m1 * Ky * 4 * I * O, I, O, m1 * m2, m1, m2, m2, s);
+  if (rc) return rc;
+  const long long HK = (long long)H * Ky;
+  // 5'. pl[(b,o)][ri][h][ky] = sum_w dy[(b,o,h)][w] fs_y[w][(ky,ri)]
+  GemmP g = gemm_default();
+  g.A = dy; g.B = fs_y; g.C = pl;
+  g.M = B * O * H; g.N = 2 * Ky; g.K = W;
+  g.a = MatDesc{lin(0), lin(W), lin(1)};
+  g.b = MatDesc{lin(0), lin(2 * Ky), lin(1)};
+  g.c = MatDesc{lin(0), two(H, 2 * HK, Ky), two(2, 1, HK)};
+  RPDE_CUDA(gemm(g, s));
+  // 4'. dom[j][ky][b][ri][o] = sum_(ro,h) gi[(h,ro)][(j,ri)] pl[(b,o)][ro][h][ky]
+  g = gemm_default();
+  g.A = gi; g.B = pl; g.C = dom;
+  g.batch = B * O; g.M = 2 * J; g.N = Ky; g.K = 2 * H;
+  g.a = MatDesc{lin(0), lin(1), two(H, 2LL * J, 4LL * J)};
+  g.b = MatDesc{lin(2 * HK), lin(Ky), lin(1)};
+  g.c = MatDesc{two(O, 2LL * O, 1), two(2, (long long)Ky * B * 2 * O, O), lin((long long)B * 2 * O)};
+  RPDE_CUDA(gemm(g, s));
+  if (dw1 || dw2) {
+    RPDE_CUDA(cudaMemsetAsync(P, 0, (size_t)J * Ky * 4 * I * O * sizeof(float), s));
+    g = gemm_default();
+    g.A = spec; g.B = dom; g.C = P;
+    g.batch = J * Ky; g.M = 2 * I; g.N = 2 * O; g.K = B;
+    g.a = MatDesc{lin((long long)B * 2 * I), lin(1), lin(2 * I)};
+    g.b = MatDesc{lin((long long)B * 2 * O), lin(2 * O), lin(1)};
+    g.c = MatDesc{lin(4LL * I * O), lin(2 * O), lin(1)};
+    g.splitk = 0;
+    RPDE_CUDA(gemm(g, s));
+    if (dw1) { rc = unpack_g(P, dw1, I, O, m1 * m2, m1, m2, m2, 0, s); if (rc) return rc; }
+    if (dw2) { rc = unpack_g(P + (size_t)m1 * Ky * 4 * I * O, dw2, I, O, m1 * m2, m1, m2, m2, 0, s); if (rc) return rc; }
+  }
+  if (dx) {
+    // 3'. dsp[mode] = dom[mode] wp[mode]^T
+    g = gemm_default();
+    g.A = dom; g.B = wp; g.C = dsp;
+    g.batch = J * Ky; g.M = B; g.N = 2 * I; g.K = 2 * O;
+    g.a = MatDesc{lin((long long)B * 2 * O), lin(2 * O), lin(1)};
+    g.b = MatDesc{lin(4LL * I * O), lin(1), lin(2 * O)};
+    g.c = MatDesc{lin((long long)B * 2 * I), lin(2 * I), lin(1)};
+    RPDE_CUDA(gemm(g, s));
+    // 2'. pl[(b,i)][ri][h][ky] = sum_(j,ro) gf[(j,ro)][(ri,h)] dsp[j][ky][b][ro][i]
+    g = gemm_default();
+    g.A = gf; g.B = dsp; g.C = pl;
+    g.batch = B * I; g.M = 2 * H; g.N = Ky; g.K = 2 * J;
+    g.a = MatDesc{lin(0), lin(1), lin(2 * H)};
+    g.b = MatDesc{two(I, 2LL * I, 1), two(2, (long long)Ky * B * 2 * I, I), lin((long long)B * 2 * I)};
+    g.c = MatDesc{lin(2 * HK), lin(Ky), lin(1)};
+    RPDE_CUDA(gemm(g, s));
+    // 1'. dx[(b,i,h)][w] (+)= sum_(ri,ky) pl[(b,i)][ri][h][ky] fa_y[(ky,ri)][w]
+    g = gemm_default();
+    g.A = pl; g.B = fa_y; g.C = dx;
+    g.M = B * I * H; g.N = W; g.K = 2 * Ky;
+    g.a = MatDesc{lin(0), two(H, 2 * HK, Ky), two(Ky, HK, 1)};
+    g.b = MatDesc{lin(0), two(Ky, W, 2LL * W), lin(1)};
+    g.c = MatDesc{lin(0), lin(W), lin(1)};
+    g.beta = dx_accumulate;
+    RPDE_CUDA(gemm(g, s));
+  }
+  return RPDE_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// F-FNO factorised pass along one axis of a channels-last tensor  [outer][n][rest][C]
+// ------------------------------------------------------------------------------------------------
+size_t rpde_ffno_axis_workspace_bytes(long long outer, int n, long long rest, int C, int k) {
+  (void)n;
+  const size_t sp = (size_t)outer * 2 * k * rest * C;
+  size_t f = 0;
+  f += align_up((size_t)k * 4 * C * C * 4);  // packed weights
+  f += align_up(sp * 4);                     // mixed spectrum / its gradient
+  f += align_up(sp * 4);                     // gradient of the input spectrum
+  f += align_up((size_t)k * 4 * C * C * 4);  // packed weight gradient
+  return f;
+}
+
+int rpde_ffno_axis_fwd(const float* x, const float* w, const float* fa, const float* fs, float* spec, float* y,
+                       int accumulate, long long outer, int n, long long rest, int C, int k, int w_modes, int mix,
+                       void* ws, size_t ws_bytes, rpde_stream_t stream) {
+  if (!x || !fa || !fs || !spec || !y || outer <= 0 || n <= 0 || rest <= 0 || C <= 0 || k <= 0 || k > n / 2 + 1 ||
+      (mix == RPDE_MIX_FULL && (!w || k > w_modes)) || outer > INT_MAX || outer * rest > INT_MAX ||
+      rest * C > INT_MAX)
+    return fail(RPDE_E_INVALID, "rpde_ffno_axis_fwd: bad arguments%s");
+  if (!ws || ws_bytes < rpde_ffno_axis_workspace_bytes(outer, n, rest, C, k))
+    return fail(RPDE_E_WORKSPACE, "rpde_ffno_axis_fwd: workspace too small%s");
+  cudaStream_t s = (cudaStream_t)stream;
+  const long long inner = rest * C;
+  const size_t sp = (size_t)outer * 2 * k * inner;
+  Carver cv{(char*)ws, 0, ws_bytes};
+  float* wp = cv.take((size_t)k * 4 * C * C);
+  float* om = cv.take(sp);
+  // 1. analysis: spec[o][(k,ri)][inner] = fa[(k,ri)][n] x[o][n][inner]
+  GemmP g = gemm_default();
+  g.A = fa; g.B = x; g.C = spec;
+  g.batch = (int)outer; g.M = 2 * k; g.N = (int)inner; g.K = n;
+  g.a = MatDesc{lin(0), lin(n), lin(1)};
+  g.b = MatDesc{lin((long long)n * inner), lin(inner), lin(1)};
+  g.c = MatDesc{lin(2LL * k * inner), lin(inner), lin(1)};
+  RPDE_CUDA(gemm(g, s));
+  const float* mixed = spec;
+  if (mix == RPDE_MIX_FULL) {
+    int rc = pack_w(w, wp, C, C, w_modes, k, 1, 1, s);
+    if (rc) return rc;
+    // 2. per mode: om[(o,r)][(ro,c')] = spec[(o,r)][(ri,c)] wp[k]
+    g = gemm_default();
+    g.A = spec; g.B = wp; g.C = om;
+    g.batch = k; g.M = (int)(outer * rest); g.N = 2 * C; g.K = 2 * C;
+    g.a = MatDesc{lin(2 * inner), two((int)rest, 2LL * k * inner, C), two(C, inner, 1)};
+    g.b = MatDesc{lin(4LL * C * C), lin(2 * C), lin(1)};
+    g.c = g.a;
+    RPDE_CUDA(gemm(g, s));
+    mixed = om;
+  }
+  // 3. synthesis: y[o][n][inner] (+)= fs[n][(k,ri)] mixed[o][(k,ri)][inner]
+  g = gemm_default();
+  g.A = fs; g.B = mixed; g.C = y;
+  g.batch = (int)outer; g.M = n; g.N = (int)inner; g.K = 2 * k;
+  g.a = MatDesc{lin(0), lin(2 * k), lin(1)};
+  g.b = MatDesc{lin(2LL * k * inner), lin(inner), lin(1)};
+  g.c = MatDesc{lin((long long)n * inner), lin(inner), lin(1)};
+  g.beta = accumulate;
+  RPDE_CUDA(gemm(g, s));
+  return RPDE_OK;
+}
+
+int rpde_ffno_axis_bwd(const float* dy, const float* w, const float* fa, const float* fs, const float* spec,
+                       float* dx, int dx_accumulate, float* dw, int dw_accumulate, long long outer, int n,
+                       long long rest, int C, int k, int w_modes, int mix, void* ws, size_t ws_bytes,
+                       rpde_stream_t stream) {
+  if (!dy || !fa || !fs || outer <= 0 || n <= 0 || rest <= 0 || C <= 0 || k <= 0 || k > n / 2 + 1 ||
+      (mix == RPDE_MIX_FULL && (!w || (dw && !spec) || k > w_modes)) || outer > INT_MAX || outer * rest > INT_MAX ||
+      rest * C > INT_MAX)
+    return fail(RPDE_E_INVALID, "rpde_ffno_axis_bwd: bad arguments%s");
+  if (!ws || ws_bytes < rpde_ffno_axis_workspace_bytes(outer, n, rest, C, k))
+    return fail(RPDE_E_WORKSPACE, "rpde_ffno_axis_bwd: workspace too small%s");
+  cudaStream_t s = (cudaStream_t)stream;
+  const long long inner = rest * C;
+  const size_t sp = (size_t)outer * 2 * k * inner;
+  Carver cv{(char*)ws, 0, ws_bytes};
+  float* wp = cv.take((size_t)k * 4 * C * C);
+  float* dom = cv.take(sp);
+  float* dsp = cv.take(sp);
+  float* P = cv.take((size_t)k * 4 * C * C);
+  // 3'. dom[o] = fs^T dy[o]
+  GemmP g = gemm_default();
+  g.A = fs; g.B = dy; g.C = dom;
+  g.batch = (int)outer; g.M = 2 * k; g.N = (int)inner; g.K = n;
+  g.a = MatDesc{lin(0), lin(1), lin(2 * k)};
+  g.b = MatDesc{lin((long long)n * inner), lin(inner), lin(1)};
+  g.c = MatDesc{lin(2LL * k * inner), lin(inner), lin(1)};
+  RPDE_CUDA(gemm(g, s));
+  const float* dspec = dom;
+  if (mix == RPDE_MIX_FULL) {
+    int rc;
+    if (dw) {
+      RPDE_CUDA(cudaMemsetAsync(P, 0, (size_t)k * 4 * C * C * sizeof(float), s));
+      // dWp[k] = spec_k^T dom_k  (contraction over (o,r))
+      g = gemm_default();
+      g.A = spec; g.B = dom; g.C = P;
+      g.batch = k; g.M = 2 * C; g.N = 2 * C; g.K = (int)(outer * rest);
+      g.a = MatDesc{lin(2 * inner), two(C, inner, 1), two((int)rest, 2LL * k * inner, C)};
+      g.b = MatDesc{lin(2 * inner), two((int)rest, 2LL * k * inner, C), two(C, inner, 1)};
+      g.c = MatDesc{lin(4LL * C * C), lin(2 * C), lin(1)};
+      g.splitk = 0;
+      RPDE_CUDA(gemm(g, s));
+      rc = unpack_g(P, dw, C, C, w_modes, k, 1, 1, dw_accumulate, s);
+      if (rc) return rc;
+    }
+    if (dx) {
+      rc = pack_w(w, wp, C, C, w_modes, k, 1, 1, s);
+      if (rc) return rc;
+      // 2'. dsp_k = dom_k wp_k^T
+      g = gemm_default();
+      g.A = dom; g.B = wp; g.C = dsp;
+      g.batch = k; g.M = (int)(outer * rest); g.N = 2 * C; g.K = 2 * C;
+      g.a = MatDesc{lin(2 * inner), two((int)rest, 2LL * k * inner, C), two(C, inner, 1)};
+      g.b = MatDesc{lin(4LL * C * C), lin(1), lin(2 * C)};
+      g.c = g.a;
+      RPDE_CUDA(gemm(g, s));
+      dspec = dsp;
+    }
+  }
+  if (dx) {
+    // 1'. dx[o] (+)= fa^T dspec[o]
+    g = gemm_default();
+    g.A = fa; g.B = dspec; g.C = dx;
+    g.batch = (int)outer; g.M = n; g.N = (int)inner; g.K = 2 * k;
+    g.a = MatDesc{lin(0), lin(1), lin(n)};
+    g.b = MatDesc{lin(2LL * k * inner), lin(inner), lin(1)};
+    g.c = MatDesc{lin((long long)n * inner), lin(inner), lin(1)};
+    g.beta = dx_accumulate;
+    RPDE_CUDA(gemm(g, s));
+  }
+  return RPDE_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// channels-last Linear
+// ------------------------------------------------------------------------------------------------
+static MatDesc rows_cf(long long T, int ch, long long S) {
+  // element (t, c) of a channels-first tensor (T/S, ch, S): t = b*S + s -> b*ch*S + c*S + s
+  (void)T;
+  return MatDesc{lin(0), two((int)S, (long long)ch * S, 1), lin(S)};
+}
+
+int rpde_linear_fwd(const float* x, const float* w, const float* bias, float* y, float* z, long long T, int in,
+                    int out, int act, long long y_cf_spatial, rpde_stream_t stream) {
+  if (!x || !w || !y || T <= 0 || in <= 0 || out <= 0 || T > INT_MAX || y_cf_spatial > INT_MAX ||
+      (y_cf_spatial > 0 && T % y_cf_spatial != 0))
+    return fail(RPDE_E_INVALID, "rpde_linear_fwd: bad arguments%s");
+  GemmP g = gemm_default();
+  g.A = x; g.B = w; g.C = y;
+  g.M = (int)T; g.N = out; g.K = in;
+  g.a = MatDesc{lin(0), lin(in), lin(1)};
+  g.b = MatDesc{lin(0), lin(1), lin(in)};
+  g.c = y_cf_spatial > 0 ? rows_cf(T, out, y_cf_spatial) : MatDesc{lin(0), lin(out), lin(1)};
+  g.bias = bias; g.bias_mode = bias ? 1 : 0;
+  g.act = act; g.Z = z;
+  RPDE_CUDA(gemm(g, (cudaStream_t)stream));
+  return RPDE_OK;
+}
+
+int rpde_linear_bwd_input(const float* dy, const float* w, const float* zprev, int dact, float* dx, int accumulate,
+                          long long T, int in, int out, long long dy_cf_spatial, rpde_stream_t stream) {
+  if (!dy || !w || !dx || T <= 0 || in <= 0 || out <= 0 || T > INT_MAX || (dact && !zprev) ||
+      (dy_cf_spatial > 0 && T % dy_cf_spatial != 0))
+    return fail(RPDE_E_INVALID, "rpde_linear_bwd_input: bad arguments%s");
+  GemmP g = gemm_default();
+  g.A = dy; g.B = w; g.C = dx;
+  g.M = (int)T; g.N = in; g.K = out;
+  g.a = dy_cf_spatial > 0 ? rows_cf(T, out, dy_cf_spatial) : MatDesc{lin(0), lin(out), lin(1)};
+  g.b = MatDesc{lin(0), lin(in), lin(1)};
+  g.c = MatDesc{lin(0), lin(in), lin(1)};
+  g.beta = accumulate;
+  g.aux = zprev; g.dact = dact;
+  if (accumulate && dact) return fail(RPDE_E_INVALID, "rpde_linear_bwd_input: accumulate with dact is ambiguous%s");
+  RPDE_CUDA(gemm(g, (cudaStream_t)stream));
+  return RPDE_OK;
+}
+
+static int reduce_channels(const float* X, float* out, long long outer, int C, long long inner, cudaStream_t s) {
+  RPDE_CUDA(cudaMemsetAsync(out, 0, (size_t)C * sizeof(float), s));
+  if (inner == 1) {
+    long long chunk = (outer + 148 * 4 - 1) / (148 * 4);
+    if (chunk < 64) chunk = 64;
+    dim3 grid((unsigned)((outer + chunk - 1) / chunk), (unsigned)((C + 31) / 32));
+    reduce_channels_kernel<<<grid, 256, 0, s>>>(X, out, outer, C, 1, chunk);
+  } else {
+    const long long total = outer * inner;
+    long long chunk = (total + 63) / 64;
+    if (chunk < 2048) chunk = 2048;
+    dim3 grid((unsigned)((total + chunk - 1) / chunk), (unsigned)C);
+    reduce_channels_kernel<<<grid, 256, 0, s>>>(X, out, outer, C, inner, chunk);
+  }
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+
+int rpde_linear_bwd_params(const float* dy, const float* x, float* dw, float* db, long long T, int in, int out,
+                           long long dy_cf_spatial, rpde_stream_t stream) {
+  if (!dy || !x || !dw || T <= 0 || in <= 0 || out <= 0 || T > INT_MAX ||
+      (dy_cf_spatial > 0 && T % dy_cf_spatial != 0))
+    return fail(RPDE_E_INVALID, "rpde_linear_bwd_params: bad arguments%s");
+  cudaStream_t s = (cudaStream_t)stream;
+  RPDE_CUDA(cudaMemsetAsync(dw, 0, (size_t)out * in * sizeof(float), s));
+  GemmP g = gemm_default();
+  g.A = dy; g.B = x; g.C = dw;
+  g.M = out; g.N = in; g.K = (int)T;
+  if (dy_cf_spatial > 0) {
+    const long long S = dy_cf_spatial;
+    g.a = MatDesc{lin(0), lin(S), two((int)S, (long long)out * S, 1)};
+  } else {
+    g.a = MatDesc{lin(0), lin(1), lin(out)};
+  }
+  g.b = MatDesc{lin(0), lin(in), lin(1)};
+  g.c = MatDesc{lin(0), lin(in), lin(1)};
+  g.splitk = 0;
+  RPDE_CUDA(gemm(g, s));
+  if (db) {
+    if (dy_cf_spatial > 0) return reduce_channels(dy, db, T / dy_cf_spatial, out, dy_cf_spatial, s);
+    return reduce_channels(dy, db, T, out, 1, s);
+  }
+  return RPDE_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// channels-first 1x1 convolution
+// ------------------------------------------------------------------------------------------------
+int rpde_conv1x1_fwd(const float* x, const float* w, const float* bias, float* y, float* z, int B, int I, int O,
+                     long long S, int act, int beta, rpde_stream_t stream) {
+  if (!x || !w || !y || B <= 0 || I <= 0 || O <= 0 || S <= 0 || S > INT_MAX)
+    return fail(RPDE_E_INVALID, "rpde_conv1x1_fwd: bad arguments%s");
+  GemmP g = gemm_default();
+  g.A = w; g.B = x; g.C = y;
+  g.batch = B; g.M = O; g.N = (int)S; g.K = I;
+  g.a = MatDesc{lin(0), lin(I), lin(1)};
+  g.b = MatDesc{lin((long long)I * S), lin(S), lin(1)};
+  g.c = MatDesc{lin((long long)O * S), lin(S), lin(1)};
+  g.bias = bias; g.bias_mode = bias ? 2 : 0;
+  g.act = act; g.Z = z; g.beta = beta;
+  RPDE_CUDA(gemm(g, (cudaStream_t)stream));
+  return RPDE_OK;
+}
+
+int rpde_conv1x1_bwd_input(const float* dy, const float* w, const float* zprev, int dact, float* dx, int accumulate,
+                           int B, int I, int O, long long S, rpde_stream_t stream) {
+  if (!dy || !w || !dx || B <= 0 || I <= 0 || O <= 0 || S <= 0 || S > INT_MAX || (dact && !zprev) ||
+      (accumulate && dact))
+    return fail(RPDE_E_INVALID, "rpde_conv1x1_bwd_input: bad arguments%s");
+  GemmP g = gemm_default();
+  g.A = w; g.B = dy; g.C = dx;
+  g.batch = B; g.M = I; g.N = (int)S; g.K = O;
+  g.a = MatDesc{lin(0), lin(1), lin(I)};
+  g.b = MatDesc{lin((long long)O * S), lin(S), lin(1)};
+  g.c = MatDesc{lin((long long)I * S), lin(S), lin(1)};
+  g.beta = accumulate; g.aux = zprev; g.dact = dact;
+  RPDE_CUDA(gemm(g, (cudaStream_t)stream));
+  return RPDE_OK;
+}
+
+int rpde_conv1x1_bwd_params(const float* dy, const float* x, float* dw, float* db, int B, int I, int O,
+                            long long S, rpde_stream_t stream) {
+  if (!dy || !x || !dw || B <= 0 || I <= 0 || O <= 0 || S <= 0 || S > INT_MAX || (long long)B * S > INT_MAX)
+    return fail(RPDE_E_INVALID, "rpde_conv1x1_bwd_params: bad arguments%s");
+  cudaStream_t s = (cudaStream_t)stream;
+  RPDE_CUDA(cudaMemsetAsync(dw, 0, (size_t)O * I * sizeof(float), s));
+  GemmP g = gemm_default();
+  g.A = dy; g.B = x; g.C = dw;
+  g.M = O; g.N = I; g.K = (int)(B * S);
+  g.a = MatDesc{lin(0), lin(S), two((int)S, (long long)O * S, 1)};
+  g.b = MatDesc{lin(0), two((int)S, (long long)I * S, 1), lin(S)};
+  g.c = MatDesc{lin(0), lin(I), lin(1)};
+  g.splitk = 0;
+  RPDE_CUDA(gemm(g, s));
+  if (db) return reduce_channels(dy, db, B, O, S, s);
+  return RPDE_OK;
+}
+
+int rpde_act_bwd(const float* dy, const float* z, float* out, long long n, int act, rpde_stream_t stream) {
+  if (!dy || !z || !out || n <= 0) return fail(RPDE_E_INVALID, "rpde_act_bwd: bad arguments%s");
+  dact_mul_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(dy, z, out, n, act);
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+int rpde_act_fwd(const float* x, const float* res, float* out, long long n, int act, rpde_stream_t stream) {
+  if (!x || !out || n <= 0) return fail(RPDE_E_INVALID, "rpde_act_fwd: bad arguments%s");
+  act_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(x, res, out, n, act);
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+int rpde_layernorm_fwd(const float* x, const float* res, const float* gamma, const float* beta, float* y,
+                       float* mean, float* rstd, long long T, int C, float eps, rpde_stream_t stream) {
+  if (!x || !gamma || !beta || !y || T <= 0 || C <= 0 || (mean && !rstd))
+    return fail(RPDE_E_INVALID, "rpde_layernorm_fwd: bad arguments%s");
+  const long long threads = T * 32;
+  layernorm_fwd_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>(x, res, gamma, beta, y,
+                                                                                           mean, rstd, T, C, eps);
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+int rpde_layernorm_bwd(const float* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
+                       float* dx, float* dgamma, float* dbeta, long long T, int C, rpde_stream_t stream) {
+  if (!dy || !x || !gamma || !mean || !rstd || !dx || !dgamma || !dbeta || T <= 0 || C <= 0 || C > 4096)
+    return fail(RPDE_E_INVALID, "rpde_layernorm_bwd: bad arguments%s");
+  cudaStream_t s = (cudaStream_t)stream;
+  RPDE_CUDA(cudaMemsetAsync(dgamma, 0, (size_t)C * sizeof(float), s));
+  RPDE_CUDA(cudaMemsetAsync(dbeta, 0, (size_t)C * sizeof(float), s));
+  long long rpb = (T + 148 * 8 - 1) / (148 * 8);
+  if (rpb < 8) rpb = 8;
+  const unsigned grid = (unsigned)((T + rpb - 1) / rpb);
+  layernorm_bwd_kernel<<<grid, 256, 2 * C * sizeof(float), s>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, T, C,
+                                                               (int)rpb);
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+
+int rpde_weight_norm_fwd(const float* v, const float* g, float* w, float* norms, int out, int in,
+                         rpde_stream_t stream) {
+  if (!v || !g || !w || !norms || out <= 0 || in <= 0) return fail(RPDE_E_INVALID, "rpde_weight_norm_fwd: bad arguments%s");
+  weight_norm_fwd_kernel<<<(out * 32 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(v, g, w, norms, out, in);
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+int rpde_weight_norm_bwd(const float* dw, const float* v, const float* g, const float* norms, float* dv, float* dg,
+                         int out, int in, rpde_stream_t stream) {
+  if (!dw || !v || !g || !norms || !dv || !dg || out <= 0 || in <= 0)
+    return fail(RPDE_E_INVALID, "rpde_weight_norm_bwd: bad arguments%s");
+  weight_norm_bwd_kernel<<<(out * 32 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(dw, v, g, norms, dv, dg, out, in);
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+
+int rpde_concat_grid_fwd(const float* x, const float* g0, const float* g1, float* out, int B, int Cin, int S0,
+                         int S1, int channels_last, rpde_stream_t stream) {
+  if (!x || !out || B <= 0 || Cin <= 0 || S0 <= 0 || S1 <= 0 || (g1 && !g0))
+    return fail(RPDE_E_INVALID, "rpde_concat_grid_fwd: bad arguments%s");
+  const int G = (g0 ? 1 : 0) + (g1 ? 1 : 0);
+  const long long total = (long long)B * (Cin + G) * S0 * S1;
+  concat_grid_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(x, g0, g1, out, B, Cin, S0, S1, G,
+                                                                        channels_last);
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+int rpde_concat_grid_bwd(const float* dout, float* dx, int B, int Cin, int S0, int S1, int G, int channels_last,
+                         rpde_stream_t stream) {
+  if (!dout || !dx || B <= 0 || Cin <= 0 || S0 <= 0 || S1 <= 0 || G < 0)
+    return fail(RPDE_E_INVALID, "rpde_concat_grid_bwd: bad arguments%s");
+  const long long total = (long long)B * Cin * S0 * S1;
+  concat_grid_bwd_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>(dout, dx, B, Cin, S0, S1, G,
+                                                                            channels_last);
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+
+int rpde_rel_l2_fwd(const float* x, const float* y, float* acc, float* per_sample, float* loss, int B, long long S,
+                    int reduce_mode, rpde_stream_t stream) {
+  if (!x || !y || !acc || !per_sample || B <= 0 || S <= 0 || (reduce_mode && !loss))
+    return fail(RPDE_E_INVALID, "rpde_rel_l2_fwd: bad arguments%s");
+  cudaStream_t s = (cudaStream_t)stream;
+  RPDE_CUDA(cudaMemsetAsync(acc, 0, (size_t)2 * B * sizeof(float), s));
+  long long per = (148LL * 8 + B - 1) / B;
+  long long chunk = (S + per - 1) / per;
+  if (chunk < 4096) chunk = 4096;
+  dim3 grid((unsigned)((S + chunk - 1) / chunk), (unsigned)B);
+  rel_l2_partial_kernel<<<grid, 256, 0, s>>>(x, y, acc, S, chunk);
+  RPDE_LAUNCH_CHECK();
+  rel_l2_finalize_kernel<<<1, 256, 0, s>>>(acc, per_sample, loss, B, reduce_mode);
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+int rpde_rel_l2_bwd(const float* x, const float* y, const float* acc, const float* gout, float* dx, int B,
+                    long long S, int reduce_mode, rpde_stream_t stream) {
+  if (!x || !y || !acc || !gout || !dx || B <= 0 || S <= 0) return fail(RPDE_E_INVALID, "rpde_rel_l2_bwd: bad arguments%s");
+  long long gx = (S + 255) / 256;
+  const long long cap = (148LL * 16 + B - 1) / B;
+  if (gx > cap) gx = cap;
+  dim3 grid((unsigned)gx, (unsigned)B);
+  rel_l2_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, y, acc, gout, dx, S, B, reduce_mode);
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+
+int rpde_matmul(const float* a, const float* b, float* c, int M, int N, int K, int trans_a, int trans_b,
+                rpde_stream_t stream) {
+  if (!a || !b || !c || M <= 0 || N <= 0 || K <= 0) return fail(RPDE_E_INVALID, "rpde_matmul: bad arguments%s");
+  GemmP g = gemm_default();
+  g.A = a; g.B = b; g.C = c;
+  g.M = M; g.N = N; g.K = K;
+  g.a = trans_a ? MatDesc{lin(0), lin(1), lin(M)} : MatDesc{lin(0), lin(K), lin(1)};
+  g.b = trans_b ? MatDesc{lin(0), lin(1), lin(K)} : MatDesc{lin(0), lin(N), lin(1)};
+  g.c = MatDesc{lin(0), lin(N), lin(1)};
+  RPDE_CUDA(gemm(g, (cudaStream_t)stream));
+  return RPDE_OK;
+}
+
+}  // extern "C"

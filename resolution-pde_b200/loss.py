@@ -1,0 +1,14 @@
+"""RelativeL2Loss (reference: utils/loss.py:17-59) on the CUDA extension."""
+import torch.nn as nn
+
+from . import ops
+
+
+class RelativeL2Loss(nn.Module):
+    def __init__(self, size_average=True, reduction=True):
+        super().__init__()
+        self.size_average = size_average
+        self.reduction = reduction
+
+    def forward(self, x, y):
+        return ops.relative_l2(x, y, self.size_average, self.reduction)
