@@ -41,6 +41,8 @@ const char* rpde_last_error(void);
 /* Selects the contraction engine for aligned shapes (per thread). FP32 = CUDA-core FMA everywhere. */
 int rpde_set_precision(int prec);
 int rpde_get_precision(void);
+/* Number of kernels this library has enqueued since it was loaded (statistics for the benchmark). */
+unsigned long long rpde_launch_count(void);
 
 /* Twiddle / truncated-DFT tables, generated on the device in fp64 and rounded once to fp32.
  * Replaces the cuFFT/pocketfft plans behind torch.fft.rfft/irfft/rfft2/irfft2

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <string.h>
+#include <atomic>
 
 #include "../../include/rpde_b200.h"
 #include "common.cuh"
@@ -27,9 +28,16 @@ static int fail(int code, const char* fmt, const char* a = "") {
     cudaError_t _e = (expr);                                                   \
     if (_e != cudaSuccess) return fail(RPDE_E_CUDA, "CUDA error: %s", cudaGetErrorString(_e)); \
   } while (0)
-#define RPDE_LAUNCH_CHECK() RPDE_CUDA(cudaGetLastError())
+// launch statistics only (monotonic counter of kernels this library enqueued; read by bench.py)
+static std::atomic<unsigned long long> g_launches{0};
+#define RPDE_LAUNCH_CHECK()        \
+  do {                             \
+    g_launches.fetch_add(1);       \
+    RPDE_CUDA(cudaGetLastError()); \
+  } while (0)
 
 static cudaError_t gemm(const GemmP& p, cudaStream_t s) {
+  if (p.M > 0 && p.N > 0 && p.batch > 0) g_launches.fetch_add(1);
 #ifdef RPDE_WITH_TC
   if (g_prec != RPDE_PREC_FP32 && gemm_tc_supported(p)) return gemm_tc_launch(p, g_prec, s);
 #endif
@@ -60,6 +68,7 @@ int rpde_set_precision(int prec) {
   return RPDE_OK;
 }
 int rpde_get_precision(void) { return g_prec; }
+unsigned long long rpde_launch_count(void) { return g_launches.load(); }
 
 // ------------------------------------------------------------------------------------------------
 int rpde_dft_table(float* out, int kind, int n, int k, int m1, double scale, rpde_stream_t stream) {
