@@ -43,6 +43,8 @@ int rpde_set_precision(int prec);
 int rpde_get_precision(void);
 /* Number of kernels this library has enqueued since it was loaded (statistics for the benchmark). */
 unsigned long long rpde_launch_count(void);
+/* ... of which contractions executed by the tcgen05/TMA tensor-core engine (0 under RPDE_PREC_FP32). */
+unsigned long long rpde_tc_launch_count(void);
 
 /* Twiddle / truncated-DFT tables, generated on the device in fp64 and rounded once to fp32.
  * Replaces the cuFFT/pocketfft plans behind torch.fft.rfft/irfft/rfft2/irfft2

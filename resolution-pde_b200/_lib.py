@@ -26,6 +26,7 @@ SIGNATURES = {
     "rpde_set_precision": (I, [I]),
     "rpde_get_precision": (I, []),
     "rpde_launch_count": (ctypes.c_ulonglong, []),
+    "rpde_tc_launch_count": (ctypes.c_ulonglong, []),
     "rpde_dft_table": (I, [P, I, I, I, I, c_double, S]),
     "rpde_spectral1d_workspace_bytes": (Z, [I, I, I, I, I]),
     "rpde_spectral1d_fwd": (I, [P, P, P, P, P, P, P, I, I, I, I, I, I, I, P, Z, S]),

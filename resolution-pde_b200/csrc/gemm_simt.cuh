@@ -28,6 +28,7 @@ struct GemmP {
   float* Z;           // optional pre-activation output (same layout as C)
   const float* aux;   // with dact: result *= act'(aux) (same layout as C)
   int dact;
+  int a_act, b_act;   // activation applied to the elements of A / B as they are loaded (operand = act(stored tensor))
   // filled by gemm_launch
   int a_kfast, b_kfast, a_kuni, b_kuni, tiles_m, tiles_n;
 };
@@ -89,14 +90,14 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(const GemmP p) {
       const long long ko = p.a_kuni ? off2(p.a.c, k0) + (long long)kk * p.a.c.sl : off2(p.a.c, k);
       const bool kin = k < kend;
 #pragma unroll
-      for (int j = 0; j < LA; ++j) ra[j] = (kin && aval[j]) ? __ldg(A + arow[j] + ko) : 0.f;
+      for (int j = 0; j < LA; ++j) ra[j] = (kin && aval[j]) ? act_f(p.a_act, __ldg(A + arow[j] + ko)) : 0.f;
     } else {
       const long long kb = p.a_kuni ? off2(p.a.c, k0) : 0;
 #pragma unroll
       for (int j = 0; j < LA; ++j) {
         const int kk = t / BM + (256 / BM) * j, k = k0 + kk;
         const long long ko = p.a_kuni ? kb + (long long)kk * p.a.c.sl : off2(p.a.c, k);
-        ra[j] = (k < kend && aval[0]) ? __ldg(A + arow[0] + ko) : 0.f;
+        ra[j] = (k < kend && aval[0]) ? act_f(p.a_act, __ldg(A + arow[0] + ko)) : 0.f;
       }
     }
     if (p.b_kfast) {
@@ -104,14 +105,14 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(const GemmP p) {
       const long long ko = p.b_kuni ? off2(p.b.r, k0) + (long long)kk * p.b.r.sl : off2(p.b.r, k);
       const bool kin = k < kend;
 #pragma unroll
-      for (int j = 0; j < LB; ++j) rb[j] = (kin && bval[j]) ? __ldg(B + bcol[j] + ko) : 0.f;
+      for (int j = 0; j < LB; ++j) rb[j] = (kin && bval[j]) ? act_f(p.b_act, __ldg(B + bcol[j] + ko)) : 0.f;
     } else {
       const long long kb = p.b_kuni ? off2(p.b.r, k0) : 0;
 #pragma unroll
       for (int j = 0; j < LB; ++j) {
         const int kk = t / BN + (256 / BN) * j, k = k0 + kk;
         const long long ko = p.b_kuni ? kb + (long long)kk * p.b.r.sl : off2(p.b.r, k);
-        rb[j] = (k < kend && bval[0]) ? __ldg(B + bcol[0] + ko) : 0.f;
+        rb[j] = (k < kend && bval[0]) ? act_f(p.b_act, __ldg(B + bcol[0] + ko)) : 0.f;
       }
     }
   };
@@ -218,7 +219,7 @@ static inline GemmP gemm_default() {
   p.splitk = 1; p.kchunk = 0;
   p.alpha = 1.f; p.beta = 0;
   p.bias = nullptr; p.bias_mode = 0;
-  p.act = ACT_NONE; p.Z = nullptr; p.aux = nullptr; p.dact = 0;
+  p.act = ACT_NONE; p.Z = nullptr; p.aux = nullptr; p.dact = 0; p.a_act = p.b_act = 0;
   p.a_kfast = p.b_kfast = p.a_kuni = p.b_kuni = 0; p.tiles_m = p.tiles_n = 0;
   return p;
 }

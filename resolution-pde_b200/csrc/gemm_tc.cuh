@@ -1,0 +1,698 @@
+// Tensor-core contraction engine for sm_100a: TMA -> 128B-swizzled shared memory -> tcgen05.mma (kind::tf32,
+// accumulators in TMEM) -> tcgen05.ld epilogue.  Same GemmP contract as gemm_simt.cuh.
+//
+// Precision variants (rpde_set_precision):
+//   3xTF32 : every fp32 operand tile is split on chip into hi = tf32(x) and lo = x - hi and the product is formed as
+//            lo*hi + hi*lo + hi*hi with fp32 accumulation in TMEM -> fp32-level accuracy (the parity engine).
+//   TF32   : one pass on the raw fp32 bits (~5e-4 relative), the fast variant with its own stated tolerance.
+//
+// One persistent CTA per SM, warp-specialised:
+//   warp 0      TMA producer (one lane): fills a ring of {A,B} stages, full[s] <- complete_tx
+//   warp 1      UMMA issuer (one lane) + TMEM owner: 4 (x3) tcgen05.mma per stage, commit -> empty[s]; last -> acc_full
+//   warps 2-5   splitter (3xTF32 only): hi/lo split of the landed tiles in place, fence.proxy.async, -> ready[s]
+//   warps 6-9   epilogue: tcgen05.ld 32x32b.x32, bias / beta / activation / act' / split-K atomics, global stores;
+//               two TMEM accumulators so the epilogue of tile i overlaps the main loop of tile i+1.
+// Operands are addressed through TMA tensor maps derived from the GemmP index maps (K-major or MN-major, up to two
+// levels per index), so the channels-last / channels-first / interleaved layouts of the spectral path need no copies.
+#pragma once
+#include <cuda.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <mutex>
+
+#include "common.cuh"
+#include "gemm_simt.cuh"
+#include "tc_ptx.cuh"
+
+namespace rpde {
+
+struct TcOpnd {
+  int major;    // 0: K-major (K contiguous), 1: MN-major (M or N contiguous)
+  int ndim;     // tensor-map rank
+  int boxes;    // TMA issues per stage (1 unless the MN-major slab fallback is in use)
+  int box_mn;   // MN elements covered by one issue
+  int box_bytes;
+  int grouped;  // MN-major: the 32-element MN groups are a tensor dimension of their own (one box per stage)
+  int mn_d, k_d, b_d;                            // level divisors (INT_MAX: single level)
+  signed char dm0, dm1, dk0, dk1, db0, db1, dg;  // tensor-map dimension of each level, -1 if absent
+};
+
+struct TcParams {
+  GemmP g;
+  TcOpnd a, b;
+  int tiles_m, tiles_n, kblocks, kchunk_blocks, total_tiles;
+  int kc;       // k-blocks per TMEM accumulation chain (chunk); chunks are summed in registers with RN adds
+  int c_vec;    // C / Z / aux / bias base pointers are 16-byte aligned
+  int dbg;
+};
+
+namespace tc {
+
+constexpr int BM = 128, BK = 32;
+constexpr int A_TILE_BYTES = BM * BK * 4;
+constexpr int kThreads = 320;
+constexpr int kScratchBytes = 4 * 32 * 36 * 4;  // epilogue transposition scratch, one 32x36 fp32 pad per warp
+constexpr int kSmemBudget = 227 * 1024 - 2048 - kScratchBytes;
+
+template <int BN, bool SPLIT>
+struct Cfg {
+  static constexpr int b_tile = BN * BK * 4;
+  static constexpr int stage_bytes = (A_TILE_BYTES + b_tile) * (SPLIT ? 2 : 1);
+  static constexpr int raw = kSmemBudget / stage_bytes;
+  static constexpr int stages = raw > 6 ? 6 : raw;
+  static constexpr int smem_bytes = stages * stage_bytes + kScratchBytes + 2048;  // + alignment slack + barriers
+  static constexpr int tmem_cols = 2 * BN < 32 ? 32 : 2 * BN;
+};
+
+// Coordinates live in registers: slots are written with compare-selects, never with dynamic indexing (which would
+// push the array to local memory on the producer's critical path).
+__device__ __forceinline__ void put(int (&c)[5], int slot, int val) {
+#pragma unroll
+  for (int i = 0; i < 5; ++i) c[i] = (slot == i) ? val : c[i];
+}
+// coordinates of the box at (mn, k = 0, bz)
+__device__ __forceinline__ void opnd_coords(const TcOpnd& o, int mn, int bz, int (&c)[5]) {
+#pragma unroll
+  for (int i = 0; i < 5; ++i) c[i] = 0;
+  if (o.grouped) {
+    put(c, o.dg, ((o.mn_d == INT_MAX) ? mn : mn % o.mn_d) >> 5);
+    if (o.dm1 >= 0) put(c, o.dm1, mn / o.mn_d);
+  } else {
+    if (o.dm0 >= 0) put(c, o.dm0, (o.mn_d == INT_MAX) ? mn : mn % o.mn_d);
+    if (o.dm1 >= 0) put(c, o.dm1, mn / o.mn_d);
+  }
+  if (o.db0 >= 0) put(c, o.db0, (o.b_d == INT_MAX) ? bz : bz % o.b_d);
+  if (o.db1 >= 0) put(c, o.db1, bz / o.b_d);
+}
+__device__ __forceinline__ void opnd_set_k(int k_d, int dk0, int dk1, int k, int (&c)[5]) {
+  if (k_d == INT_MAX) {
+    put(c, dk0, k);
+  } else {
+    put(c, dk0, k % k_d);
+    if (dk1 >= 0) put(c, dk1, k / k_d);
+  }
+}
+__device__ __forceinline__ void opnd_load(const TcOpnd& o, const CUtensorMap* map, uint32_t dst, uint32_t bar, int (&c)[5], int mn0) {
+  if (o.boxes == 1) {
+    tma_load(dst, map, bar, o.ndim, c);
+    return;
+  }
+  for (int i = 0; i < o.boxes; ++i) {  // MN-major slab fallback (ragged / deeply nested MN index)
+    const int mn = mn0 + i * o.box_mn;
+    if (o.dm0 >= 0) put(c, o.dm0, (o.mn_d == INT_MAX) ? mn : mn % o.mn_d);
+    if (o.dm1 >= 0) put(c, o.dm1, mn / o.mn_d);
+    tma_load(dst + i * o.box_bytes, map, bar, o.ndim, c);
+  }
+}
+
+// Activation code is kept out of line: inlined, the compiler if-converts the erff/expf sequences and every
+// epilogue iteration pays for them even when no activation is requested.
+__device__ __noinline__ float4 act4_slow(int act, float4 x) {
+  x.x = act_f(act, x.x); x.y = act_f(act, x.y); x.z = act_f(act, x.z); x.w = act_f(act, x.w);
+  return x;
+}
+__device__ __noinline__ float4 dact4_slow(int act, float4 z) {
+  z.x = dact_f(act, z.x); z.y = dact_f(act, z.y); z.z = dact_f(act, z.z); z.w = dact_f(act, z.w);
+  return z;
+}
+__device__ __noinline__ float act1_slow(int act, float x) { return act_f(act, x); }
+__device__ __noinline__ float dact1_slow(int act, float z) { return dact_f(act, z); }
+
+__device__ __forceinline__ float tf32_trunc(float v) { return __uint_as_float(__float_as_uint(v) & 0xffffe000u); }
+
+// in-place preparation of one landed operand region: optional activation-on-load, optional hi/lo split.
+// The tensor core truncates fp32 operands to TF32 itself, so the hi tile is the raw tile; lo = x - trunc(x) is exact.
+template <bool SPLIT>
+__device__ __forceinline__ void prep_region(uint32_t hi0, uint32_t lo0, int n16, int act, int ct) {
+#pragma unroll 4
+  for (int i = ct; i < n16; i += 128) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(hi0 + 16 * i));
+    if (act) {
+      v = act4_slow(act, v);
+      asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(hi0 + 16 * i), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+    }
+    if (SPLIT) {
+      asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(lo0 + 16 * i), "f"(v.x - tf32_trunc(v.x)),
+                   "f"(v.y - tf32_trunc(v.y)), "f"(v.z - tf32_trunc(v.z)), "f"(v.w - tf32_trunc(v.w)) : "memory");
+    }
+  }
+}
+
+// CH = true: a tile's K range is cut into chunks of P.kc k-blocks, each accumulated in TMEM from zero and then added
+// (round-to-nearest) into fp32 registers of the epilogue warps.  The tensor core truncates its accumulator after
+// every UMMA, so the chain length bounds the rounding bias (measured 2.2e-8 relative per UMMA).
+template <int BN, bool SPLIT, bool CH>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUtensorMap mapA,
+               const __grid_constant__ CUtensorMap mapB) {
+  using C = Cfg<BN, SPLIT>;
+  constexpr int S = C::stages;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  // stage s: [A_hi][B_hi]([A_lo][B_lo])
+  auto a_hi = [&](int s) { return smem_base + s * C::stage_bytes; };
+  auto b_hi = [&](int s) { return smem_base + s * C::stage_bytes + A_TILE_BYTES; };
+  auto a_lo = [&](int s) { return smem_base + s * C::stage_bytes + A_TILE_BYTES + C::b_tile; };
+  auto b_lo = [&](int s) { return smem_base + s * C::stage_bytes + 2 * A_TILE_BYTES + C::b_tile; };
+  const uint32_t scratch_base = smem_base + S * C::stage_bytes;
+  const uint32_t bar_base = scratch_base + kScratchBytes;
+  auto full = [&](int s) { return bar_base + 8 * s; };
+  auto ready = [&](int s) { return bar_base + 8 * (S + s); };
+  auto empty = [&](int s) { return bar_base + 8 * (2 * S + s); };
+  auto acc_full = [&](int a) { return bar_base + 8 * (3 * S + a); };
+  auto acc_empty = [&](int a) { return bar_base + 8 * (3 * S + 2 + a); };
+  const uint32_t tmem_slot = bar_base + 8 * (3 * S + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const GemmP& p = P.g;
+  const bool use_prep = SPLIT || p.a_act || p.b_act;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&mapA);
+    tma_prefetch_desc(&mapB);
+    for (int s = 0; s < S; ++s) {
+      mbar_init(full(s), 1);
+      mbar_init(ready(s), 128);
+      mbar_init(empty(s), 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(acc_full(a), 1);
+      mbar_init(acc_empty(a), 128);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, C::tmem_cols);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+  const int tiles_mn = P.tiles_m * P.tiles_n;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      uint32_t it = 0;
+      const int a_kd = P.a.k_d, a_dk0 = P.a.dk0, a_dk1 = P.a.dk1, b_kd = P.b.k_d, b_dk0 = P.b.dk0, b_dk1 = P.b.dk1;
+      for (int t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
+        const int tm = t % P.tiles_m, tn = (t / P.tiles_m) % P.tiles_n;
+        const int z = t / tiles_mn, sk = z % p.splitk, bz = z / p.splitk;
+        const int kb0 = sk * P.kchunk_blocks, kb1 = min(P.kblocks, kb0 + P.kchunk_blocks);
+        int ca[5], cb[5];
+        opnd_coords(P.a, tm * BM, bz, ca);
+        opnd_coords(P.b, tn * BN, bz, cb);
+        for (int kb = kb0; kb < kb1; ++kb, ++it) {
+          const int s = it % S;
+          const uint32_t ph = (it / S) & 1;
+          opnd_set_k(a_kd, a_dk0, a_dk1, kb * BK, ca);
+          opnd_set_k(b_kd, b_dk0, b_dk1, kb * BK, cb);
+          mbar_wait(empty(s), ph ^ 1);
+          mbar_arrive_expect_tx(full(s), A_TILE_BYTES + C::b_tile);
+          opnd_load(P.a, &mapA, a_hi(s), full(s), ca, tm * BM);
+          opnd_load(P.b, &mapB, b_hi(s), full(s), cb, tn * BN);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ UMMA issuer
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_tf32(BM, BN, P.a.major, P.b.major);
+      const uint32_t a_step = P.a.major ? 1024u : 32u, b_step = P.b.major ? 1024u : 32u;
+      const uint32_t a_lbo = P.a.major ? BK * 128u : 16u, b_lbo = P.b.major ? BK * 128u : 16u;
+      const uint32_t a_sbo = P.a.major ? 512u : 1024u, b_sbo = P.b.major ? 512u : 1024u;
+      const uint32_t a_lay = P.a.major ? UMMA_LAYOUT_SW128_BASE32B : UMMA_LAYOUT_SW128;
+      const uint32_t b_lay = P.b.major ? UMMA_LAYOUT_SW128_BASE32B : UMMA_LAYOUT_SW128;
+      uint32_t it = 0, cit = 0;
+      for (int t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
+        const int z = t / tiles_mn, sk = z % p.splitk;
+        const int kb0 = sk * P.kchunk_blocks, kb1 = min(P.kblocks, kb0 + P.kchunk_blocks);
+        for (int c0 = kb0; c0 < kb1; c0 += P.kc, ++cit) {
+          const int c1 = min(kb1, c0 + P.kc);
+          const int buf = cit & 1;
+          mbar_wait(acc_empty(buf), ((cit >> 1) & 1) ^ 1);
+          tc_fence_after_sync();
+          const uint32_t d = tmem_base + buf * BN;
+          for (int kb = c0; kb < c1; ++kb, ++it) {
+            const int s = it % S;
+            const uint32_t ph = (it / S) & 1;
+            mbar_wait(use_prep ? ready(s) : full(s), ph);
+            tc_fence_after_sync();
+#pragma unroll
+            for (int k4 = 0; k4 < BK / 8; ++k4) {
+              const uint32_t acc = (kb > c0 || k4 > 0) ? 1u : 0u;
+              const uint64_t ah = umma_desc(a_hi(s) + k4 * a_step, a_lbo, a_sbo, a_lay);
+              const uint64_t bh = umma_desc(b_hi(s) + k4 * b_step, b_lbo, b_sbo, b_lay);
+              if (SPLIT) {
+                const uint64_t al = umma_desc(a_lo(s) + k4 * a_step, a_lbo, a_sbo, a_lay);
+                const uint64_t bl = umma_desc(b_lo(s) + k4 * b_step, b_lbo, b_sbo, b_lay);
+                umma_tf32(d, al, bh, idesc, acc);
+                umma_tf32(d, ah, bl, idesc, 1u);
+                umma_tf32(d, ah, bh, idesc, 1u);
+              } else {
+                umma_tf32(d, ah, bh, idesc, acc);
+              }
+            }
+            umma_commit(empty(s));
+          }
+          umma_commit(acc_full(buf));
+        }
+      }
+    }
+  } else if (warp < 6) {
+    // ------------------------------------------------------------------ operand preparation (activation-on-load, hi/lo split)
+    if (use_prep) {
+      const int ct = threadIdx.x - 64;
+      uint32_t it = 0;
+      for (int t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
+        const int z = t / tiles_mn, sk = z % p.splitk;
+        const int kb0 = sk * P.kchunk_blocks, kb1 = min(P.kblocks, kb0 + P.kchunk_blocks);
+        for (int kb = kb0; kb < kb1; ++kb, ++it) {
+          const int s = it % S;
+          const uint32_t ph = (it / S) & 1;
+          mbar_wait(full(s), ph);
+          if (SPLIT || p.a_act) prep_region<SPLIT>(a_hi(s), a_lo(s), A_TILE_BYTES / 16, p.a_act, ct);
+          if (SPLIT || p.b_act) prep_region<SPLIT>(b_hi(s), b_lo(s), C::b_tile / 16, p.b_act, ct);
+          fence_proxy_async_smem();
+          mbar_arrive(ready(s));
+        }
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue (warps 6..9 -> TMEM lane quadrant warp % 4)
+    const int quad = warp & 3;
+    const uint32_t scr = scratch_base + quad * (32 * 36 * 4);
+    const bool col_contig = (p.c.c.sl == 1) && (p.c.c.d == INT_MAX || (p.c.c.d % 32) == 0) && P.dbg != 3;
+    uint32_t cit = 0;
+    long long t_wait = 0, t_ld = 0, t_emit = 0, t_all0 = clock64();
+    for (int t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
+      const int tm = t % P.tiles_m, tn = (t / P.tiles_m) % P.tiles_n;
+      const int z = t / tiles_mn, sk = z % p.splitk, bz = z / p.splitk;
+      const int kb0 = sk * P.kchunk_blocks, kb1 = min(P.kblocks, kb0 + P.kchunk_blocks);
+      const int m_base = tm * BM + quad * 32;
+      const int m = m_base + lane;
+      const bool mval = m < p.M;
+      const long long ro = off2(p.c.b, bz) + off2(p.c.r, mval ? m : 0);
+      const float bias_m = (p.bias_mode == 2 && mval) ? __ldg(p.bias + m) : 0.f;
+
+      // one 32-column slice of this warp's 32 rows: v[j] = accumulator of (row m, column n0 + j)
+      auto emit = [&](const float* v, int n0) {
+        if (P.dbg == 5) return;
+        if (col_contig) {
+          // transpose through shared memory so that global accesses run along the contiguous columns
+#pragma unroll
+          for (int q = 0; q < 8; ++q)
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(scr + (lane * 36 + 4 * q) * 4), "f"(v[4 * q]),
+                         "f"(v[4 * q + 1]), "f"(v[4 * q + 2]), "f"(v[4 * q + 3]) : "memory");
+          __syncwarp();
+          const long long coff = off2(p.c.c, n0);
+          const bool aligned = !mval || (((ro + coff) & 3) == 0);
+          const bool vec = P.c_vec && (n0 + 32 <= p.N) && __all_sync(0xffffffffu, aligned);
+          if (vec) {
+            const int rs = lane >> 3, c4 = (lane & 7) * 4;
+            float4 bn = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (p.bias_mode == 1) bn = __ldg(reinterpret_cast<const float4*>(p.bias + n0 + c4));
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int r = i * 4 + rs;
+              const long long ror = __shfl_sync(0xffffffffu, ro, r);
+              const float bm = __shfl_sync(0xffffffffu, bias_m, r);
+              const bool mv = (m_base + r) < p.M;
+              float4 x;
+              asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x.x), "=f"(x.y), "=f"(x.z), "=f"(x.w) : "r"(scr + (r * 36 + c4) * 4));
+              if (!mv) continue;
+              const long long o = ror + coff + c4;
+              x.x *= p.alpha; x.y *= p.alpha; x.z *= p.alpha; x.w *= p.alpha;
+              if (p.splitk > 1) {
+                atomicAdd(p.C + o, x.x); atomicAdd(p.C + o + 1, x.y); atomicAdd(p.C + o + 2, x.z); atomicAdd(p.C + o + 3, x.w);
+                continue;
+              }
+              if (p.bias_mode == 1) { x.x += bn.x; x.y += bn.y; x.z += bn.z; x.w += bn.w; }
+              else if (p.bias_mode == 2) { x.x += bm; x.y += bm; x.z += bm; x.w += bm; }
+              if (p.beta) {
+                const float4 cv = *reinterpret_cast<const float4*>(p.C + o);
+                x.x += cv.x; x.y += cv.y; x.z += cv.z; x.w += cv.w;
+              }
+              if (p.Z) *reinterpret_cast<float4*>(p.Z + o) = x;
+              if (p.act) x = act4_slow(p.act, x);
+              if (p.dact) {
+                const float4 dv = dact4_slow(p.dact, __ldg(reinterpret_cast<const float4*>(p.aux + o)));
+                x.x *= dv.x; x.y *= dv.y; x.z *= dv.z; x.w *= dv.w;
+              }
+              if (P.dbg != 4) *reinterpret_cast<float4*>(p.C + o) = x;
+            }
+          } else {
+            const int n = n0 + lane;
+            const bool nval = n < p.N;
+            const long long co = off2(p.c.c, nval ? n : 0);
+            const float bn = (p.bias_mode == 1 && nval) ? __ldg(p.bias + n) : 0.f;
+#pragma unroll 4
+            for (int r = 0; r < 32; ++r) {
+              const long long ror = __shfl_sync(0xffffffffu, ro, r);
+              const float bm = __shfl_sync(0xffffffffu, bias_m, r);
+              float x;
+              asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x) : "r"(scr + (r * 36 + lane) * 4));
+              if (!nval || (m_base + r) >= p.M) continue;
+              const long long o = ror + co;
+              x *= p.alpha;
+              if (p.splitk > 1) {
+                atomicAdd(p.C + o, x);
+                continue;
+              }
+              if (p.bias_mode == 1) x += bn;
+              else if (p.bias_mode == 2) x += bm;
+              if (p.beta) x += p.C[o];
+              if (p.Z) p.Z[o] = x;
+              if (p.act) x = act1_slow(p.act, x);
+              if (p.dact) x *= dact1_slow(p.dact, __ldg(p.aux + o));
+              p.C[o] = x;
+            }
+          }
+          __syncwarp();
+        } else if (mval) {
+          // rows are the contiguous (or an arbitrary) direction: one row per lane is already the coalesced order
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int n = n0 + j;
+            if (n >= p.N) break;
+            const long long o = ro + off2(p.c.c, n);
+            float x = p.alpha * v[j];
+            if (p.splitk > 1) {
+              atomicAdd(p.C + o, x);
+              continue;
+            }
+            if (p.bias_mode == 1) x += __ldg(p.bias + n);
+            else if (p.bias_mode == 2) x += bias_m;
+            if (p.beta) x += p.C[o];
+            if (p.Z) p.Z[o] = x;
+            if (p.act) x = act1_slow(p.act, x);
+            if (p.dact) x *= dact1_slow(p.dact, __ldg(p.aux + o));
+            p.C[o] = x;
+          }
+        }
+      };
+
+      if (!CH) {
+        const int buf = cit & 1;
+        long long c0 = clock64();
+        mbar_wait(acc_full(buf), (cit >> 1) & 1);
+        tc_fence_after_sync();
+        t_wait += clock64() - c0;
+#pragma unroll 1
+        for (int cc = 0; cc < BN / 32; ++cc) {
+          const int n0 = tn * BN + cc * 32;
+          if (n0 >= p.N) break;  // warp-uniform
+          uint32_t r[32];
+          c0 = clock64();
+          tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + buf * BN + cc * 32, r);
+          tmem_ld_wait();
+          long long c1 = clock64();
+          t_ld += c1 - c0;
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+          emit(v, n0);
+          __syncwarp();
+          t_emit += clock64() - c1;
+        }
+        tc_fence_before_sync();
+        mbar_arrive(acc_empty(buf));
+        ++cit;
+      } else {
+        float acc[BN];
+#pragma unroll
+        for (int j = 0; j < BN; ++j) acc[j] = 0.f;
+        for (int c0 = kb0; c0 < kb1; c0 += P.kc, ++cit) {
+          const int buf = cit & 1;
+          mbar_wait(acc_full(buf), (cit >> 1) & 1);
+          tc_fence_after_sync();
+#pragma unroll
+          for (int cc = 0; cc < BN / 32; ++cc) {
+            uint32_t r[32];
+            tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + buf * BN + cc * 32, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) acc[cc * 32 + j] += __uint_as_float(r[j]);
+          }
+          tc_fence_before_sync();
+          mbar_arrive(acc_empty(buf));
+        }
+#pragma unroll
+        for (int cc = 0; cc < BN / 32; ++cc) {
+          const int n0 = tn * BN + cc * 32;
+          if (n0 < p.N) emit(&acc[cc * 32], n0);
+          __syncwarp();
+        }
+      }
+    }
+    if (P.dbg == 8 && blockIdx.x == 0 && lane == 0)
+      printf("[tc epi] warp %d: total %lld wait_acc %lld tmem_ld %lld emit %lld cycles\n", warp, clock64() - t_all0, t_wait, t_ld, t_emit);
+  }
+
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after_sync();
+    tmem_dealloc(tmem_base, C::tmem_cols);
+  }
+}
+
+}  // namespace tc
+
+// ================================================================================================
+// Host side: GemmP index maps -> TMA tensor maps, tile/split-K choice, launch.
+// ================================================================================================
+namespace tc {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess) p = nullptr;
+    return (EncodeTiledFn)p;
+  }();
+  return fn;
+}
+
+struct Lvl {
+  long long size, stride;  // elements
+};
+
+// index map + extent -> one or two (size, stride) levels; *d = divisor of the two-level form
+static int split_levels(const Idx2& m, long long extent, Lvl out[2], int* d) {
+  if (m.d == INT_MAX || m.d >= extent) {
+    out[0] = Lvl{extent, m.sl};
+    *d = INT_MAX;
+    return 1;
+  }
+  if (m.d == 1) {  // degenerate split: i / 1 * sh
+    out[0] = Lvl{extent, m.sh};
+    *d = INT_MAX;
+    return 1;
+  }
+  if (extent % m.d) return -1;
+  out[0] = Lvl{m.d, m.sl};
+  out[1] = Lvl{extent / m.d, m.sh};
+  *d = m.d;
+  return 2;
+}
+
+// Builds the tensor map + device recipe of one operand.  Returns false when TMA cannot address it (-> CUDA-core engine).
+static bool build_operand(const float* base, const Idx2& mn_map, long long MN, const Idx2& k_map, long long K, const Idx2& b_map,
+                          long long BT, int tile_mn, CUtensorMap* map, TcOpnd* o) {
+  EncodeTiledFn enc = encode_fn();
+  if (!enc || (reinterpret_cast<uintptr_t>(base) & 15)) return false;
+  Lvl lm[2], lk[2], lb[2];
+  const int nm = split_levels(mn_map, MN, lm, &o->mn_d);
+  const int nk = split_levels(k_map, K, lk, &o->k_d);
+  const int nb = split_levels(b_map, BT, lb, &o->b_d);
+  if (nm < 0 || nk < 0 || nb < 0) return false;
+  if (lk[0].stride == 1 && (nk == 1 || lk[0].size % BK == 0)) o->major = 0;
+  else if (lm[0].stride == 1 && (nm == 1 || lm[0].size % 32 == 0)) o->major = 1;
+  else return false;
+
+  struct Dim {
+    long long size, stride;
+    int box;
+    signed char* slot;
+  };
+  Dim dims[8];
+  int nd = 0;
+  o->dm0 = o->dm1 = o->dk0 = o->dk1 = o->db0 = o->db1 = o->dg = -1;
+  o->grouped = 0;
+  if (o->major == 0) {
+    int bm0 = tile_mn, bm1 = 1;
+    if (nm == 2) {
+      const long long d = lm[0].size;
+      if (d % tile_mn == 0) { bm0 = tile_mn; bm1 = 1; }
+      else if (tile_mn % d == 0) { bm0 = (int)d; bm1 = (int)(tile_mn / d); }
+      else return false;
+    }
+    dims[nd++] = Dim{lk[0].size, lk[0].stride, BK, &o->dk0};
+    if (nk == 2) dims[nd++] = Dim{lk[1].size, lk[1].stride, 1, &o->dk1};
+    dims[nd++] = Dim{lm[0].size, lm[0].stride, bm0, &o->dm0};
+    if (nm == 2) dims[nd++] = Dim{lm[1].size, lm[1].stride, bm1, &o->dm1};
+    o->boxes = 1;
+    o->box_mn = tile_mn;
+    o->box_bytes = tile_mn * BK * 4;
+  } else {
+    if (nk == 2 && lk[0].size % BK) return false;
+    // preferred: the 32-element MN groups become a tensor dimension, so one box brings the whole tile
+    const long long lo_ext = lm[0].size;
+    const bool can_group = (lo_ext % 32 == 0) && (nm == 1 || lo_ext % tile_mn == 0 || tile_mn % lo_ext == 0);
+    const int nb_live = (lb[0].size > 1 && lb[0].stride != 0 ? 1 : 0) + (nb == 2 && lb[1].size > 1 && lb[1].stride != 0 ? 1 : 0);
+    const int rank_grouped = 1 + nk + 1 + (nm == 2 ? 1 : 0) + nb_live;
+    if (can_group && rank_grouped <= 5) {
+      int bg = tile_mn / 32, bm1 = 1;
+      if (nm == 2 && lo_ext < tile_mn) { bg = (int)(lo_ext / 32); bm1 = (int)(tile_mn / lo_ext); }
+      static signed char dummy;
+      dims[nd++] = Dim{32, 1, 32, &dummy};
+      dims[nd++] = Dim{lk[0].size, lk[0].stride, BK, &o->dk0};
+      if (nk == 2) dims[nd++] = Dim{lk[1].size, lk[1].stride, 1, &o->dk1};
+      dims[nd++] = Dim{lo_ext / 32, 32, bg, &o->dg};
+      if (nm == 2) dims[nd++] = Dim{lm[1].size, lm[1].stride, bm1, &o->dm1};
+      o->grouped = 1;
+      o->boxes = 1;
+      o->box_mn = tile_mn;
+      o->box_bytes = tile_mn * BK * 4;
+    } else {
+      dims[nd++] = Dim{lm[0].size, lm[0].stride, 32, &o->dm0};
+      dims[nd++] = Dim{lk[0].size, lk[0].stride, BK, &o->dk0};
+      if (nk == 2) dims[nd++] = Dim{lk[1].size, lk[1].stride, 1, &o->dk1};
+      if (nm == 2) dims[nd++] = Dim{lm[1].size, lm[1].stride, 1, &o->dm1};
+      o->boxes = tile_mn / 32;
+      o->box_mn = 32;
+      o->box_bytes = 32 * BK * 4;
+    }
+  }
+  dims[nd++] = Dim{lb[0].size, lb[0].stride, 1, &o->db0};
+  if (nb == 2) dims[nd++] = Dim{lb[1].size, lb[1].stride, 1, &o->db1};
+
+  cuuint64_t gdim[5], gstr[5];
+  cuuint32_t box[5], estr[5] = {1, 1, 1, 1, 1};
+  int r = 0;
+  for (int i = 0; i < nd; ++i) {
+    Dim& dm = dims[i];
+    if (i > 0 && dm.box == 1 && (dm.size == 1 || dm.stride == 0)) continue;  // coordinate contributes nothing
+    if (i > 0) {
+      if (dm.size == 1 && (dm.stride <= 0 || (dm.stride & 3))) dm.stride = 1LL << 20;  // never dereferenced beyond index 0
+      if (dm.stride <= 0 || (dm.stride & 3)) return false;                              // TMA: 16-byte multiples
+    }
+    if (r == 5 || dm.size <= 0 || dm.size > 0xffffffffLL) return false;
+    gdim[r] = (cuuint64_t)dm.size;
+    gstr[r] = (cuuint64_t)dm.stride * 4;
+    box[r] = (cuuint32_t)dm.box;
+    *dm.slot = (signed char)r;
+    ++r;
+  }
+  o->ndim = r;
+  if (r < 2) return false;
+  const CUresult rc = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)r, const_cast<float*>(base), gdim, gstr + 1, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, o->major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return rc == CUDA_SUCCESS;
+}
+
+template <int BN, bool SPLIT, bool CH>
+static cudaError_t launch_cfg(const TcParams& P, const CUtensorMap& ma, const CUtensorMap& mb, int sms, cudaStream_t s) {
+  using C = Cfg<BN, SPLIT>;
+  static std::once_flag once;
+  static cudaError_t attr_rc = cudaSuccess;
+  std::call_once(once, [] {
+    attr_rc = cudaFuncSetAttribute(gemm_tc_kernel<BN, SPLIT, CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::smem_bytes);
+  });
+  if (attr_rc != cudaSuccess) return attr_rc;
+  const int grid = P.total_tiles < sms ? P.total_tiles : sms;
+  gemm_tc_kernel<BN, SPLIT, CH><<<grid, kThreads, C::smem_bytes, s>>>(P, ma, mb);
+  return cudaGetLastError();
+}
+
+}  // namespace tc
+
+// Tries the tensor-core engine; *launched = false means the shape is not TMA-addressable (caller falls back).
+static cudaError_t gemm_tc_try_launch(const GemmP& g, int prec, cudaStream_t s, bool* launched) {
+  using namespace tc;
+  *launched = false;
+  if (g.M <= 0 || g.N <= 0 || g.K <= 0 || g.batch <= 0) return cudaSuccess;
+  if ((long long)g.M * g.N * g.K * g.batch < (1LL << 18)) return cudaSuccess;  // launch-bound: CUDA cores do as well
+  TcParams P;
+  P.g = g;
+  {
+    const char* e = getenv("RPDE_TC_DBG");
+    P.dbg = e ? atoi(e) : 0;
+  }
+  CUtensorMap ma, mb;
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  static const int kc_env = getenv("RPDE_TC_KC") ? atoi(getenv("RPDE_TC_KC")) : 0;
+  const int kc = kc_env > 0 ? kc_env : 8;  // k-blocks (x32) per TMEM accumulation chain
+  const int kblocks = (g.K + BK - 1) / BK;
+  const int tiles_m = (g.M + BM - 1) / BM;
+  // split-K (only when the caller allows atomically accumulated output)
+  auto choose_split = [&](int BN) {
+    int splitk = g.splitk;
+    if (splitk == 0) {
+      const long long ctas = (long long)tiles_m * ((g.N + BN - 1) / BN) * g.batch;
+      long long want = (sms + ctas - 1) / ctas;
+      const long long maxs = (kblocks + 7) / 8;  // at least 256 k per split
+      if (want > maxs) want = maxs;
+      if (want < 1) want = 1;
+      splitk = (int)want;
+    }
+    return splitk;
+  };
+  int BN = g.N > 128 ? 256 : (g.N > 64 ? 128 : 64);
+  // long reductions are chunked and summed in registers: that variant holds BN accumulators per thread
+  {
+    const int sk = choose_split(BN);
+    const int per_tile = (kblocks + sk - 1) / sk;
+    if (per_tile > kc && BN > 128) BN = 128;
+  }
+  bool ok = false;
+  for (; BN >= 64; BN >>= 1) {
+    ok = build_operand(g.A, g.a.r, g.M, g.a.c, g.K, g.a.b, g.batch, BM, &ma, &P.a) &&
+         build_operand(g.B, g.b.c, g.N, g.b.r, g.K, g.b.b, g.batch, BN, &mb, &P.b);
+    if (ok) break;
+  }
+  if (!ok) return cudaSuccess;
+  P.tiles_m = tiles_m;
+  P.tiles_n = (g.N + BN - 1) / BN;
+  P.kblocks = kblocks;
+  int splitk = choose_split(BN);
+  P.kchunk_blocks = (P.kblocks + splitk - 1) / splitk;
+  splitk = (P.kblocks + P.kchunk_blocks - 1) / P.kchunk_blocks;
+  P.g.splitk = splitk;
+  const bool chunked = P.kchunk_blocks > kc;
+  P.kc = chunked ? kc : P.kchunk_blocks;
+  auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+  P.c_vec = al16(g.C) && al16(g.Z) && al16(g.aux) && al16(g.bias);
+  const long long total = (long long)P.tiles_m * P.tiles_n * g.batch * splitk;
+  if (total > 0x7fffffffLL) return cudaSuccess;
+  P.total_tiles = (int)total;
+  const bool split3 = (prec == 1);
+  cudaError_t rc;
+  if (chunked) {
+    if (BN == 128) rc = split3 ? launch_cfg<128, true, true>(P, ma, mb, sms, s) : launch_cfg<128, false, true>(P, ma, mb, sms, s);
+    else rc = split3 ? launch_cfg<64, true, true>(P, ma, mb, sms, s) : launch_cfg<64, false, true>(P, ma, mb, sms, s);
+  } else if (BN == 256) {
+    rc = split3 ? launch_cfg<256, true, false>(P, ma, mb, sms, s) : launch_cfg<256, false, false>(P, ma, mb, sms, s);
+  } else if (BN == 128) {
+    rc = split3 ? launch_cfg<128, true, false>(P, ma, mb, sms, s) : launch_cfg<128, false, false>(P, ma, mb, sms, s);
+  } else {
+    rc = split3 ? launch_cfg<64, true, false>(P, ma, mb, sms, s) : launch_cfg<64, false, false>(P, ma, mb, sms, s);
+  }
+  *launched = (rc == cudaSuccess);
+  if (P.dbg == 9)
+    fprintf(stderr, "[rpde tc] M=%d N=%d K=%d batch=%d BN=%d splitk=%d majorA=%d majorB=%d tiles=%d beta=%d act=%d\n", g.M, g.N, g.K,
+            g.batch, BN, splitk, P.a.major, P.b.major, P.total_tiles, g.beta, g.act);
+  return rc;
+}
+
+}  // namespace rpde

@@ -3,6 +3,7 @@
 // contractions (gemm_*.cuh) and pointwise kernels (pointwise.cuh) enqueued on the caller's stream.
 #include <cuda_runtime.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <atomic>
 
@@ -30,6 +31,7 @@ static int fail(int code, const char* fmt, const char* a = "") {
   } while (0)
 // launch statistics only (monotonic counter of kernels this library enqueued; read by bench.py)
 static std::atomic<unsigned long long> g_launches{0};
+static std::atomic<unsigned long long> g_tc_launches{0};  // contractions that ran on the tcgen05 engine
 #define RPDE_LAUNCH_CHECK()        \
   do {                             \
     g_launches.fetch_add(1);       \
@@ -39,8 +41,20 @@ static std::atomic<unsigned long long> g_launches{0};
 static cudaError_t gemm(const GemmP& p, cudaStream_t s) {
   if (p.M > 0 && p.N > 0 && p.batch > 0) g_launches.fetch_add(1);
 #ifdef RPDE_WITH_TC
-  if (g_prec != RPDE_PREC_FP32 && gemm_tc_supported(p)) return gemm_tc_launch(p, g_prec, s);
+  if (g_prec != RPDE_PREC_FP32) {
+    bool launched = false;
+    const cudaError_t rc = gemm_tc_try_launch(p, g_prec, s, &launched);
+    if (rc != cudaSuccess) return rc;
+    if (launched) {
+      g_tc_launches.fetch_add(1);
+      return cudaSuccess;
+    }
+  }
 #endif
+  {
+    static const bool log = getenv("RPDE_TC_DBG") && atoi(getenv("RPDE_TC_DBG")) == 9;
+    if (log) fprintf(stderr, "[rpde simt] M=%d N=%d K=%d batch=%d splitk=%d\n", p.M, p.N, p.K, p.batch, p.splitk);
+  }
   return gemm_simt_launch(p, s);
 }
 
@@ -69,6 +83,7 @@ int rpde_set_precision(int prec) {
 }
 int rpde_get_precision(void) { return g_prec; }
 unsigned long long rpde_launch_count(void) { return g_launches.load(); }
+unsigned long long rpde_tc_launch_count(void) { return g_tc_launches.load(); }
 
 // ------------------------------------------------------------------------------------------------
 int rpde_dft_table(float* out, int kind, int n, int k, int m1, double scale, rpde_stream_t stream) {

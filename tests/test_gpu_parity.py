@@ -16,10 +16,15 @@ CASES = sorted(os.path.basename(p) for p in glob.glob(os.path.join(GOLD, "*.npz"
 DEV = "cuda:0"
 
 
-@pytest.fixture(autouse=True)
-def _fp32_engine():
+# Every parity test runs on both fp32-accurate engines: the CUDA-core FMA engine ("fp32") and the tcgen05 3xTF32
+# engine ("3xtf32"); the tolerance is the same 1e-5 (BASELINE.json north_star).  RPDE_TEST_PRECISION restricts the set.
+ENGINES = [e for e in os.environ.get("RPDE_TEST_PRECISION", "fp32,3xtf32").split(",") if e]
+
+
+@pytest.fixture(autouse=True, params=ENGINES)
+def _engine(request):
     import resolution_pde_b200 as R
-    R.set_precision("fp32")
+    R.set_precision(request.param)
     yield
     R.set_precision("fp32")
 
@@ -247,7 +252,8 @@ def test_matmul_engine_vs_fp64():
         b = torch.randn((N, K) if tb else (K, N), device=DEV)
         got = R.ops.matmul(a, b, bool(ta), bool(tb))
         want = (a.double().T if ta else a.double()) @ (b.double().T if tb else b.double())
-        assert rel(got, want) < 2e-6, (M, N, K, ta, tb, rel(got, want))
+        # 3xTF32 chains are cut at 256 k: the accumulator-truncation bias of the tensor core stays near 2e-6 (fp32 FMA: < 1e-6)
+        assert rel(got, want) < (4e-6 if R.get_precision() == "3xtf32" else 2e-6), (M, N, K, ta, tb, rel(got, want))
 
 
 def test_weight_grad_long_reduction_accuracy():
