@@ -10,14 +10,18 @@
 //   warp 0      TMA producer (one lane): fills a ring of {A,B} stages, full[s] <- complete_tx
 //   warp 1      UMMA issuer (one lane) + TMEM owner: 4 (x3) tcgen05.mma per stage, commit -> empty[s]; last -> acc_full
 //   warps 2-5   splitter (3xTF32 only): hi/lo split of the landed tiles in place, fence.proxy.async, -> ready[s]
-//   warps 6-9   epilogue: tcgen05.ld 32x32b.x32, bias / beta / activation / act' / split-K atomics, global stores;
-//               two TMEM accumulators so the epilogue of tile i overlaps the main loop of tile i+1.
+//   warps 6-13  epilogue (two warps per TMEM lane quadrant, half of the columns each): tcgen05.ld 32x32b.x32, bias /
+//               activation / act' in registers, rows staged in a 128B-swizzled 32x32 box per warp and written with bulk tensor
+//               stores (Z and C), old C / aux fetched into the same box with bulk tensor loads, beta-only as a bulk
+//               reduce-add; outputs TMA cannot address (split-K atomics, row-contiguous or unaligned C) take the
+//               register/transposition path.  Two TMEM accumulators: the epilogue of tile i overlaps the main loop of i+1.
 // Operands are addressed through TMA tensor maps derived from the GemmP index maps (K-major or MN-major, up to two
 // levels per index), so the channels-last / channels-first / interleaved layouts of the spectral path need no copies.
 #pragma once
 #include <cuda.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
 #include <mutex>
 
 #include "common.cuh"
@@ -39,7 +43,10 @@ struct TcOpnd {
 
 struct TcParams {
   GemmP g;
-  TcOpnd a, b;
+  TcOpnd a, b, c;   // c: the output viewed as rows x contiguous columns (TMA epilogue), boxes of 32 x 32
+  int epi_tma;      // 1: C / Z leave through bulk tensor stores from the staging boxes, aux / old C arrive the same way
+  int epi_reduce;   // 1: beta is realised as a bulk tensor reduce-add (no activation, no Z)
+  int n_fast;       // tile order: n runs fastest
   int tiles_m, tiles_n, kblocks, kchunk_blocks, total_tiles;
   int kc;       // k-blocks per TMEM accumulation chain (chunk); chunks are summed in registers with RN adds
   int c_vec;    // C / Z / aux / bias base pointers are 16-byte aligned
@@ -50,9 +57,10 @@ namespace tc {
 
 constexpr int BM = 128, BK = 32;
 constexpr int A_TILE_BYTES = BM * BK * 4;
-constexpr int kThreads = 320;
-constexpr int kScratchBytes = 4 * 32 * 36 * 4;  // epilogue transposition scratch, one 32x36 fp32 pad per warp
-constexpr int kSmemBudget = 227 * 1024 - 2048 - kScratchBytes;
+constexpr int kEpiWarps = 8;                         // two warps per TMEM lane quadrant, each owning half of the tile's columns
+constexpr int kThreads = 32 * (6 + kEpiWarps);
+constexpr int kEpiBytes = kEpiWarps * 4096;          // one 128B-swizzled 32x32 fp32 staging box per epilogue warp
+constexpr int kSmemBudget = 227 * 1024 - 2048 - kEpiBytes;
 
 template <int BN, bool SPLIT>
 struct Cfg {
@@ -60,7 +68,7 @@ struct Cfg {
   static constexpr int stage_bytes = (A_TILE_BYTES + b_tile) * (SPLIT ? 2 : 1);
   static constexpr int raw = kSmemBudget / stage_bytes;
   static constexpr int stages = raw > 6 ? 6 : raw;
-  static constexpr int smem_bytes = stages * stage_bytes + kScratchBytes + 2048;  // + alignment slack + barriers
+  static constexpr int smem_bytes = stages * stage_bytes + kEpiBytes + 2048;  // + alignment slack + barriers
   static constexpr int tmem_cols = 2 * BN < 32 ? 32 : 2 * BN;
 };
 
@@ -105,36 +113,81 @@ __device__ __forceinline__ void opnd_load(const TcOpnd& o, const CUtensorMap* ma
   }
 }
 
-// Activation code is kept out of line: inlined, the compiler if-converts the erff/expf sequences and every
-// epilogue iteration pays for them even when no activation is requested.
-__device__ __noinline__ float4 act4_slow(int act, float4 x) {
+// tile id -> (tm, tn, z): the dimension with fewer tiles runs fastest so that concurrently resident CTAs share the
+// larger operand's tiles through L2
+__device__ __forceinline__ void tile_coords(const TcParams& P, int t, int& tm, int& tn, int& z) {
+  const int tiles_mn = P.tiles_m * P.tiles_n;
+  z = t / tiles_mn;
+  const int r = t - z * tiles_mn;
+  if (P.n_fast) {
+    tn = r % P.tiles_n;
+    tm = r / P.tiles_n;
+  } else {
+    tm = r % P.tiles_m;
+    tn = r / P.tiles_m;
+  }
+}
+
+// warp-uniform activation over one 32-column slice (branches are uniform, the unrolled bodies give the ILP)
+__device__ __forceinline__ void act32(int act, float (&v)[32]) {
+  if (act == ACT_GELU) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = gelu_f(v[j]);
+  } else if (act == ACT_RELU) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = v[j] > 0.f ? v[j] : 0.f;
+  }
+}
+__device__ __forceinline__ void dact32_mul(int act, float (&v)[32], const float (&z)[32]) {
+  if (act == ACT_GELU) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] *= dgelu_f(z[j]);
+  } else if (act == ACT_RELU) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = z[j] > 0.f ? v[j] : 0.f;
+  }
+}
+__device__ __forceinline__ float4 act4(int act, float4 x) {
   x.x = act_f(act, x.x); x.y = act_f(act, x.y); x.z = act_f(act, x.z); x.w = act_f(act, x.w);
   return x;
 }
-__device__ __noinline__ float4 dact4_slow(int act, float4 z) {
+__device__ __forceinline__ float4 dact4(int act, float4 z) {
   z.x = dact_f(act, z.x); z.y = dact_f(act, z.y); z.z = dact_f(act, z.z); z.w = dact_f(act, z.w);
   return z;
 }
-__device__ __noinline__ float act1_slow(int act, float x) { return act_f(act, x); }
-__device__ __noinline__ float dact1_slow(int act, float z) { return dact_f(act, z); }
 
 __device__ __forceinline__ float tf32_trunc(float v) { return __uint_as_float(__float_as_uint(v) & 0xffffe000u); }
+__device__ __forceinline__ float4 lds128(uint32_t a) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t a, float4 v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
 
 // in-place preparation of one landed operand region: optional activation-on-load, optional hi/lo split.
 // The tensor core truncates fp32 operands to TF32 itself, so the hi tile is the raw tile; lo = x - trunc(x) is exact.
+// n16 (float4 count) is a multiple of 512: every thread handles whole batches of four, loads first, so the shared-memory
+// latency is paid once per batch instead of once per element.
 template <bool SPLIT>
 __device__ __forceinline__ void prep_region(uint32_t hi0, uint32_t lo0, int n16, int act, int ct) {
-#pragma unroll 4
-  for (int i = ct; i < n16; i += 128) {
-    float4 v;
-    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(hi0 + 16 * i));
+  for (int i0 = ct; i0 < n16; i0 += 512) {
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) v[u] = lds128(hi0 + 16 * (i0 + 128 * u));
     if (act) {
-      v = act4_slow(act, v);
-      asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(hi0 + 16 * i), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        v[u] = act4(act, v[u]);
+        sts128(hi0 + 16 * (i0 + 128 * u), v[u]);
+      }
     }
     if (SPLIT) {
-      asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(lo0 + 16 * i), "f"(v.x - tf32_trunc(v.x)),
-                   "f"(v.y - tf32_trunc(v.y)), "f"(v.z - tf32_trunc(v.z)), "f"(v.w - tf32_trunc(v.w)) : "memory");
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        sts128(lo0 + 16 * (i0 + 128 * u), make_float4(v[u].x - tf32_trunc(v[u].x), v[u].y - tf32_trunc(v[u].y),
+                                                      v[u].z - tf32_trunc(v[u].z), v[u].w - tf32_trunc(v[u].w)));
     }
   }
 }
@@ -145,7 +198,8 @@ __device__ __forceinline__ void prep_region(uint32_t hi0, uint32_t lo0, int n16,
 template <int BN, bool SPLIT, bool CH>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUtensorMap mapA,
-               const __grid_constant__ CUtensorMap mapB) {
+               const __grid_constant__ CUtensorMap mapB, const __grid_constant__ CUtensorMap mapC,
+               const __grid_constant__ CUtensorMap mapZ, const __grid_constant__ CUtensorMap mapI) {
   using C = Cfg<BN, SPLIT>;
   constexpr int S = C::stages;
   extern __shared__ uint8_t smem_raw[];
@@ -155,14 +209,15 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
   auto b_hi = [&](int s) { return smem_base + s * C::stage_bytes + A_TILE_BYTES; };
   auto a_lo = [&](int s) { return smem_base + s * C::stage_bytes + A_TILE_BYTES + C::b_tile; };
   auto b_lo = [&](int s) { return smem_base + s * C::stage_bytes + 2 * A_TILE_BYTES + C::b_tile; };
-  const uint32_t scratch_base = smem_base + S * C::stage_bytes;
-  const uint32_t bar_base = scratch_base + kScratchBytes;
+  const uint32_t epi_base = smem_base + S * C::stage_bytes;  // 1024-aligned: the staging boxes use the TMA 128B swizzle
+  const uint32_t bar_base = epi_base + kEpiBytes;
   auto full = [&](int s) { return bar_base + 8 * s; };
   auto ready = [&](int s) { return bar_base + 8 * (S + s); };
   auto empty = [&](int s) { return bar_base + 8 * (2 * S + s); };
   auto acc_full = [&](int a) { return bar_base + 8 * (3 * S + a); };
   auto acc_empty = [&](int a) { return bar_base + 8 * (3 * S + 2 + a); };
-  const uint32_t tmem_slot = bar_base + 8 * (3 * S + 4);
+  auto epi_in = [&](int w) { return bar_base + 8 * (3 * S + 4 + w); };
+  const uint32_t tmem_slot = bar_base + 8 * (3 * S + 4 + kEpiWarps);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const GemmP& p = P.g;
@@ -171,6 +226,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&mapA);
     tma_prefetch_desc(&mapB);
+    if (P.epi_tma) tma_prefetch_desc(&mapC);
     for (int s = 0; s < S; ++s) {
       mbar_init(full(s), 1);
       mbar_init(ready(s), 128);
@@ -178,8 +234,9 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(acc_full(a), 1);
-      mbar_init(acc_empty(a), 128);
+      mbar_init(acc_empty(a), 32 * kEpiWarps);
     }
+    for (int w = 0; w < kEpiWarps; ++w) mbar_init(epi_in(w), 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, C::tmem_cols);
@@ -189,16 +246,15 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
-  const int tiles_mn = P.tiles_m * P.tiles_n;
-
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
       uint32_t it = 0;
       const int a_kd = P.a.k_d, a_dk0 = P.a.dk0, a_dk1 = P.a.dk1, b_kd = P.b.k_d, b_dk0 = P.b.dk0, b_dk1 = P.b.dk1;
       for (int t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
-        const int tm = t % P.tiles_m, tn = (t / P.tiles_m) % P.tiles_n;
-        const int z = t / tiles_mn, sk = z % p.splitk, bz = z / p.splitk;
+        int tm, tn, z;
+        tile_coords(P, t, tm, tn, z);
+        const int sk = z % p.splitk, bz = z / p.splitk;
         const int kb0 = sk * P.kchunk_blocks, kb1 = min(P.kblocks, kb0 + P.kchunk_blocks);
         int ca[5], cb[5];
         opnd_coords(P.a, tm * BM, bz, ca);
@@ -226,7 +282,9 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
       const uint32_t b_lay = P.b.major ? UMMA_LAYOUT_SW128_BASE32B : UMMA_LAYOUT_SW128;
       uint32_t it = 0, cit = 0;
       for (int t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
-        const int z = t / tiles_mn, sk = z % p.splitk;
+        int tm, tn, z;
+        tile_coords(P, t, tm, tn, z);
+        const int sk = z % p.splitk;
         const int kb0 = sk * P.kchunk_blocks, kb1 = min(P.kblocks, kb0 + P.kchunk_blocks);
         for (int c0 = kb0; c0 < kb1; c0 += P.kc, ++cit) {
           const int c1 = min(kb1, c0 + P.kc);
@@ -266,7 +324,9 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
       const int ct = threadIdx.x - 64;
       uint32_t it = 0;
       for (int t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
-        const int z = t / tiles_mn, sk = z % p.splitk;
+        int tm, tn, z;
+        tile_coords(P, t, tm, tn, z);
+        const int sk = z % p.splitk;
         const int kb0 = sk * P.kchunk_blocks, kb1 = min(P.kblocks, kb0 + P.kchunk_blocks);
         for (int kb = kb0; kb < kb1; ++kb, ++it) {
           const int s = it % S;
@@ -280,31 +340,119 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
       }
     }
   } else {
-    // ------------------------------------------------------------------ epilogue (warps 6..9 -> TMEM lane quadrant warp % 4)
-    const int quad = warp & 3;
-    const uint32_t scr = scratch_base + quad * (32 * 36 * 4);
+    // ------------------------------------------------------------------ epilogue: warps 6..13.  A warp may only touch the
+    // TMEM lane quadrant (warp % 4); the two warps of a quadrant split the tile's columns in halves.
+    const int ew = warp - 6;
+    const int quad = warp & 3, half = ew >> 2;
+    constexpr int CPW = (BN / 32) / 2;  // 32-column slices per epilogue warp
+    const uint32_t stg = epi_base + ew * 4096;
+    const uint32_t row_addr = stg + lane * 128;
+    const uint32_t sw = lane & 7;
+    const uint32_t inbar = epi_in(ew);
+    uint32_t in_phase = 0;
+    bool pending = false;  // a bulk store may still be reading the staging box
     const bool col_contig = (p.c.c.sl == 1) && (p.c.c.d == INT_MAX || (p.c.c.d % 32) == 0) && P.dbg != 3;
+    const bool tma_in = P.epi_tma && (p.dact || (p.beta && !P.epi_reduce));
     uint32_t cit = 0;
-    long long t_wait = 0, t_ld = 0, t_emit = 0, t_all0 = clock64();
+
+    auto stage_free = [&]() {
+      if (pending) {
+        if (lane == 0) bulk_wait_read0();
+        __syncwarp();
+        pending = false;
+      }
+    };
+    auto stage_write = [&](const float (&v)[32]) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) sts128(row_addr + ((q ^ sw) << 4), make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]));
+    };
+
     for (int t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
-      const int tm = t % P.tiles_m, tn = (t / P.tiles_m) % P.tiles_n;
-      const int z = t / tiles_mn, sk = z % p.splitk, bz = z / p.splitk;
+      int tm, tn, z;
+      tile_coords(P, t, tm, tn, z);
+      const int sk = z % p.splitk, bz = z / p.splitk;
       const int kb0 = sk * P.kchunk_blocks, kb1 = min(P.kblocks, kb0 + P.kchunk_blocks);
       const int m_base = tm * BM + quad * 32;
       const int m = m_base + lane;
       const bool mval = m < p.M;
       const long long ro = off2(p.c.b, bz) + off2(p.c.r, mval ? m : 0);
       const float bias_m = (p.bias_mode == 2 && mval) ? __ldg(p.bias + m) : 0.f;
+      int cc5[5];
+      if (P.epi_tma) opnd_coords(P.c, m_base, bz, cc5);
 
-      // one 32-column slice of this warp's 32 rows: v[j] = accumulator of (row m, column n0 + j)
-      auto emit = [&](const float* v, int n0) {
+      // ---- one 32-column slice of this warp's 32 rows: v[j] = accumulator of (row m, column n0 + j)
+      auto emit = [&](float (&v)[32], int n0) {
         if (P.dbg == 5) return;
-        if (col_contig) {
-          // transpose through shared memory so that global accesses run along the contiguous columns
+        if (P.epi_tma) {
+          // TMA epilogue: rows are staged in the swizzled box and leave (or arrive) as one bulk tensor copy
+          if (m_base >= p.M) return;  // warp-uniform
+          opnd_set_k(P.c.k_d, P.c.dk0, P.c.dk1, n0, cc5);
+          if (tma_in) {
+            stage_free();
+            if (lane == 0) {
+              mbar_arrive_expect_tx(inbar, 4096);
+              tma_load(stg, &mapI, inbar, P.c.ndim, cc5);
+            }
+          }
 #pragma unroll
-          for (int q = 0; q < 8; ++q)
-            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(scr + (lane * 36 + 4 * q) * 4), "f"(v[4 * q]),
-                         "f"(v[4 * q + 1]), "f"(v[4 * q + 2]), "f"(v[4 * q + 3]) : "memory");
+          for (int j = 0; j < 32; ++j) v[j] *= p.alpha;
+          if (p.bias_mode == 1) {
+            if (n0 + 32 <= p.N && P.c_vec) {
+#pragma unroll
+              for (int q = 0; q < 8; ++q) {
+                const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + n0) + q);
+                v[4 * q] += b4.x; v[4 * q + 1] += b4.y; v[4 * q + 2] += b4.z; v[4 * q + 3] += b4.w;
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] += (n0 + j < p.N) ? __ldg(p.bias + n0 + j) : 0.f;
+            }
+          } else if (p.bias_mode == 2) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] += bias_m;
+          }
+          if (tma_in) {
+            mbar_wait(inbar, in_phase);
+            in_phase ^= 1;
+            float u[32];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              const float4 x = lds128(row_addr + ((q ^ sw) << 4));
+              u[4 * q] = x.x; u[4 * q + 1] = x.y; u[4 * q + 2] = x.z; u[4 * q + 3] = x.w;
+            }
+            if (p.dact) {
+              dact32_mul(p.dact, v, u);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] += u[j];
+            }
+          }
+          if (p.Z) {
+            stage_free();
+            stage_write(v);
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              tma_store(stg, &mapZ, P.c.ndim, cc5, false);
+              bulk_commit();
+            }
+            pending = true;
+          }
+          act32(p.act, v);
+          stage_free();
+          stage_write(v);
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0 && P.dbg != 4) {
+            tma_store(stg, &mapC, P.c.ndim, cc5, P.epi_reduce != 0);
+            bulk_commit();
+          }
+          pending = true;
+          return;
+        }
+        if (col_contig) {
+          // transpose through the staging box so that global accesses run along the contiguous columns
+          stage_write(v);
           __syncwarp();
           const long long coff = off2(p.c.c, n0);
           const bool aligned = !mval || (((ro + coff) & 3) == 0);
@@ -319,8 +467,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
               const long long ror = __shfl_sync(0xffffffffu, ro, r);
               const float bm = __shfl_sync(0xffffffffu, bias_m, r);
               const bool mv = (m_base + r) < p.M;
-              float4 x;
-              asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x.x), "=f"(x.y), "=f"(x.z), "=f"(x.w) : "r"(scr + (r * 36 + c4) * 4));
+              float4 x = lds128(stg + r * 128 + ((((uint32_t)lane & 7u) ^ ((uint32_t)r & 7u)) << 4));
               if (!mv) continue;
               const long long o = ror + coff + c4;
               x.x *= p.alpha; x.y *= p.alpha; x.z *= p.alpha; x.w *= p.alpha;
@@ -335,9 +482,9 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
                 x.x += cv.x; x.y += cv.y; x.z += cv.z; x.w += cv.w;
               }
               if (p.Z) *reinterpret_cast<float4*>(p.Z + o) = x;
-              if (p.act) x = act4_slow(p.act, x);
+              if (p.act) x = act4(p.act, x);
               if (p.dact) {
-                const float4 dv = dact4_slow(p.dact, __ldg(reinterpret_cast<const float4*>(p.aux + o)));
+                const float4 dv = dact4(p.dact, __ldg(reinterpret_cast<const float4*>(p.aux + o)));
                 x.x *= dv.x; x.y *= dv.y; x.z *= dv.z; x.w *= dv.w;
               }
               if (P.dbg != 4) *reinterpret_cast<float4*>(p.C + o) = x;
@@ -352,7 +499,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
               const long long ror = __shfl_sync(0xffffffffu, ro, r);
               const float bm = __shfl_sync(0xffffffffu, bias_m, r);
               float x;
-              asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x) : "r"(scr + (r * 36 + lane) * 4));
+              asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x) : "r"(stg + r * 128 + (((((uint32_t)lane >> 2) ^ ((uint32_t)r & 7u)) << 4) | (((uint32_t)lane & 3u) << 2))));
               if (!nval || (m_base + r) >= p.M) continue;
               const long long o = ror + co;
               x *= p.alpha;
@@ -364,8 +511,8 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
               else if (p.bias_mode == 2) x += bm;
               if (p.beta) x += p.C[o];
               if (p.Z) p.Z[o] = x;
-              if (p.act) x = act1_slow(p.act, x);
-              if (p.dact) x *= dact1_slow(p.dact, __ldg(p.aux + o));
+              if (p.act) x = act_f(p.act, x);
+              if (p.dact) x *= dact_f(p.dact, __ldg(p.aux + o));
               p.C[o] = x;
             }
           }
@@ -386,8 +533,8 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
             else if (p.bias_mode == 2) x += bias_m;
             if (p.beta) x += p.C[o];
             if (p.Z) p.Z[o] = x;
-            if (p.act) x = act1_slow(p.act, x);
-            if (p.dact) x *= dact1_slow(p.dact, __ldg(p.aux + o));
+            if (p.act) x = act_f(p.act, x);
+            if (p.dact) x *= dact_f(p.dact, __ldg(p.aux + o));
             p.C[o] = x;
           }
         }
@@ -395,59 +542,57 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
 
       if (!CH) {
         const int buf = cit & 1;
-        long long c0 = clock64();
         mbar_wait(acc_full(buf), (cit >> 1) & 1);
         tc_fence_after_sync();
-        t_wait += clock64() - c0;
 #pragma unroll 1
-        for (int cc = 0; cc < BN / 32; ++cc) {
+        for (int ci = 0; ci < CPW; ++ci) {
+          const int cc = half * CPW + ci;
           const int n0 = tn * BN + cc * 32;
           if (n0 >= p.N) break;  // warp-uniform
           uint32_t r[32];
-          c0 = clock64();
           tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + buf * BN + cc * 32, r);
           tmem_ld_wait();
-          long long c1 = clock64();
-          t_ld += c1 - c0;
           float v[32];
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
           emit(v, n0);
-          __syncwarp();
-          t_emit += clock64() - c1;
         }
         tc_fence_before_sync();
         mbar_arrive(acc_empty(buf));
         ++cit;
       } else {
-        float acc[BN];
+        float acc[CPW * 32];
 #pragma unroll
-        for (int j = 0; j < BN; ++j) acc[j] = 0.f;
+        for (int j = 0; j < CPW * 32; ++j) acc[j] = 0.f;
         for (int c0 = kb0; c0 < kb1; c0 += P.kc, ++cit) {
           const int buf = cit & 1;
           mbar_wait(acc_full(buf), (cit >> 1) & 1);
           tc_fence_after_sync();
 #pragma unroll
-          for (int cc = 0; cc < BN / 32; ++cc) {
+          for (int ci = 0; ci < CPW; ++ci) {
             uint32_t r[32];
-            tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + buf * BN + cc * 32, r);
+            tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + buf * BN + (half * CPW + ci) * 32, r);
             tmem_ld_wait();
 #pragma unroll
-            for (int j = 0; j < 32; ++j) acc[cc * 32 + j] += __uint_as_float(r[j]);
+            for (int j = 0; j < 32; ++j) acc[ci * 32 + j] += __uint_as_float(r[j]);
           }
           tc_fence_before_sync();
           mbar_arrive(acc_empty(buf));
         }
 #pragma unroll
-        for (int cc = 0; cc < BN / 32; ++cc) {
-          const int n0 = tn * BN + cc * 32;
-          if (n0 < p.N) emit(&acc[cc * 32], n0);
-          __syncwarp();
+        for (int ci = 0; ci < CPW; ++ci) {
+          const int n0 = tn * BN + (half * CPW + ci) * 32;
+          if (n0 < p.N) {
+            float v[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = acc[ci * 32 + j];
+            emit(v, n0);
+          }
         }
       }
     }
-    if (P.dbg == 8 && blockIdx.x == 0 && lane == 0)
-      printf("[tc epi] warp %d: total %lld wait_acc %lld tmem_ld %lld emit %lld cycles\n", warp, clock64() - t_all0, t_wait, t_ld, t_emit);
+    if (lane == 0) bulk_wait0();  // the staging boxes must outlive the bulk stores that read them
+    __syncwarp();
   }
 
   tc_fence_before_sync();
@@ -599,8 +744,13 @@ static bool build_operand(const float* base, const Idx2& mn_map, long long MN, c
   return rc == CUDA_SUCCESS;
 }
 
+struct EpiMaps {
+  CUtensorMap c, z, i;
+};
+
 template <int BN, bool SPLIT, bool CH>
-static cudaError_t launch_cfg(const TcParams& P, const CUtensorMap& ma, const CUtensorMap& mb, int sms, cudaStream_t s) {
+static cudaError_t launch_cfg(const TcParams& P, const CUtensorMap& ma, const CUtensorMap& mb, const EpiMaps& em, int sms,
+                              cudaStream_t s) {
   using C = Cfg<BN, SPLIT>;
   static std::once_flag once;
   static cudaError_t attr_rc = cudaSuccess;
@@ -609,7 +759,7 @@ static cudaError_t launch_cfg(const TcParams& P, const CUtensorMap& ma, const CU
   });
   if (attr_rc != cudaSuccess) return attr_rc;
   const int grid = P.total_tiles < sms ? P.total_tiles : sms;
-  gemm_tc_kernel<BN, SPLIT, CH><<<grid, kThreads, C::smem_bytes, s>>>(P, ma, mb);
+  gemm_tc_kernel<BN, SPLIT, CH><<<grid, kThreads, C::smem_bytes, s>>>(P, ma, mb, em.c, em.z, em.i);
   return cudaGetLastError();
 }
 
@@ -632,7 +782,10 @@ static cudaError_t gemm_tc_try_launch(const GemmP& g, int prec, cudaStream_t s, 
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   static const int kc_env = getenv("RPDE_TC_KC") ? atoi(getenv("RPDE_TC_KC")) : 0;
-  const int kc = kc_env > 0 ? kc_env : 8;  // k-blocks (x32) per TMEM accumulation chain
+  // k-blocks (x32) per TMEM accumulation chain.  3xTF32: 2 (24 UMMAs, accumulated truncation ~5e-7 relative; 8 leaves
+  // 2e-6 per contraction, which compounds to >1e-5 on some gradients of the 4-layer models).  TF32: accuracy is set by the
+  // operand rounding, long chains are fine.
+  const int kc = kc_env > 0 ? kc_env : (prec == 1 ? 2 : 8);
   const int kblocks = (g.K + BK - 1) / BK;
   const int tiles_m = (g.M + BM - 1) / BM;
   // split-K (only when the caller allows atomically accumulated output)
@@ -676,22 +829,47 @@ static cudaError_t gemm_tc_try_launch(const GemmP& g, int prec, cudaStream_t s, 
   const long long total = (long long)P.tiles_m * P.tiles_n * g.batch * splitk;
   if (total > 0x7fffffffLL) return cudaSuccess;
   P.total_tiles = (int)total;
+  P.n_fast = P.tiles_n <= P.tiles_m;
+  // TMA epilogue: the output (and Z / aux / the old C) addressed as 32 x 32 boxes of rows x contiguous columns
+  EpiMaps em;
+  memset(&em, 0, sizeof(em));
+  P.epi_tma = P.epi_reduce = 0;
+  memset(&P.c, 0, sizeof(P.c));
+  static const bool no_epi_tma = getenv("RPDE_TC_NO_EPI_TMA") != nullptr;
+  if (splitk == 1 && !no_epi_tma && P.dbg != 3) {
+    TcOpnd co, tmp;
+    bool okc = build_operand(g.C, g.c.r, g.M, g.c.c, g.N, g.c.b, g.batch, 32, &em.c, &co) && co.major == 0 && co.boxes == 1;
+    if (okc && g.Z) okc = build_operand(g.Z, g.c.r, g.M, g.c.c, g.N, g.c.b, g.batch, 32, &em.z, &tmp) && tmp.major == 0;
+    if (okc && g.dact) {
+      okc = build_operand(g.aux, g.c.r, g.M, g.c.c, g.N, g.c.b, g.batch, 32, &em.i, &tmp) && tmp.major == 0;
+    } else if (okc && g.beta) {
+      if (g.act || g.Z) em.i = em.c;
+      else P.epi_reduce = 1;
+    }
+    if (okc) {
+      P.epi_tma = 1;
+      P.c = co;
+    } else {
+      P.epi_reduce = 0;
+    }
+  }
   const bool split3 = (prec == 1);
   cudaError_t rc;
   if (chunked) {
-    if (BN == 128) rc = split3 ? launch_cfg<128, true, true>(P, ma, mb, sms, s) : launch_cfg<128, false, true>(P, ma, mb, sms, s);
-    else rc = split3 ? launch_cfg<64, true, true>(P, ma, mb, sms, s) : launch_cfg<64, false, true>(P, ma, mb, sms, s);
+    if (BN == 128) rc = split3 ? launch_cfg<128, true, true>(P, ma, mb, em, sms, s) : launch_cfg<128, false, true>(P, ma, mb, em, sms, s);
+    else rc = split3 ? launch_cfg<64, true, true>(P, ma, mb, em, sms, s) : launch_cfg<64, false, true>(P, ma, mb, em, sms, s);
   } else if (BN == 256) {
-    rc = split3 ? launch_cfg<256, true, false>(P, ma, mb, sms, s) : launch_cfg<256, false, false>(P, ma, mb, sms, s);
+    rc = split3 ? launch_cfg<256, true, false>(P, ma, mb, em, sms, s) : launch_cfg<256, false, false>(P, ma, mb, em, sms, s);
   } else if (BN == 128) {
-    rc = split3 ? launch_cfg<128, true, false>(P, ma, mb, sms, s) : launch_cfg<128, false, false>(P, ma, mb, sms, s);
+    rc = split3 ? launch_cfg<128, true, false>(P, ma, mb, em, sms, s) : launch_cfg<128, false, false>(P, ma, mb, em, sms, s);
   } else {
-    rc = split3 ? launch_cfg<64, true, false>(P, ma, mb, sms, s) : launch_cfg<64, false, false>(P, ma, mb, sms, s);
+    rc = split3 ? launch_cfg<64, true, false>(P, ma, mb, em, sms, s) : launch_cfg<64, false, false>(P, ma, mb, em, sms, s);
   }
   *launched = (rc == cudaSuccess);
   if (P.dbg == 9)
-    fprintf(stderr, "[rpde tc] M=%d N=%d K=%d batch=%d BN=%d splitk=%d majorA=%d majorB=%d tiles=%d beta=%d act=%d\n", g.M, g.N, g.K,
-            g.batch, BN, splitk, P.a.major, P.b.major, P.total_tiles, g.beta, g.act);
+    fprintf(stderr, "[rpde tc] M=%d N=%d K=%d batch=%d BN=%d splitk=%d majorA=%d majorB=%d tiles=%d beta=%d act=%d dact=%d Z=%d epi_tma=%d red=%d ch=%d\n",
+            g.M, g.N, g.K, g.batch, BN, splitk, P.a.major, P.b.major, P.total_tiles, g.beta, g.act, g.dact, g.Z != nullptr, P.epi_tma,
+            P.epi_reduce, (int)chunked);
   return rc;
 }
 

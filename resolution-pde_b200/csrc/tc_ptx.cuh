@@ -83,6 +83,55 @@ __device__ __forceinline__ void tma_load(uint32_t dst, const CUtensorMap* m, uin
   }
 }
 
+// tile-mode store of one box from shared memory (bulk async-group completion); reduce = element-wise fp32 add into global
+__device__ __forceinline__ void tma_store(uint32_t src, const CUtensorMap* m, int ndim, const int* c, bool reduce) {
+  const uint64_t mp = (uint64_t)m;
+  if (!reduce) {
+    switch (ndim) {
+      case 2:
+        asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%1, {%2, %3}], [%0];"
+                     ::"r"(src), "l"(mp), "r"(c[0]), "r"(c[1]) : "memory");
+        break;
+      case 3:
+        asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%1, {%2, %3, %4}], [%0];"
+                     ::"r"(src), "l"(mp), "r"(c[0]), "r"(c[1]), "r"(c[2]) : "memory");
+        break;
+      case 4:
+        asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%1, {%2, %3, %4, %5}], [%0];"
+                     ::"r"(src), "l"(mp), "r"(c[0]), "r"(c[1]), "r"(c[2]), "r"(c[3]) : "memory");
+        break;
+      default:
+        asm volatile("cp.async.bulk.tensor.5d.global.shared::cta.tile.bulk_group [%1, {%2, %3, %4, %5, %6}], [%0];"
+                     ::"r"(src), "l"(mp), "r"(c[0]), "r"(c[1]), "r"(c[2]), "r"(c[3]), "r"(c[4]) : "memory");
+        break;
+    }
+  } else {
+    switch (ndim) {
+      case 2:
+        asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%1, {%2, %3}], [%0];"
+                     ::"r"(src), "l"(mp), "r"(c[0]), "r"(c[1]) : "memory");
+        break;
+      case 3:
+        asm volatile("cp.reduce.async.bulk.tensor.3d.global.shared::cta.add.tile.bulk_group [%1, {%2, %3, %4}], [%0];"
+                     ::"r"(src), "l"(mp), "r"(c[0]), "r"(c[1]), "r"(c[2]) : "memory");
+        break;
+      case 4:
+        asm volatile("cp.reduce.async.bulk.tensor.4d.global.shared::cta.add.tile.bulk_group [%1, {%2, %3, %4, %5}], [%0];"
+                     ::"r"(src), "l"(mp), "r"(c[0]), "r"(c[1]), "r"(c[2]), "r"(c[3]) : "memory");
+        break;
+      default:
+        asm volatile("cp.reduce.async.bulk.tensor.5d.global.shared::cta.add.tile.bulk_group [%1, {%2, %3, %4, %5, %6}], [%0];"
+                     ::"r"(src), "l"(mp), "r"(c[0]), "r"(c[1]), "r"(c[2]), "r"(c[3]), "r"(c[4]) : "memory");
+        break;
+    }
+  }
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// all bulk groups of this thread have finished READING their shared-memory source
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+// ... and have completed entirely (global writes performed)
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
 // ---------------------------------------------------------------------------------------------- TMEM
 // whole-warp calls (.sync.aligned)
 __device__ __forceinline__ void tmem_alloc(uint32_t smem_result, uint32_t cols) {

@@ -56,3 +56,44 @@ for prec in ("tf32", "3xtf32"):
         err = ((dw.double() - ref).norm() / ref.norm()).item()
         print(json.dumps({"prec": prec, "wgrad": [T, i, o], "ms": round(ms, 4), "tflops": round(2.0 * T * i * o / ms / 1e9, 1),
                           "gbs": round(4.0 * T * (i + o) / ms / 1e6, 1), "rel_err_T65536": err}), flush=True)
+
+# FeedForward-shaped Linear calls with their fused epilogues (bias + GELU + pre-activation store; dgrad * gelu'(z))
+def _time(fn, reps=5):
+    for _ in range(2):
+        fn()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(reps):
+        fn()
+    e.record()
+    torch.cuda.synchronize()
+    return s.elapsed_time(e) / reps
+
+
+for prec in ("tf32", "3xtf32"):
+    R.set_precision(prec)
+    lib = R._lib.load()
+    st = torch.cuda.current_stream().cuda_stream
+    T = 1048576
+    for (i, o) in [(64, 256), (256, 256), (256, 64)]:
+        x = torch.randn(T, i, device="cuda")
+        w = torch.randn(o, i, device="cuda") / i ** 0.5
+        b = torch.randn(o, device="cuda")
+        y = torch.empty(T, o, device="cuda")
+        z = torch.empty(T, o, device="cuda")
+        ms_plain = _time(lambda: lib.rpde_linear_fwd(x.data_ptr(), w.data_ptr(), b.data_ptr(), y.data_ptr(), None, T, i, o, 0, 0, st))
+        ms_gelu = _time(lambda: lib.rpde_linear_fwd(x.data_ptr(), w.data_ptr(), b.data_ptr(), y.data_ptr(), z.data_ptr(), T, i, o, 1, 0, st))
+        ref = torch.nn.functional.gelu(x[:4096].double() @ w.double().T + b.double())
+        err = ((y[:4096].double() - ref).norm() / ref.norm()).item()
+        dy = torch.randn(T, o, device="cuda")
+        zp = torch.randn(T, i, device="cuda")
+        dx = torch.empty(T, i, device="cuda")
+        ms_dgrad = _time(lambda: lib.rpde_linear_bwd_input(dy.data_ptr(), w.data_ptr(), None, 0, dx.data_ptr(), 0, T, i, o, 0, st))
+        ms_dact = _time(lambda: lib.rpde_linear_bwd_input(dy.data_ptr(), w.data_ptr(), zp.data_ptr(), 1, dx.data_ptr(), 0, T, i, o, 0, st))
+        zd = zp[:4096].double()
+        dg = 0.5 * (1 + torch.erf(zd / 2 ** 0.5)) + zd * torch.exp(-0.5 * zd * zd) / (2 * torch.pi) ** 0.5
+        ref = (dy[:4096].double() @ w.double()) * dg
+        err2 = ((dx[:4096].double() - ref).norm() / ref.norm()).item()
+        print(json.dumps({"prec": prec, "linear": [T, i, o], "fwd_bias_ms": round(ms_plain, 4), "fwd_bias_gelu_z_ms": round(ms_gelu, 4),
+                          "fwd_err": err, "dgrad_ms": round(ms_dgrad, 4), "dgrad_dact_ms": round(ms_dact, 4), "dgrad_err": err2}), flush=True)
+        del x, y, z, dy, zp, dx
