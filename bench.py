@@ -195,6 +195,7 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch override")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch every op eagerly instead of replaying the captured step")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     name = args.workload
@@ -233,10 +234,22 @@ def main():
     lib = R._lib.load()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev) if wl["bytes"] / 4 < 200e6 else None
 
+    from resolution_pde_b200.training import GraphedTrainStep
+    gstep = None if args.no_graph else GraphedTrainStep(model, loss_fn)
+    launches_per_step = None
+    if gstep is not None:
+        c0 = lib.rpde_launch_count()
+        gstep(xd, yd)                                       # warm-up + capture (one captured step = one count)
+        launches_per_step = (lib.rpde_launch_count() - c0) // (gstep.warmup + 1)
+        xd, yd = gstep.static_inputs(xd.shape, yd.shape)    # device-resident arm feeds the graph's own buffers
+
     def step(x, y):
-        model.zero_grad(set_to_none=True)
-        loss = loss_fn(model(x), y)
-        loss.backward()
+        if gstep is not None:
+            loss = gstep(x, y)
+        else:
+            model.zero_grad(set_to_none=True)
+            loss = loss_fn(model(x), y)
+            loss.backward()
         if world > 1:
             bucket.allreduce_mean()
         return loss
@@ -249,7 +262,10 @@ def main():
                 flush.zero_()
             s.record()
             if from_host:
-                last = step(xh.to(dev, non_blocking=True), yh.to(dev, non_blocking=True)).item()
+                if gstep is not None:
+                    last = step(xh, yh).item()             # H2D into the graph's input buffers, replay, D2H of the loss
+                else:
+                    last = step(xh.to(dev, non_blocking=True), yh.to(dev, non_blocking=True)).item()
             else:
                 last = step(xd, yd)
             e.record()
@@ -267,6 +283,8 @@ def main():
     l0 = lib.rpde_launch_count() if hasattr(lib, "rpde_launch_count") else 0
     ms, loss = timed(args.steps, False)
     launches = (lib.rpde_launch_count() - l0) if hasattr(lib, "rpde_launch_count") else None
+    if launches_per_step is not None:
+        launches = launches_per_step * args.steps           # replayed graph nodes (counted once, at capture)
     clocks = sampler.stop() if rank == 0 else None
     loss_val = float(loss)
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
@@ -325,6 +343,7 @@ def main():
                            "grid": list(wl["shape"][1:]), "precision_engine": prec, "parallelism": f"dp{world}",
                            "l2": "L2 flushed between timed steps" if flush is not None else "working set >> L2 (no flush)",
                            "step": "zero_grad + forward + RelativeL2 + backward" + (" + flat NCCL grad all-reduce" if world > 1 else ""),
+                           "launch": "eager" if gstep is None else "CUDA graph replay (one graph per input shape)",
                            "grad_bytes": bucket.nbytes},
                 "loss": loss_val, "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roof}
         if not args.no_cpu_baseline and world == 1:

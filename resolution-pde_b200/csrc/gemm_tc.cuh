@@ -69,7 +69,9 @@ struct Cfg {
   static constexpr int raw = kSmemBudget / stage_bytes;
   static constexpr int stages = raw > 6 ? 6 : raw;
   static constexpr int smem_bytes = stages * stage_bytes + kEpiBytes + 2048;  // + alignment slack + barriers
-  static constexpr int tmem_cols = 2 * BN < 32 ? 32 : 2 * BN;
+  static constexpr int acc_cols = SPLIT ? 2 * BN : BN;  // 3xTF32: [hi*hi | hi*lo + lo*hi] accumulated side by side
+  static constexpr int tmem_cols = 2 * acc_cols < 32 ? 32 : 2 * acc_cols;
+  static_assert(tmem_cols <= 512, "TMEM holds 512 columns");
 };
 
 // Coordinates live in registers: slots are written with compare-selects, never with dynamic indexing (which would
@@ -204,11 +206,11 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
   constexpr int S = C::stages;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  // stage s: [A_hi][B_hi]([A_lo][B_lo])
+  // stage s: [A_hi]([A_lo])[B_hi]([B_lo]) -- B_lo directly behind B_hi, so one UMMA of width 2*BN sees [B_hi; B_lo]
   auto a_hi = [&](int s) { return smem_base + s * C::stage_bytes; };
-  auto b_hi = [&](int s) { return smem_base + s * C::stage_bytes + A_TILE_BYTES; };
-  auto a_lo = [&](int s) { return smem_base + s * C::stage_bytes + A_TILE_BYTES + C::b_tile; };
-  auto b_lo = [&](int s) { return smem_base + s * C::stage_bytes + 2 * A_TILE_BYTES + C::b_tile; };
+  auto a_lo = [&](int s) { return smem_base + s * C::stage_bytes + A_TILE_BYTES; };
+  auto b_hi = [&](int s) { return smem_base + s * C::stage_bytes + (SPLIT ? 2 : 1) * A_TILE_BYTES; };
+  auto b_lo = [&](int s) { return smem_base + s * C::stage_bytes + (SPLIT ? 2 : 1) * A_TILE_BYTES + C::b_tile; };
   const uint32_t epi_base = smem_base + S * C::stage_bytes;  // 1024-aligned: the staging boxes use the TMA 128B swizzle
   const uint32_t bar_base = epi_base + kEpiBytes;
   auto full = [&](int s) { return bar_base + 8 * s; };
@@ -275,6 +277,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
     // ------------------------------------------------------------------ UMMA issuer
     if (lane == 0) {
       const uint32_t idesc = umma_idesc_tf32(BM, BN, P.a.major, P.b.major);
+      const uint32_t idesc2 = umma_idesc_tf32(BM, SPLIT ? 2 * BN : BN, P.a.major, P.b.major);
       const uint32_t a_step = P.a.major ? 1024u : 32u, b_step = P.b.major ? 1024u : 32u;
       const uint32_t a_lbo = P.a.major ? BK * 128u : 16u, b_lbo = P.b.major ? BK * 128u : 16u;
       const uint32_t a_sbo = P.a.major ? 512u : 1024u, b_sbo = P.b.major ? 512u : 1024u;
@@ -291,7 +294,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
           const int buf = cit & 1;
           mbar_wait(acc_empty(buf), ((cit >> 1) & 1) ^ 1);
           tc_fence_after_sync();
-          const uint32_t d = tmem_base + buf * BN;
+          const uint32_t d = tmem_base + buf * C::acc_cols;
           for (int kb = c0; kb < c1; ++kb, ++it) {
             const int s = it % S;
             const uint32_t ph = (it / S) & 1;
@@ -299,15 +302,16 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
             tc_fence_after_sync();
 #pragma unroll
             for (int k4 = 0; k4 < BK / 8; ++k4) {
+              if (P.dbg == 7) break;
               const uint32_t acc = (kb > c0 || k4 > 0) ? 1u : 0u;
               const uint64_t ah = umma_desc(a_hi(s) + k4 * a_step, a_lbo, a_sbo, a_lay);
               const uint64_t bh = umma_desc(b_hi(s) + k4 * b_step, b_lbo, b_sbo, b_lay);
               if (SPLIT) {
+                // [big | small] (+)= A_hi [B_hi; B_lo]   then   small += A_lo B_hi.  The large products meet one
+                // accumulator truncation per k-step; the 2^-11 corrections live in their own columns.
                 const uint64_t al = umma_desc(a_lo(s) + k4 * a_step, a_lbo, a_sbo, a_lay);
-                const uint64_t bl = umma_desc(b_lo(s) + k4 * b_step, b_lbo, b_sbo, b_lay);
-                umma_tf32(d, al, bh, idesc, acc);
-                umma_tf32(d, ah, bl, idesc, 1u);
-                umma_tf32(d, ah, bh, idesc, 1u);
+                umma_tf32(d, ah, bh, idesc2, acc);
+                umma_tf32(d + BN, al, bh, idesc, 1u);
               } else {
                 umma_tf32(d, ah, bh, idesc, acc);
               }
@@ -332,8 +336,10 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
           const int s = it % S;
           const uint32_t ph = (it / S) & 1;
           mbar_wait(full(s), ph);
-          if (SPLIT || p.a_act) prep_region<SPLIT>(a_hi(s), a_lo(s), A_TILE_BYTES / 16, p.a_act, ct);
-          if (SPLIT || p.b_act) prep_region<SPLIT>(b_hi(s), b_lo(s), C::b_tile / 16, p.b_act, ct);
+          if (P.dbg != 6) {
+            if (SPLIT || p.a_act) prep_region<SPLIT>(a_hi(s), a_lo(s), A_TILE_BYTES / 16, p.a_act, ct);
+            if (SPLIT || p.b_act) prep_region<SPLIT>(b_hi(s), b_lo(s), C::b_tile / 16, p.b_act, ct);
+          }
           fence_proxy_async_smem();
           mbar_arrive(ready(s));
         }
@@ -550,11 +556,20 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
           const int n0 = tn * BN + cc * 32;
           if (n0 >= p.N) break;  // warp-uniform
           uint32_t r[32];
-          tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + buf * BN + cc * 32, r);
-          tmem_ld_wait();
           float v[32];
+          const uint32_t ta = tmem_base + ((uint32_t)(quad * 32) << 16) + buf * C::acc_cols + cc * 32;
+          tmem_ld32(ta, r);
+          if (SPLIT) {
+            uint32_t r2[32];
+            tmem_ld32(ta + BN, r2);
+            tmem_ld_wait();
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + __uint_as_float(r2[j]);
+          } else {
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+          }
           emit(v, n0);
         }
         tc_fence_before_sync();
@@ -571,10 +586,19 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
 #pragma unroll
           for (int ci = 0; ci < CPW; ++ci) {
             uint32_t r[32];
-            tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + buf * BN + (half * CPW + ci) * 32, r);
-            tmem_ld_wait();
+            const uint32_t ta = tmem_base + ((uint32_t)(quad * 32) << 16) + buf * C::acc_cols + (half * CPW + ci) * 32;
+            tmem_ld32(ta, r);
+            if (SPLIT) {
+              uint32_t r2[32];
+              tmem_ld32(ta + BN, r2);
+              tmem_ld_wait();
 #pragma unroll
-            for (int j = 0; j < 32; ++j) acc[ci * 32 + j] += __uint_as_float(r[j]);
+              for (int j = 0; j < 32; ++j) acc[ci * 32 + j] += __uint_as_float(r[j]) + __uint_as_float(r2[j]);
+            } else {
+              tmem_ld_wait();
+#pragma unroll
+              for (int j = 0; j < 32; ++j) acc[ci * 32 + j] += __uint_as_float(r[j]);
+            }
           }
           tc_fence_before_sync();
           mbar_arrive(acc_empty(buf));
@@ -782,10 +806,9 @@ static cudaError_t gemm_tc_try_launch(const GemmP& g, int prec, cudaStream_t s, 
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   static const int kc_env = getenv("RPDE_TC_KC") ? atoi(getenv("RPDE_TC_KC")) : 0;
-  // k-blocks (x32) per TMEM accumulation chain.  3xTF32: 2 (24 UMMAs, accumulated truncation ~5e-7 relative; 8 leaves
-  // 2e-6 per contraction, which compounds to >1e-5 on some gradients of the 4-layer models).  TF32: accuracy is set by the
-  // operand rounding, long chains are fine.
-  const int kc = kc_env > 0 ? kc_env : (prec == 1 ? 2 : 8);
+  // k-blocks (x32) per TMEM accumulation chain: 8 = 256 k = 32 UMMAs into the hi*hi accumulator (~7e-7 relative
+  // truncation); longer reductions are chunked and summed in registers.
+  const int kc = kc_env > 0 ? kc_env : 8;
   const int kblocks = (g.K + BK - 1) / BK;
   const int tiles_m = (g.M + BM - 1) / BM;
   // split-K (only when the caller allows atomically accumulated output)
@@ -801,7 +824,9 @@ static cudaError_t gemm_tc_try_launch(const GemmP& g, int prec, cudaStream_t s, 
     }
     return splitk;
   };
-  int BN = g.N > 128 ? 256 : (g.N > 64 ? 128 : 64);
+  const bool split3 = (prec == 1);
+  // 3xTF32 keeps two accumulator column blocks per tile (and two tiles in flight): 4 * BN <= 512 TMEM columns
+  int BN = (g.N > 128 && !split3) ? 256 : (g.N > 64 ? 128 : 64);
   // long reductions are chunked and summed in registers: that variant holds BN accumulators per thread
   {
     const int sk = choose_split(BN);
@@ -853,13 +878,12 @@ static cudaError_t gemm_tc_try_launch(const GemmP& g, int prec, cudaStream_t s, 
       P.epi_reduce = 0;
     }
   }
-  const bool split3 = (prec == 1);
   cudaError_t rc;
   if (chunked) {
     if (BN == 128) rc = split3 ? launch_cfg<128, true, true>(P, ma, mb, em, sms, s) : launch_cfg<128, false, true>(P, ma, mb, em, sms, s);
     else rc = split3 ? launch_cfg<64, true, true>(P, ma, mb, em, sms, s) : launch_cfg<64, false, true>(P, ma, mb, em, sms, s);
   } else if (BN == 256) {
-    rc = split3 ? launch_cfg<256, true, false>(P, ma, mb, em, sms, s) : launch_cfg<256, false, false>(P, ma, mb, em, sms, s);
+    rc = launch_cfg<256, false, false>(P, ma, mb, em, sms, s);
   } else if (BN == 128) {
     rc = split3 ? launch_cfg<128, true, false>(P, ma, mb, em, sms, s) : launch_cfg<128, false, false>(P, ma, mb, em, sms, s);
   } else {

@@ -1,0 +1,72 @@
+"""Graph-captured training step for the spectral path.
+
+The reference's loop (train/training.py:19-88) launches every op eagerly, rebuilds the coordinate grid on the
+host each forward (fno.py:51-54, ffno.py:199-208) and synchronises on loss.item() every step (training.py:47).
+On the small 1-D configs the HBM floor of a step is tens of microseconds, so launch latency dominates.  Here the
+whole `zero_grad -> forward -> RelativeL2 -> backward` sequence of one (model, batch shape) is captured once into a
+CUDA graph and replayed: the C-ABI entry points never synchronise or allocate, workspaces come from torch's
+capture-aware caching allocator, DFT tables and grids are cached device tensors created during the warm-up.
+
+One graph per input shape, as ResolutionGroupedDataLoader (train/mres_training.py:108-128) yields one
+resolution per batch.  Gradients land in `p.grad` of the model's parameters (static tensors owned by the graph's
+memory pool), so any torch optimizer and the flat NCCL all-reduce (distributed.GradBucket) work unchanged.
+"""
+from __future__ import annotations
+
+from typing import Callable, Dict, Optional, Tuple
+
+import torch
+
+
+class GraphedTrainStep:
+    """step(x, y) -> loss (0-dim device tensor).  x, y may live on the device or in pinned host memory."""
+
+    def __init__(self, model: torch.nn.Module, loss_fn: Callable, warmup: int = 2):
+        self.model = model
+        self.loss_fn = loss_fn
+        self.warmup = warmup
+        self._graphs: Dict[Tuple, Tuple] = {}
+
+    def _capture(self, x: torch.Tensor, y: torch.Tensor):
+        dev = next(self.model.parameters()).device
+        sx = torch.empty(x.shape, dtype=torch.float32, device=dev)
+        sy = torch.empty(y.shape, dtype=torch.float32, device=dev)
+        sx.copy_(x)
+        sy.copy_(y)
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):          # warm-up off the capture: builds tables/grids, sizes the allocator
+            for _ in range(self.warmup):
+                self.model.zero_grad(set_to_none=True)
+                self.loss_fn(self.model(sx), sy).backward()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.model.zero_grad(set_to_none=True)  # grads are (re)created inside the capture, in the graph's pool
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            loss = self.loss_fn(self.model(sx), sy)
+            loss.backward()
+        # the gradient tensors written by this graph (its pool owns them); re-attached to the parameters after a replay
+        params = [q for q in self.model.parameters() if q.grad is not None]
+        grads = [q.grad for q in params]
+        return g, sx, sy, loss, params, grads
+
+    def __call__(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        key = (tuple(x.shape), tuple(y.shape))
+        ent = self._graphs.get(key)
+        if ent is None:
+            ent = self._capture(x, y)
+            self._graphs[key] = ent
+        g, sx, sy, loss, params, grads = ent
+        if x.data_ptr() != sx.data_ptr():
+            sx.copy_(x, non_blocking=True)
+        if y.data_ptr() != sy.data_ptr():
+            sy.copy_(y, non_blocking=True)
+        g.replay()
+        for q, gr in zip(params, grads):
+            q.grad = gr
+        return loss
+
+    def static_inputs(self, x_shape, y_shape) -> Optional[Tuple[torch.Tensor, torch.Tensor]]:
+        ent = self._graphs.get((tuple(x_shape), tuple(y_shape)))
+        return (ent[1], ent[2]) if ent else None

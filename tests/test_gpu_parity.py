@@ -283,3 +283,33 @@ def test_no_grad_inference_and_eval_sweep():
         want = rp.ffno1d_forward({k: v.double() for k, v in sd.items()}, x.double(), n_layers=2, n_modes=16,
                                  n_ff_layers=2, layer_norm=True)
         assert rel(got, want) < TOL, n
+
+
+# ---------------------------------------------------------------------------------------------------------
+# graph-captured step == eager step (same kernels, same order), one graph per resolution
+# ---------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("kind", ["FNO1d", "FFNO2D"])
+def test_graphed_step_matches_eager(kind):
+    import resolution_pde_b200 as R
+    torch.manual_seed(7)
+    if kind == "FNO1d":
+        m = R.FNO1d(1, 1, modes=8, width=16).to(DEV)
+        shapes = [(3, 1, 64), (2, 1, 128)]
+    else:
+        m = R.FFNO2D(1, 1, width=16, n_layers=2, n_modes=8, n_ff_layers=2, layer_norm=True, ff_weight_norm=True).to(DEV)
+        shapes = [(2, 1, 32, 32), (1, 1, 48, 40)]
+    loss_fn = R.RelativeL2Loss()
+    gstep = R.GraphedTrainStep(m, loss_fn)
+    for rep in range(2):                       # second round replays the cached graphs with new data
+        for shp in shapes:
+            x, y = torch.randn(*shp, device=DEV), torch.randn(*shp, device=DEV)
+            lg = gstep(x, y).clone()
+            gg = {k: p.grad.clone() for k, p in m.named_parameters()}
+            m.zero_grad(set_to_none=True)
+            le = loss_fn(m(x), y)
+            le.backward()
+            torch.cuda.synchronize()
+            assert abs(lg.item() - le.item()) <= 1e-6 * max(1.0, abs(le.item()))
+            for k, p in m.named_parameters():
+                assert rel(gg[k], p.grad) < 2e-6 or p.grad.abs().max() < 1e-7, (k, rel(gg[k], p.grad))
+            m.zero_grad(set_to_none=True)
