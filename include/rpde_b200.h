@@ -30,6 +30,10 @@ enum {
   RPDE_E_MODES = -4        /* more modes requested than the spectrum holds (reference raises RuntimeError) */
 };
 enum { RPDE_ACT_NONE = 0, RPDE_ACT_GELU = 1, RPDE_ACT_RELU = 2 };
+/* rpde_linear_fwd: or-ed into `act`: z receives act'(pre-activation) instead of the pre-activation, so the backward
+ * pass multiplies by a stored factor (dact = RPDE_DACT_SAVED) and evaluates no transcendental. */
+enum { RPDE_ACT_SAVE_GRAD = 0x100 };
+enum { RPDE_DACT_SAVED = 3 };
 enum { RPDE_MIX_FULL = 0, RPDE_MIX_LOWPASS = 1 };
 /* DFT table kinds (rpde_dft_table) */
 enum { RPDE_DFT_R2C_ANALYSIS = 0, RPDE_DFT_C2R_SYNTHESIS = 1, RPDE_DFT_C2C_ANALYSIS_ROWS = 2, RPDE_DFT_C2C_SYNTHESIS_ROWS = 3 };
@@ -100,9 +104,12 @@ int rpde_ffno_axis_bwd(const float* dy, const float* w, const float* fa, const f
  * y_cf_spatial > 0: y is written channels-first (T/S, out, S) (ffno.py:123, 235 final permute). */
 int rpde_linear_fwd(const float* x, const float* w, const float* bias, float* y, float* z, long long T, int in,
                     int out, int act, long long y_cf_spatial, rpde_stream_t stream);
-/* dx (+)= (dy W) * act'(zprev)   (zprev/dact describe the activation that produced this layer's input) */
+/* dx (+)= (dy W) * act'(zprev)   (zprev/dact describe the activation that produced this layer's input;
+ * dact = RPDE_DACT_SAVED: zprev already holds act').  dbias_prev (optional, `in` floats, overwritten) receives the
+ * column sums of dx = the bias gradient of the layer that produced this layer's input. */
 int rpde_linear_bwd_input(const float* dy, const float* w, const float* zprev, int dact, float* dx, int accumulate,
-                          long long T, int in, int out, long long dy_cf_spatial, rpde_stream_t stream);
+                          float* dbias_prev, long long T, int in, int out, long long dy_cf_spatial,
+                          rpde_stream_t stream);
 /* dw[out,in] = dy^T x ; db[out] = column sums of dy (db may be NULL) */
 int rpde_linear_bwd_params(const float* dy, const float* x, float* dw, float* db, long long T, int in, int out,
                            long long dy_cf_spatial, rpde_stream_t stream);
@@ -125,8 +132,9 @@ int rpde_act_fwd(const float* x, const float* res, float* out, long long n, int 
  * y = (res ? res : 0) + LN(x) * gamma + beta ; mean/rstd (T floats each, optional) kept for backward. */
 int rpde_layernorm_fwd(const float* x, const float* res, const float* gamma, const float* beta, float* y,
                        float* mean, float* rstd, long long T, int C, float eps, rpde_stream_t stream);
+/* dxsum (optional, C floats): column sums of dx = bias gradient of the Linear that feeds the LayerNorm */
 int rpde_layernorm_bwd(const float* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
-                       float* dx, float* dgamma, float* dbeta, long long T, int C, rpde_stream_t stream);
+                       float* dx, float* dgamma, float* dbeta, float* dxsum, long long T, int C, rpde_stream_t stream);
 
 /* ---- weight-normed Linear weights (custom_layer.py:70-108, legacy weight_norm dim=0) ------------------- */
 int rpde_weight_norm_fwd(const float* v, const float* g, float* w, float* norms, int out, int in,

@@ -38,7 +38,7 @@ SIGNATURES = {
     "rpde_ffno_axis_fwd": (I, [P, P, P, P, P, P, I, L, I, L, I, I, I, I, P, Z, S]),
     "rpde_ffno_axis_bwd": (I, [P, P, P, P, P, P, I, P, I, L, I, L, I, I, I, I, P, Z, S]),
     "rpde_linear_fwd": (I, [P, P, P, P, P, L, I, I, I, L, S]),
-    "rpde_linear_bwd_input": (I, [P, P, P, I, P, I, L, I, I, L, S]),
+    "rpde_linear_bwd_input": (I, [P, P, P, I, P, I, P, L, I, I, L, S]),
     "rpde_linear_bwd_params": (I, [P, P, P, P, L, I, I, L, S]),
     "rpde_conv1x1_fwd": (I, [P, P, P, P, P, I, I, I, L, I, I, S]),
     "rpde_conv1x1_bwd_input": (I, [P, P, P, I, P, I, I, I, I, L, S]),
@@ -46,7 +46,7 @@ SIGNATURES = {
     "rpde_act_bwd": (I, [P, P, P, L, I, S]),
     "rpde_act_fwd": (I, [P, P, P, L, I, S]),
     "rpde_layernorm_fwd": (I, [P, P, P, P, P, P, P, L, I, c_float, S]),
-    "rpde_layernorm_bwd": (I, [P, P, P, P, P, P, P, P, L, I, S]),
+    "rpde_layernorm_bwd": (I, [P, P, P, P, P, P, P, P, P, L, I, S]),
     "rpde_weight_norm_fwd": (I, [P, P, P, P, I, I, S]),
     "rpde_weight_norm_bwd": (I, [P, P, P, P, P, P, I, I, S]),
     "rpde_concat_grid_fwd": (I, [P, P, P, P, I, I, I, I, I, S]),

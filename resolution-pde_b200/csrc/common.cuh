@@ -32,6 +32,13 @@ __device__ __forceinline__ float dgelu_f(float x) {
   const float pdf = 0.39894228040143267794f * expf(-0.5f * x * x);
   return cdf + x * pdf;
 }
+// h = gelu(x), g = gelu'(x) from one erf evaluation
+__device__ __forceinline__ void gelu_both(float x, float& h, float& g) {
+  const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
+  const float pdf = 0.39894228040143267794f * expf(-0.5f * x * x);
+  h = x * cdf;
+  g = cdf + x * pdf;
+}
 __device__ __forceinline__ float act_f(int act, float v) {
   if (act == ACT_GELU) return gelu_f(v);
   if (act == ACT_RELU) return v > 0.f ? v : 0.f;

@@ -26,8 +26,10 @@ struct GemmP {
   int bias_mode;
   int act;            // activation applied after bias/beta
   float* Z;           // optional pre-activation output (same layout as C)
-  const float* aux;   // with dact: result *= act'(aux) (same layout as C)
+  const float* aux;   // with dact: result *= act'(aux) (same layout as C); dact == 3: aux already holds act'
   int dact;
+  int z_grad;         // 1: Z receives act'(pre-activation) instead of the pre-activation
+  float* colsum;      // optional: += column sums of the final result (bias gradient of the producing layer), N floats
   int a_act, b_act;   // activation applied to the elements of A / B as they are loaded (operand = act(stored tensor))
   // filled by gemm_launch
   int a_kfast, b_kfast, a_kuni, b_kuni, tiles_m, tiles_n;
@@ -202,10 +204,11 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(const GemmP p) {
       if (p.bias_mode == 1) v += __ldg(p.bias + ncol[j]);
       else if (p.bias_mode == 2) v += __ldg(p.bias + m);
       if (p.beta) v += p.C[o];
-      if (p.Z) p.Z[o] = v;
+      if (p.Z) p.Z[o] = p.z_grad ? dact_f(p.act, v) : v;
       v = act_f(p.act, v);
-      if (p.dact) v *= dact_f(p.dact, __ldg(p.aux + o));
+      if (p.dact) v *= (p.dact == 3) ? __ldg(p.aux + o) : dact_f(p.dact, __ldg(p.aux + o));
       p.C[o] = v;
+      if (p.colsum) atomicAdd(p.colsum + ncol[j], v);
     }
   }
 }
@@ -219,7 +222,7 @@ static inline GemmP gemm_default() {
   p.splitk = 1; p.kchunk = 0;
   p.alpha = 1.f; p.beta = 0;
   p.bias = nullptr; p.bias_mode = 0;
-  p.act = ACT_NONE; p.Z = nullptr; p.aux = nullptr; p.dact = 0; p.a_act = p.b_act = 0;
+  p.act = ACT_NONE; p.Z = nullptr; p.aux = nullptr; p.dact = 0; p.a_act = p.b_act = 0; p.z_grad = 0; p.colsum = nullptr;
   p.a_kfast = p.b_kfast = p.a_kuni = p.b_kuni = 0; p.tiles_m = p.tiles_n = 0;
   return p;
 }

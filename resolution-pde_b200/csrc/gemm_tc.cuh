@@ -141,7 +141,10 @@ __device__ __forceinline__ void act32(int act, float (&v)[32]) {
   }
 }
 __device__ __forceinline__ void dact32_mul(int act, float (&v)[32], const float (&z)[32]) {
-  if (act == ACT_GELU) {
+  if (act == 3) {  // z already holds act'(pre-activation)
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] *= z[j];
+  } else if (act == ACT_GELU) {
 #pragma unroll
     for (int j = 0; j < 32; ++j) v[j] *= dgelu_f(z[j]);
   } else if (act == ACT_RELU) {
@@ -433,9 +436,29 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
               for (int j = 0; j < 32; ++j) v[j] += u[j];
             }
           }
+          bool acted = false;
           if (p.Z) {
             stage_free();
-            stage_write(v);
+            if (p.z_grad) {
+              float w[32];
+              if (P.dbg == 2) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) w[j] = v[j];
+              } else if (p.act == ACT_GELU) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) gelu_both(v[j], v[j], w[j]);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                  w[j] = dact_f(p.act, v[j]);
+                  v[j] = act_f(p.act, v[j]);
+                }
+              }
+              acted = true;
+              stage_write(w);
+            } else {
+              stage_write(v);
+            }
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) {
@@ -444,7 +467,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
             }
             pending = true;
           }
-          act32(p.act, v);
+          if (!acted) act32(p.act, v);
           stage_free();
           stage_write(v);
           fence_proxy_async_smem();
@@ -454,6 +477,17 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
             bulk_commit();
           }
           pending = true;
+          if (p.colsum) {
+            // bias gradient of the producing layer: column sums of the rows just staged (valid rows only)
+            const int rows = min(32, p.M - m_base);
+            float cs = 0.f;
+            for (int r = 0; r < rows; ++r) {
+              float x;
+              asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x) : "r"(stg + r * 128 + (((((uint32_t)lane >> 2) ^ ((uint32_t)r & 7u)) << 4) | (((uint32_t)lane & 3u) << 2))));
+              cs += x;
+            }
+            if (n0 + lane < p.N) atomicAdd(p.colsum + n0 + lane, cs);
+          }
           return;
         }
         if (col_contig) {
@@ -487,13 +521,18 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
                 const float4 cv = *reinterpret_cast<const float4*>(p.C + o);
                 x.x += cv.x; x.y += cv.y; x.z += cv.z; x.w += cv.w;
               }
-              if (p.Z) *reinterpret_cast<float4*>(p.Z + o) = x;
+              if (p.Z) *reinterpret_cast<float4*>(p.Z + o) = p.z_grad ? dact4(p.act, x) : x;
               if (p.act) x = act4(p.act, x);
               if (p.dact) {
-                const float4 dv = dact4(p.dact, __ldg(reinterpret_cast<const float4*>(p.aux + o)));
+                const float4 av = __ldg(reinterpret_cast<const float4*>(p.aux + o));
+                const float4 dv = (p.dact == 3) ? av : dact4(p.dact, av);
                 x.x *= dv.x; x.y *= dv.y; x.z *= dv.z; x.w *= dv.w;
               }
               if (P.dbg != 4) *reinterpret_cast<float4*>(p.C + o) = x;
+              if (p.colsum) {
+                atomicAdd(p.colsum + n0 + c4, x.x); atomicAdd(p.colsum + n0 + c4 + 1, x.y);
+                atomicAdd(p.colsum + n0 + c4 + 2, x.z); atomicAdd(p.colsum + n0 + c4 + 3, x.w);
+              }
             }
           } else {
             const int n = n0 + lane;
@@ -516,10 +555,11 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
               if (p.bias_mode == 1) x += bn;
               else if (p.bias_mode == 2) x += bm;
               if (p.beta) x += p.C[o];
-              if (p.Z) p.Z[o] = x;
+              if (p.Z) p.Z[o] = p.z_grad ? dact_f(p.act, x) : x;
               if (p.act) x = act_f(p.act, x);
-              if (p.dact) x *= dact_f(p.dact, __ldg(p.aux + o));
+              if (p.dact) x *= (p.dact == 3) ? __ldg(p.aux + o) : dact_f(p.dact, __ldg(p.aux + o));
               p.C[o] = x;
+              if (p.colsum) atomicAdd(p.colsum + n, x);
             }
           }
           __syncwarp();
@@ -538,10 +578,11 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
             if (p.bias_mode == 1) x += __ldg(p.bias + n);
             else if (p.bias_mode == 2) x += bias_m;
             if (p.beta) x += p.C[o];
-            if (p.Z) p.Z[o] = x;
+            if (p.Z) p.Z[o] = p.z_grad ? dact_f(p.act, x) : x;
             if (p.act) x = act_f(p.act, x);
-            if (p.dact) x *= dact_f(p.dact, __ldg(p.aux + o));
+            if (p.dact) x *= (p.dact == 3) ? __ldg(p.aux + o) : dact_f(p.dact, __ldg(p.aux + o));
             p.C[o] = x;
+            if (p.colsum) atomicAdd(p.colsum + n, x);
           }
         }
       };

@@ -157,12 +157,13 @@ __global__ void layernorm_fwd_kernel(const float* __restrict__ x, const float* _
 __global__ void layernorm_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ x,
                                      const float* __restrict__ gamma, const float* __restrict__ mean,
                                      const float* __restrict__ rstd, float* __restrict__ dx,
-                                     float* __restrict__ dgamma, float* __restrict__ dbeta, long long T, int C,
-                                     int rows_per_block) {
-  extern __shared__ float sm[];  // [2][C]
+                                     float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                     float* __restrict__ dxsum, long long T, int C, int rows_per_block) {
+  extern __shared__ float sm[];  // [3][C]
   float* sg = sm;
   float* sb = sm + C;
-  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) sm[c] = 0.f;
+  float* sx = sm + 2 * C;
+  for (int c = threadIdx.x; c < 3 * C; c += blockDim.x) sm[c] = 0.f;
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
   const long long r0 = (long long)blockIdx.x * rows_per_block;
@@ -181,15 +182,81 @@ __global__ void layernorm_bwd_kernel(const float* __restrict__ dy, const float* 
     s2 = warp_sum(s2) / (float)C;
     for (int c = lane; c < C; c += 32) {
       const float xh = (xr[c] - mu) * rs, d = gr[c];
-      dx[row * C + c] = rs * (d * gamma[c] - s1 - xh * s2);
+      const float dxv = rs * (d * gamma[c] - s1 - xh * s2);
+      dx[row * C + c] = dxv;
       atomicAdd(&sg[c], d * xh);
       atomicAdd(&sb[c], d);
+      if (dxsum) atomicAdd(&sx[c], dxv);
     }
   }
   __syncthreads();
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     atomicAdd(&dgamma[c], sg[c]);
     atomicAdd(&dbeta[c], sb[c]);
+    if (dxsum) atomicAdd(&dxsum[c], sx[c]);
+  }
+}
+
+// ----------------------------------------------------------------------------------------------
+// Linear layers with a handful of input features (in_proj of the F-FNO: 1-3 channels): pure streaming kernels.
+//   fwd   : y[t][o] = b[o] + sum_i x[t][i] w[o][i]          (thread = one row, four consecutive outputs)
+//   wgrad : dw[o][i] += sum_t dy[t][o] x[t][i],  db[o] += sum_t dy[t][o]
+// ----------------------------------------------------------------------------------------------
+template <int IN>
+__global__ void linear_smallk_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                         const float* __restrict__ bias, float* __restrict__ y, long long T, int OUT) {
+  extern __shared__ float sm[];  // w [OUT][IN], b [OUT]
+  for (int e = threadIdx.x; e < OUT * IN; e += blockDim.x) sm[e] = w[e];
+  for (int e = threadIdx.x; e < OUT; e += blockDim.x) sm[OUT * IN + e] = bias ? bias[e] : 0.f;
+  __syncthreads();
+  const int q = OUT >> 2;
+  const long long total = T * q;
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
+    const long long t = e / q;
+    const int o = (int)(e - t * q) * 4;
+    float xi[IN];
+#pragma unroll
+    for (int i = 0; i < IN; ++i) xi[i] = __ldg(x + t * IN + i);
+    float r[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float a = sm[OUT * IN + o + j];
+#pragma unroll
+      for (int i = 0; i < IN; ++i) a = fmaf(xi[i], sm[(o + j) * IN + i], a);
+      r[j] = a;
+    }
+    *reinterpret_cast<float4*>(y + t * OUT + o) = make_float4(r[0], r[1], r[2], r[3]);
+  }
+}
+
+template <int IN>
+__global__ void linear_smallk_wgrad_kernel(const float* __restrict__ dy, const float* __restrict__ x,
+                                           float* __restrict__ dw, float* __restrict__ db, long long T, int OUT,
+                                           long long rows_per_block) {
+  // blockDim.x = 256 = (256 / OUT) row lanes x OUT columns
+  extern __shared__ float sm[];  // [(IN + 1)][256]
+  const int o = threadIdx.x % OUT, rl = threadIdx.x / OUT, nr = blockDim.x / OUT;
+  const long long r0 = blockIdx.x * rows_per_block, r1 = min(T, r0 + rows_per_block);
+  float acc[IN + 1];
+#pragma unroll
+  for (int i = 0; i <= IN; ++i) acc[i] = 0.f;
+  for (long long t = r0 + rl; t < r1; t += nr) {
+    const float g = dy[t * OUT + o];
+#pragma unroll
+    for (int i = 0; i < IN; ++i) acc[i] = fmaf(g, __ldg(x + t * IN + i), acc[i]);
+    acc[IN] += g;
+  }
+#pragma unroll
+  for (int i = 0; i <= IN; ++i) sm[i * blockDim.x + threadIdx.x] = acc[i];
+  __syncthreads();
+  if (rl == 0) {
+#pragma unroll
+    for (int i = 0; i <= IN; ++i) {
+      float s = 0.f;
+      for (int k = 0; k < nr; ++k) s += sm[i * blockDim.x + k * OUT + o];
+      if (i < IN) atomicAdd(dw + o * IN + i, s);
+      else if (db) atomicAdd(db + o, s);
+    }
   }
 }
 

@@ -539,6 +539,23 @@ int rpde_linear_fwd(const float* x, const float* w, const float* bias, float* y,
   if (!x || !w || !y || T <= 0 || in <= 0 || out <= 0 || T > INT_MAX || y_cf_spatial > INT_MAX ||
       (y_cf_spatial > 0 && T % y_cf_spatial != 0))
     return fail(RPDE_E_INVALID, "rpde_linear_fwd: bad arguments%s");
+  const int save_grad = (act & RPDE_ACT_SAVE_GRAD) ? 1 : 0;
+  act &= 0xff;
+  if (in <= 4 && (out & 3) == 0 && out <= 1024 && act == RPDE_ACT_NONE && !z && y_cf_spatial == 0 &&
+      (reinterpret_cast<uintptr_t>(y) & 15) == 0) {
+    // a handful of input channels (in_proj): streaming kernel, one pass over the output
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t smem = (size_t)(out * in + out) * sizeof(float);
+    const unsigned grid = grid_for(T * (out / 4));
+    switch (in) {
+      case 1: linear_smallk_fwd_kernel<1><<<grid, 256, smem, s>>>(x, w, bias, y, T, out); break;
+      case 2: linear_smallk_fwd_kernel<2><<<grid, 256, smem, s>>>(x, w, bias, y, T, out); break;
+      case 3: linear_smallk_fwd_kernel<3><<<grid, 256, smem, s>>>(x, w, bias, y, T, out); break;
+      default: linear_smallk_fwd_kernel<4><<<grid, 256, smem, s>>>(x, w, bias, y, T, out); break;
+    }
+    RPDE_LAUNCH_CHECK();
+    return RPDE_OK;
+  }
   GemmP g = gemm_default();
   g.A = x; g.B = w; g.C = y;
   g.M = (int)T; g.N = out; g.K = in;
@@ -546,16 +563,18 @@ int rpde_linear_fwd(const float* x, const float* w, const float* bias, float* y,
   g.b = MatDesc{lin(0), lin(1), lin(in)};
   g.c = y_cf_spatial > 0 ? rows_cf(T, out, y_cf_spatial) : MatDesc{lin(0), lin(out), lin(1)};
   g.bias = bias; g.bias_mode = bias ? 1 : 0;
-  g.act = act; g.Z = z;
+  g.act = act; g.Z = z; g.z_grad = save_grad;
   RPDE_CUDA(gemm(g, (cudaStream_t)stream));
   return RPDE_OK;
 }
 
 int rpde_linear_bwd_input(const float* dy, const float* w, const float* zprev, int dact, float* dx, int accumulate,
-                          long long T, int in, int out, long long dy_cf_spatial, rpde_stream_t stream) {
-  if (!dy || !w || !dx || T <= 0 || in <= 0 || out <= 0 || T > INT_MAX || (dact && !zprev) ||
-      (dy_cf_spatial > 0 && T % dy_cf_spatial != 0))
+                          float* dbias_prev, long long T, int in, int out, long long dy_cf_spatial,
+                          rpde_stream_t stream) {
+  if (!dy || !w || !dx || T <= 0 || in <= 0 || out <= 0 || T > INT_MAX || (dact && !zprev) || dact < 0 || dact > 3 ||
+      (dy_cf_spatial > 0 && T % dy_cf_spatial != 0) || (dbias_prev && accumulate))
     return fail(RPDE_E_INVALID, "rpde_linear_bwd_input: bad arguments%s");
+  if (dbias_prev) RPDE_CUDA(cudaMemsetAsync(dbias_prev, 0, (size_t)in * sizeof(float), (cudaStream_t)stream));
   GemmP g = gemm_default();
   g.A = dy; g.B = w; g.C = dx;
   g.M = (int)T; g.N = in; g.K = out;
@@ -563,7 +582,7 @@ int rpde_linear_bwd_input(const float* dy, const float* w, const float* zprev, i
   g.b = MatDesc{lin(0), lin(in), lin(1)};
   g.c = MatDesc{lin(0), lin(in), lin(1)};
   g.beta = accumulate;
-  g.aux = zprev; g.dact = dact;
+  g.aux = zprev; g.dact = dact; g.colsum = dbias_prev;
   if (accumulate && dact) return fail(RPDE_E_INVALID, "rpde_linear_bwd_input: accumulate with dact is ambiguous%s");
   RPDE_CUDA(gemm(g, (cudaStream_t)stream));
   return RPDE_OK;
@@ -594,6 +613,22 @@ int rpde_linear_bwd_params(const float* dy, const float* x, float* dw, float* db
     return fail(RPDE_E_INVALID, "rpde_linear_bwd_params: bad arguments%s");
   cudaStream_t s = (cudaStream_t)stream;
   RPDE_CUDA(cudaMemsetAsync(dw, 0, (size_t)out * in * sizeof(float), s));
+  if (in <= 4 && dy_cf_spatial == 0 && out <= 256 && 256 % out == 0) {
+    // a handful of input channels: one streaming pass over dy gives dw and db together
+    if (db) RPDE_CUDA(cudaMemsetAsync(db, 0, (size_t)out * sizeof(float), s));
+    long long rpb = (T + 148 * 4 - 1) / (148 * 4);
+    if (rpb < 256) rpb = 256;
+    const unsigned grid = (unsigned)((T + rpb - 1) / rpb);
+    const size_t smem = (size_t)(in + 1) * 256 * sizeof(float);
+    switch (in) {
+      case 1: linear_smallk_wgrad_kernel<1><<<grid, 256, smem, s>>>(dy, x, dw, db, T, out, rpb); break;
+      case 2: linear_smallk_wgrad_kernel<2><<<grid, 256, smem, s>>>(dy, x, dw, db, T, out, rpb); break;
+      case 3: linear_smallk_wgrad_kernel<3><<<grid, 256, smem, s>>>(dy, x, dw, db, T, out, rpb); break;
+      default: linear_smallk_wgrad_kernel<4><<<grid, 256, smem, s>>>(dy, x, dw, db, T, out, rpb); break;
+    }
+    RPDE_LAUNCH_CHECK();
+    return RPDE_OK;
+  }
   GemmP g = gemm_default();
   g.A = dy; g.B = x; g.C = dw;
   g.M = out; g.N = in; g.K = (int)T;
@@ -692,17 +727,18 @@ int rpde_layernorm_fwd(const float* x, const float* res, const float* gamma, con
   return RPDE_OK;
 }
 int rpde_layernorm_bwd(const float* dy, const float* x, const float* gamma, const float* mean, const float* rstd,
-                       float* dx, float* dgamma, float* dbeta, long long T, int C, rpde_stream_t stream) {
+                       float* dx, float* dgamma, float* dbeta, float* dxsum, long long T, int C, rpde_stream_t stream) {
   if (!dy || !x || !gamma || !mean || !rstd || !dx || !dgamma || !dbeta || T <= 0 || C <= 0 || C > 4096)
     return fail(RPDE_E_INVALID, "rpde_layernorm_bwd: bad arguments%s");
   cudaStream_t s = (cudaStream_t)stream;
   RPDE_CUDA(cudaMemsetAsync(dgamma, 0, (size_t)C * sizeof(float), s));
   RPDE_CUDA(cudaMemsetAsync(dbeta, 0, (size_t)C * sizeof(float), s));
+  if (dxsum) RPDE_CUDA(cudaMemsetAsync(dxsum, 0, (size_t)C * sizeof(float), s));
   long long rpb = (T + 148 * 8 - 1) / (148 * 8);
   if (rpb < 8) rpb = 8;
   const unsigned grid = (unsigned)((T + rpb - 1) / rpb);
-  layernorm_bwd_kernel<<<grid, 256, 2 * C * sizeof(float), s>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, T, C,
-                                                               (int)rpb);
+  layernorm_bwd_kernel<<<grid, 256, 3 * C * sizeof(float), s>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, dxsum, T,
+                                                               C, (int)rpb);
   RPDE_LAUNCH_CHECK();
   return RPDE_OK;
 }

@@ -16,6 +16,7 @@ import torch
 from . import _lib
 
 ACT_NONE, ACT_GELU, ACT_RELU = 0, 1, 2
+ACT_SAVE_GRAD, DACT_SAVED = 0x100, 3   # forward stores act'(z); backward multiplies by the stored factor
 MIX_FULL, MIX_LOWPASS = 0, 1
 PREC = {"fp32": 0, "3xtf32": 1, "tf32": 2}
 _ACT_BY_NAME = {"identity": ACT_NONE, "none": ACT_NONE, "gelu": ACT_GELU, "relu": ACT_RELU}
@@ -361,7 +362,7 @@ class _LinearFn(torch.autograd.Function):
         with _Ctx(x) as c:
             if ctx.needs_input_grad[0]:
                 dx = torch.empty_like(x)
-                _lib.check(c.lib.rpde_linear_bwd_input(_p(dy), _p(w), None, 0, _p(dx), 0, T, in_f, out_f, S, c.stream),
+                _lib.check(c.lib.rpde_linear_bwd_input(_p(dy), _p(w), None, 0, _p(dx), 0, None, T, in_f, out_f, S, c.stream),
                            "rpde_linear_bwd_input")
             if ctx.needs_input_grad[1] or (has_b and ctx.needs_input_grad[2]):
                 dw = torch.empty_like(w)
@@ -399,7 +400,9 @@ class _FeedForwardFn(torch.autograd.Function):
                 out_f, in_f = Ws[i].shape
                 h = torch.empty((T, out_f), dtype=torch.float32, device=dev)
                 z = torch.empty_like(h) if need_grad else None
-                _lib.check(c.lib.rpde_linear_fwd(_p(a), _p(Ws[i]), _p(bs[i]), _p(h), _p(z), T, in_f, out_f, ACT_GELU, 0, c.stream),
+                # z holds gelu'(pre-activation): the backward pass multiplies, no erf/exp there
+                _lib.check(c.lib.rpde_linear_fwd(_p(a), _p(Ws[i]), _p(bs[i]), _p(h), _p(z), T, in_f, out_f,
+                                                 ACT_GELU | (ACT_SAVE_GRAD if z is not None else 0), 0, c.stream),
                            "rpde_linear_fwd")
                 acts.append(h)
                 zs.append(z)
@@ -448,6 +451,7 @@ class _FeedForwardFn(torch.autograd.Function):
         dev = dy.device
         grads = [None] * (2 * n + (2 if ctx.use_ln else 0))
         dres = dy if ctx.has_res else None
+        db_next = None  # bias gradient of layer i, when an earlier kernel already reduced the columns of g
         with _Ctx(dy) as c:
             g = dy
             if ctx.final_act != ACT_NONE:
@@ -459,23 +463,32 @@ class _FeedForwardFn(torch.autograd.Function):
                 du = torch.empty_like(dy)
                 dgamma = torch.empty_like(gamma)
                 dbeta = torch.empty_like(gamma)
-                _lib.check(c.lib.rpde_layernorm_bwd(_p(g), _p(u), _p(gamma), _p(mean), _p(rstd), _p(du), _p(dgamma), _p(dbeta), T,
-                                                    Cn, c.stream), "rpde_layernorm_bwd")
+                # the column sums of du are the bias gradient of the last Linear: produced in the same pass
+                if n > 0 and ctx.has_bias[n - 1]:
+                    db_next = torch.empty(Cn, dtype=torch.float32, device=dev)
+                _lib.check(c.lib.rpde_layernorm_bwd(_p(g), _p(u), _p(gamma), _p(mean), _p(rstd), _p(du), _p(dgamma), _p(dbeta),
+                                                    _p(db_next), T, Cn, c.stream), "rpde_layernorm_bwd")
                 grads[2 * n], grads[2 * n + 1] = dgamma, dbeta
                 g = du
             dx = g if (n == 0 and ctx.needs_input_grad[0]) else None
             for i in range(n - 1, -1, -1):
                 out_f, in_f = Ws[i].shape
                 dw = torch.empty_like(Ws[i])
-                db = torch.empty(out_f, dtype=torch.float32, device=dev) if ctx.has_bias[i] else None
-                _lib.check(c.lib.rpde_linear_bwd_params(_p(g), _p(acts[i]), _p(dw), _p(db), T, in_f, out_f, 0, c.stream),
-                           "rpde_linear_bwd_params")
+                if db_next is not None:
+                    db, fused = db_next, True
+                else:
+                    db, fused = (torch.empty(out_f, dtype=torch.float32, device=dev) if ctx.has_bias[i] else None), False
+                db_next = None
+                _lib.check(c.lib.rpde_linear_bwd_params(_p(g), _p(acts[i]), _p(dw), None if fused else _p(db), T, in_f, out_f, 0,
+                                                        c.stream), "rpde_linear_bwd_params")
                 grads[2 * i], grads[2 * i + 1] = dw, db
                 if i > 0 or ctx.needs_input_grad[0]:
                     gin = torch.empty((T, in_f), dtype=torch.float32, device=dev)
                     zprev = zs[i - 1] if i > 0 else None
-                    _lib.check(c.lib.rpde_linear_bwd_input(_p(g), _p(Ws[i]), _p(zprev), ACT_GELU if i > 0 else 0, _p(gin), 0, T,
-                                                           in_f, out_f, 0, c.stream), "rpde_linear_bwd_input")
+                    if i > 0 and ctx.has_bias[i - 1]:
+                        db_next = torch.empty(in_f, dtype=torch.float32, device=dev)
+                    _lib.check(c.lib.rpde_linear_bwd_input(_p(g), _p(Ws[i]), _p(zprev), DACT_SAVED if i > 0 else 0, _p(gin), 0,
+                                                           _p(db_next), T, in_f, out_f, 0, c.stream), "rpde_linear_bwd_input")
                     g = gin
                     if i == 0:
                         dx = gin.reshape(acts[0].shape)

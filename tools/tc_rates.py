@@ -88,8 +88,8 @@ for prec in ("tf32", "3xtf32"):
         dy = torch.randn(T, o, device="cuda")
         zp = torch.randn(T, i, device="cuda")
         dx = torch.empty(T, i, device="cuda")
-        ms_dgrad = _time(lambda: lib.rpde_linear_bwd_input(dy.data_ptr(), w.data_ptr(), None, 0, dx.data_ptr(), 0, T, i, o, 0, st))
-        ms_dact = _time(lambda: lib.rpde_linear_bwd_input(dy.data_ptr(), w.data_ptr(), zp.data_ptr(), 1, dx.data_ptr(), 0, T, i, o, 0, st))
+        ms_dgrad = _time(lambda: lib.rpde_linear_bwd_input(dy.data_ptr(), w.data_ptr(), None, 0, dx.data_ptr(), 0, None, T, i, o, 0, st))
+        ms_dact = _time(lambda: lib.rpde_linear_bwd_input(dy.data_ptr(), w.data_ptr(), zp.data_ptr(), 1, dx.data_ptr(), 0, None, T, i, o, 0, st))
         zd = zp[:4096].double()
         dg = 0.5 * (1 + torch.erf(zd / 2 ** 0.5)) + zd * torch.exp(-0.5 * zd * zd) / (2 * torch.pi) ** 0.5
         ref = (dy[:4096].double() @ w.double()) * dg
