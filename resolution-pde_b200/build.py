@@ -27,6 +27,7 @@ def build(force=False, verbose=False):
     if not force and up_to_date():
         return OUT
     defs = ["-DRPDE_WITH_TC"] if os.path.exists(os.path.join(SRC, "gemm_tc.cuh")) else []
+    defs += os.environ.get("RPDE_NVCC_DEFS", "").split()
     cmd = [NVCC] + FLAGS + defs + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT, os.path.join(SRC, "rpde.cu")]
     subprocess.run(cmd, check=True)
     return OUT

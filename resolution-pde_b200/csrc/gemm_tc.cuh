@@ -2,14 +2,16 @@
 // accumulators in TMEM) -> tcgen05.ld epilogue.  Same GemmP contract as gemm_simt.cuh.
 //
 // Precision variants (rpde_set_precision):
-//   3xTF32 : every fp32 operand tile is split on chip into hi = tf32(x) and lo = x - hi and the product is formed as
-//            lo*hi + hi*lo + hi*hi with fp32 accumulation in TMEM -> fp32-level accuracy (the parity engine).
+//   3xTF32 : every fp32 operand tile is split on chip into hi = tf32(x) and lo = x - hi (two-deep lo ring beside the raw
+//            TMA ring); hi*hi accumulates in one TMEM column block, hi*lo + lo*hi in a second one, the epilogue adds
+//            them -> fp32-level accuracy (the parity engine).
 //   TF32   : one pass on the raw fp32 bits (~5e-4 relative), the fast variant with its own stated tolerance.
 //
 // One persistent CTA per SM, warp-specialised:
 //   warp 0      TMA producer (one lane): fills a ring of {A,B} stages, full[s] <- complete_tx
 //   warp 1      UMMA issuer (one lane) + TMEM owner: 4 (x3) tcgen05.mma per stage, commit -> empty[s]; last -> acc_full
-//   warps 2-5   splitter (3xTF32 only): hi/lo split of the landed tiles in place, fence.proxy.async, -> ready[s]
+//   warps 2-5   splitter (3xTF32 only): lo = x - tf32(x) of the landed tiles into a two-deep lo ring, fence.proxy.async,
+//               one arrival per warp -> ready[s]
 //   warps 6-13  epilogue (two warps per TMEM lane quadrant, half of the columns each): tcgen05.ld 32x32b.x32, bias /
 //               activation / act' in registers, rows staged in a 128B-swizzled 32x32 box per warp and written with bulk tensor
 //               stores (Z and C), old C / aux fetched into the same box with bulk tensor loads, beta-only as a bulk
@@ -47,13 +49,26 @@ struct TcParams {
   int epi_tma;      // 1: C / Z leave through bulk tensor stores from the staging boxes, aux / old C arrive the same way
   int epi_reduce;   // 1: beta is realised as a bulk tensor reduce-add (no activation, no Z)
   int n_fast;       // tile order: n runs fastest
+  int l2_prefetch;  // bit 0 / 1: prefetch the next tile's A / B boxes into L2
   int tiles_m, tiles_n, kblocks, kchunk_blocks, total_tiles;
   int kc;       // k-blocks per TMEM accumulation chain (chunk); chunks are summed in registers with RN adds
   int c_vec;    // C / Z / aux / bias base pointers are 16-byte aligned
   int dbg;
+  int skip;  // bring-up only (RPDE_TC_SKIP bitmask): 1 epilogue emit, 2 operand prep, 4 UMMA issue, 8 TMA loads
 };
 
 namespace tc {
+
+// -DRPDE_TC_PROFILE: cycle counters around the waits / issues of the two single-thread roles (bring-up only)
+#ifdef RPDE_TC_PROFILE
+#define TCP_DECL(...) long long __VA_ARGS__
+#define TCP_T0(v) const long long v = clock64()
+#define TCP_ADD(acc, v) acc += clock64() - v
+#else
+#define TCP_DECL(...)
+#define TCP_T0(v)
+#define TCP_ADD(acc, v)
+#endif
 
 constexpr int BM = 128, BK = 32;
 constexpr int A_TILE_BYTES = BM * BK * 4;
@@ -65,10 +80,14 @@ constexpr int kSmemBudget = 227 * 1024 - 2048 - kEpiBytes;
 template <int BN, bool SPLIT>
 struct Cfg {
   static constexpr int b_tile = BN * BK * 4;
-  static constexpr int stage_bytes = (A_TILE_BYTES + b_tile) * (SPLIT ? 2 : 1);
-  static constexpr int raw = kSmemBudget / stage_bytes;
+  // The TMA ring holds raw fp32 tiles only.  3xTF32: the lo tiles live in a separate two-deep ring that is occupied just
+  // from the split until the UMMAs that read it retire, so the bytes in flight behind the tensor core are not halved.
+  static constexpr int stage_bytes = A_TILE_BYTES + b_tile;
+  static constexpr int lo_bufs = SPLIT ? 2 : 0;
+  static constexpr int lo_bytes = lo_bufs * stage_bytes;
+  static constexpr int raw = (kSmemBudget - lo_bytes) / stage_bytes;
   static constexpr int stages = raw > 6 ? 6 : raw;
-  static constexpr int smem_bytes = stages * stage_bytes + kEpiBytes + 2048;  // + alignment slack + barriers
+  static constexpr int smem_bytes = stages * stage_bytes + lo_bytes + kEpiBytes + 2048;  // + alignment slack + barriers
   static constexpr int acc_cols = SPLIT ? 2 * BN : BN;  // 3xTF32: [hi*hi | hi*lo + lo*hi] accumulated side by side
   static constexpr int tmem_cols = 2 * acc_cols < 32 ? 32 : 2 * acc_cols;
   static_assert(tmem_cols <= 512, "TMEM holds 512 columns");
@@ -209,12 +228,13 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
   constexpr int S = C::stages;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  // stage s: [A_hi]([A_lo])[B_hi]([B_lo]) -- B_lo directly behind B_hi, so one UMMA of width 2*BN sees [B_hi; B_lo]
+  // stage s: [A][B] raw fp32 (the tensor core truncates to TF32 itself: raw = hi); lo buffer l: [A_lo][B_lo]
   auto a_hi = [&](int s) { return smem_base + s * C::stage_bytes; };
-  auto a_lo = [&](int s) { return smem_base + s * C::stage_bytes + A_TILE_BYTES; };
-  auto b_hi = [&](int s) { return smem_base + s * C::stage_bytes + (SPLIT ? 2 : 1) * A_TILE_BYTES; };
-  auto b_lo = [&](int s) { return smem_base + s * C::stage_bytes + (SPLIT ? 2 : 1) * A_TILE_BYTES + C::b_tile; };
-  const uint32_t epi_base = smem_base + S * C::stage_bytes;  // 1024-aligned: the staging boxes use the TMA 128B swizzle
+  auto b_hi = [&](int s) { return smem_base + s * C::stage_bytes + A_TILE_BYTES; };
+  const uint32_t lo_base = smem_base + S * C::stage_bytes;
+  auto a_lo = [&](int l) { return lo_base + l * C::stage_bytes; };
+  auto b_lo = [&](int l) { return lo_base + l * C::stage_bytes + A_TILE_BYTES; };
+  const uint32_t epi_base = lo_base + C::lo_bytes;  // 1024-aligned: the staging boxes use the TMA 128B swizzle
   const uint32_t bar_base = epi_base + kEpiBytes;
   auto full = [&](int s) { return bar_base + 8 * s; };
   auto ready = [&](int s) { return bar_base + 8 * (S + s); };
@@ -222,7 +242,8 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
   auto acc_full = [&](int a) { return bar_base + 8 * (3 * S + a); };
   auto acc_empty = [&](int a) { return bar_base + 8 * (3 * S + 2 + a); };
   auto epi_in = [&](int w) { return bar_base + 8 * (3 * S + 4 + w); };
-  const uint32_t tmem_slot = bar_base + 8 * (3 * S + 4 + kEpiWarps);
+  auto lo_empty = [&](int l) { return bar_base + 8 * (3 * S + 4 + kEpiWarps + l); };
+  const uint32_t tmem_slot = bar_base + 8 * (3 * S + 4 + kEpiWarps + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const GemmP& p = P.g;
@@ -234,14 +255,15 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
     if (P.epi_tma) tma_prefetch_desc(&mapC);
     for (int s = 0; s < S; ++s) {
       mbar_init(full(s), 1);
-      mbar_init(ready(s), 128);
+      mbar_init(ready(s), 4);
       mbar_init(empty(s), 1);
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(acc_full(a), 1);
-      mbar_init(acc_empty(a), 32 * kEpiWarps);
+      mbar_init(acc_empty(a), kEpiWarps);
     }
     for (int w = 0; w < kEpiWarps; ++w) mbar_init(epi_in(w), 1);
+    for (int l = 0; l < 2; ++l) mbar_init(lo_empty(l), 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, C::tmem_cols);
@@ -253,9 +275,23 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
+    // One thread feeds the whole tensor core: the k loop is kept to a handful of integer multiply-adds (coordinates
+    // advance as base + k0*e0 + k1*e1 with 0/1 masks chosen once per kernel; ring slot and phase are carried).
     if (lane == 0) {
-      uint32_t it = 0;
-      const int a_kd = P.a.k_d, a_dk0 = P.a.dk0, a_dk1 = P.a.dk1, b_kd = P.b.k_d, b_dk0 = P.b.dk0, b_dk1 = P.b.dk1;
+      const int a_kd = P.a.k_d, b_kd = P.b.k_d;
+      int ea0[5], ea1[5], eb0[5], eb1[5];
+#pragma unroll
+      for (int j = 0; j < 5; ++j) {
+        ea0[j] = (j == P.a.dk0) ? 1 : 0;
+        ea1[j] = (a_kd != INT_MAX && j == P.a.dk1) ? 1 : 0;
+        eb0[j] = (j == P.b.dk0) ? 1 : 0;
+        eb1[j] = (b_kd != INT_MAX && j == P.b.dk1) ? 1 : 0;
+      }
+      const bool simple = P.a.boxes == 1 && P.b.boxes == 1;
+      const int a_nd = P.a.ndim, b_nd = P.b.ndim;
+      int s = 0;
+      uint32_t ph = 0;
+      TCP_DECL(pw = 0, pi = 0, pall = clock64(), pn = 0);
       for (int t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
         int tm, tn, z;
         tile_coords(P, t, tm, tn, z);
@@ -264,29 +300,62 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
         int ca[5], cb[5];
         opnd_coords(P.a, tm * BM, bz, ca);
         opnd_coords(P.b, tn * BN, bz, cb);
-        for (int kb = kb0; kb < kb1; ++kb, ++it) {
-          const int s = it % S;
-          const uint32_t ph = (it / S) & 1;
-          opnd_set_k(a_kd, a_dk0, a_dk1, kb * BK, ca);
-          opnd_set_k(b_kd, b_dk0, b_dk1, kb * BK, cb);
+        const int k_start = kb0 * BK;
+        int ka0 = (a_kd == INT_MAX) ? k_start : k_start % a_kd, ka1 = (a_kd == INT_MAX) ? 0 : k_start / a_kd;
+        int kb0_ = (b_kd == INT_MAX) ? k_start : k_start % b_kd, kb1_ = (b_kd == INT_MAX) ? 0 : k_start / b_kd;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          int xa[5], xb[5];
+#pragma unroll
+          for (int j = 0; j < 5; ++j) {
+            xa[j] = ca[j] + ka0 * ea0[j] + ka1 * ea1[j];
+            xb[j] = cb[j] + kb0_ * eb0[j] + kb1_ * eb1[j];
+          }
+          const uint32_t fb = full(s), dst = a_hi(s);
+          TCP_T0(q0);
           mbar_wait(empty(s), ph ^ 1);
-          mbar_arrive_expect_tx(full(s), A_TILE_BYTES + C::b_tile);
-          opnd_load(P.a, &mapA, a_hi(s), full(s), ca, tm * BM);
-          opnd_load(P.b, &mapB, b_hi(s), full(s), cb, tn * BN);
+          TCP_ADD(pw, q0);
+          TCP_T0(q1);
+          if (P.skip & 8) {
+            mbar_arrive(fb);
+          } else {
+            mbar_arrive_expect_tx(fb, A_TILE_BYTES + C::b_tile);
+            if (simple) {
+              tma_load(dst, &mapA, fb, a_nd, xa);
+              tma_load(dst + A_TILE_BYTES, &mapB, fb, b_nd, xb);
+            } else {
+              opnd_load(P.a, &mapA, dst, fb, xa, tm * BM);
+              opnd_load(P.b, &mapB, dst + A_TILE_BYTES, fb, xb, tn * BN);
+            }
+          }
+          TCP_ADD(pi, q1);
+#ifdef RPDE_TC_PROFILE
+          ++pn;
+#endif
+          ka0 += BK;
+          if (ka0 >= a_kd) { ka0 = 0; ++ka1; }
+          kb0_ += BK;
+          if (kb0_ >= b_kd) { kb0_ = 0; ++kb1_; }
+          if (++s == S) { s = 0; ph ^= 1; }
         }
       }
+#ifdef RPDE_TC_PROFILE
+      if (blockIdx.x == 0) printf("[tc producer] iters %lld total %lld wait_empty %lld issue %lld\n", pn, clock64() - pall, pw, pi);
+#endif
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ UMMA issuer
     if (lane == 0) {
       const uint32_t idesc = umma_idesc_tf32(BM, BN, P.a.major, P.b.major);
-      const uint32_t idesc2 = umma_idesc_tf32(BM, SPLIT ? 2 * BN : BN, P.a.major, P.b.major);
-      const uint32_t a_step = P.a.major ? 1024u : 32u, b_step = P.b.major ? 1024u : 32u;
+      const uint32_t a_step = (P.a.major ? 1024u : 32u) >> 4, b_step = (P.b.major ? 1024u : 32u) >> 4;
       const uint32_t a_lbo = P.a.major ? BK * 128u : 16u, b_lbo = P.b.major ? BK * 128u : 16u;
       const uint32_t a_sbo = P.a.major ? 512u : 1024u, b_sbo = P.b.major ? 512u : 1024u;
       const uint32_t a_lay = P.a.major ? UMMA_LAYOUT_SW128_BASE32B : UMMA_LAYOUT_SW128;
       const uint32_t b_lay = P.b.major ? UMMA_LAYOUT_SW128_BASE32B : UMMA_LAYOUT_SW128;
-      uint32_t it = 0, cit = 0;
+      // descriptors with a zero start address: the 14-bit address field (smem offset >> 4 < 2^14) is added per use
+      const uint64_t dA = umma_desc(0, a_lbo, a_sbo, a_lay), dB = umma_desc(0, b_lbo, b_sbo, b_lay);
+      int s = 0, l = 0;
+      uint32_t ph = 0, cit = 0;
+      TCP_DECL(mw = 0, ma = 0, mi = 0, mc = 0, mall = clock64(), mn = 0);
       for (int t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
         int tm, tn, z;
         tile_coords(P, t, tm, tn, z);
@@ -295,56 +364,82 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
         for (int c0 = kb0; c0 < kb1; c0 += P.kc, ++cit) {
           const int c1 = min(kb1, c0 + P.kc);
           const int buf = cit & 1;
+          TCP_T0(r0);
           mbar_wait(acc_empty(buf), ((cit >> 1) & 1) ^ 1);
+          TCP_ADD(ma, r0);
           tc_fence_after_sync();
           const uint32_t d = tmem_base + buf * C::acc_cols;
-          for (int kb = c0; kb < c1; ++kb, ++it) {
-            const int s = it % S;
-            const uint32_t ph = (it / S) & 1;
+          for (int kb = c0; kb < c1; ++kb) {
+            TCP_T0(r1);
             mbar_wait(use_prep ? ready(s) : full(s), ph);
+            TCP_ADD(mw, r1);
+            TCP_T0(r2);
             tc_fence_after_sync();
+            const uint64_t ah0 = dA + (a_hi(s) >> 4), bh0 = dB + (b_hi(s) >> 4);
+            const uint64_t al0 = dA + (a_lo(l) >> 4), bl0 = dB + (b_lo(l) >> 4);
+            if (!(P.skip & 4)) {
 #pragma unroll
-            for (int k4 = 0; k4 < BK / 8; ++k4) {
-              if (P.dbg == 7) break;
-              const uint32_t acc = (kb > c0 || k4 > 0) ? 1u : 0u;
-              const uint64_t ah = umma_desc(a_hi(s) + k4 * a_step, a_lbo, a_sbo, a_lay);
-              const uint64_t bh = umma_desc(b_hi(s) + k4 * b_step, b_lbo, b_sbo, b_lay);
-              if (SPLIT) {
-                // [big | small] (+)= A_hi [B_hi; B_lo]   then   small += A_lo B_hi.  The large products meet one
-                // accumulator truncation per k-step; the 2^-11 corrections live in their own columns.
-                const uint64_t al = umma_desc(a_lo(s) + k4 * a_step, a_lbo, a_sbo, a_lay);
-                umma_tf32(d, ah, bh, idesc2, acc);
-                umma_tf32(d + BN, al, bh, idesc, 1u);
-              } else {
-                umma_tf32(d, ah, bh, idesc, acc);
+              for (int k4 = 0; k4 < BK / 8; ++k4) {
+                const uint32_t acc = (kb > c0 || k4 > 0) ? 1u : 0u;
+                const uint64_t ah = ah0 + k4 * a_step, bh = bh0 + k4 * b_step;
+                if (SPLIT) {
+                  // big (+)= A_hi B_hi ; small (+)= A_hi B_lo + A_lo B_hi.  The large products meet one accumulator
+                  // truncation per k-step; the 2^-11 corrections live in their own TMEM columns.
+                  umma_tf32(d, ah, bh, idesc, acc);
+                  umma_tf32(d + BN, ah, bl0 + k4 * b_step, idesc, acc);
+                  umma_tf32(d + BN, al0 + k4 * a_step, bh, idesc, 1u);
+                } else {
+                  umma_tf32(d, ah, bh, idesc, acc);
+                }
               }
             }
+            TCP_ADD(mi, r2);
+            TCP_T0(r3);
             umma_commit(empty(s));
+            if (SPLIT) {
+              umma_commit(lo_empty(l));
+              l ^= 1;
+            }
+            TCP_ADD(mc, r3);
+#ifdef RPDE_TC_PROFILE
+            ++mn;
+#endif
+            if (++s == S) { s = 0; ph ^= 1; }
           }
           umma_commit(acc_full(buf));
         }
       }
+#ifdef RPDE_TC_PROFILE
+      if (blockIdx.x == 0)
+        printf("[tc mma] iters %lld total %lld wait_ready %lld wait_acc_empty %lld issue %lld commit %lld\n", mn, clock64() - mall, mw, ma, mi, mc);
+#endif
     }
   } else if (warp < 6) {
     // ------------------------------------------------------------------ operand preparation (activation-on-load, hi/lo split)
     if (use_prep) {
       const int ct = threadIdx.x - 64;
-      uint32_t it = 0;
+      int s = 0, l = 0;
+      uint32_t ph = 0, lph = 0;
       for (int t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
         int tm, tn, z;
         tile_coords(P, t, tm, tn, z);
         const int sk = z % p.splitk;
         const int kb0 = sk * P.kchunk_blocks, kb1 = min(P.kblocks, kb0 + P.kchunk_blocks);
-        for (int kb = kb0; kb < kb1; ++kb, ++it) {
-          const int s = it % S;
-          const uint32_t ph = (it / S) & 1;
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(full(s), ph);
-          if (P.dbg != 6) {
-            if (SPLIT || p.a_act) prep_region<SPLIT>(a_hi(s), a_lo(s), A_TILE_BYTES / 16, p.a_act, ct);
-            if (SPLIT || p.b_act) prep_region<SPLIT>(b_hi(s), b_lo(s), C::b_tile / 16, p.b_act, ct);
+          if (SPLIT) mbar_wait(lo_empty(l), lph ^ 1);  // the UMMAs of two iterations ago have released lo buffer l
+          if (!(P.skip & 2)) {
+            if (SPLIT || p.a_act) prep_region<SPLIT>(a_hi(s), a_lo(l), A_TILE_BYTES / 16, p.a_act, ct);
+            if (SPLIT || p.b_act) prep_region<SPLIT>(b_hi(s), b_lo(l), C::b_tile / 16, p.b_act, ct);
           }
           fence_proxy_async_smem();
-          mbar_arrive(ready(s));
+          __syncwarp();
+          if (lane == 0) mbar_arrive(ready(s));  // one arrival per warp
+          if (SPLIT) {
+            if (l == 1) lph ^= 1;
+            l ^= 1;
+          }
+          if (++s == S) { s = 0; ph ^= 1; }
         }
       }
     }
@@ -391,7 +486,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
 
       // ---- one 32-column slice of this warp's 32 rows: v[j] = accumulator of (row m, column n0 + j)
       auto emit = [&](float (&v)[32], int n0) {
-        if (P.dbg == 5) return;
+        if (P.dbg == 5 || (P.skip & 1)) return;
         if (P.epi_tma) {
           // TMA epilogue: rows are staged in the swizzled box and leave (or arrive) as one bulk tensor copy
           if (m_base >= p.M) return;  // warp-uniform
@@ -614,7 +709,8 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
           emit(v, n0);
         }
         tc_fence_before_sync();
-        mbar_arrive(acc_empty(buf));
+        __syncwarp();
+        if (lane == 0) mbar_arrive(acc_empty(buf));
         ++cit;
       } else {
         float acc[CPW * 32];
@@ -642,7 +738,8 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
             }
           }
           tc_fence_before_sync();
-          mbar_arrive(acc_empty(buf));
+          __syncwarp();
+          if (lane == 0) mbar_arrive(acc_empty(buf));
         }
 #pragma unroll
         for (int ci = 0; ci < CPW; ++ci) {
@@ -841,6 +938,8 @@ static cudaError_t gemm_tc_try_launch(const GemmP& g, int prec, cudaStream_t s, 
   {
     const char* e = getenv("RPDE_TC_DBG");
     P.dbg = e ? atoi(e) : 0;
+    const char* sk = getenv("RPDE_TC_SKIP");
+    P.skip = sk ? atoi(sk) : 0;
   }
   CUtensorMap ma, mb;
   int dev = 0, sms = 148;
@@ -896,6 +995,10 @@ static cudaError_t gemm_tc_try_launch(const GemmP& g, int prec, cudaStream_t s, 
   if (total > 0x7fffffffLL) return cudaSuccess;
   P.total_tiles = (int)total;
   P.n_fast = P.tiles_n <= P.tiles_m;
+  {
+    static const int pf_env = getenv("RPDE_TC_L2PF") ? atoi(getenv("RPDE_TC_L2PF")) : 0;  // measured: the extra TMA requests cost more than the latency they hide
+    P.l2_prefetch = pf_env;
+  }
   // TMA epilogue: the output (and Z / aux / the old C) addressed as 32 x 32 boxes of rows x contiguous columns
   EpiMaps em;
   memset(&em, 0, sizeof(em));

@@ -29,11 +29,11 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
       "selp.u32 %0, 1, 0, p;\n\t}"
       : "=r"(ok)
-      : "r"(bar), "r"(parity)
-      : "memory");
+      : "r"(bar), "r"(parity), "r"(0x989680u)  // suspend-time hint: the waiting warp sleeps in hardware instead of
+      : "memory");                             // spinning through the issue slots of the producer / UMMA threads
   return ok != 0;
 }
 __device__ __forceinline__ uint64_t global_timer_ns() {
@@ -83,6 +83,26 @@ __device__ __forceinline__ void tma_load(uint32_t dst, const CUtensorMap* m, uin
   }
 }
 
+// L2 prefetch of one box (no shared-memory destination, no completion tracking)
+__device__ __forceinline__ void tma_prefetch_l2(const CUtensorMap* m, int ndim, const int* c) {
+  const uint64_t mp = (uint64_t)m;
+  switch (ndim) {
+    case 2:
+      asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(mp), "r"(c[0]), "r"(c[1]) : "memory");
+      break;
+    case 3:
+      asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];" ::"l"(mp), "r"(c[0]), "r"(c[1]), "r"(c[2]) : "memory");
+      break;
+    case 4:
+      asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global.tile [%0, {%1, %2, %3, %4}];"
+                   ::"l"(mp), "r"(c[0]), "r"(c[1]), "r"(c[2]), "r"(c[3]) : "memory");
+      break;
+    default:
+      asm volatile("cp.async.bulk.prefetch.tensor.5d.L2.global.tile [%0, {%1, %2, %3, %4, %5}];"
+                   ::"l"(mp), "r"(c[0]), "r"(c[1]), "r"(c[2]), "r"(c[3]), "r"(c[4]) : "memory");
+      break;
+  }
+}
 // tile-mode store of one box from shared memory (bulk async-group completion); reduce = element-wise fp32 add into global
 __device__ __forceinline__ void tma_store(uint32_t src, const CUtensorMap* m, int ndim, const int* c, bool reduce) {
   const uint64_t mp = (uint64_t)m;
