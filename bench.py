@@ -324,8 +324,16 @@ def main():
             torch.cuda.synchronize()
             kms = s.elapsed_time(e) / reps
             ach = 2.0 * T * d * d / (kms * 1e-3) / 1e12
+            # DRAM bytes per launch of this kernel from the ncu --set full capture (profiles/r1d_ncu_full_ffgemm_3xtf32.csv:
+            # dram__bytes_read.sum + dram__bytes_write.sum); only known for the captured shape / engine
+            traffic = 2.1027e9 if (name == "ffno2d_ns256" and B == 16 and prec == "3xtf32") else None
+            vdiv = {"3xtf32": 6.0, "tf32": 2.0}.get(prec)
             roof = {"bound": "tensor", "achieved": ach, "peak": pk["tensor_burst"], "unit": "TFLOP/s", "frac": ach / pk["tensor_burst"],
-                    "traffic": None, "kernel": f"contraction engine ({prec}), FeedForward hidden GEMM {T}x{d}x{d}", "kernel_ms": kms,
+                    "traffic": traffic, "kernel": f"contraction engine ({prec}), FeedForward hidden GEMM {T}x{d}x{d}", "kernel_ms": kms,
+                    "algorithmic_bytes": 4.0 * (2 * T * d + d * d), "hbm_frac": 4.0 * (2 * T * d + d * d) / (kms * 1e-3) / 1e9 / pk["hbm"],
+                    "peak_variant": ({"engine": prec, "peak": pk["tensor_burst"] / vdiv, "frac": ach / (pk["tensor_burst"] / vdiv),
+                                      "note": "kind::tf32 UMMA runs at half the bf16 rate; 3xTF32 issues three UMMAs per credited product"}
+                                     if vdiv else None),
                     "peak_source": pk["src"] + " bf16 burst (kernel timed alone)",
                     "step": {"achieved": wl["flops"] / (ms / args.steps * 1e-3) / 1e12, "peak": pk["tensor"], "unit": "TFLOP/s",
                              "frac": wl["flops"] / (ms / args.steps * 1e-3) / 1e12 / pk["tensor"],

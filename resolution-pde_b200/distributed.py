@@ -35,28 +35,31 @@ class GradBucket:
     def _views(self, tensors: Sequence[torch.Tensor]):
         return [torch.view_as_real(t).reshape(-1) if t.is_complex() else t.reshape(-1) for t in tensors]
 
-    def pack(self) -> torch.Tensor:
-        off = 0
-        for p, n in zip(self.params, self.sizes):
-            if p.grad is None:
-                self.flat[off:off + n].zero_()
-            else:
-                self.flat[off:off + n].copy_(self._views([p.grad])[0])
+    def _flat_views(self):
+        views, off = [], 0
+        for n in self.sizes:
+            views.append(self.flat[off:off + n])
             off += n
+        return views
+
+    def pack(self) -> torch.Tensor:
+        """One multi-tensor copy of every gradient into the flat buffer (missing grads are zero)."""
+        flat_views = self._flat_views()
+        have = [(fv, p.grad) for fv, p in zip(flat_views, self.params) if p.grad is not None]
+        for fv, p in zip(flat_views, self.params):
+            if p.grad is None:
+                fv.zero_()
+        if have:
+            torch._foreach_copy_([fv for fv, _ in have], self._views([g for _, g in have]))
         return self.flat
 
     def unpack(self, scale: float = 1.0) -> None:
-        off = 0
-        for p, n in zip(self.params, self.sizes):
-            src = self.flat[off:off + n]
+        if scale != 1.0:
+            self.flat.mul_(scale)
+        for p in self.params:
             if p.grad is None:
                 p.grad = torch.zeros_like(p)
-            dst = self._views([p.grad])[0]
-            if scale != 1.0:
-                torch.mul(src, scale, out=dst)
-            else:
-                dst.copy_(src)
-            off += n
+        torch._foreach_copy_(self._views([p.grad for p in self.params]), self._flat_views())
 
     def allreduce_mean(self, group=None, weight: float = 1.0, total_weight: float = None) -> None:
         """grad <- sum_r weight_r * grad_r / sum_r weight_r.  With equal per-rank batches weight = 1; with ragged
