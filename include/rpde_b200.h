@@ -59,8 +59,8 @@ int rpde_dft_table(float* out, int kind, int n, int k, int m1, double scale, rpd
 
 /* ---- FNO SpectralConv1d (models/spectral_convolution.py:24-55), channels-first (B,I,N) -> (B,O,N) --------
  * w: complex64 (I,O,modes) interleaved.  fa: kind-0 table [modes][2][N] scale 1, fs: kind-1 table scale 1/N.
- * y = act(spectral(x) + (beta ? y : 0)); z (optional) receives the pre-activation.  spec (B*2I*modes floats)
- * receives the retained spectrum for the backward pass.  modes > N/2+1 -> RPDE_E_MODES. */
+ * y = act(spectral(x) + (beta ? y : 0)); z (optional) receives the pre-activation.  spec (B*2I*modes floats,
+ * laid out [mode][re|im][b][i]) receives the retained spectrum for the backward pass.  modes > N/2+1 -> RPDE_E_MODES. */
 size_t rpde_spectral1d_workspace_bytes(int B, int I, int O, int N, int modes);
 int rpde_spectral1d_fwd(const float* x, const float* w, const float* fa, const float* fs, float* spec, float* y,
                         float* z, int B, int I, int O, int N, int modes, int beta, int act, void* ws,

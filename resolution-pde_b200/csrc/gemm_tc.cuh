@@ -957,7 +957,7 @@ static cudaError_t gemm_tc_try_launch(const GemmP& g, int prec, cudaStream_t s, 
     if (splitk == 0) {
       const long long ctas = (long long)tiles_m * ((g.N + BN - 1) / BN) * g.batch;
       long long want = (sms + ctas - 1) / ctas;
-      const long long maxs = (kblocks + 7) / 8;  // at least 256 k per split
+      const long long maxs = (kblocks + 1) / 2;  // at least 64 k per split
       if (want > maxs) want = maxs;
       if (want < 1) want = 1;
       splitk = (int)want;

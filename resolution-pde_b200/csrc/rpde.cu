@@ -138,28 +138,33 @@ int rpde_spectral1d_fwd(const float* x, const float* w, const float* fa, const f
   float* om = cv.take((size_t)K * B * 2 * O);
   int rc = pack_w(w, wp, I, O, modes, K, 1, 1, s);
   if (rc) return rc;
-  // 1. analysis: spec[k][b][(ri,i)] = sum_n x[(b,i)][n] fa[(k,ri)][n]
+  // Layouts: spec[k][ri][b][i], om[k][ro][b][o] -- the (mode, re/im) pair is the slow index, so the synthesis reads its
+  // A operand with a single-level K stride (B*O) and unit-stride rows: both are TMA-addressable.
+  const long long BI = (long long)B * I, BO = (long long)B * O;
+  // 1. analysis (split-K: only B*I/128 row tiles exist): spec[(k,ri)][(b,i)] = sum_n x[(b,i)][n] fa[(k,ri)][n]
+  RPDE_CUDA(cudaMemsetAsync(spec, 0, (size_t)K * 2 * BI * sizeof(float), s));
   GemmP g = gemm_default();
   g.A = x; g.B = fa; g.C = spec;
   g.M = B * I; g.N = 2 * K; g.K = N;
   g.a = MatDesc{lin(0), lin(N), lin(1)};
   g.b = MatDesc{lin(0), lin(1), lin(N)};
-  g.c = MatDesc{lin(0), two(I, 2LL * I, 1), two(2, (long long)B * 2 * I, I)};
+  g.c = MatDesc{lin(0), lin(1), lin(BI)};
+  g.splitk = 0;
   RPDE_CUDA(gemm(g, s));
-  // 2. mixing per mode: om[k][b][(ro,o)] = spec[k][b][:] wp[k]
+  // 2. mixing per mode: om[k][ro][b][o] = sum_(ri,i) spec[k][ri][b][i] wp[k][(ri,i)][(ro,o)]
   g = gemm_default();
   g.A = spec; g.B = wp; g.C = om;
   g.batch = K; g.M = B; g.N = 2 * O; g.K = 2 * I;
-  g.a = MatDesc{lin((long long)B * 2 * I), lin(2 * I), lin(1)};
+  g.a = MatDesc{lin(2 * BI), lin(I), two(I, BI, 1)};
   g.b = MatDesc{lin(4LL * I * O), lin(2 * O), lin(1)};
-  g.c = MatDesc{lin((long long)B * 2 * O), lin(2 * O), lin(1)};
+  g.c = MatDesc{lin(2 * BO), lin(O), two(O, BO, 1)};
   RPDE_CUDA(gemm(g, s));
-  // 3. synthesis: y[(b,o)][n] = sum_(ro,k) om[k][b][(ro,o)] fs[n][(k,ro)]
+  // 3. synthesis: y[(b,o)][n] = sum_(k,ro) om[(k,ro)][(b,o)] fs[n][(k,ro)]
   g = gemm_default();
   g.A = om; g.B = fs; g.C = y;
   g.M = B * O; g.N = N; g.K = 2 * K;
-  g.a = MatDesc{lin(0), two(O, 2LL * O, 1), two(K, O, (long long)B * 2 * O)};
-  g.b = MatDesc{lin(0), two(K, 1, 2), lin(2 * K)};
+  g.a = MatDesc{lin(0), lin(1), lin(BO)};
+  g.b = MatDesc{lin(0), lin(1), lin(2 * K)};
   g.c = MatDesc{lin(0), lin(N), lin(1)};
   g.beta = beta; g.act = act; g.Z = z;
   RPDE_CUDA(gemm(g, s));
@@ -183,13 +188,16 @@ int rpde_spectral1d_bwd(const float* dy, const float* w, const float* fa, const 
   float* P = cv.take((size_t)K * 4 * I * O);
   int rc = pack_w(w, wp, I, O, modes, K, 1, 1, s);
   if (rc) return rc;
-  // 3'. dom[k][b][(ro,o)] = sum_n dy[(b,o)][n] fs[n][(k,ro)]
+  const long long BI = (long long)B * I, BO = (long long)B * O;
+  // 3'. dom[(k,ro)][(b,o)] = sum_n dy[(b,o)][n] fs[n][(k,ro)]
+  RPDE_CUDA(cudaMemsetAsync(dom, 0, (size_t)K * 2 * BO * sizeof(float), s));
   GemmP g = gemm_default();
   g.A = dy; g.B = fs; g.C = dom;
   g.M = B * O; g.N = 2 * K; g.K = N;
   g.a = MatDesc{lin(0), lin(N), lin(1)};
   g.b = MatDesc{lin(0), lin(2 * K), lin(1)};
-  g.c = MatDesc{lin(0), two(O, 2LL * O, 1), two(2, (long long)B * 2 * O, O)};
+  g.c = MatDesc{lin(0), lin(1), lin(BO)};
+  g.splitk = 0;
   RPDE_CUDA(gemm(g, s));
   if (dw) {
     // dWp[k] = spec[k]^T dom[k]
@@ -197,8 +205,8 @@ int rpde_spectral1d_bwd(const float* dy, const float* w, const float* fa, const 
     g = gemm_default();
     g.A = spec; g.B = dom; g.C = P;
     g.batch = K; g.M = 2 * I; g.N = 2 * O; g.K = B;
-    g.a = MatDesc{lin((long long)B * 2 * I), lin(1), lin(2 * I)};
-    g.b = MatDesc{lin((long long)B * 2 * O), lin(2 * O), lin(1)};
+    g.a = MatDesc{lin(2 * BI), two(I, BI, 1), lin(I)};
+    g.b = MatDesc{lin(2 * BO), lin(O), two(O, BO, 1)};
     g.c = MatDesc{lin(4LL * I * O), lin(2 * O), lin(1)};
     g.splitk = 0;
     RPDE_CUDA(gemm(g, s));
@@ -210,16 +218,16 @@ int rpde_spectral1d_bwd(const float* dy, const float* w, const float* fa, const 
     g = gemm_default();
     g.A = dom; g.B = wp; g.C = dsp;
     g.batch = K; g.M = B; g.N = 2 * I; g.K = 2 * O;
-    g.a = MatDesc{lin((long long)B * 2 * O), lin(2 * O), lin(1)};
+    g.a = MatDesc{lin(2 * BO), lin(O), two(O, BO, 1)};
     g.b = MatDesc{lin(4LL * I * O), lin(1), lin(2 * O)};
-    g.c = MatDesc{lin((long long)B * 2 * I), lin(2 * I), lin(1)};
+    g.c = MatDesc{lin(2 * BI), lin(I), two(I, BI, 1)};
     RPDE_CUDA(gemm(g, s));
-    // 1'. dx[(b,i)][n] (+)= sum_(ri,k) dsp[k][b][(ri,i)] fa[(k,ri)][n]
+    // 1'. dx[(b,i)][n] (+)= sum_(k,ri) dsp[(k,ri)][(b,i)] fa[(k,ri)][n]
     g = gemm_default();
     g.A = dsp; g.B = fa; g.C = dx;
     g.M = B * I; g.N = N; g.K = 2 * K;
-    g.a = MatDesc{lin(0), two(I, 2LL * I, 1), two(K, I, (long long)B * 2 * I)};
-    g.b = MatDesc{lin(0), two(K, N, 2LL * N), lin(1)};
+    g.a = MatDesc{lin(0), lin(1), lin(BI)};
+    g.b = MatDesc{lin(0), lin(N), lin(1)};
     g.c = MatDesc{lin(0), lin(N), lin(1)};
     g.beta = dx_accumulate;
     RPDE_CUDA(gemm(g, s));
