@@ -36,7 +36,8 @@ enum { RPDE_ACT_SAVE_GRAD = 0x100 };
 enum { RPDE_DACT_SAVED = 3 };
 enum { RPDE_MIX_FULL = 0, RPDE_MIX_LOWPASS = 1 };
 /* DFT table kinds (rpde_dft_table) */
-enum { RPDE_DFT_R2C_ANALYSIS = 0, RPDE_DFT_C2R_SYNTHESIS = 1, RPDE_DFT_C2C_ANALYSIS_ROWS = 2, RPDE_DFT_C2C_SYNTHESIS_ROWS = 3 };
+enum { RPDE_DFT_R2C_ANALYSIS = 0, RPDE_DFT_C2R_SYNTHESIS = 1, RPDE_DFT_C2C_ANALYSIS_ROWS = 2, RPDE_DFT_C2C_SYNTHESIS_ROWS = 3,
+       RPDE_DFT_C2R_SYNTHESIS_PLANES = 4 };
 /* precision of the contraction engine */
 enum { RPDE_PREC_FP32 = 0, RPDE_PREC_3XTF32 = 1, RPDE_PREC_TF32 = 2 };
 
@@ -54,7 +55,8 @@ unsigned long long rpde_tc_launch_count(void);
  * Replaces the cuFFT/pocketfft plans behind torch.fft.rfft/irfft/rfft2/irfft2
  * (models/spectral_convolution.py:41,54,82,97,165,198,265,284,289,308).
  *   kind 0: out[k][2][n]   analysis, scale s          kind 1: out[n][k][2]   synthesis (c_k weights), scale s
- *   kind 2: out[j][2][2][n] C2C analysis of rows [0,m1) U [n-m1,n)   kind 3: out[n][2][j][2] its inverse  */
+ *   kind 2: out[j][2][2][n] C2C analysis of rows [0,m1) U [n-m1,n)   kind 3: out[n][2][j][2] its inverse
+ *   kind 4: out[2][k][n]   the kind-1 coefficients as two planes (re, im) with unit stride along n  */
 int rpde_dft_table(float* out, int kind, int n, int k, int m1, double scale, rpde_stream_t stream);
 
 /* ---- FNO SpectralConv1d (models/spectral_convolution.py:24-55), channels-first (B,I,N) -> (B,O,N) --------
@@ -71,7 +73,7 @@ int rpde_spectral1d_bwd(const float* dy, const float* w, const float* fa, const 
                         size_t ws_bytes, rpde_stream_t stream);
 
 /* ---- FNO SpectralConv2d (models/spectral_convolution.py:61-98), (B,I,H,W) -> (B,O,H,W) ---------------------
- * w1, w2: complex64 (I,O,m1,m2).  fa_y/fs_y: kind 0/1 tables for axis W with k = m2 (scales 1, 1/W);
+ * w1, w2: complex64 (I,O,m1,m2).  fa_y/fs_y: kind 0/4 tables for axis W with k = m2 (scales 1, 1/W);
  * gf/gi: kind 2/3 tables for axis H with j = 2*m1 (scales 1, 1/H).  spec: (2*m1*m2*B*2I floats). */
 size_t rpde_spectral2d_workspace_bytes(int B, int I, int O, int H, int W, int m1, int m2);
 int rpde_spectral2d_fwd(const float* x, const float* w1, const float* w2, const float* fa_y, const float* fs_y,

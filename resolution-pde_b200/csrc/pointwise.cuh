@@ -16,7 +16,7 @@ namespace rpde {
 //         first block whose row index is overwritten by the second block (2*m1 > N) are zero.
 // ----------------------------------------------------------------------------------------------
 __global__ void dft_table_kernel(float* __restrict__ out, int kind, int N, int K, int m1, double s) {
-  const long long total = (kind <= 1) ? 2LL * K * N : 4LL * K * N;
+  const long long total = (kind <= 1 || kind == 4) ? 2LL * K * N : 4LL * K * N;
   for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total;
        e += (long long)gridDim.x * blockDim.x) {
     if (kind == 0) {
@@ -31,6 +31,17 @@ __global__ void dft_table_kernel(float* __restrict__ out, int kind, int N, int K
       const int ri = (int)(e & 1);
       const int k = (int)((e >> 1) % K);
       const int n = (int)(e / (2LL * K));
+      const long long r = ((long long)k * n) % N;
+      double sn, cs;
+      sincospi(2.0 * (double)r / (double)N, &sn, &cs);
+      const bool edge = (k == 0) || (2 * k == N);
+      const double c = edge ? 1.0 : 2.0;
+      out[e] = (float)(ri == 0 ? c * s * cs : (edge ? 0.0 : -c * s * sn));
+    } else if (kind == 4) {
+      // synthesis coefficients as kind 1, laid out [ri][k][n] (unit stride along n)
+      const int n = (int)(e % N);
+      const int k = (int)((e / N) % K);
+      const int ri = (int)(e / ((long long)K * N));
       const long long r = ((long long)k * n) % N;
       double sn, cs;
       sincospi(2.0 * (double)r / (double)N, &sn, &cs);

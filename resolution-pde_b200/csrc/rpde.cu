@@ -87,9 +87,9 @@ unsigned long long rpde_tc_launch_count(void) { return g_tc_launches.load(); }
 
 // ------------------------------------------------------------------------------------------------
 int rpde_dft_table(float* out, int kind, int n, int k, int m1, double scale, rpde_stream_t stream) {
-  if (!out || n <= 0 || k <= 0 || kind < 0 || kind > 3) return fail(RPDE_E_INVALID, "rpde_dft_table: bad arguments%s");
+  if (!out || n <= 0 || k <= 0 || kind < 0 || kind > 4) return fail(RPDE_E_INVALID, "rpde_dft_table: bad arguments%s");
   cudaStream_t s = (cudaStream_t)stream;
-  const long long total = (kind <= 1 ? 2LL : 4LL) * k * n;
+  const long long total = ((kind <= 1 || kind == 4) ? 2LL : 4LL) * k * n;
   dft_table_kernel<<<grid_for(total), 256, 0, s>>>(out, kind, n, k, m1, scale);
   RPDE_LAUNCH_CHECK();
   return RPDE_OK;
@@ -304,15 +304,23 @@ int rpde_spectral2d_fwd(const float* x, const float* w1, const float* w2, const 
   g.b = MatDesc{two(O, 2LL * O, 1), two(2, (long long)Ky * B * 2 * O, O), lin((long long)B * 2 * O)};
   g.c = MatDesc{lin(2 * HK), two(2, Ky, HK), lin(1)};
   RPDE_CUDA(gemm(g, s));
-  // 5. y-synthesis: y[(b,o,h)][w] = sum_(ri,ky) pl[(b,o)][ri][h][ky] fs_y[w][(ky,ri)]
-  g = gemm_default();
-  g.A = pl; g.B = fs_y; g.C = y;
-  g.M = B * O * H; g.N = W; g.K = 2 * Ky;
-  g.a = MatDesc{lin(0), two(H, 2 * HK, Ky), two(Ky, HK, 1)};
-  g.b = MatDesc{lin(0), two(Ky, 1, 2), lin(2 * Ky)};
-  g.c = MatDesc{lin(0), lin(W), lin(1)};
-  g.beta = beta; g.act = act; g.Z = z;
-  RPDE_CUDA(gemm(g, s));
+  // 5. y-synthesis: y[(b,o,h)][w] = sum_(ri,ky) pl[(b,o)][ri][h][ky] fs_y[ri][ky][w], one contraction per plane ri so
+  //    that both operands keep a single-level, unit-stride reduction index (TMA-addressable): the re plane writes
+  //    (on top of the bypass result when beta), the im plane accumulates and applies the activation.
+  for (int ri = 0; ri < 2; ++ri) {
+    g = gemm_default();
+    g.A = pl + (size_t)ri * HK; g.B = fs_y + (size_t)ri * Ky * W; g.C = y;
+    g.M = B * O * H; g.N = W; g.K = Ky;
+    g.a = MatDesc{lin(0), two(H, 2 * HK, Ky), lin(1)};
+    g.b = MatDesc{lin(0), lin(W), lin(1)};
+    g.c = MatDesc{lin(0), lin(W), lin(1)};
+    if (ri == 0) {
+      g.beta = beta;
+    } else {
+      g.beta = 1; g.act = act; g.Z = z;
+    }
+    RPDE_CUDA(gemm(g, s));
+  }
   return RPDE_OK;
 }
 
@@ -340,13 +348,13 @@ int rpde_spectral2d_bwd(const float* dy, const float* w1, const float* w2, const
   rc = pack_w(w2, wp + (size_t)m1 * Ky * 4 * I * O, I, O, m1 * m2, m1, m2, m2, s);
   if (rc) return rc;
   const long long HK = (long long)H * Ky;
-  // 5'. pl[(b,o)][ri][h][ky] = sum_w dy[(b,o,h)][w] fs_y[w][(ky,ri)]
+  // 5'. pl[(b,o)][ri][h][ky] = sum_w dy[(b,o,h)][w] fs_y[ri][ky][w]      (columns n = ri*Ky + ky)
   GemmP g = gemm_default();
   g.A = dy; g.B = fs_y; g.C = pl;
   g.M = B * O * H; g.N = 2 * Ky; g.K = W;
   g.a = MatDesc{lin(0), lin(W), lin(1)};
-  g.b = MatDesc{lin(0), lin(2 * Ky), lin(1)};
-  g.c = MatDesc{lin(0), two(H, 2 * HK, Ky), two(2, 1, HK)};
+  g.b = MatDesc{lin(0), lin(1), lin(W)};
+  g.c = MatDesc{lin(0), two(H, 2 * HK, Ky), two(Ky, HK, 1)};
   RPDE_CUDA(gemm(g, s));
   // 4'. dom[j][ky][b][ri][o] = sum_(ro,h) gi[(h,ro)][(j,ri)] pl[(b,o)][ro][h][ky]
   g = gemm_default();
@@ -386,15 +394,17 @@ int rpde_spectral2d_bwd(const float* dy, const float* w1, const float* w2, const
     g.b = MatDesc{two(I, 2LL * I, 1), two(2, (long long)Ky * B * 2 * I, I), lin((long long)B * 2 * I)};
     g.c = MatDesc{lin(2 * HK), lin(Ky), lin(1)};
     RPDE_CUDA(gemm(g, s));
-    // 1'. dx[(b,i,h)][w] (+)= sum_(ri,ky) pl[(b,i)][ri][h][ky] fa_y[(ky,ri)][w]
-    g = gemm_default();
-    g.A = pl; g.B = fa_y; g.C = dx;
-    g.M = B * I * H; g.N = W; g.K = 2 * Ky;
-    g.a = MatDesc{lin(0), two(H, 2 * HK, Ky), two(Ky, HK, 1)};
-    g.b = MatDesc{lin(0), two(Ky, W, 2LL * W), lin(1)};
-    g.c = MatDesc{lin(0), lin(W), lin(1)};
-    g.beta = dx_accumulate;
-    RPDE_CUDA(gemm(g, s));
+    // 1'. dx[(b,i,h)][w] (+)= sum_(ri,ky) pl[(b,i)][ri][h][ky] fa_y[(ky,ri)][w], one contraction per plane ri
+    for (int ri = 0; ri < 2; ++ri) {
+      g = gemm_default();
+      g.A = pl + (size_t)ri * HK; g.B = fa_y + (size_t)ri * W; g.C = dx;
+      g.M = B * I * H; g.N = W; g.K = Ky;
+      g.a = MatDesc{lin(0), two(H, 2 * HK, Ky), lin(1)};
+      g.b = MatDesc{lin(0), lin(2LL * W), lin(1)};
+      g.c = MatDesc{lin(0), lin(W), lin(1)};
+      g.beta = ri == 0 ? dx_accumulate : 1;
+      RPDE_CUDA(gemm(g, s));
+    }
   }
   return RPDE_OK;
 }

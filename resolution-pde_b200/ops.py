@@ -102,7 +102,7 @@ def dft_table(kind: int, n: int, k: int, m1: int, scale: float, device) -> torch
         with _tables_lock:
             t = _tables.get(key)
             if t is None:
-                t = torch.empty((2 if kind <= 1 else 4) * k * n, dtype=torch.float32, device=device)
+                t = torch.empty((2 if kind in (0, 1, 4) else 4) * k * n, dtype=torch.float32, device=device)
                 with _Ctx(t) as c:
                     _lib.check(c.lib.rpde_dft_table(_p(t), kind, n, k, m1, float(scale), c.stream), "rpde_dft_table")
                 _tables[key] = t
@@ -147,7 +147,7 @@ def _spectral_tables(ndim, shape, modes, device):
         return (dft_table(0, n, k, 0, 1.0, device), dft_table(1, n, k, 0, 1.0 / n, device))
     h, w = shape
     m1, m2 = modes
-    return (dft_table(0, w, m2, 0, 1.0, device), dft_table(1, w, m2, 0, 1.0 / w, device),
+    return (dft_table(0, w, m2, 0, 1.0, device), dft_table(4, w, m2, 0, 1.0 / w, device),
             dft_table(2, h, 2 * m1, m1, 1.0, device), dft_table(3, h, 2 * m1, m1, 1.0 / h, device))
 
 
