@@ -288,20 +288,22 @@ int rpde_spectral2d_fwd(const float* x, const float* w1, const float* w2, const 
   g.b = MatDesc{lin(2 * HK), lin(Ky), lin(1)};
   g.c = MatDesc{two(I, 2LL * I, 1), two(2, (long long)Ky * B * 2 * I, I), lin((long long)B * 2 * I)};
   RPDE_CUDA(gemm(g, s));
-  // 3. mixing per retained mode
+  // 3. mixing per retained mode, written as om[b][o][j][ri][ky]: the x-synthesis then reads a [(j,ri)][ky] matrix per
+  //    (b,o) with single-level strides (TMA-addressable); the scattered store here touches only J*Ky*B*2O floats
+  const long long JK2 = 2LL * J * Ky;
   g = gemm_default();
   g.A = spec; g.B = wp; g.C = om;
   g.batch = J * Ky; g.M = B; g.N = 2 * O; g.K = 2 * I;
   g.a = MatDesc{lin((long long)B * 2 * I), lin(2 * I), lin(1)};
   g.b = MatDesc{lin(4LL * I * O), lin(2 * O), lin(1)};
-  g.c = MatDesc{lin((long long)B * 2 * O), lin(2 * O), lin(1)};
+  g.c = MatDesc{two(Ky, 2LL * Ky, 1), lin((long long)O * JK2), two(O, Ky, JK2)};
   RPDE_CUDA(gemm(g, s));
-  // 4. x-synthesis: pl[(b,o)][ro][h][ky] = sum_(j,ri) gi[(h,ro)][(j,ri)] om[j][ky][b][ri][o]
+  // 4. x-synthesis: pl[(b,o)][ro][h][ky] = sum_(j,ri) gi[(h,ro)][(j,ri)] om[(b,o)][(j,ri)][ky]
   g = gemm_default();
   g.A = gi; g.B = om; g.C = pl;
   g.batch = B * O; g.M = 2 * H; g.N = Ky; g.K = 2 * J;
   g.a = MatDesc{lin(0), lin(2 * J), lin(1)};
-  g.b = MatDesc{two(O, 2LL * O, 1), two(2, (long long)Ky * B * 2 * O, O), lin((long long)B * 2 * O)};
+  g.b = MatDesc{lin(JK2), lin(Ky), lin(1)};
   g.c = MatDesc{lin(2 * HK), two(2, Ky, HK), lin(1)};
   RPDE_CUDA(gemm(g, s));
   // 5. y-synthesis: y[(b,o,h)][w] = sum_(ri,ky) pl[(b,o)][ri][h][ky] fs_y[ri][ky][w], one contraction per plane ri so
@@ -378,20 +380,21 @@ int rpde_spectral2d_bwd(const float* dy, const float* w1, const float* w2, const
     if (dw2) { rc = unpack_g(P + (size_t)m1 * Ky * 4 * I * O, dw2, I, O, m1 * m2, m1, m2, m2, 0, s); if (rc) return rc; }
   }
   if (dx) {
-    // 3'. dsp[mode] = dom[mode] wp[mode]^T
+    // 3'. dsp[mode] = dom[mode] wp[mode]^T, written as dsp[b][i][j][ro][ky] (see step 3 of the forward pass)
+    const long long JK2 = 2LL * J * Ky;
     g = gemm_default();
     g.A = dom; g.B = wp; g.C = dsp;
     g.batch = J * Ky; g.M = B; g.N = 2 * I; g.K = 2 * O;
     g.a = MatDesc{lin((long long)B * 2 * O), lin(2 * O), lin(1)};
     g.b = MatDesc{lin(4LL * I * O), lin(1), lin(2 * O)};
-    g.c = MatDesc{lin((long long)B * 2 * I), lin(2 * I), lin(1)};
+    g.c = MatDesc{two(Ky, 2LL * Ky, 1), lin((long long)I * JK2), two(I, Ky, JK2)};
     RPDE_CUDA(gemm(g, s));
-    // 2'. pl[(b,i)][ri][h][ky] = sum_(j,ro) gf[(j,ro)][(ri,h)] dsp[j][ky][b][ro][i]
+    // 2'. pl[(b,i)][ri][h][ky] = sum_(j,ro) gf[(j,ro)][(ri,h)] dsp[(b,i)][(j,ro)][ky]
     g = gemm_default();
     g.A = gf; g.B = dsp; g.C = pl;
     g.batch = B * I; g.M = 2 * H; g.N = Ky; g.K = 2 * J;
     g.a = MatDesc{lin(0), lin(1), lin(2 * H)};
-    g.b = MatDesc{two(I, 2LL * I, 1), two(2, (long long)Ky * B * 2 * I, I), lin((long long)B * 2 * I)};
+    g.b = MatDesc{lin(JK2), lin(Ky), lin(1)};
     g.c = MatDesc{lin(2 * HK), lin(Ky), lin(1)};
     RPDE_CUDA(gemm(g, s));
     // 1'. dx[(b,i,h)][w] (+)= sum_(ri,ky) pl[(b,i)][ri][h][ky] fa_y[(ky,ri)][w], one contraction per plane ri
