@@ -8,7 +8,7 @@
 //   TF32   : one pass on the raw fp32 bits (~5e-4 relative), the fast variant with its own stated tolerance.
 //
 // One persistent CTA per SM, warp-specialised:
-//   warp 0      TMA producer (one lane): fills a ring of {A,B} stages, full[s] <- complete_tx
+//   warp 0, 14  TMA producers (one lane each: A tiles / B tiles) filling a ring of raw fp32 stages, full[s] <- complete_tx
 //   warp 1      UMMA issuer (one lane) + TMEM owner: 4 (x3) tcgen05.mma per stage, commit -> empty[s]; last -> acc_full
 //   warps 2-5   splitter (3xTF32 only): lo = x - tf32(x) of the landed tiles into a two-deep lo ring, fence.proxy.async,
 //               one arrival per warp -> ready[s]
@@ -73,7 +73,8 @@ namespace tc {
 constexpr int BM = 128, BK = 32;
 constexpr int A_TILE_BYTES = BM * BK * 4;
 constexpr int kEpiWarps = 8;                         // two warps per TMEM lane quadrant, each owning half of the tile's columns
-constexpr int kThreads = 32 * (6 + kEpiWarps);
+constexpr int kProducerBWarp = 6 + kEpiWarps;         // second TMA producer (B operand) behind the epilogue warps
+constexpr int kThreads = 32 * (7 + kEpiWarps);
 constexpr int kEpiBytes = kEpiWarps * 4096;          // one 128B-swizzled 32x32 fp32 staging box per epilogue warp
 constexpr int kSmemBudget = 227 * 1024 - 2048 - kEpiBytes;
 
@@ -254,7 +255,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
     tma_prefetch_desc(&mapB);
     if (P.epi_tma) tma_prefetch_desc(&mapC);
     for (int s = 0; s < S; ++s) {
-      mbar_init(full(s), 1);
+      mbar_init(full(s), 2);  // one arrive.expect_tx per producer
       mbar_init(ready(s), 4);
       mbar_init(empty(s), 1);
     }
@@ -273,22 +274,29 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
-  if (warp == 0) {
-    // ------------------------------------------------------------------ TMA producer
-    // One thread feeds the whole tensor core: the k loop is kept to a handful of integer multiply-adds (coordinates
-    // advance as base + k0*e0 + k1*e1 with 0/1 masks chosen once per kernel; ring slot and phase are carried).
+  if (warp == 0 || warp == kProducerBWarp) {
+    // ------------------------------------------------------------------ TMA producers: warp 0 loads the A tiles, the last
+    // warp the B tiles (issuing one bulk tensor load costs a thread ~200 cycles; two threads keep the ring ahead of the
+    // tensor core).  The k loop is a handful of integer multiply-adds: coordinates advance as base + k0*e0 + k1*e1 with
+    // 0/1 masks chosen once per kernel; ring slot and phase are carried.
     if (lane == 0) {
-      const int a_kd = P.a.k_d, b_kd = P.b.k_d;
-      int ea0[5], ea1[5], eb0[5], eb1[5];
+      const bool isA = warp == 0;
+      const TcOpnd& o = isA ? P.a : P.b;
+      const CUtensorMap* map = isA ? &mapA : &mapB;
+      const int kd = o.k_d, nd = o.ndim;
+      const int tile_mn = isA ? BM : BN;
+      const uint32_t bytes = isA ? (uint32_t)A_TILE_BYTES : (uint32_t)C::b_tile;
+      const uint32_t dst_off = isA ? 0u : (uint32_t)A_TILE_BYTES;
+      int e0[5], e1[5];
 #pragma unroll
       for (int j = 0; j < 5; ++j) {
-        ea0[j] = (j == P.a.dk0) ? 1 : 0;
-        ea1[j] = (a_kd != INT_MAX && j == P.a.dk1) ? 1 : 0;
-        eb0[j] = (j == P.b.dk0) ? 1 : 0;
-        eb1[j] = (b_kd != INT_MAX && j == P.b.dk1) ? 1 : 0;
+        e0[j] = (j == o.dk0) ? 1 : 0;
+        e1[j] = (kd != INT_MAX && j == o.dk1) ? 1 : 0;
       }
-      const bool simple = P.a.boxes == 1 && P.b.boxes == 1;
-      const int a_nd = P.a.ndim, b_nd = P.b.ndim;
+      const bool simple = o.boxes == 1;
+      // the B producer also pulls the NEXT tile's A boxes into L2 (bit 0 of l2_prefetch), one box per k-block
+      const bool pf = !isA && (P.l2_prefetch & 1) && P.a.boxes == 1;
+      const int a_kd = P.a.k_d;
       int s = 0;
       uint32_t ph = 0;
       TCP_DECL(pw = 0, pi = 0, pall = clock64(), pn = 0);
@@ -297,20 +305,31 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
         tile_coords(P, t, tm, tn, z);
         const int sk = z % p.splitk, bz = z / p.splitk;
         const int kb0 = sk * P.kchunk_blocks, kb1 = min(P.kblocks, kb0 + P.kchunk_blocks);
-        int ca[5], cb[5];
-        opnd_coords(P.a, tm * BM, bz, ca);
-        opnd_coords(P.b, tn * BN, bz, cb);
+        const int mn0 = (isA ? tm : tn) * tile_mn;
+        int cbase[5];
+        opnd_coords(o, mn0, bz, cbase);
         const int k_start = kb0 * BK;
-        int ka0 = (a_kd == INT_MAX) ? k_start : k_start % a_kd, ka1 = (a_kd == INT_MAX) ? 0 : k_start / a_kd;
-        int kb0_ = (b_kd == INT_MAX) ? k_start : k_start % b_kd, kb1_ = (b_kd == INT_MAX) ? 0 : k_start / b_kd;
+        int k0 = (kd == INT_MAX) ? k_start : k_start % kd, k1 = (kd == INT_MAX) ? 0 : k_start / kd;
+        // next tile (prefetch target)
+        int pbase[5], pk0 = 0, pk1 = 0, pkn = 0;
+        bool pf_on = false;
+        if (pf && t + (int)gridDim.x < P.total_tiles) {
+          int tm2, tn2, z2;
+          tile_coords(P, t + gridDim.x, tm2, tn2, z2);
+          const int sk2 = z2 % p.splitk, bz2 = z2 / p.splitk;
+          const int q0 = sk2 * P.kchunk_blocks;
+          pkn = min(P.kblocks, q0 + P.kchunk_blocks) - q0;
+          pf_on = (tm2 != tm || bz2 != bz || sk2 != sk);
+          opnd_coords(P.a, tm2 * BM, bz2, pbase);
+          const int ks = q0 * BK;
+          pk0 = (a_kd == INT_MAX) ? ks : ks % a_kd;
+          pk1 = (a_kd == INT_MAX) ? 0 : ks / a_kd;
+        }
         for (int kb = kb0; kb < kb1; ++kb) {
-          int xa[5], xb[5];
+          int x[5];
 #pragma unroll
-          for (int j = 0; j < 5; ++j) {
-            xa[j] = ca[j] + ka0 * ea0[j] + ka1 * ea1[j];
-            xb[j] = cb[j] + kb0_ * eb0[j] + kb1_ * eb1[j];
-          }
-          const uint32_t fb = full(s), dst = a_hi(s);
+          for (int j = 0; j < 5; ++j) x[j] = cbase[j] + k0 * e0[j] + k1 * e1[j];
+          const uint32_t fb = full(s), dst = a_hi(s) + dst_off;
           TCP_T0(q0);
           mbar_wait(empty(s), ph ^ 1);
           TCP_ADD(pw, q0);
@@ -318,28 +337,30 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
           if (P.skip & 8) {
             mbar_arrive(fb);
           } else {
-            mbar_arrive_expect_tx(fb, A_TILE_BYTES + C::b_tile);
-            if (simple) {
-              tma_load(dst, &mapA, fb, a_nd, xa);
-              tma_load(dst + A_TILE_BYTES, &mapB, fb, b_nd, xb);
-            } else {
-              opnd_load(P.a, &mapA, dst, fb, xa, tm * BM);
-              opnd_load(P.b, &mapB, dst + A_TILE_BYTES, fb, xb, tn * BN);
-            }
+            mbar_arrive_expect_tx(fb, bytes);
+            if (simple) tma_load(dst, map, fb, nd, x);
+            else opnd_load(o, map, dst, fb, x, mn0);
+          }
+          if (pf_on && kb - kb0 < pkn) {
+            int y[5];
+#pragma unroll
+            for (int j = 0; j < 5; ++j)
+              y[j] = pbase[j] + ((j == P.a.dk0) ? pk0 : 0) + ((a_kd != INT_MAX && j == P.a.dk1) ? pk1 : 0);
+            tma_prefetch_l2(&mapA, P.a.ndim, y);
+            pk0 += BK;
+            if (pk0 >= a_kd) { pk0 = 0; ++pk1; }
           }
           TCP_ADD(pi, q1);
 #ifdef RPDE_TC_PROFILE
           ++pn;
 #endif
-          ka0 += BK;
-          if (ka0 >= a_kd) { ka0 = 0; ++ka1; }
-          kb0_ += BK;
-          if (kb0_ >= b_kd) { kb0_ = 0; ++kb1_; }
+          k0 += BK;
+          if (k0 >= kd) { k0 = 0; ++k1; }
           if (++s == S) { s = 0; ph ^= 1; }
         }
       }
 #ifdef RPDE_TC_PROFILE
-      if (blockIdx.x == 0) printf("[tc producer] iters %lld total %lld wait_empty %lld issue %lld\n", pn, clock64() - pall, pw, pi);
+      if (blockIdx.x == 0) printf("[tc producer %c] iters %lld total %lld wait_empty %lld issue %lld\n", isA ? 'A' : 'B', pn, clock64() - pall, pw, pi);
 #endif
     }
   } else if (warp == 1) {
@@ -443,7 +464,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
         }
       }
     }
-  } else {
+  } else if (warp < kProducerBWarp) {
     // ------------------------------------------------------------------ epilogue: warps 6..13.  A warp may only touch the
     // TMEM lane quadrant (warp % 4); the two warps of a quadrant split the tile's columns in halves.
     const int ew = warp - 6;

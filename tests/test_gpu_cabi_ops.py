@@ -1,0 +1,119 @@
+"""GPU tests of individual C-ABI entry points (include/rpde_b200.h) against plain torch fp64 references of the same op:
+fused FeedForward epilogues (stored gelu', fused bias gradients), few-channel streaming Linear kernels, LayerNorm
+backward column sums, DFT table layouts.  Tolerances: 1e-5 relative L2 (fp32 / 3xTF32 engines)."""
+import ctypes
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+TOL = 1e-5
+
+
+def rel(a, b):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return ((a - b).norm() / b.norm().clamp_min(1e-30)).item()
+
+
+@pytest.fixture(params=["fp32", "3xtf32"])
+def lib(request):
+    import resolution_pde_b200 as R
+    R.set_precision(request.param)
+    R.ops.matmul(torch.randn(8, 8, device=DEV), torch.randn(8, 8, device=DEV))  # pushes the engine choice to the C side
+    yield R._lib.load()
+    R.set_precision("fp32")
+    R.ops.matmul(torch.randn(8, 8, device=DEV), torch.randn(8, 8, device=DEV))
+
+
+def _st():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _gelu_grad(z):
+    return 0.5 * (1 + torch.erf(z / math.sqrt(2))) + z * torch.exp(-0.5 * z * z) / math.sqrt(2 * math.pi)
+
+
+@pytest.mark.parametrize("T,i,o", [(4096, 64, 256), (1000, 32, 96), (8192, 256, 64)])
+def test_linear_fwd_saves_gelu_grad(lib, T, i, o):
+    torch.manual_seed(T + i)
+    x = torch.randn(T, i, device=DEV)
+    w = torch.randn(o, i, device=DEV) / math.sqrt(i)
+    b = torch.randn(o, device=DEV)
+    y = torch.empty(T, o, device=DEV)
+    g = torch.empty(T, o, device=DEV)
+    rc = lib.rpde_linear_fwd(x.data_ptr(), w.data_ptr(), b.data_ptr(), y.data_ptr(), g.data_ptr(), T, i, o, 0x101, 0, _st())
+    assert rc == 0, lib.rpde_last_error()
+    z = x.double() @ w.double().T + b.double()
+    assert rel(y, torch.nn.functional.gelu(z)) < TOL
+    assert rel(g, _gelu_grad(z)) < TOL
+
+
+@pytest.mark.parametrize("T,i,o", [(4096, 256, 64), (3000, 96, 32), (8192, 256, 256)])
+def test_linear_bwd_input_saved_factor_and_bias_grad(lib, T, i, o):
+    torch.manual_seed(T + o)
+    dy = torch.randn(T, o, device=DEV)
+    w = torch.randn(o, i, device=DEV) / math.sqrt(o)
+    f = torch.rand(T, i, device=DEV) + 0.1            # stored act'(z) of the producing layer
+    dx = torch.empty(T, i, device=DEV)
+    db = torch.full((i,), 7.0, device=DEV)            # must be overwritten
+    rc = lib.rpde_linear_bwd_input(dy.data_ptr(), w.data_ptr(), f.data_ptr(), 3, dx.data_ptr(), 0, db.data_ptr(), T, i, o, 0, _st())
+    assert rc == 0, lib.rpde_last_error()
+    ref = (dy.double() @ w.double()) * f.double()
+    assert rel(dx, ref) < TOL
+    assert rel(db, ref.sum(0)) < TOL
+
+
+@pytest.mark.parametrize("cin", [1, 2, 3, 4])
+def test_few_channel_linear_streaming_kernels(lib, cin):
+    T, o = 5000, 64
+    torch.manual_seed(cin)
+    x = torch.randn(T, cin, device=DEV)
+    w = torch.randn(o, cin, device=DEV)
+    b = torch.randn(o, device=DEV)
+    y = torch.empty(T, o, device=DEV)
+    assert lib.rpde_linear_fwd(x.data_ptr(), w.data_ptr(), b.data_ptr(), y.data_ptr(), None, T, cin, o, 0, 0, _st()) == 0
+    assert rel(y, x.double() @ w.double().T + b.double()) < TOL
+    dy = torch.randn(T, o, device=DEV)
+    dw = torch.empty(o, cin, device=DEV)
+    dbv = torch.empty(o, device=DEV)
+    assert lib.rpde_linear_bwd_params(dy.data_ptr(), x.data_ptr(), dw.data_ptr(), dbv.data_ptr(), T, cin, o, 0, _st()) == 0
+    assert rel(dw, dy.double().T @ x.double()) < TOL
+    assert rel(dbv, dy.double().sum(0)) < TOL
+
+
+def test_layernorm_bwd_column_sums(lib):
+    T, C = 3000, 64
+    torch.manual_seed(5)
+    x = torch.randn(T, C, device=DEV, dtype=torch.float64, requires_grad=True)
+    gamma = torch.randn(C, device=DEV, dtype=torch.float64, requires_grad=True)
+    beta = torch.randn(C, device=DEV, dtype=torch.float64, requires_grad=True)
+    dy = torch.randn(T, C, device=DEV, dtype=torch.float64)
+    torch.nn.functional.layer_norm(x, (C,), gamma, beta, 1e-5).backward(dy)
+    xf, gf, dyf = x.detach().float(), gamma.detach().float(), dy.float()
+    mean = xf.mean(1).contiguous()
+    rstd = (1.0 / torch.sqrt(xf.double().var(1, unbiased=False) + 1e-5)).float().contiguous()
+    dx = torch.empty(T, C, device=DEV)
+    dg, dbt, dxs = (torch.empty(C, device=DEV) for _ in range(3))
+    rc = lib.rpde_layernorm_bwd(dyf.data_ptr(), xf.data_ptr(), gf.data_ptr(), mean.data_ptr(), rstd.data_ptr(), dx.data_ptr(),
+                                dg.data_ptr(), dbt.data_ptr(), dxs.data_ptr(), T, C, _st())
+    assert rc == 0, lib.rpde_last_error()
+    assert rel(dx, x.grad) < TOL and rel(dg, gamma.grad) < TOL and rel(dbt, beta.grad) < TOL
+    assert rel(dxs, x.grad.sum(0)) < 1e-4            # a sum of T cancelling terms: absolute accuracy, looser relative bound
+
+
+@pytest.mark.parametrize("n,k", [(64, 12), (33, 7), (256, 129)])
+def test_dft_table_planes_match_interleaved(n, k):
+    import resolution_pde_b200 as R
+    t1 = R.ops.dft_table(1, n, k, 0, 1.0 / n, DEV).reshape(n, k, 2)
+    t4 = R.ops.dft_table(4, n, k, 0, 1.0 / n, DEV).reshape(2, k, n)
+    assert torch.equal(t4, t1.permute(2, 1, 0).contiguous())
+    # synthesis table reproduces irfft of a truncated spectrum
+    torch.manual_seed(n)
+    spec = torch.randn(k, dtype=torch.complex128)
+    full = torch.zeros(n // 2 + 1, dtype=torch.complex128)
+    full[:k] = spec
+    want = torch.fft.irfft(full, n=n)
+    got = t4[0].double().cpu().T @ spec.real + t4[1].double().cpu().T @ spec.imag
+    assert rel(got, want) < 1e-6
