@@ -83,15 +83,22 @@ struct Cfg {
   static constexpr int b_tile = BN * BK * 4;
   // The TMA ring holds raw fp32 tiles only.  3xTF32: the lo tiles live in a separate two-deep ring that is occupied just
   // from the split until the UMMAs that read it retire, so the bytes in flight behind the tensor core are not halved.
+  // 3xTF32 feeds A from TMEM (hi and lo written there by the splitter warps), so only B_lo needs shared memory.
   static constexpr int stage_bytes = A_TILE_BYTES + b_tile;
   static constexpr int lo_bufs = SPLIT ? 2 : 0;
-  static constexpr int lo_bytes = lo_bufs * stage_bytes;
+  static constexpr int lo_bytes = lo_bufs * b_tile;
   static constexpr int raw = (kSmemBudget - lo_bytes) / stage_bytes;
   static constexpr int stages = raw > 6 ? 6 : raw;
   static constexpr int smem_bytes = stages * stage_bytes + lo_bytes + kEpiBytes + 2048;  // + alignment slack + barriers
-  static constexpr int acc_cols = SPLIT ? 2 * BN : BN;  // 3xTF32: [hi*hi | hi*lo + lo*hi] accumulated side by side
-  static constexpr int tmem_cols = 2 * acc_cols < 32 ? 32 : 2 * acc_cols;
-  static_assert(tmem_cols <= 512, "TMEM holds 512 columns");
+  // TMEM columns.  TF32: two accumulators [acc0 | acc1].  3xTF32: [big0 | big1 | small | A ring: 2 x (hi 32 | lo 32)]:
+  // hi*hi accumulates in big (double-buffered across tiles), hi*lo + lo*hi in small (single: the epilogue folds it into
+  // big first thing and hands it back), and the A operand of the next two k-blocks lives in the ring.
+  static constexpr int acc_cols = BN;
+  static constexpr int small_col = 2 * BN;
+  static constexpr int aring_col = 3 * BN;
+  static constexpr int need_cols = SPLIT ? 3 * BN + 128 : 2 * BN;
+  static constexpr int tmem_cols = need_cols <= 32 ? 32 : need_cols <= 64 ? 64 : need_cols <= 128 ? 128 : need_cols <= 256 ? 256 : 512;
+  static_assert(need_cols <= 512, "TMEM holds 512 columns");
 };
 
 // Coordinates live in registers: slots are written with compare-selects, never with dynamic indexing (which would
@@ -217,6 +224,41 @@ __device__ __forceinline__ void prep_region(uint32_t hi0, uint32_t lo0, int n16,
   }
 }
 
+// 3xTF32, A operand: thread (quad, lane) owns row quad*32 + lane of the landed 128 x 32 tile.  It gathers the row from the
+// swizzled stage (K-major: 8 x 16 B chunks, chunk c at c ^ (row & 7); MN-major: 32 words, one per k, the 32-byte chunk
+// (lane / 8) ^ (k & 3) of row k inside group quad), applies the optional activation, and writes tf32(x) and x - tf32(x)
+// into the TMEM ring slot (lane = row, 32 + 32 columns).  The UMMAs then fetch A from TMEM, B from shared memory.
+__device__ __forceinline__ void prep_a_tmem(uint32_t a_smem, uint32_t taddr, int quad, int lane, int mn_major, int act) {
+  float x[32];
+  if (!mn_major) {
+    const uint32_t row = a_smem + (uint32_t)(quad * 32 + lane) * 128u, sw = lane & 7;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      const float4 v = lds128(row + ((c ^ sw) << 4));
+      x[4 * c] = v.x; x[4 * c + 1] = v.y; x[4 * c + 2] = v.z; x[4 * c + 3] = v.w;
+    }
+  } else {
+    const uint32_t base = a_smem + (uint32_t)quad * 4096u + (((uint32_t)lane & 7u) << 2), hi3 = (uint32_t)lane >> 3;
+#pragma unroll
+    for (int k = 0; k < 32; ++k)
+      asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x[k]) : "r"(base + k * 128u + ((hi3 ^ (k & 3u)) << 5)));
+  }
+  if (act) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) x[j] = act_f(act, x[j]);
+  }
+  uint32_t hi[32], lo[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    const float h = tf32_trunc(x[j]);
+    hi[j] = __float_as_uint(h);
+    lo[j] = __float_as_uint(x[j] - h);
+  }
+  tmem_st32(taddr, hi);
+  tmem_st32(taddr + 32, lo);
+  tmem_st_wait();
+}
+
 // CH = true: a tile's K range is cut into chunks of P.kc k-blocks, each accumulated in TMEM from zero and then added
 // (round-to-nearest) into fp32 registers of the epilogue warps.  The tensor core truncates its accumulator after
 // every UMMA, so the chain length bounds the rounding bias (measured 2.2e-8 relative per UMMA).
@@ -233,8 +275,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
   auto a_hi = [&](int s) { return smem_base + s * C::stage_bytes; };
   auto b_hi = [&](int s) { return smem_base + s * C::stage_bytes + A_TILE_BYTES; };
   const uint32_t lo_base = smem_base + S * C::stage_bytes;
-  auto a_lo = [&](int l) { return lo_base + l * C::stage_bytes; };
-  auto b_lo = [&](int l) { return lo_base + l * C::stage_bytes + A_TILE_BYTES; };
+  auto b_lo = [&](int l) { return lo_base + l * C::b_tile; };
   const uint32_t epi_base = lo_base + C::lo_bytes;  // 1024-aligned: the staging boxes use the TMA 128B swizzle
   const uint32_t bar_base = epi_base + kEpiBytes;
   auto full = [&](int s) { return bar_base + 8 * s; };
@@ -244,7 +285,8 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
   auto acc_empty = [&](int a) { return bar_base + 8 * (3 * S + 2 + a); };
   auto epi_in = [&](int w) { return bar_base + 8 * (3 * S + 4 + w); };
   auto lo_empty = [&](int l) { return bar_base + 8 * (3 * S + 4 + kEpiWarps + l); };
-  const uint32_t tmem_slot = bar_base + 8 * (3 * S + 4 + kEpiWarps + 2);
+  const uint32_t small_empty = bar_base + 8 * (3 * S + 4 + kEpiWarps + 2);
+  const uint32_t tmem_slot = bar_base + 8 * (3 * S + 4 + kEpiWarps + 3);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const GemmP& p = P.g;
@@ -265,6 +307,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
     }
     for (int w = 0; w < kEpiWarps; ++w) mbar_init(epi_in(w), 1);
     for (int l = 0; l < 2; ++l) mbar_init(lo_empty(l), 1);
+    mbar_init(small_empty, kEpiWarps);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, C::tmem_cols);
@@ -367,6 +410,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
     // ------------------------------------------------------------------ UMMA issuer
     if (lane == 0) {
       const uint32_t idesc = umma_idesc_tf32(BM, BN, P.a.major, P.b.major);
+      const uint32_t idesc_ts = umma_idesc_tf32(BM, BN, 0, P.b.major);  // A from TMEM is never transposed
       const uint32_t a_step = (P.a.major ? 1024u : 32u) >> 4, b_step = (P.b.major ? 1024u : 32u) >> 4;
       const uint32_t a_lbo = P.a.major ? BK * 128u : 16u, b_lbo = P.b.major ? BK * 128u : 16u;
       const uint32_t a_sbo = P.a.major ? 512u : 1024u, b_sbo = P.b.major ? 512u : 1024u;
@@ -387,9 +431,11 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
           const int buf = cit & 1;
           TCP_T0(r0);
           mbar_wait(acc_empty(buf), ((cit >> 1) & 1) ^ 1);
+          if (SPLIT) mbar_wait(small_empty, (cit & 1) ^ 1);  // the epilogue has folded the previous chain's small block
           TCP_ADD(ma, r0);
           tc_fence_after_sync();
           const uint32_t d = tmem_base + buf * C::acc_cols;
+          const uint32_t dsm = tmem_base + C::small_col;
           for (int kb = c0; kb < c1; ++kb) {
             TCP_T0(r1);
             mbar_wait(use_prep ? ready(s) : full(s), ph);
@@ -397,7 +443,8 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
             TCP_T0(r2);
             tc_fence_after_sync();
             const uint64_t ah0 = dA + (a_hi(s) >> 4), bh0 = dB + (b_hi(s) >> 4);
-            const uint64_t al0 = dA + (a_lo(l) >> 4), bl0 = dB + (b_lo(l) >> 4);
+            const uint64_t bl0 = dB + (b_lo(l) >> 4);
+            const uint32_t at = tmem_base + C::aring_col + l * 64;  // A of this k-block in TMEM: [hi 32 cols | lo 32 cols]
             if (!(P.skip & 4)) {
 #pragma unroll
               for (int k4 = 0; k4 < BK / 8; ++k4) {
@@ -405,10 +452,10 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
                 const uint64_t ah = ah0 + k4 * a_step, bh = bh0 + k4 * b_step;
                 if (SPLIT) {
                   // big (+)= A_hi B_hi ; small (+)= A_hi B_lo + A_lo B_hi.  The large products meet one accumulator
-                  // truncation per k-step; the 2^-11 corrections live in their own TMEM columns.
-                  umma_tf32(d, ah, bh, idesc, acc);
-                  umma_tf32(d + BN, ah, bl0 + k4 * b_step, idesc, acc);
-                  umma_tf32(d + BN, al0 + k4 * a_step, bh, idesc, 1u);
+                  // truncation per k-step; the 2^-11 corrections live in their own TMEM columns.  A comes from TMEM.
+                  umma_tf32_ts(d, at + k4 * 8, bh, idesc_ts, acc);
+                  umma_tf32_ts(dsm, at + k4 * 8, bl0 + k4 * b_step, idesc_ts, acc);
+                  umma_tf32_ts(dsm, at + 32 + k4 * 8, bh, idesc_ts, 1u);
                 } else {
                   umma_tf32(d, ah, bh, idesc, acc);
                 }
@@ -450,9 +497,16 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
           mbar_wait(full(s), ph);
           if (SPLIT) mbar_wait(lo_empty(l), lph ^ 1);  // the UMMAs of two iterations ago have released lo buffer l
           if (!(P.skip & 2)) {
-            if (SPLIT || p.a_act) prep_region<SPLIT>(a_hi(s), a_lo(l), A_TILE_BYTES / 16, p.a_act, ct);
+            if (SPLIT) {
+              // A: this thread's row (TMEM lane = tile row) -> hi / lo -> TMEM ring slot l
+              const uint32_t at = tmem_base + C::aring_col + l * 64 + ((uint32_t)((warp & 3) * 32) << 16);
+              prep_a_tmem(a_hi(s), at, warp & 3, lane, P.a.major, p.a_act);
+            } else if (p.a_act) {
+              prep_region<false>(a_hi(s), 0, A_TILE_BYTES / 16, p.a_act, ct);
+            }
             if (SPLIT || p.b_act) prep_region<SPLIT>(b_hi(s), b_lo(l), C::b_tile / 16, p.b_act, ct);
           }
+          if (SPLIT) tc_fence_before_sync();
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) mbar_arrive(ready(s));  // one arrival per warp
@@ -707,6 +761,25 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
         const int buf = cit & 1;
         mbar_wait(acc_full(buf), (cit >> 1) & 1);
         tc_fence_after_sync();
+        const uint32_t tq = tmem_base + ((uint32_t)(quad * 32) << 16);
+        if (SPLIT) {
+          // fold the small block into big (in TMEM) and hand it back, so the next tile's main loop starts at once
+#pragma unroll 1
+          for (int ci = 0; ci < CPW; ++ci) {
+            const int cc = half * CPW + ci;
+            uint32_t r[32], r2[32];
+            tmem_ld32(tq + buf * C::acc_cols + cc * 32, r);
+            tmem_ld32(tq + C::small_col + cc * 32, r2);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r2[j]));
+            tmem_st32(tq + buf * C::acc_cols + cc * 32, r);
+          }
+          tmem_st_wait();
+          tc_fence_before_sync();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(small_empty);
+        }
 #pragma unroll 1
         for (int ci = 0; ci < CPW; ++ci) {
           const int cc = half * CPW + ci;
@@ -714,19 +787,10 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
           if (n0 >= p.N) break;  // warp-uniform
           uint32_t r[32];
           float v[32];
-          const uint32_t ta = tmem_base + ((uint32_t)(quad * 32) << 16) + buf * C::acc_cols + cc * 32;
-          tmem_ld32(ta, r);
-          if (SPLIT) {
-            uint32_t r2[32];
-            tmem_ld32(ta + BN, r2);
-            tmem_ld_wait();
+          tmem_ld32(tq + buf * C::acc_cols + cc * 32, r);
+          tmem_ld_wait();
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + __uint_as_float(r2[j]);
-          } else {
-            tmem_ld_wait();
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-          }
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
           emit(v, n0);
         }
         tc_fence_before_sync();
@@ -744,11 +808,12 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
 #pragma unroll
           for (int ci = 0; ci < CPW; ++ci) {
             uint32_t r[32];
-            const uint32_t ta = tmem_base + ((uint32_t)(quad * 32) << 16) + buf * C::acc_cols + (half * CPW + ci) * 32;
+            const uint32_t tq = tmem_base + ((uint32_t)(quad * 32) << 16);
+            const uint32_t ta = tq + buf * C::acc_cols + (half * CPW + ci) * 32;
             tmem_ld32(ta, r);
             if (SPLIT) {
               uint32_t r2[32];
-              tmem_ld32(ta + BN, r2);
+              tmem_ld32(tq + C::small_col + (half * CPW + ci) * 32, r2);
               tmem_ld_wait();
 #pragma unroll
               for (int j = 0; j < 32; ++j) acc[ci * 32 + j] += __uint_as_float(r[j]) + __uint_as_float(r2[j]);
@@ -760,7 +825,10 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
           }
           tc_fence_before_sync();
           __syncwarp();
-          if (lane == 0) mbar_arrive(acc_empty(buf));
+          if (lane == 0) {
+            mbar_arrive(acc_empty(buf));
+            if (SPLIT) mbar_arrive(small_empty);
+          }
         }
 #pragma unroll
         for (int ci = 0; ci < CPW; ++ci) {
