@@ -255,8 +255,7 @@ __device__ __forceinline__ void prep_a_tmem(uint32_t a_smem, uint32_t taddr, int
     lo[j] = __float_as_uint(x[j] - h);
   }
   tmem_st32(taddr, hi);
-  tmem_st32(taddr + 32, lo);
-  tmem_st_wait();
+  tmem_st32(taddr + 32, lo);  // the caller overlaps the B split with these stores and then waits (tmem_st_wait)
 }
 
 // CH = true: a tile's K range is cut into chunks of P.kc k-blocks, each accumulated in TMEM from zero and then added
@@ -505,6 +504,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
               prep_region<false>(a_hi(s), 0, A_TILE_BYTES / 16, p.a_act, ct);
             }
             if (SPLIT || p.b_act) prep_region<SPLIT>(b_hi(s), b_lo(l), C::b_tile / 16, p.b_act, ct);
+            if (SPLIT) tmem_st_wait();
           }
           if (SPLIT) tc_fence_before_sync();
           fence_proxy_async_smem();
@@ -1021,7 +1021,9 @@ static cudaError_t gemm_tc_try_launch(const GemmP& g, int prec, cudaStream_t s, 
   using namespace tc;
   *launched = false;
   if (g.M <= 0 || g.N <= 0 || g.K <= 0 || g.batch <= 0) return cudaSuccess;
-  if ((long long)g.M * g.N * g.K * g.batch < (1LL << 18)) return cudaSuccess;  // launch-bound: CUDA cores do as well
+  // launch-bound sizes: the CUDA-core kernel starts faster than a 231 KB-smem persistent CTA with a TMEM allocation
+  static const long long min_macs = getenv("RPDE_TC_MIN_MACS") ? atoll(getenv("RPDE_TC_MIN_MACS")) : (1LL << 18);
+  if ((long long)g.M * g.N * g.K * g.batch < min_macs) return cudaSuccess;
   TcParams P;
   P.g = g;
   {
