@@ -25,6 +25,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <mutex>
+#include <type_traits>
 
 #include "common.cuh"
 #include "gemm_simt.cuh"
@@ -49,11 +50,12 @@ struct TcParams {
   int epi_tma;      // 1: C / Z leave through bulk tensor stores from the staging boxes, aux / old C arrive the same way
   int epi_reduce;   // 1: beta is realised as a bulk tensor reduce-add (no activation, no Z)
   int n_fast;       // tile order: n runs fastest
-  int l2_prefetch;  // bit 0 / 1: prefetch the next tile's A / B boxes into L2
+  int l2_prefetch;  // bit 0 / 1: prefetch the next tile's A / B boxes into L2; bit 2: the epilogue's input boxes
   int tiles_m, tiles_n, kblocks, kchunk_blocks, total_tiles;
   int kc;       // k-blocks per TMEM accumulation chain (chunk); chunks are summed in registers with RN adds
   int c_vec;    // C / Z / aux / bias base pointers are 16-byte aligned
   int dbg;
+  int epi_mode;  // EM_* bits when the epilogue matches a compiled mode, else -1
   int skip;  // bring-up only (RPDE_TC_SKIP bitmask): 1 epilogue emit, 2 operand prep, 4 UMMA issue, 8 TMA loads
 };
 
@@ -71,11 +73,13 @@ namespace tc {
 #endif
 
 constexpr int BM = 128, BK = 32;
+// compile-time epilogue modes of the TMA epilogue (TcParams::epi_mode; -1 = every flag read at run time)
+constexpr int EM_IN_MUL = 1, EM_BIAS = 2, EM_GELU_G = 4, EM_COLSUM = 8;
 constexpr int A_TILE_BYTES = BM * BK * 4;
 constexpr int kEpiWarps = 8;                         // two warps per TMEM lane quadrant, each owning half of the tile's columns
 constexpr int kProducerBWarp = 6 + kEpiWarps;         // second TMA producer (B operand) behind the epilogue warps
 constexpr int kThreads = 32 * (7 + kEpiWarps);
-constexpr int kEpiBytes = kEpiWarps * 4096;          // one 128B-swizzled 32x32 fp32 staging box per epilogue warp
+constexpr int kEpiBytes = kEpiWarps * 8192;          // two 128B-swizzled 32x32 fp32 staging boxes per epilogue warp
 constexpr int kSmemBudget = 227 * 1024 - 2048 - kEpiBytes;
 
 template <int BN, bool SPLIT>
@@ -487,14 +491,20 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
       const int ct = threadIdx.x - 64;
       int s = 0, l = 0;
       uint32_t ph = 0, lph = 0;
+      TCP_DECL(qf = 0, ql = 0, qa = 0, qb = 0, qt = 0, qall = clock64(), qn = 0);
       for (int t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
         int tm, tn, z;
         tile_coords(P, t, tm, tn, z);
         const int sk = z % p.splitk;
         const int kb0 = sk * P.kchunk_blocks, kb1 = min(P.kblocks, kb0 + P.kchunk_blocks);
         for (int kb = kb0; kb < kb1; ++kb) {
+          TCP_T0(w0);
           mbar_wait(full(s), ph);
+          TCP_ADD(qf, w0);
+          TCP_T0(w1);
           if (SPLIT) mbar_wait(lo_empty(l), lph ^ 1);  // the UMMAs of two iterations ago have released lo buffer l
+          TCP_ADD(ql, w1);
+          TCP_T0(w2);
           if (!(P.skip & 2)) {
             if (SPLIT) {
               // A: this thread's row (TMEM lane = tile row) -> hi / lo -> TMEM ring slot l
@@ -503,13 +513,21 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
             } else if (p.a_act) {
               prep_region<false>(a_hi(s), 0, A_TILE_BYTES / 16, p.a_act, ct);
             }
+            TCP_ADD(qa, w2);
+            TCP_T0(w3);
             if (SPLIT || p.b_act) prep_region<SPLIT>(b_hi(s), b_lo(l), C::b_tile / 16, p.b_act, ct);
-            if (SPLIT) tmem_st_wait();
+            TCP_ADD(qb, w3);
           }
+          TCP_T0(w4);
+          if (SPLIT && !(P.skip & 2)) tmem_st_wait();
           if (SPLIT) tc_fence_before_sync();
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) mbar_arrive(ready(s));  // one arrival per warp
+          TCP_ADD(qt, w4);
+#ifdef RPDE_TC_PROFILE
+          ++qn;
+#endif
           if (SPLIT) {
             if (l == 1) lph ^= 1;
             l ^= 1;
@@ -517,6 +535,10 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
           if (++s == S) { s = 0; ph ^= 1; }
         }
       }
+#ifdef RPDE_TC_PROFILE
+      if (blockIdx.x == 0 && threadIdx.x == 64)
+        printf("[tc prep] iters %lld total %lld wait_full %lld wait_lo_empty %lld A %lld B %lld tail %lld\n", qn, clock64() - qall, qf, ql, qa, qb, qt);
+#endif
     }
   } else if (warp < kProducerBWarp) {
     // ------------------------------------------------------------------ epilogue: warps 6..13.  A warp may only touch the
@@ -524,28 +546,80 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
     const int ew = warp - 6;
     const int quad = warp & 3, half = ew >> 2;
     constexpr int CPW = (BN / 32) / 2;  // 32-column slices per epilogue warp
-    const uint32_t stg = epi_base + ew * 4096;
-    const uint32_t row_addr = stg + lane * 128;
+    // Two staging boxes per warp.  Box 1 receives the bulk loads (saved act' / old C), prefetched one slice ahead, or
+    // the second output stream (Z); box 0 stages C.  With a single output stream and no input the boxes alternate, so
+    // a slice never waits for the bulk store of the one before it.
+    const uint32_t stg = epi_base + ew * 8192;
+    const uint32_t stg1 = stg + 4096;
     const uint32_t sw = lane & 7;
     const uint32_t inbar = epi_in(ew);
     uint32_t in_phase = 0;
-    bool pending = false;  // a bulk store may still be reading the staging box
     const bool col_contig = (p.c.c.sl == 1) && (p.c.c.d == INT_MAX || (p.c.c.d % 32) == 0) && P.dbg != 3;
     const bool tma_in = P.epi_tma && (p.dact || (p.beta && !P.epi_reduce));
     uint32_t cit = 0;
+    // bulk-store bookkeeping (lane 0 owns the groups; the counters are warp-uniform): ncommit groups committed so far,
+    // groups <= done have finished reading shared memory, last[b] = the last group that reads box b
+    uint32_t ncommit = 0, done = 0, last0 = 0, last1 = 0, flip = 0;
+    float cs_acc[CPW];  // running column sums (bias gradient) of the column slices this warp owns
+    int cs_n0[CPW];
+#pragma unroll
+    for (int i = 0; i < CPW; ++i) { cs_acc[i] = 0.f; cs_n0[i] = -1; }
+    TCP_DECL(ea = 0, ef = 0, ee = 0, ei = 0, eb = 0, eall = clock64(), en = 0, e1 = 0, e2 = 0, e3 = 0, g1 = 0, g2 = 0, g3 = 0, g4 = 0);
+    bool pf_valid = false;  // a prefetched input box is in flight ...
+    int pf_t = -1, pf_n0 = -1;  // ... for this (tile, first column)
 
-    auto stage_free = [&]() {
-      if (pending) {
-        if (lane == 0) bulk_wait_read0();
+    auto box_free = [&](uint32_t last) {
+      if (last > done) {
+        TCP_T0(b0);
+        const bool one = (ncommit - last) >= 1;
+        if (lane == 0) {
+          if (one) bulk_wait_read1();
+          else bulk_wait_read0();
+        }
         __syncwarp();
-        pending = false;
+        done = ncommit - (one ? 1u : 0u);
+        TCP_ADD(eb, b0);
       }
     };
-    auto stage_write = [&](const float (&v)[32]) {
+    auto stage_write = [&](uint32_t box, const float (&v)[32]) {
+      const uint32_t row_addr = box + lane * 128;
 #pragma unroll
       for (int q = 0; q < 8; ++q) sts128(row_addr + ((q ^ sw) << 4), make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]));
     };
+    // bulk load of the input box of (tile tt, slice ci) into box 1; false when that slice does not exist
+    auto in_issue = [&](int tt, int ci) -> bool {
+      if (tt >= P.total_tiles) return false;
+      int tm2, tn2, z2;
+      tile_coords(P, tt, tm2, tn2, z2);
+      const int mb = tm2 * BM + quad * 32, nn = tn2 * BN + (half * CPW + ci) * 32;
+      if (mb >= p.M || nn >= p.N) return false;
+      int c5[5];
+      opnd_coords(P.c, mb, z2 / p.splitk, c5);
+      opnd_set_k(P.c.k_d, P.c.dk0, P.c.dk1, nn, c5);
+      if (lane == 0) {
+        mbar_arrive_expect_tx(inbar, 4096);
+        tma_load(stg1, &mapI, inbar, P.c.ndim, c5);
+      }
+      pf_valid = true;
+      pf_t = tt;
+      pf_n0 = nn;
+      return true;
+    };
 
+    // The tile loop is instantiated once per common epilogue mode (MODE >= 0: the flag tests fold at compile time, which
+    // matters because an epilogue warp is a serial instruction stream with little to hide behind) and once with every
+    // flag read at run time (MODE < 0).
+    auto run_tiles = [&](auto mode_tag) {
+    constexpr int MODE = decltype(mode_tag)::value;
+    constexpr bool RT = MODE < 0;
+    const bool f_tma = RT ? (P.epi_tma != 0) : true;
+    const bool f_in = RT ? tma_in : ((MODE & EM_IN_MUL) != 0);
+    const int f_bias = RT ? p.bias_mode : ((MODE & EM_BIAS) ? 1 : 0);
+    const bool f_Z = RT ? (p.Z != nullptr) : ((MODE & EM_GELU_G) != 0);
+    const bool f_zgrad = RT ? (p.z_grad != 0) : true;
+    const int f_act = RT ? p.act : ((MODE & EM_GELU_G) ? (int)ACT_GELU : 0);
+    const int f_dact = RT ? p.dact : ((MODE & EM_IN_MUL) ? 3 : 0);
+    const bool f_colsum = RT ? (p.colsum != nullptr) : ((MODE & EM_COLSUM) != 0);
     for (int t = blockIdx.x; t < P.total_tiles; t += gridDim.x) {
       int tm, tn, z;
       tile_coords(P, t, tm, tn, z);
@@ -557,26 +631,60 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
       const long long ro = off2(p.c.b, bz) + off2(p.c.r, mval ? m : 0);
       const float bias_m = (p.bias_mode == 2 && mval) ? __ldg(p.bias + m) : 0.f;
       int cc5[5];
-      if (P.epi_tma) opnd_coords(P.c, m_base, bz, cc5);
-
-      // ---- one 32-column slice of this warp's 32 rows: v[j] = accumulator of (row m, column n0 + j)
-      auto emit = [&](float (&v)[32], int n0) {
-        if (P.dbg == 5 || (P.skip & 1)) return;
-        if (P.epi_tma) {
-          // TMA epilogue: rows are staged in the swizzled box and leave (or arrive) as one bulk tensor copy
-          if (m_base >= p.M) return;  // warp-uniform
-          opnd_set_k(P.c.k_d, P.c.dk0, P.c.dk1, n0, cc5);
-          if (tma_in) {
-            stage_free();
-            if (lane == 0) {
-              mbar_arrive_expect_tx(inbar, 4096);
-              tma_load(stg, &mapI, inbar, P.c.ndim, cc5);
+      if (f_tma) opnd_coords(P.c, m_base, bz, cc5);
+      if (RT && tma_in && (P.l2_prefetch & 4)) {
+        // pull the input boxes of this warp's NEXT tile into L2 now: the bulk load one slice ahead then has L2 latency
+        const int tt = t + (int)gridDim.x;
+        if (tt < P.total_tiles) {
+          int tm2, tn2, z2;
+          tile_coords(P, tt, tm2, tn2, z2);
+          const int mb = tm2 * BM + quad * 32;
+          if (mb < p.M) {
+            int c5[5];
+            opnd_coords(P.c, mb, z2 / p.splitk, c5);
+#pragma unroll
+            for (int ci = 0; ci < CPW; ++ci) {
+              const int nn = tn2 * BN + (half * CPW + ci) * 32;
+              if (nn < p.N) {
+                opnd_set_k(P.c.k_d, P.c.dk0, P.c.dk1, nn, c5);
+                if (lane == 0) tma_prefetch_l2(&mapI, P.c.ndim, c5);
+              }
             }
           }
+        }
+      }
+
+      // ---- one 32-column slice of this warp's 32 rows: v[j] = accumulator of (row m, column n0 + j)
+      auto emit = [&](float (&v)[32], int n0, int ci) {
+        if (RT && (P.dbg == 5 || (P.skip & 1))) return;
+        if (f_tma) {
+          // TMA epilogue: rows are staged in the swizzled box and leave (or arrive) as one bulk tensor copy
+          if (m_base >= p.M) return;  // warp-uniform
+          TCP_T0(h0);
+          opnd_set_k(P.c.k_d, P.c.dk0, P.c.dk1, n0, cc5);
+          TCP_ADD(g1, h0);
+          TCP_T0(h1);
+          if (f_in) {
+            if (pf_valid && (pf_t != t || pf_n0 != n0)) {  // cannot happen with the fixed slice order; drain defensively
+              mbar_wait(inbar, in_phase);
+              in_phase ^= 1;
+              pf_valid = false;
+            }
+            if (!pf_valid) {
+              __syncwarp();
+              if (lane == 0) {
+                mbar_arrive_expect_tx(inbar, 4096);
+                tma_load(stg1, &mapI, inbar, P.c.ndim, cc5);
+              }
+            }
+            pf_valid = false;
+          }
+          if (RT) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] *= p.alpha;
-          if (p.bias_mode == 1) {
-            if (n0 + 32 <= p.N && P.c_vec) {
+            for (int j = 0; j < 32; ++j) v[j] *= p.alpha;
+          }
+          if (f_bias == 1) {
+            if (!RT || (n0 + 32 <= p.N && P.c_vec)) {
 #pragma unroll
               for (int q = 0; q < 8; ++q) {
                 const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + n0) + q);
@@ -586,83 +694,148 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
 #pragma unroll
               for (int j = 0; j < 32; ++j) v[j] += (n0 + j < p.N) ? __ldg(p.bias + n0 + j) : 0.f;
             }
-          } else if (p.bias_mode == 2) {
+          } else if (f_bias == 2) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] += bias_m;
           }
-          if (tma_in) {
+          TCP_ADD(g2, h1);
+          if (f_in) {
+            TCP_T0(i0);
             mbar_wait(inbar, in_phase);
+            TCP_ADD(ei, i0);
             in_phase ^= 1;
             float u[32];
+            const uint32_t row1 = stg1 + lane * 128;
 #pragma unroll
             for (int q = 0; q < 8; ++q) {
-              const float4 x = lds128(row_addr + ((q ^ sw) << 4));
+              const float4 x = lds128(row1 + ((q ^ sw) << 4));
               u[4 * q] = x.x; u[4 * q + 1] = x.y; u[4 * q + 2] = x.z; u[4 * q + 3] = x.w;
             }
-            if (p.dact) {
-              dact32_mul(p.dact, v, u);
+            __syncwarp();  // every lane has read its row: box 1 may be refilled
+            // prefetch the input of the slice this warp emits next (same tile, or the first slice of its next tile)
+            if (ci + 1 < CPW && n0 + 32 < p.N) {
+              int c5[5];
+#pragma unroll
+              for (int i = 0; i < 5; ++i) c5[i] = cc5[i];
+              opnd_set_k(P.c.k_d, P.c.dk0, P.c.dk1, n0 + 32, c5);
+              if (lane == 0) {
+                mbar_arrive_expect_tx(inbar, 4096);
+                tma_load(stg1, &mapI, inbar, P.c.ndim, c5);
+              }
+              pf_valid = true;
+              pf_t = t;
+              pf_n0 = n0 + 32;
+            } else {
+              in_issue(t + (int)gridDim.x, 0);
+            }
+            if (f_dact) {
+              dact32_mul(f_dact, v, u);
             } else {
 #pragma unroll
               for (int j = 0; j < 32; ++j) v[j] += u[j];
             }
           }
+          TCP_T0(h4);
           bool acted = false;
-          if (p.Z) {
-            stage_free();
-            if (p.z_grad) {
+          // box of the C slice: box 0, or alternating when nothing else uses box 1
+          const bool alt = !f_in && !f_Z && (flip & 1);
+          flip ^= 1;
+          const uint32_t boxc = alt ? stg1 : stg;
+          if (f_Z) {
+            const bool zb1 = !f_in;  // Z rides in box 1 unless the input loads own it
+            const uint32_t boxz = zb1 ? stg1 : stg;
+            box_free(zb1 ? last1 : last0);
+            if (f_zgrad) {
               float w[32];
-              if (P.dbg == 2) {
+              if (RT && P.dbg == 2) {
 #pragma unroll
                 for (int j = 0; j < 32; ++j) w[j] = v[j];
-              } else if (p.act == ACT_GELU) {
+              } else if (f_act == ACT_GELU) {
 #pragma unroll
                 for (int j = 0; j < 32; ++j) gelu_both(v[j], v[j], w[j]);
               } else {
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
-                  w[j] = dact_f(p.act, v[j]);
-                  v[j] = act_f(p.act, v[j]);
+                  w[j] = dact_f(f_act, v[j]);
+                  v[j] = act_f(f_act, v[j]);
                 }
               }
               acted = true;
-              stage_write(w);
+              stage_write(boxz, w);
             } else {
-              stage_write(v);
+              stage_write(boxz, v);
             }
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) {
-              tma_store(stg, &mapZ, P.c.ndim, cc5, false);
+              tma_store(boxz, &mapZ, P.c.ndim, cc5, false);
               bulk_commit();
             }
-            pending = true;
+            ++ncommit;
+            if (zb1) last1 = ncommit;
+            else last0 = ncommit;
           }
-          if (!acted) act32(p.act, v);
-          stage_free();
-          stage_write(v);
+          TCP_ADD(g4, h4);
+          TCP_T0(h3);
+          if (!acted) act32(f_act, v);
+          TCP_ADD(g3, h3);
+          box_free(alt ? last1 : last0);
+          TCP_T0(s2);
+          stage_write(boxc, v);
           fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0 && P.dbg != 4) {
-            tma_store(stg, &mapC, P.c.ndim, cc5, P.epi_reduce != 0);
+          TCP_ADD(e2, s2);
+          TCP_T0(s3);
+          if (lane == 0) {
+            if (!RT || P.dbg != 4) tma_store(boxc, &mapC, P.c.ndim, cc5, P.epi_reduce != 0);
             bulk_commit();
           }
-          pending = true;
-          if (p.colsum) {
+          TCP_ADD(e3, s3);
+          ++ncommit;
+          if (alt) last1 = ncommit;
+          else last0 = ncommit;
+          if (f_colsum) {
             // bias gradient of the producing layer: column sums of the rows just staged (valid rows only)
             const int rows = min(32, p.M - m_base);
             float cs = 0.f;
-            for (int r = 0; r < rows; ++r) {
+            const uint32_t cb = boxc + (((uint32_t)lane & 3u) << 2), chk = (uint32_t)lane >> 2;
+            auto ldcol = [&](int r) {
               float x;
-              asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x) : "r"(stg + r * 128 + (((((uint32_t)lane >> 2) ^ ((uint32_t)r & 7u)) << 4) | (((uint32_t)lane & 3u) << 2))));
-              cs += x;
+              asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x) : "r"(cb + r * 128 + ((chk ^ ((uint32_t)r & 7u)) << 4)));
+              return x;
+            };
+            if (rows == 32) {
+              float c0 = 0.f, c1 = 0.f, c2 = 0.f, c3 = 0.f;
+#pragma unroll
+              for (int r = 0; r < 32; r += 4) {
+                c0 += ldcol(r);
+                c1 += ldcol(r + 1);
+                c2 += ldcol(r + 2);
+                c3 += ldcol(r + 3);
+              }
+              cs = (c0 + c1) + (c2 + c3);
+            } else {
+              for (int r = 0; r < rows; ++r) cs += ldcol(r);
             }
-            if (n0 + lane < p.N) atomicAdd(p.colsum + n0 + lane, cs);
+            // a CTA usually keeps its column block from tile to tile: accumulate in a register, flush on change / at the end
+#pragma unroll
+            for (int i = 0; i < CPW; ++i) {
+              if (i == ci) {
+                if (cs_n0[i] != n0) {
+                  if (cs_n0[i] >= 0 && cs_n0[i] + lane < p.N) atomicAdd(p.colsum + cs_n0[i] + lane, cs_acc[i]);
+                  cs_acc[i] = 0.f;
+                  cs_n0[i] = n0;
+                }
+                cs_acc[i] += cs;
+              }
+            }
           }
           return;
         }
+        if (!RT) return;
         if (col_contig) {
           // transpose through the staging box so that global accesses run along the contiguous columns
-          stage_write(v);
+          stage_write(stg, v);
           __syncwarp();
           const long long coff = off2(p.c.c, n0);
           const bool aligned = !mval || (((ro + coff) & 3) == 0);
@@ -759,9 +932,12 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
 
       if (!CH) {
         const int buf = cit & 1;
+        TCP_T0(a0);
         mbar_wait(acc_full(buf), (cit >> 1) & 1);
+        TCP_ADD(ea, a0);
         tc_fence_after_sync();
         const uint32_t tq = tmem_base + ((uint32_t)(quad * 32) << 16);
+        TCP_T0(f0);
         if (SPLIT) {
           // fold the small block into big (in TMEM) and hand it back, so the next tile's main loop starts at once
 #pragma unroll 1
@@ -780,6 +956,8 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
           __syncwarp();
           if (lane == 0) mbar_arrive(small_empty);
         }
+        TCP_ADD(ef, f0);
+        TCP_T0(e0);
 #pragma unroll 1
         for (int ci = 0; ci < CPW; ++ci) {
           const int cc = half * CPW + ci;
@@ -787,12 +965,18 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
           if (n0 >= p.N) break;  // warp-uniform
           uint32_t r[32];
           float v[32];
+          TCP_T0(s1);
           tmem_ld32(tq + buf * C::acc_cols + cc * 32, r);
           tmem_ld_wait();
+          TCP_ADD(e1, s1);
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-          emit(v, n0);
+          emit(v, n0, ci);
         }
+        TCP_ADD(ee, e0);
+#ifdef RPDE_TC_PROFILE
+        ++en;
+#endif
         tc_fence_before_sync();
         __syncwarp();
         if (lane == 0) mbar_arrive(acc_empty(buf));
@@ -837,10 +1021,33 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
             float v[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = acc[ci * 32 + j];
-            emit(v, n0);
+            emit(v, n0, ci);
           }
         }
       }
+    }
+    };  // run_tiles
+    if constexpr (CH) {  // chunked chains emit once per many accumulator hand-overs: one instantiation is enough
+      run_tiles(std::integral_constant<int, -1>{});
+    } else
+    switch (P.epi_mode) {
+      case 0: run_tiles(std::integral_constant<int, 0>{}); break;
+      case EM_BIAS: run_tiles(std::integral_constant<int, EM_BIAS>{}); break;
+      case EM_GELU_G: run_tiles(std::integral_constant<int, EM_GELU_G>{}); break;
+      case EM_BIAS | EM_GELU_G: run_tiles(std::integral_constant<int, EM_BIAS | EM_GELU_G>{}); break;
+      case EM_IN_MUL: run_tiles(std::integral_constant<int, EM_IN_MUL>{}); break;
+      case EM_IN_MUL | EM_COLSUM: run_tiles(std::integral_constant<int, EM_IN_MUL | EM_COLSUM>{}); break;
+      default: run_tiles(std::integral_constant<int, -1>{}); break;
+    }
+    if (pf_valid) mbar_wait(inbar, in_phase);  // never leave a bulk load in flight
+#ifdef RPDE_TC_PROFILE
+    if (blockIdx.x == 0 && lane == 0 && (ew == 0 || ew == 7))
+      printf("[tc epi %d] tiles %lld total %lld wait_acc_full %lld fold %lld emit %lld (wait_in %lld box_free %lld tmem_ld %lld stage %lld store %lld setk %lld alpha_bias %lld act %lld zblock %lld)\n", ew, en, clock64() - eall, ea, ef, ee, ei, eb, e1, e2, e3, g1, g2, g3, g4);
+#endif
+    if (p.colsum) {
+#pragma unroll
+      for (int i = 0; i < CPW; ++i)
+        if (cs_n0[i] >= 0 && cs_n0[i] + lane < p.N) atomicAdd(p.colsum + cs_n0[i] + lane, cs_acc[i]);
     }
     if (lane == 0) bulk_wait0();  // the staging boxes must outlive the bulk stores that read them
     __syncwarp();
@@ -1087,7 +1294,7 @@ static cudaError_t gemm_tc_try_launch(const GemmP& g, int prec, cudaStream_t s, 
   P.total_tiles = (int)total;
   P.n_fast = P.tiles_n <= P.tiles_m;
   {
-    static const int pf_env = getenv("RPDE_TC_L2PF") ? atoi(getenv("RPDE_TC_L2PF")) : 0;  // measured: the extra TMA requests cost more than the latency they hide
+    static const int pf_env = getenv("RPDE_TC_L2PF") ? atoi(getenv("RPDE_TC_L2PF")) : 4;  // measured: the extra TMA requests cost more than the latency they hide
     P.l2_prefetch = pf_env;
   }
   // TMA epilogue: the output (and Z / aux / the old C) addressed as 32 x 32 boxes of rows x contiguous columns
@@ -1112,6 +1319,16 @@ static cudaError_t gemm_tc_try_launch(const GemmP& g, int prec, cudaStream_t s, 
     } else {
       P.epi_reduce = 0;
     }
+  }
+  // compiled epilogue modes (see EM_*): everything else reads its flags at run time
+  P.epi_mode = -1;
+  static const bool no_modes = getenv("RPDE_TC_NO_EPI_MODES") != nullptr;
+  if (P.epi_tma && !no_modes && g.alpha == 1.f && P.dbg == 0 && P.skip == 0 && (g.N % 32) == 0 &&
+      (g.bias_mode == 0 || (g.bias_mode == 1 && P.c_vec))) {
+    const int bbit = g.bias_mode == 1 ? EM_BIAS : 0;
+    if (!g.dact && !g.act && !g.Z && !g.colsum && (!g.beta || P.epi_reduce)) P.epi_mode = bbit;
+    else if (g.act == ACT_GELU && g.Z && g.z_grad && !g.dact && !g.beta && !g.colsum) P.epi_mode = EM_GELU_G | bbit;
+    else if (g.dact == 3 && !g.act && !g.Z && !g.beta && !bbit) P.epi_mode = EM_IN_MUL | (g.colsum ? EM_COLSUM : 0);
   }
   cudaError_t rc;
   if (chunked) {

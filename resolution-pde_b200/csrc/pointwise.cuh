@@ -163,6 +163,126 @@ __global__ void layernorm_fwd_kernel(const float* __restrict__ x, const float* _
   }
 }
 
+// Vectorised LayerNorm for C = 4 * LPR (LPR = 4, 8, 16 or 32 lanes per row, one float4 per lane): 32 / LPR rows per warp
+// and U row groups in flight per thread, so the pass runs at HBM rate instead of at shuffle latency.
+template <int LPR>
+__device__ __forceinline__ float group_sum(float v) {
+#pragma unroll
+  for (int o = LPR / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+template <int LPR>
+__global__ void __launch_bounds__(256) layernorm_fwd_vec_kernel(const float* __restrict__ x, const float* __restrict__ res,
+                                                                const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                                float* __restrict__ y, float* __restrict__ mean,
+                                                                float* __restrict__ rstd, long long T, float eps) {
+  constexpr int C = LPR * 4, RPW = 32 / LPR, U = 4;
+  const int lane = threadIdx.x & 31, sub = lane % LPR, rsel = lane / LPR;
+  const long long gwarp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  const float4 g4 = __ldg(reinterpret_cast<const float4*>(gamma) + sub);
+  const float4 b4 = __ldg(reinterpret_cast<const float4*>(beta) + sub);
+  const float inv_c = 1.f / (float)C;
+  for (long long row0 = gwarp * (RPW * U); row0 < T; row0 += nwarps * (RPW * U)) {
+    float4 xv[U], rv[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long row = row0 + u * RPW + rsel;
+      xv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      rv[u] = xv[u];
+      if (row < T) {
+        xv[u] = __ldcs(reinterpret_cast<const float4*>(x + row * C) + sub);
+        if (res) rv[u] = __ldcs(reinterpret_cast<const float4*>(res + row * C) + sub);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long row = row0 + u * RPW + rsel;
+      const float mu = group_sum<LPR>((xv[u].x + xv[u].y) + (xv[u].z + xv[u].w)) * inv_c;
+      const float dx0 = xv[u].x - mu, dx1 = xv[u].y - mu, dx2 = xv[u].z - mu, dx3 = xv[u].w - mu;
+      const float var = group_sum<LPR>((dx0 * dx0 + dx1 * dx1) + (dx2 * dx2 + dx3 * dx3)) * inv_c;
+      const float rs = rsqrtf(var + eps);
+      if (row < T) {
+        float4 o;
+        o.x = dx0 * rs * g4.x + b4.x + rv[u].x;
+        o.y = dx1 * rs * g4.y + b4.y + rv[u].y;
+        o.z = dx2 * rs * g4.z + b4.z + rv[u].z;
+        o.w = dx3 * rs * g4.w + b4.w + rv[u].w;
+        reinterpret_cast<float4*>(y + row * C)[sub] = o;
+        if (sub == 0 && mean) {
+          mean[row] = mu;
+          rstd[row] = rs;
+        }
+      }
+    }
+  }
+}
+template <int LPR>
+__global__ void __launch_bounds__(256) layernorm_bwd_vec_kernel(const float* __restrict__ dy, const float* __restrict__ x,
+                                                                const float* __restrict__ gamma, const float* __restrict__ mean,
+                                                                const float* __restrict__ rstd, float* __restrict__ dx,
+                                                                float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                                float* __restrict__ dxsum, long long T) {
+  constexpr int C = LPR * 4, RPW = 32 / LPR, U = 4;
+  __shared__ float sm[3 * C];
+  for (int c = threadIdx.x; c < 3 * C; c += blockDim.x) sm[c] = 0.f;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, sub = lane % LPR, rsel = lane / LPR;
+  const long long gwarp = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  const float4 g4 = __ldg(reinterpret_cast<const float4*>(gamma) + sub);
+  const float inv_c = 1.f / (float)C;
+  float ag[4] = {0.f, 0.f, 0.f, 0.f}, ab[4] = {0.f, 0.f, 0.f, 0.f}, ax[4] = {0.f, 0.f, 0.f, 0.f};
+  for (long long row0 = gwarp * (RPW * U); row0 < T; row0 += nwarps * (RPW * U)) {
+    float4 xv[U], dv[U];
+    float mu[U], rs[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long row = row0 + u * RPW + rsel;
+      xv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      dv[u] = xv[u];
+      mu[u] = 0.f;
+      rs[u] = 0.f;
+      if (row < T) {
+        xv[u] = __ldcs(reinterpret_cast<const float4*>(x + row * C) + sub);
+        dv[u] = __ldcs(reinterpret_cast<const float4*>(dy + row * C) + sub);
+        mu[u] = __ldg(mean + row);
+        rs[u] = __ldg(rstd + row);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long row = row0 + u * RPW + rsel;
+      const float xh0 = (xv[u].x - mu[u]) * rs[u], xh1 = (xv[u].y - mu[u]) * rs[u];
+      const float xh2 = (xv[u].z - mu[u]) * rs[u], xh3 = (xv[u].w - mu[u]) * rs[u];
+      const float g0 = dv[u].x * g4.x, g1 = dv[u].y * g4.y, g2 = dv[u].z * g4.z, g3 = dv[u].w * g4.w;
+      const float s1 = group_sum<LPR>((g0 + g1) + (g2 + g3)) * inv_c;
+      const float s2 = group_sum<LPR>((g0 * xh0 + g1 * xh1) + (g2 * xh2 + g3 * xh3)) * inv_c;
+      float4 o;
+      o.x = rs[u] * (g0 - s1 - xh0 * s2);
+      o.y = rs[u] * (g1 - s1 - xh1 * s2);
+      o.z = rs[u] * (g2 - s1 - xh2 * s2);
+      o.w = rs[u] * (g3 - s1 - xh3 * s2);
+      if (row < T) reinterpret_cast<float4*>(dx + row * C)[sub] = o;  // rows >= T carry zeros: no contribution below
+      ag[0] += dv[u].x * xh0; ag[1] += dv[u].y * xh1; ag[2] += dv[u].z * xh2; ag[3] += dv[u].w * xh3;
+      ab[0] += dv[u].x; ab[1] += dv[u].y; ab[2] += dv[u].z; ab[3] += dv[u].w;
+      ax[0] += o.x; ax[1] += o.y; ax[2] += o.z; ax[3] += o.w;
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    atomicAdd(&sm[sub * 4 + j], ag[j]);
+    atomicAdd(&sm[C + sub * 4 + j], ab[j]);
+    if (dxsum) atomicAdd(&sm[2 * C + sub * 4 + j], ax[j]);
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    atomicAdd(&dgamma[c], sm[c]);
+    atomicAdd(&dbeta[c], sm[C + c]);
+    if (dxsum) atomicAdd(&dxsum[c], sm[2 * C + c]);
+  }
+}
+
 // dx = rstd * (g - mean(g) - xhat * mean(g * xhat)),  g = dy * gamma;  dgamma += dy * xhat;  dbeta += dy.
 // Block = 8 warps, each warp walks rows; per-block partial dgamma/dbeta in shared memory (C <= 1024).
 __global__ void layernorm_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ x,

@@ -741,6 +741,21 @@ int rpde_layernorm_fwd(const float* x, const float* res, const float* gamma, con
                        float* mean, float* rstd, long long T, int C, float eps, rpde_stream_t stream) {
   if (!x || !gamma || !beta || !y || T <= 0 || C <= 0 || (mean && !rstd))
     return fail(RPDE_E_INVALID, "rpde_layernorm_fwd: bad arguments%s");
+  auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+  if ((C == 16 || C == 32 || C == 64 || C == 128) && al16(x) && al16(res) && al16(gamma) && al16(beta) && al16(y)) {
+    // one float4 per lane, C / 4 lanes per row, four row groups in flight: streams at HBM rate
+    const long long groups = (T * (C / 4) + 4 * 256 - 1) / (4 * 256);
+    const unsigned grid = (unsigned)(groups < 148 * 8 ? (groups < 1 ? 1 : groups) : 148 * 8);
+    cudaStream_t s = (cudaStream_t)stream;
+    switch (C) {
+      case 16: layernorm_fwd_vec_kernel<4><<<grid, 256, 0, s>>>(x, res, gamma, beta, y, mean, rstd, T, eps); break;
+      case 32: layernorm_fwd_vec_kernel<8><<<grid, 256, 0, s>>>(x, res, gamma, beta, y, mean, rstd, T, eps); break;
+      case 64: layernorm_fwd_vec_kernel<16><<<grid, 256, 0, s>>>(x, res, gamma, beta, y, mean, rstd, T, eps); break;
+      default: layernorm_fwd_vec_kernel<32><<<grid, 256, 0, s>>>(x, res, gamma, beta, y, mean, rstd, T, eps); break;
+    }
+    RPDE_LAUNCH_CHECK();
+    return RPDE_OK;
+  }
   const long long threads = T * 32;
   layernorm_fwd_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>(x, res, gamma, beta, y,
                                                                                            mean, rstd, T, C, eps);
@@ -755,6 +770,19 @@ int rpde_layernorm_bwd(const float* dy, const float* x, const float* gamma, cons
   RPDE_CUDA(cudaMemsetAsync(dgamma, 0, (size_t)C * sizeof(float), s));
   RPDE_CUDA(cudaMemsetAsync(dbeta, 0, (size_t)C * sizeof(float), s));
   if (dxsum) RPDE_CUDA(cudaMemsetAsync(dxsum, 0, (size_t)C * sizeof(float), s));
+  auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+  if ((C == 16 || C == 32 || C == 64 || C == 128) && al16(dy) && al16(x) && al16(gamma) && al16(dx)) {
+    const long long groups = (T * (C / 4) + 4 * 256 - 1) / (4 * 256);
+    const unsigned grid = (unsigned)(groups < 148 * 4 ? (groups < 1 ? 1 : groups) : 148 * 4);
+    switch (C) {
+      case 16: layernorm_bwd_vec_kernel<4><<<grid, 256, 0, s>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, dxsum, T); break;
+      case 32: layernorm_bwd_vec_kernel<8><<<grid, 256, 0, s>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, dxsum, T); break;
+      case 64: layernorm_bwd_vec_kernel<16><<<grid, 256, 0, s>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, dxsum, T); break;
+      default: layernorm_bwd_vec_kernel<32><<<grid, 256, 0, s>>>(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, dxsum, T); break;
+    }
+    RPDE_LAUNCH_CHECK();
+    return RPDE_OK;
+  }
   long long rpb = (T + 148 * 8 - 1) / (148 * 8);
   if (rpb < 8) rpb = 8;
   const unsigned grid = (unsigned)((T + rpb - 1) / rpb);

@@ -15,6 +15,13 @@ def main(csv_path, shapes_path, first_kernel="concat_grid_kernel"):
     # drop the trailing roofline-probe GEMMs (same shape repeated after the step) by aligning from the step's start
     n_gemm = sum(1 for r in rows if "gemm" in r["Kernel Name"])
     shapes = shapes[-n_gemm:]
+    # bench.py's roofline probe runs after the step: randn fills + the same plain GEMM repeated; cut it off
+    probe = shapes[-1] if shapes else None
+    while rows and (("gemm" in rows[-1]["Kernel Name"] and shapes and shapes[-1] == probe)
+                    or "distribution_elementwise" in rows[-1]["Kernel Name"]):
+        if "gemm" in rows[-1]["Kernel Name"]:
+            shapes.pop()
+        rows.pop()
     agg = collections.OrderedDict()
     gi = 0
     total = 0.0

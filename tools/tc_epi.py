@@ -21,3 +21,12 @@ for (i, o) in [(64, 256), (256, 256)]:
     r["gelu_z"] = tm(lambda: lib.rpde_linear_fwd(x.data_ptr(), w.data_ptr(), b.data_ptr(), y.data_ptr(), z.data_ptr(), T, i, o, 1, 0, st))
     r["gelu_gradz"] = tm(lambda: lib.rpde_linear_fwd(x.data_ptr(), w.data_ptr(), b.data_ptr(), y.data_ptr(), z.data_ptr(), T, i, o, 0x101, 0, st))
     print(json.dumps(r), flush=True)
+# dgrad with the stored act' multiply (+ bias-gradient column sums): dx(T x in) = dy(T x out) . W(out x in) * saved(T x in)
+for (i, o) in [(256, 64), (256, 256), (64, 256)]:
+    dy = torch.randn(T, o, device="cuda"); w = torch.randn(o, i, device="cuda") / i ** 0.5
+    sv = torch.rand(T, i, device="cuda"); dx = torch.empty(T, i, device="cuda"); db = torch.zeros(i, device="cuda")
+    r = {"prec": sys.argv[1], "dgrad_in_out": [i, o]}
+    r["plain"] = tm(lambda: lib.rpde_linear_bwd_input(dy.data_ptr(), w.data_ptr(), None, 0, dx.data_ptr(), 0, None, T, i, o, 0, st))
+    r["saved"] = tm(lambda: lib.rpde_linear_bwd_input(dy.data_ptr(), w.data_ptr(), sv.data_ptr(), 3, dx.data_ptr(), 0, None, T, i, o, 0, st))
+    r["saved_dbias"] = tm(lambda: lib.rpde_linear_bwd_input(dy.data_ptr(), w.data_ptr(), sv.data_ptr(), 3, dx.data_ptr(), 0, db.data_ptr(), T, i, o, 0, st))
+    print(json.dumps(r), flush=True)
