@@ -333,6 +333,37 @@ __global__ void layernorm_bwd_kernel(const float* __restrict__ dy, const float* 
 //   fwd   : y[t][o] = b[o] + sum_i x[t][i] w[o][i]          (thread = one row, four consecutive outputs)
 //   wgrad : dw[o][i] += sum_t dy[t][o] x[t][i],  db[o] += sum_t dy[t][o]
 // ----------------------------------------------------------------------------------------------
+// Channels-first 1x1 convolution with a handful of input channels (the FNO lifting layer: data + grid coordinates):
+// y[b][o][s] = bias[o] + sum_i w[o][i] x[b][i][s].  One thread owns four consecutive positions and walks the output
+// channels, so every store instruction of a warp covers 512 contiguous bytes; pure streaming at the output's HBM rate.
+template <int IN>
+__global__ void conv1x1_smallk_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                          const float* __restrict__ bias, float* __restrict__ y, int B, int O, long long S) {
+  extern __shared__ float sm[];  // w [O][IN], b [O]
+  for (int e = threadIdx.x; e < O * IN; e += blockDim.x) sm[e] = w[e];
+  for (int e = threadIdx.x; e < O; e += blockDim.x) sm[O * IN + e] = bias ? bias[e] : 0.f;
+  __syncthreads();
+  const long long q = S >> 2, total = (long long)B * q;
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
+    const long long b = e / q, s4 = (e - b * q) * 4;
+    float4 xi[IN];
+#pragma unroll
+    for (int i = 0; i < IN; ++i) xi[i] = __ldg(reinterpret_cast<const float4*>(x + (b * IN + i) * S + s4));
+    float* yo = y + b * O * S + s4;
+#pragma unroll 4
+    for (int o = 0; o < O; ++o) {
+      const float bo = sm[O * IN + o];
+      float4 r = make_float4(bo, bo, bo, bo);
+#pragma unroll
+      for (int i = 0; i < IN; ++i) {
+        const float wv = sm[o * IN + i];
+        r.x = fmaf(wv, xi[i].x, r.x); r.y = fmaf(wv, xi[i].y, r.y); r.z = fmaf(wv, xi[i].z, r.z); r.w = fmaf(wv, xi[i].w, r.w);
+      }
+      *reinterpret_cast<float4*>(yo + (long long)o * S) = r;
+    }
+  }
+}
+
 template <int IN>
 __global__ void linear_smallk_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                          const float* __restrict__ bias, float* __restrict__ y, long long T, int OUT) {
@@ -414,14 +445,24 @@ __global__ void reduce_channels_kernel(const float* __restrict__ X, float* __res
       atomicAdd(&out[c], tsum);
     }
   } else {
-    // one channel per blockIdx.y, reduce over (outer, inner) chunk
+    // one channel per blockIdx.y; blockIdx.x walks (outer row, chunk of the contiguous inner run) pairs
     const int c = blockIdx.y;
-    const long long total = outer * inner;
-    const long long e0 = blockIdx.x * chunk, e1 = min(total, e0 + chunk);
+    const long long cpi = (inner + chunk - 1) / chunk;
+    const bool vec = (inner % 4 == 0) && (chunk % 4 == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
     float s = 0.f;
-    for (long long e = e0 + threadIdx.x; e < e1; e += blockDim.x) {
-      const long long o = e / inner, i = e - o * inner;
-      s += X[(o * C + c) * inner + i];
+    for (long long q = blockIdx.x; q < outer * cpi; q += gridDim.x) {
+      const long long o = q / cpi, i0 = (q - o * cpi) * chunk, i1 = min(inner, i0 + chunk);
+      const float* src = X + (o * C + c) * inner;
+      if (vec) {
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        for (long long i = i0 + 4 * threadIdx.x; i < i1; i += 4 * blockDim.x) {
+          const float4 v = __ldcs(reinterpret_cast<const float4*>(src + i));
+          s0 += v.x; s1 += v.y; s2 += v.z; s3 += v.w;
+        }
+        s += (s0 + s1) + (s2 + s3);
+      } else {
+        for (long long i = i0 + threadIdx.x; i < i1; i += blockDim.x) s += src[i];
+      }
     }
     s = warp_sum(s);
     __shared__ float red[8];

@@ -617,10 +617,12 @@ static int reduce_channels(const float* X, float* out, long long outer, int C, l
     dim3 grid((unsigned)((outer + chunk - 1) / chunk), (unsigned)((C + 31) / 32));
     reduce_channels_kernel<<<grid, 256, 0, s>>>(X, out, outer, C, 1, chunk);
   } else {
-    const long long total = outer * inner;
-    long long chunk = (total + 63) / 64;
-    if (chunk < 2048) chunk = 2048;
-    dim3 grid((unsigned)((total + chunk - 1) / chunk), (unsigned)C);
+    long long chunk = 8192;  // floats of one contiguous inner run per block pass
+    const long long cpi = (inner + chunk - 1) / chunk, pairs = outer * cpi;
+    long long gx = (148LL * 16 + C - 1) / C;  // about 16 blocks per SM over all channels
+    if (gx > pairs) gx = pairs;
+    if (gx < 1) gx = 1;
+    dim3 grid((unsigned)gx, (unsigned)C);
     reduce_channels_kernel<<<grid, 256, 0, s>>>(X, out, outer, C, inner, chunk);
   }
   RPDE_LAUNCH_CHECK();
@@ -677,6 +679,23 @@ int rpde_conv1x1_fwd(const float* x, const float* w, const float* bias, float* y
                      long long S, int act, int beta, rpde_stream_t stream) {
   if (!x || !w || !y || B <= 0 || I <= 0 || O <= 0 || S <= 0 || S > INT_MAX)
     return fail(RPDE_E_INVALID, "rpde_conv1x1_fwd: bad arguments%s");
+  auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+  if (I <= 4 && !act && !z && !beta && (S % 4) == 0 && O <= 1024 && al16(x) && al16(y)) {
+    // few input channels (lifting layer): one streaming kernel instead of a K = I contraction
+    const long long total = (long long)B * (S / 4);
+    long long blocks = (total + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    const size_t sm = (size_t)(O * I + O) * sizeof(float);
+    cudaStream_t s = (cudaStream_t)stream;
+    switch (I) {
+      case 1: conv1x1_smallk_fwd_kernel<1><<<(unsigned)blocks, 256, sm, s>>>(x, w, bias, y, B, O, S); break;
+      case 2: conv1x1_smallk_fwd_kernel<2><<<(unsigned)blocks, 256, sm, s>>>(x, w, bias, y, B, O, S); break;
+      case 3: conv1x1_smallk_fwd_kernel<3><<<(unsigned)blocks, 256, sm, s>>>(x, w, bias, y, B, O, S); break;
+      default: conv1x1_smallk_fwd_kernel<4><<<(unsigned)blocks, 256, sm, s>>>(x, w, bias, y, B, O, S); break;
+    }
+    RPDE_LAUNCH_CHECK();
+    return RPDE_OK;
+  }
   GemmP g = gemm_default();
   g.A = w; g.B = x; g.C = y;
   g.batch = B; g.M = O; g.N = (int)S; g.K = I;

@@ -80,16 +80,37 @@ def _compare_model(kind, m, x, y, hyper, tol=TOL):
     assert_grads_close(g, {k: v for k, v in g_o.items()}, tol)
 
 
+def _relu_margin(kind, m, x, y, hyper):
+    """Smallest |pre-activation| / rms over every ReLU input of the fp64 oracle.  Below fp32 resolution the mask of that
+    element is a coin toss in any fp32 implementation (the gradient is discontinuous there), so such a draw cannot
+    be held to 1e-5; the resolution tests skip to the next seed instead."""
+    import torch.nn.functional as F
+    from oracle import reference_port as rp
+    margins = []
+
+    def rec(t, *a, **k):
+        margins.append((t.abs().min() / t.pow(2).mean().sqrt()).item())
+        return F.relu(t, *a, **k)
+
+    sd = {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+    rp.step_loss_and_grads(kind, sd, x, y, dtype=torch.float64, **dict(hyper, activation=rec))
+    return min(margins)
+
+
 @pytest.mark.parametrize("n", [32, 33, 48, 64, 128, 256, 512, 1024, 2048])
 def test_fno1d_resolutions(n):
     import resolution_pde_b200 as R
-    torch.manual_seed(n)
-    m = R.FNO1d(1, 1, modes=16, width=32)
-    with torch.no_grad():
-        for b in m.fno_blocks:
-            b.spectral_conv.weights1.mul_(20.0)
-    x, y = torch.randn(3, 1, n), torch.randn(3, 1, n)
-    _compare_model("FNO1d", m, x, y, dict(activation="relu", n_blocks=4))
+    hyper = dict(activation="relu", n_blocks=4)
+    for seed in (n, n + 10000, n + 20000):
+        torch.manual_seed(seed)
+        m = R.FNO1d(1, 1, modes=16, width=32)
+        with torch.no_grad():
+            for b in m.fno_blocks:
+                b.spectral_conv.weights1.mul_(20.0)
+        x, y = torch.randn(3, 1, n), torch.randn(3, 1, n)
+        if _relu_margin("FNO1d", m, x, y, hyper) > 1e-6:   # seed 512 draws a pre-activation at 1.2e-8 of the rms
+            break
+    _compare_model("FNO1d", m, x, y, hyper)
 
 
 @pytest.mark.parametrize("hw", [(32, 32), (64, 64), (64, 128), (128, 128), (33, 47)])
