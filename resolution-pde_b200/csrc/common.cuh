@@ -47,6 +47,54 @@ __device__ __forceinline__ void gelu_both(float x, float& h, float& g) {
   h = x * cdf;
   g = fmaf(x * 0.39894228040143267794f, e, cdf);
 }
+
+// Two elements at a time on the packed fp32x2 pipe (FFMA2 / FMUL2 / FADD2, sm_100): the same fit, 11.5 instead of 19
+// floating-point instructions per element.  The GEMM epilogues that apply GELU are instruction-issue bound.
+typedef unsigned long long f32x2_t;
+__device__ __forceinline__ f32x2_t f2_pack(float a, float b) {
+  f32x2_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ void f2_unpack(f32x2_t r, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(r)); }
+__device__ __forceinline__ f32x2_t f2_fma(f32x2_t a, f32x2_t b, f32x2_t c) {
+  f32x2_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ f32x2_t f2_mul(f32x2_t a, f32x2_t b) {
+  f32x2_t d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ f32x2_t f2_add(f32x2_t a, f32x2_t b) {
+  f32x2_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ f32x2_t f2_c(float c) { return f2_pack(c, c); }
+__device__ __forceinline__ void gelu_both2(float x0, float x1, float& h0, float& h1, float& g0, float& g1) {
+  float s0, s1, e0, e1, a0, a1, d0, d1;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(s0) : "f"(fmaf(fabsf(x0), 0.35355339059327376f, 1.0f)));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(s1) : "f"(fmaf(fabsf(x1), 0.35355339059327376f, 1.0f)));
+  const f32x2_t x = f2_pack(x0, x1);
+  f2_unpack(f2_mul(f2_mul(x, x), f2_c(-0.72134752044448170f)), a0, a1);
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(a0));  // exp(-x^2/2)
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(a1));
+  const f32x2_t s = f2_pack(s0, s1), e = f2_pack(e0, e1);
+  f32x2_t q = f2_c(0.5f * 0.0588021083f);  // the 1/2 of Phi(-|x|) = q(s) s e / 2 rides in the coefficients (exact)
+  q = f2_fma(q, s, f2_c(0.5f * -0.218240167f));
+  q = f2_fma(q, s, f2_c(0.5f * 0.12218285f));
+  q = f2_fma(q, s, f2_c(0.5f * 0.307675597f));
+  q = f2_fma(q, s, f2_c(0.5f * 0.130846771f));
+  q = f2_fma(q, s, f2_c(0.5f * 0.321697673f));
+  q = f2_fma(q, s, f2_c(0.5f * 0.277035179f));
+  const f32x2_t tail = f2_mul(f2_mul(q, s), e);                      // Phi(-|x|) <= 1/2
+  f2_unpack(f2_fma(tail, f2_c(-1.0f), f2_c(0.5f)), d0, d1);          // 1/2 - Phi(-|x|) >= 0
+  const f32x2_t cdf = f2_add(f2_pack(copysignf(d0, x0), copysignf(d1, x1)), f2_c(0.5f));
+  f2_unpack(f2_mul(x, cdf), h0, h1);
+  f2_unpack(f2_fma(f2_mul(x, e), f2_c(0.39894228040143267794f), cdf), g0, g1);
+}
 __device__ __forceinline__ float gelu_f(float x) {
   float h, g;
   gelu_both(x, h, g);

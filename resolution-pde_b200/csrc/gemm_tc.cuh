@@ -165,7 +165,10 @@ __device__ __forceinline__ void tile_coords(const TcParams& P, int t, int& tm, i
 __device__ __forceinline__ void act32(int act, float (&v)[32]) {
   if (act == ACT_GELU) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] = gelu_f(v[j]);
+    for (int j = 0; j < 32; j += 2) {
+      float g0, g1;
+      gelu_both2(v[j], v[j + 1], v[j], v[j + 1], g0, g1);
+    }
   } else if (act == ACT_RELU) {
 #pragma unroll
     for (int j = 0; j < 32; ++j) v[j] = v[j] > 0.f ? v[j] : 0.f;
@@ -752,7 +755,7 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
                 for (int j = 0; j < 32; ++j) w[j] = v[j];
               } else if (f_act == ACT_GELU) {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) gelu_both(v[j], v[j], w[j]);
+                for (int j = 0; j < 32; j += 2) gelu_both2(v[j], v[j + 1], v[j], v[j + 1], w[j], w[j + 1]);
               } else {
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
