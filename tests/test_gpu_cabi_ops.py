@@ -117,3 +117,57 @@ def test_dft_table_planes_match_interleaved(n, k):
     want = torch.fft.irfft(full, n=n)
     got = t4[0].double().cpu().T @ spec.real + t4[1].double().cpu().T @ spec.imag
     assert rel(got, want) < 1e-6
+
+
+@pytest.mark.parametrize("T,C", [(3001, 16), (777, 32), (4099, 64), (1025, 128), (513, 48), (300, 20)])
+@pytest.mark.parametrize("with_res", [False, True])
+def test_layernorm_fwd_bwd_all_widths(lib, T, C, with_res):
+    """C in {16, 32, 64, 128} runs the vectorised kernels (float4 per lane, ragged row tails), other widths the scalar ones."""
+    torch.manual_seed(T + C)
+    x = torch.randn(T, C, device=DEV, dtype=torch.float64, requires_grad=True) * 3 + 0.5
+    x.retain_grad()
+    gamma = torch.randn(C, device=DEV, dtype=torch.float64, requires_grad=True)
+    beta = torch.randn(C, device=DEV, dtype=torch.float64, requires_grad=True)
+    res = torch.randn(T, C, device=DEV, dtype=torch.float64)
+    dy = torch.randn(T, C, device=DEV, dtype=torch.float64)
+    ref = torch.nn.functional.layer_norm(x, (C,), gamma, beta, 1e-5) + (res if with_res else 0)
+    ref.backward(dy)
+    xf, gf, bf, rf, dyf = x.detach().float(), gamma.detach().float(), beta.detach().float(), res.float(), dy.float()
+    y = torch.empty(T, C, device=DEV)
+    mean, rstd = torch.empty(T, device=DEV), torch.empty(T, device=DEV)
+    rc = lib.rpde_layernorm_fwd(xf.data_ptr(), rf.data_ptr() if with_res else None, gf.data_ptr(), bf.data_ptr(), y.data_ptr(),
+                                mean.data_ptr(), rstd.data_ptr(), T, C, ctypes.c_float(1e-5), _st())
+    assert rc == 0, lib.rpde_last_error()
+    assert rel(y, ref) < TOL
+    assert rel(mean, xf.double().mean(1)) < TOL
+    assert rel(rstd, 1.0 / torch.sqrt(xf.double().var(1, unbiased=False) + 1e-5)) < TOL
+    dx = torch.empty(T, C, device=DEV)
+    dg, dbt, dxs = (torch.empty(C, device=DEV) for _ in range(3))
+    rc = lib.rpde_layernorm_bwd(dyf.data_ptr(), xf.data_ptr(), gf.data_ptr(), mean.data_ptr(), rstd.data_ptr(), dx.data_ptr(),
+                                dg.data_ptr(), dbt.data_ptr(), dxs.data_ptr(), T, C, _st())
+    assert rc == 0, lib.rpde_last_error()
+    assert rel(dx, x.grad) < TOL and rel(dg, gamma.grad) < TOL and rel(dbt, beta.grad) < TOL
+    assert (dxs.double() - x.grad.sum(0)).abs().max().item() < 1e-4 * x.grad.abs().sum(0).max().item()
+
+
+@pytest.mark.parametrize("cin,S", [(1, 1024), (2, 512), (3, 64 * 64), (4, 260), (3, 33 * 47), (5, 256)])
+def test_lifting_conv_and_bias_grad_reduction(lib, cin, S):
+    """Channels-first 1x1 conv with few input channels (streaming kernel when S % 4 == 0 and cin <= 4, contraction engine
+    otherwise) and its parameter gradients (the bias gradient is the vectorised channel reduction)."""
+    B, O = 3, 32
+    torch.manual_seed(cin * 1000 + S)
+    x = torch.randn(B, cin, S, device=DEV, dtype=torch.float64)
+    w = torch.randn(O, cin, device=DEV, dtype=torch.float64, requires_grad=True)
+    b = torch.randn(O, device=DEV, dtype=torch.float64, requires_grad=True)
+    dy = torch.randn(B, O, S, device=DEV, dtype=torch.float64)
+    ref = torch.einsum("oi,bis->bos", w, x) + b[None, :, None]
+    ref.backward(dy)
+    xf, wf, bf, dyf = x.float(), w.detach().float().contiguous(), b.detach().float(), dy.float()
+    y = torch.empty(B, O, S, device=DEV)
+    rc = lib.rpde_conv1x1_fwd(xf.data_ptr(), wf.data_ptr(), bf.data_ptr(), y.data_ptr(), None, B, cin, O, S, 0, 0, _st())
+    assert rc == 0, lib.rpde_last_error()
+    assert rel(y, ref) < TOL
+    dw, db = torch.empty(O, cin, device=DEV), torch.empty(O, device=DEV)
+    rc = lib.rpde_conv1x1_bwd_params(dyf.data_ptr(), xf.data_ptr(), dw.data_ptr(), db.data_ptr(), B, cin, O, S, _st())
+    assert rc == 0, lib.rpde_last_error()
+    assert rel(dw, w.grad) < TOL and rel(db, b.grad) < TOL
