@@ -158,6 +158,17 @@ int rpde_rel_l2_fwd(const float* x, const float* y, float* acc, float* per_sampl
 int rpde_rel_l2_bwd(const float* x, const float* y, const float* acc, const float* gout, float* dx, int B,
                     long long S, int reduce_mode, rpde_stream_t stream);
 
+/* ---- fused multi-tensor AdamW (torch.optim.AdamW as the reference builds it: main_1d.py:144, main_2d.py:173;
+ * SURVEY 8f rank 1).  table: device array of ntensors records {float* p; const float* g; float* m; float* v;
+ * int64 n; int64 chunk0} (48 bytes each; chunk0 = index of the tensor's first 1024-element chunk, ascending);
+ * nchunks = total chunks; hyper: device float[4] = {lr, step count, 1 - beta1^t, 1 - beta2^t} (the last two are written
+ * by the call; betas are doubles because torch forms 1 - beta on the host in double).  The call advances the step count on the
+ * device, then applies   p *= 1 - lr*wd;  m += (g - m)(1 - beta1);  v = beta2 v + (1 - beta2) g*g;
+ * p -= lr / (1 - beta1^t) * m / (sqrt(v) / sqrt(1 - beta2^t) + eps)   to every element of every tensor in one
+ * launch.  Complex parameters ride as their (re, im) fp32 view, as in torch.  Graph-capturable. */
+int rpde_adamw_step(const void* table, int ntensors, long long nchunks, float* hyper, double beta1, double beta2,
+                    float eps, float weight_decay, rpde_stream_t stream);
+
 /* ---- raw contraction (test hook): C[M,N] = A[M,K] B[K,N], row-major, through the selected engine -------- */
 int rpde_matmul(const float* a, const float* b, float* c, int M, int N, int K, int trans_a, int trans_b,
                 rpde_stream_t stream);

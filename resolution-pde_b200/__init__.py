@@ -13,10 +13,11 @@ from .fno_blocks import FNOBlock1d, FNOBlock2d, MLP1d, MLP2d
 from .loss import RelativeL2Loss
 from .ops import get_precision, set_precision
 from .training import GraphedTrainStep
+from .optim import FusedAdamW
 from .spectral_convolution import FSpectralConv1d, FSpectralConv2d, SpectralConv1d, SpectralConv2d
 
 __all__ = [
     "SpectralConv1d", "SpectralConv2d", "FSpectralConv1d", "FSpectralConv2d", "FNOBlock1d", "FNOBlock2d", "MLP1d",
     "MLP2d", "FNO1d", "FNO2d", "FFNO1D", "FFNO2D", "FeedForward", "WNLinear", "Linear", "RelativeL2Loss",
-    "set_precision", "get_precision", "ops", "GraphedTrainStep",
+    "set_precision", "get_precision", "ops", "GraphedTrainStep", "FusedAdamW",
 ]

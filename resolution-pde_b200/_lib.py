@@ -53,6 +53,7 @@ SIGNATURES = {
     "rpde_concat_grid_bwd": (I, [P, P, I, I, I, I, I, I, S]),
     "rpde_rel_l2_fwd": (I, [P, P, P, P, P, I, L, I, S]),
     "rpde_rel_l2_bwd": (I, [P, P, P, P, P, I, L, I, S]),
+    "rpde_adamw_step": (I, [P, I, L, P, c_double, c_double, c_float, c_float, S]),
     "rpde_matmul": (I, [P, P, P, I, I, I, I, I, S]),
 }
 

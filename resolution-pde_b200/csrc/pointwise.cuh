@@ -643,4 +643,68 @@ static inline unsigned grid_for(long long n, int threads = 256, int cap = 148 * 
   return (unsigned)g;
 }
 
+// ------------------------------------------------------------------------------------------------ fused AdamW
+// One launch updates every parameter tensor of the model (torch.optim.AdamW semantics, main_1d.py:144, main_2d.py:173):
+//   p *= 1 - lr*wd;  m += (g - m)(1 - b1);  v = b2 v + (1 - b2) g^2;  p -= lr/(1 - b1^t) * m / (sqrt(v)/sqrt(1 - b2^t) + eps)
+// The tensor table lives on the device (pointers + element counts + the first 1024-element chunk of each tensor); lr
+// and the step count are device scalars (hyper = {lr, t, 1 - b1^t, 1 - b2^t}), so the launch can sit inside a captured
+// training step: adamw_tick advances t and refreshes the bias corrections.
+struct AdamWTensor {
+  float* p;
+  const float* g;
+  float* m;
+  float* v;
+  long long n;
+  long long chunk0;  // index of this tensor's first chunk in the flattened chunk range
+};
+__global__ void adamw_tick_kernel(float* __restrict__ hyper, double beta1, double beta2) {
+  const float t = hyper[1] + 1.0f;  // bias corrections in double, as torch computes them on the host
+  hyper[1] = t;
+  hyper[2] = (float)(1.0 - pow(beta1, (double)t));
+  hyper[3] = (float)(1.0 - pow(beta2, (double)t));
+}
+__global__ void __launch_bounds__(256) adamw_multi_kernel(const AdamWTensor* __restrict__ tab, int ntensors,
+                                                          const float* __restrict__ hyper, float beta1, float beta2,
+                                                          float omb1, float omb2, float eps, float wd, long long nchunks) {
+  const float lr = hyper[0], bc1 = hyper[2], bc2 = hyper[3];
+  const float step_size = lr / bc1, rs_bc2 = 1.0f / sqrtf(bc2), decay = 1.0f - lr * wd;
+  for (long long c = blockIdx.x; c < nchunks; c += gridDim.x) {
+    int lo = 0, hi = ntensors - 1;  // last tensor whose chunk0 <= c
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (tab[mid].chunk0 <= c) lo = mid;
+      else hi = mid - 1;
+    }
+    const AdamWTensor T = tab[lo];
+    const long long e = (c - T.chunk0) * 1024 + threadIdx.x * 4;
+    if (e >= T.n) continue;
+    if (e + 4 <= T.n && ((reinterpret_cast<uintptr_t>(T.p) | reinterpret_cast<uintptr_t>(T.g) | reinterpret_cast<uintptr_t>(T.m) |
+                          reinterpret_cast<uintptr_t>(T.v)) & 15) == 0) {
+      float4 p4 = *reinterpret_cast<const float4*>(T.p + e);
+      const float4 g4 = *reinterpret_cast<const float4*>(T.g + e);
+      float4 m4 = *reinterpret_cast<const float4*>(T.m + e);
+      float4 v4 = *reinterpret_cast<const float4*>(T.v + e);
+      float* pp = &p4.x; const float* gg = &g4.x; float* mm = &m4.x; float* vv = &v4.x;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        mm[j] = mm[j] + (gg[j] - mm[j]) * omb1;
+        vv[j] = vv[j] * beta2 + omb2 * gg[j] * gg[j];
+        pp[j] = pp[j] * decay - step_size * (mm[j] / (sqrtf(vv[j]) * rs_bc2 + eps));
+      }
+      *reinterpret_cast<float4*>(T.p + e) = p4;
+      *reinterpret_cast<float4*>(T.m + e) = m4;
+      *reinterpret_cast<float4*>(T.v + e) = v4;
+    } else {
+      for (long long i = e; i < T.n && i < e + 4; ++i) {
+        const float g = T.g[i];
+        const float m = T.m[i] + (g - T.m[i]) * omb1;
+        const float v = T.v[i] * beta2 + omb2 * g * g;
+        T.m[i] = m;
+        T.v[i] = v;
+        T.p[i] = T.p[i] * decay - step_size * (m / (sqrtf(v) * rs_bc2 + eps));
+      }
+    }
+  }
+}
+
 }  // namespace rpde

@@ -877,6 +877,22 @@ int rpde_rel_l2_bwd(const float* x, const float* y, const float* acc, const floa
   return RPDE_OK;
 }
 
+int rpde_adamw_step(const void* table, int ntensors, long long nchunks, float* hyper, double beta1, double beta2,
+                    float eps, float weight_decay, rpde_stream_t stream) {
+  if (!table || !hyper || ntensors <= 0 || nchunks <= 0 || !(beta1 >= 0.f && beta1 < 1.f) || !(beta2 >= 0.f && beta2 < 1.f))
+    return fail(RPDE_E_INVALID, "rpde_adamw_step: bad arguments%s");
+  static_assert(sizeof(AdamWTensor) == 48, "the table layout is part of the ABI (6 x 8 bytes per tensor)");
+  cudaStream_t s = (cudaStream_t)stream;
+  adamw_tick_kernel<<<1, 1, 0, s>>>(hyper, beta1, beta2);
+  RPDE_LAUNCH_CHECK();
+  const long long blocks = nchunks < 148LL * 16 ? nchunks : 148LL * 16;
+  adamw_multi_kernel<<<(unsigned)blocks, 256, 0, s>>>(reinterpret_cast<const AdamWTensor*>(table), ntensors, hyper, (float)beta1,
+                                                     (float)beta2, (float)(1.0 - beta1), (float)(1.0 - beta2), eps,
+                                                     weight_decay, nchunks);
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+
 int rpde_matmul(const float* a, const float* b, float* c, int M, int N, int K, int trans_a, int trans_b,
                 rpde_stream_t stream) {
   if (!a || !b || !c || M <= 0 || N <= 0 || K <= 0) return fail(RPDE_E_INVALID, "rpde_matmul: bad arguments%s");

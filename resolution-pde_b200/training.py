@@ -21,10 +21,14 @@ import torch
 class GraphedTrainStep:
     """step(x, y) -> loss (0-dim device tensor).  x, y may live on the device or in pinned host memory."""
 
-    def __init__(self, model: torch.nn.Module, loss_fn: Callable, warmup: int = 2):
+    def __init__(self, model: torch.nn.Module, loss_fn: Callable, warmup: int = 2, optimizer=None):
+        """optimizer: an optional `optim.FusedAdamW`; its update is then captured too (a second graph replayed right
+        after the first: its device table needs the gradient pointers the first capture creates) and `step(x, y)`
+        becomes zero_grad + forward + loss + backward + AdamW with no host work besides the two replays."""
         self.model = model
         self.loss_fn = loss_fn
         self.warmup = warmup
+        self.optimizer = optimizer
         self._graphs: Dict[Tuple, Tuple] = {}
 
     def _capture(self, x: torch.Tensor, y: torch.Tensor):
@@ -49,7 +53,14 @@ class GraphedTrainStep:
         # the gradient tensors written by this graph (its pool owns them); re-attached to the parameters after a replay
         params = [q for q in self.model.parameters() if q.grad is not None]
         grads = [q.grad for q in params]
-        return g, sx, sy, loss, params, grads
+        g_opt = None
+        if self.optimizer is not None:
+            self.optimizer.prepare()            # device tables for exactly these gradient tensors (H2D, outside capture)
+            self.optimizer.sync_lr()
+            g_opt = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g_opt, pool=g.pool()):
+                self.optimizer.launch()
+        return g, sx, sy, loss, params, grads, g_opt
 
     def __call__(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
         key = (tuple(x.shape), tuple(y.shape))
@@ -57,7 +68,7 @@ class GraphedTrainStep:
         if ent is None:
             ent = self._capture(x, y)
             self._graphs[key] = ent
-        g, sx, sy, loss, params, grads = ent
+        g, sx, sy, loss, params, grads, g_opt = ent
         if x.data_ptr() != sx.data_ptr():
             sx.copy_(x, non_blocking=True)
         if y.data_ptr() != sy.data_ptr():
@@ -65,6 +76,9 @@ class GraphedTrainStep:
         g.replay()
         for q, gr in zip(params, grads):
             q.grad = gr
+        if g_opt is not None:
+            self.optimizer.sync_lr()
+            g_opt.replay()
         return loss
 
     def static_inputs(self, x_shape, y_shape) -> Optional[Tuple[torch.Tensor, torch.Tensor]]:

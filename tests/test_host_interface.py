@@ -89,3 +89,24 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in src and "/root/reference" not in src, f
+
+
+def test_fused_adamw_host_contract():
+    """Constructor mirrors torch.optim.AdamW; unsupported switches raise; CPU tensors raise at step (no fallback)."""
+    import pytest
+    import torch
+    import resolution_pde_b200 as R
+    p = torch.nn.Parameter(torch.randn(5))
+    with pytest.raises(ValueError):
+        R.FusedAdamW([p], amsgrad=True)
+    with pytest.raises(ValueError):
+        R.FusedAdamW([p], betas=(1.0, 0.999))
+    opt = R.FusedAdamW([p], lr=2e-3, weight_decay=0.1)
+    ref = torch.optim.AdamW([torch.nn.Parameter(torch.randn(5))], lr=2e-3, weight_decay=0.1)
+    for k in ("lr", "betas", "eps", "weight_decay"):
+        assert opt.param_groups[0][k] == ref.param_groups[0][k]
+    assert set(ref.param_groups[0]) <= set(opt.param_groups[0]) | {"params"}   # state dicts load both ways
+    opt.step()                                                                  # no gradients yet: nothing to do
+    p.grad = torch.randn(5)
+    with pytest.raises(RuntimeError):
+        opt.step()
