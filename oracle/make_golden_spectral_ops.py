@@ -1,0 +1,53 @@
+"""Generate tests/golden/specops_*.npz from the UNMODIFIED reference utilities (build container only).
+
+Run:  python oracle/make_golden_spectral_ops.py        (needs /root/reference; CPU only)
+utils/low_pass_filter.py and utils/res_utils.py are imported as they are; seeded fp32 inputs, reference outputs.
+"""
+from __future__ import annotations
+
+import importlib.util
+import os
+
+import numpy as np
+import torch
+
+REF = os.environ.get("RPDE_REFERENCE", "/root/reference")
+OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden")
+
+
+def _load(name, rel):
+    spec = importlib.util.spec_from_file_location(name, os.path.join(REF, rel))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def main():
+    lp = _load("ref_low_pass_filter", "utils/low_pass_filter.py")
+    ru = _load("ref_res_utils", "utils/res_utils.py")
+    g = torch.Generator().manual_seed(2024)
+    cases = {}
+    for shape, ratio in [((2, 3, 2, 64), 0.25), ((2, 3, 48), 0.5), ((1, 2, 1, 33), 0.3), ((2, 2, 32), 1.0), ((1, 1, 16), 0.05)]:
+        x = torch.randn(*shape, generator=g)
+        cases[f"lowpass1d_{'x'.join(map(str, shape))}_r{ratio}"] = dict(x=x, ratio=ratio, y=lp.lowpass_filter_1d(x.clone(), ratio))
+    for shape, ratio in [((2, 2, 1, 32, 32), 0.25), ((1, 3, 16, 16), 0.5), ((1, 1, 2, 24, 24), 0.125), ((1, 2, 15, 15), 0.4),
+                         ((1, 1, 16, 16), 1.0)]:
+        x = torch.randn(*shape, generator=g)
+        cases[f"lowpass2d_{'x'.join(map(str, shape))}_r{ratio}"] = dict(x=x, ratio=ratio, y=lp.lowpass_filter_2d(x.clone(), ratio))
+    for shape, out in [((2, 3, 64), 32), ((2, 2, 32), 64), ((1, 4, 48), 48), ((3, 33), 20), ((2, 20), 33), ((2, 64), 16)]:
+        x = torch.randn(*shape, generator=g)
+        cases[f"resize1d_{'x'.join(map(str, shape))}_to{out}"] = dict(x=x, out=out, y=ru.resize_1d(x.clone(), out))
+    for shape, out, perm in [((2, 2, 32, 32), (16, 16), False), ((1, 3, 16, 16), (32, 32), False), ((2, 1, 24, 16), (12, 32), False),
+                             ((1, 16, 16, 2), (8, 8), True), ((1, 2, 16, 20), (16, 20), False), ((1, 1, 32, 30), (16, 15), False)]:
+        x = torch.randn(*shape, generator=g)
+        cases[f"resize2d_{'x'.join(map(str, shape))}_to{out[0]}x{out[1]}_p{int(perm)}"] = dict(
+            x=x, out=np.array(out), permute=perm, y=ru.resize(x.clone(), out, permute=perm))
+    os.makedirs(OUT, exist_ok=True)
+    for name, c in cases.items():
+        np.savez_compressed(os.path.join(OUT, f"specops_{name}.npz"),
+                            **{k: (v.numpy() if torch.is_tensor(v) else np.asarray(v)) for k, v in c.items()})
+    print(f"wrote {len(cases)} fixtures")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,62 @@
+"""TEST INFRASTRUCTURE ONLY - CPU restatement of the reference's spectral data-preparation operators.
+
+Pinned by tests/golden/specops_*.npz, generated from the unmodified reference by oracle/make_golden_spectral_ops.py
+(tests/test_oracle_golden.py checks this file against them).  Nothing in the product imports it.
+Each function states the reference lines it follows; evaluated in float64 it is the arbiter of the GPU tests.
+"""
+from __future__ import annotations
+
+import torch
+
+
+def lowpass_filter_1d(data: torch.Tensor, cutoff_ratio: float = 0.25) -> torch.Tensor:
+    """utils/low_pass_filter.py:3-40: rfft along the last axis, bins >= int(n_bins * ratio) set to zero, irfft(n=N)."""
+    spec = torch.fft.rfft(data, dim=-1)
+    keep = int(spec.shape[-1] * cutoff_ratio)
+    spec = torch.cat([spec[..., :keep], torch.zeros_like(spec[..., keep:])], dim=-1)
+    return torch.fft.irfft(spec, n=data.shape[-1], dim=-1)
+
+
+def lowpass_filter_2d(data: torch.Tensor, cutoff_ratio: float = 0.25) -> torch.Tensor:
+    """utils/low_pass_filter.py:42-100: rfft2, rectangular mask |f_y| <= ratio/2 (fftfreq) x f_x <= ratio/2 (rfftfreq),
+    both grids in float32 as the reference builds them, irfft2(s=(S, S))."""
+    s = data.shape[-1]
+    spec = torch.fft.rfft2(data, dim=(-2, -1))
+    cut = cutoff_ratio * 0.5
+    keep_y = torch.abs(torch.fft.fftfreq(s)) <= cut
+    keep_x = torch.abs(torch.fft.rfftfreq(s)) <= cut
+    mask = (keep_y[:, None] & keep_x[None, :]).to(spec.real.dtype)
+    return torch.fft.irfft2(spec * mask, s=(s, s), dim=(-2, -1))
+
+
+def resize_1d(x: torch.Tensor, out_size: int) -> torch.Tensor:
+    """utils/res_utils.py:93-125: rfft, the first min(n_in/2+1, out/2+1) bins copied into a zero spectrum of out/2+1
+    bins, irfft(n=out), times out/in."""
+    n_in = x.shape[-1]
+    spec = torch.fft.rfft(x, dim=-1)
+    out_bins = out_size // 2 + 1
+    k = min(spec.shape[-1], out_bins)
+    padded = torch.zeros(*x.shape[:-1], out_bins, dtype=spec.dtype)
+    padded[..., :k] = spec[..., :k]
+    return torch.fft.irfft(padded, n=out_size, dim=-1) * (out_size / n_in)
+
+
+def resize(x: torch.Tensor, out_size, permute: bool = False) -> torch.Tensor:
+    """utils/res_utils.py:29-50: rfft2; rows [0, top) and the last `bot` rows, columns [0, kx) copied into a zero
+    spectrum of the output size; irfft2(s=out); times (H_out/H_in)(W_out/W_in)."""
+    if permute:
+        x = x.permute(0, 3, 1, 2)
+    h_in, w_in = x.shape[-2], x.shape[-1]
+    h_out, w_out = out_size
+    spec = torch.fft.rfft2(x)
+    top = min((h_in + 1) // 2, (h_out + 1) // 2)
+    bot = min(h_in // 2, h_out // 2)
+    kx = min(spec.shape[-1], w_out // 2 + 1)
+    padded = torch.zeros(*x.shape[:-2], h_out, w_out // 2 + 1, dtype=spec.dtype)
+    padded[..., :top, :kx] = spec[..., :top, :kx]
+    if bot > 0:
+        padded[..., h_out - bot:, :kx] = spec[..., h_in - bot:, :kx]
+    y = torch.fft.irfft2(padded, s=(h_out, w_out)) * (h_out / h_in) * (w_out / w_in)
+    if permute:
+        y = y.permute(0, 2, 3, 1)
+    return y
