@@ -1,4 +1,4 @@
-"""Generate tests/golden/specops_*.npz from the UNMODIFIED reference utilities (build container only).
+"""Generate tests/golden/specops/specops_*.npz from the UNMODIFIED reference utilities (build container only).
 
 Run:  python oracle/make_golden_spectral_ops.py        (needs /root/reference; CPU only)
 utils/low_pass_filter.py and utils/res_utils.py are imported as they are; seeded fp32 inputs, reference outputs.
@@ -12,7 +12,7 @@ import numpy as np
 import torch
 
 REF = os.environ.get("RPDE_REFERENCE", "/root/reference")
-OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden")
+OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden", "specops")
 
 
 def _load(name, rel):

@@ -1,6 +1,6 @@
 """TEST INFRASTRUCTURE ONLY - CPU restatement of the reference's spectral data-preparation operators.
 
-Pinned by tests/golden/specops_*.npz, generated from the unmodified reference by oracle/make_golden_spectral_ops.py
+Pinned by tests/golden/specops/*.npz, generated from the unmodified reference by oracle/make_golden_spectral_ops.py
 (tests/test_oracle_golden.py checks this file against them).  Nothing in the product imports it.
 Each function states the reference lines it follows; evaluated in float64 it is the arbiter of the GPU tests.
 """

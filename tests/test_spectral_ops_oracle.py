@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 import torch
 
-GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "specops")
 CASES = sorted(glob.glob(os.path.join(GOLDEN, "specops_*.npz")))
 
 
