@@ -322,6 +322,11 @@ gemm_tc_kernel(const __grid_constant__ TcParams P, const __grid_constant__ CUten
   tc_fence_after_sync();
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+  // Programmatic dependent launch: everything above (barriers, TMEM, descriptor prefetch) touches no global data and may
+  // run while the previous kernel of the stream drains; from here on its results are needed.  The next kernel may
+  // begin its own prologue as soon as every CTA of this one has passed this point.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
   if (warp == 0 || warp == kProducerBWarp) {
     // ------------------------------------------------------------------ TMA producers: warp 0 loads the A tiles, the last
@@ -1220,6 +1225,21 @@ static cudaError_t launch_cfg(const TcParams& P, const CUtensorMap& ma, const CU
   });
   if (attr_rc != cudaSuccess) return attr_rc;
   const int grid = P.total_tiles < sms ? P.total_tiles : sms;
+  static const bool pdl = !(getenv("RPDE_TC_PDL") && atoi(getenv("RPDE_TC_PDL")) == 0);
+  if (pdl) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = C::smem_bytes;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, SPLIT, CH>, P, ma, mb, em.c, em.z, em.i);
+  }
   gemm_tc_kernel<BN, SPLIT, CH><<<grid, kThreads, C::smem_bytes, s>>>(P, ma, mb, em.c, em.z, em.i);
   return cudaGetLastError();
 }

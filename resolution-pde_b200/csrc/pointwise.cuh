@@ -471,7 +471,8 @@ __global__ void reduce_channels_kernel(const float* __restrict__ X, float* __res
     if (threadIdx.x == 0) {
       float tsum = 0.f;
       for (int k = 0; k < (int)(blockDim.x >> 5); ++k) tsum += red[k];
-      atomicAdd(&out[c], tsum);
+      if (gridDim.x == 1) out[c] = tsum;  // one block owns the channel: plain store, the caller skips the memset
+      else atomicAdd(&out[c], tsum);
     }
   }
 }
