@@ -326,7 +326,7 @@ def main():
             ach = 2.0 * T * d * d / (kms * 1e-3) / 1e12
             # DRAM bytes per launch of this kernel from the ncu --set full capture (profiles/r1f_ncu_full_ffgemm_3xtf32.csv:
             # dram__bytes_read.sum + dram__bytes_write.sum); only known for the captured shape / engine
-            traffic = 2.1035e9 if (name == "ffno2d_ns256" and B == 16 and prec == "3xtf32") else None
+            traffic = 2.1020e9 if (name == "ffno2d_ns256" and B == 16 and prec == "3xtf32") else None
             vdiv = {"3xtf32": 6.0, "tf32": 2.0}.get(prec)
             roof = {"bound": "tensor", "achieved": ach, "peak": pk["tensor_burst"], "unit": "TFLOP/s", "frac": ach / pk["tensor_burst"],
                     "traffic": traffic, "kernel": f"contraction engine ({prec}), FeedForward hidden GEMM {T}x{d}x{d}", "kernel_ms": kms,
