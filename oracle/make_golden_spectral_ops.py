@@ -15,6 +15,18 @@ REF = os.environ.get("RPDE_REFERENCE", "/root/reference")
 OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden", "specops")
 
 
+def _stub_plotting():
+    """frequency_error.py imports matplotlib at module top for its plotting helpers; the metric functions never use it"""
+    import sys
+    import types
+    for name in ("matplotlib", "matplotlib.pyplot", "matplotlib.patches", "matplotlib.gridspec", "matplotlib.colors", "seaborn", "wandb"):
+        if name not in sys.modules:
+            try:
+                __import__(name)
+            except Exception:
+                sys.modules[name] = types.ModuleType(name)
+
+
 def _load(name, rel):
     spec = importlib.util.spec_from_file_location(name, os.path.join(REF, rel))
     mod = importlib.util.module_from_spec(spec)
@@ -42,6 +54,16 @@ def main():
         x = torch.randn(*shape, generator=g)
         cases[f"resize2d_{'x'.join(map(str, shape))}_to{out[0]}x{out[1]}_p{int(perm)}"] = dict(
             x=x, out=np.array(out), permute=perm, y=ru.resize(x.clone(), out, permute=perm))
+    _stub_plotting()
+    fe = _load("ref_frequency_error", "utils/frequency_error.py")
+    for shape, nm in [((3, 2, 64), None), ((2, 1, 48), 10), ((2, 2, 33), None), ((1, 1, 32), 100)]:
+        yh, yt = torch.randn(*shape, generator=g), torch.randn(*shape, generator=g)
+        e, m, f = fe.decompose_error_by_frequency_1d(yh.clone(), yt.clone(), nm)
+        cases[f"freqerr1d_{'x'.join(map(str, shape))}_m{nm}"] = dict(y_hat=yh, x=yt, num=-1 if nm is None else nm, err=e, mag=m, freqs=f)
+    for shape, nb in [((2, 2, 32, 32), 16), ((1, 1, 16, 24), 64), ((2, 1, 24, 16), 8), ((1, 2, 64, 64), 64)]:
+        yh, yt = torch.randn(*shape, generator=g), torch.randn(*shape, generator=g)
+        e, m, f = fe.decompose_error_by_frequency_2d(yh.clone(), yt.clone(), nb)
+        cases[f"freqerr2d_{'x'.join(map(str, shape))}_b{nb}"] = dict(y_hat=yh, x=yt, num=nb, err=e, mag=m, freqs=f)
     os.makedirs(OUT, exist_ok=True)
     for name, c in cases.items():
         np.savez_compressed(os.path.join(OUT, f"specops_{name}.npz"),

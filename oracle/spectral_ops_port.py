@@ -60,3 +60,41 @@ def resize(x: torch.Tensor, out_size, permute: bool = False) -> torch.Tensor:
     if permute:
         y = y.permute(0, 2, 3, 1)
     return y
+
+
+def decompose_error_by_frequency_1d(y_hat: torch.Tensor, y: torch.Tensor, num_modes=None):
+    """utils/frequency_error.py:37-91: for every retained rfft bin, keep only that bin of y_hat and of y, irfft(n=H), and
+    take the L2 norm over the whole batch of the difference and of the target part."""
+    import numpy as np
+    H = y.shape[-1]
+    fh, ft = torch.fft.rfft(y_hat, dim=-1), torch.fft.rfft(y, dim=-1)
+    k = ft.shape[-1] if num_modes is None else min(num_modes, ft.shape[-1])
+    err, mag = np.zeros(k), np.zeros(k)
+    for i in range(k):
+        sel = torch.zeros(ft.shape[-1], dtype=ft.real.dtype)
+        sel[i] = 1
+        sh = torch.fft.irfft(fh * sel, n=H, dim=-1)
+        st = torch.fft.irfft(ft * sel, n=H, dim=-1)
+        err[i] = torch.norm(sh - st).item()
+        mag[i] = torch.norm(st).item()
+    return err, mag, torch.fft.rfftfreq(H).numpy()[:k]
+
+
+def decompose_error_by_frequency_2d(y_hat: torch.Tensor, y: torch.Tensor, num_radial_bins: int = 64):
+    """utils/frequency_error.py:93-161: radial bands [e_i, e_{i+1}) of sqrt(fy^2 + fx^2) (float32 grids, float64 edges from
+    linspace(0, 0.5, bins + 1)); each band of rfft2 is inverse-transformed and normed; empty bands give 0."""
+    import numpy as np
+    H, W = y.shape[-2], y.shape[-1]
+    fh, ft = torch.fft.rfft2(y_hat, dim=(-2, -1)), torch.fft.rfft2(y, dim=(-2, -1))
+    radial = torch.sqrt(torch.fft.fftfreq(H).view(-1, 1) ** 2 + torch.fft.rfftfreq(W).view(1, -1) ** 2)
+    edges = np.linspace(0, 0.5, num_radial_bins + 1)
+    err, mag = np.zeros(num_radial_bins), np.zeros(num_radial_bins)
+    for i in range(num_radial_bins):
+        band = (radial >= edges[i]) & (radial < edges[i + 1])
+        if band.sum() == 0:
+            continue
+        sh = torch.fft.irfft2(fh * band, s=(H, W), dim=(-2, -1))
+        st = torch.fft.irfft2(ft * band, s=(H, W), dim=(-2, -1))
+        err[i] = torch.norm(sh - st).item()
+        mag[i] = torch.norm(st).item()
+    return err, mag, (edges[:-1] + edges[1:]) / 2

@@ -5,7 +5,7 @@ import os
 import pytest
 import torch
 
-from test_spectral_ops_oracle import CASES, rel, run_case
+from test_spectral_ops_oracle import CASES, FREQ_CASES, rel, run_case, run_freq_case, vec_rel
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
@@ -65,3 +65,27 @@ def test_cuda_matches_fp64_oracle_at_dataset_sizes(engine, case):
     else:
         x = torch.randn(3, 2, 64, 64); y = so.resize(x.to(DEV), (256, 256)); ref = port.resize(x.double(), (256, 256))
     assert rel(y, ref) < TOL
+
+
+@pytest.mark.parametrize("path", FREQ_CASES, ids=lambda p: os.path.basename(p)[8:-4])
+def test_frequency_error_matches_reference_fixture(engine, path):
+    """Parseval route on the device against the reference's mode-by-mode inverse FFTs."""
+    import resolution_pde_b200.frequency_error as fe
+    (e, m, f), (re, rm, rf) = run_freq_case(fe, path, to=DEV)
+    assert e.shape == re.shape and m.shape == rm.shape and f.shape == rf.shape
+    assert vec_rel(e, re) < TOL and vec_rel(m, rm) < TOL and vec_rel(f, rf) < 1e-7
+    assert abs(e - re).max() < 1e-5 * abs(re).max() and abs(m - rm).max() < 1e-5 * abs(rm).max()
+
+
+def test_frequency_error_at_dataset_sizes(engine):
+    from oracle import spectral_ops_port as port
+    import resolution_pde_b200.frequency_error as fe
+    torch.manual_seed(11)
+    yh, yt = torch.randn(8, 1, 1024), torch.randn(8, 1, 1024)
+    e, m, f = fe.decompose_error_by_frequency_1d(yh.to(DEV), yt.to(DEV), 64)
+    re, rm, rf = port.decompose_error_by_frequency_1d(yh.double(), yt.double(), 64)
+    assert vec_rel(e, re) < TOL and vec_rel(m, rm) < TOL
+    yh, yt = torch.randn(2, 1, 128, 128), torch.randn(2, 1, 128, 128)
+    e, m, f = fe.decompose_error_by_frequency_2d(yh.to(DEV), yt.to(DEV), 32)
+    re, rm, rf = port.decompose_error_by_frequency_2d(yh.double(), yt.double(), 32)
+    assert vec_rel(e, re) < TOL and vec_rel(m, rm) < TOL and vec_rel(f, rf) < 1e-12

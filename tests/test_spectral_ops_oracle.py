@@ -8,7 +8,8 @@ import pytest
 import torch
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "specops")
-CASES = sorted(glob.glob(os.path.join(GOLDEN, "specops_*.npz")))
+CASES = sorted(p for p in glob.glob(os.path.join(GOLDEN, "specops_*.npz")) if "freqerr" not in p)
+FREQ_CASES = sorted(glob.glob(os.path.join(GOLDEN, "specops_freqerr*.npz")))
 
 
 def run_case(mod, path, dtype=None):
@@ -33,7 +34,33 @@ def rel(a, b):
 
 
 def test_fixtures_present():
-    assert len(CASES) == 22
+    assert len(CASES) == 22 and len(FREQ_CASES) == 8
+
+
+def run_freq_case(mod, path, to=None):
+    d = np.load(path)
+    yh, yt = torch.from_numpy(d["y_hat"]), torch.from_numpy(d["x"])
+    if to is not None:
+        yh, yt = yh.to(to), yt.to(to)
+    num = int(d["num"])
+    if "freqerr1d" in path:
+        got = mod.decompose_error_by_frequency_1d(yh, yt, None if num < 0 else num)
+    else:
+        got = mod.decompose_error_by_frequency_2d(yh, yt, num)
+    return got, (d["err"], d["mag"], d["freqs"])
+
+
+def vec_rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-30))
+
+
+@pytest.mark.parametrize("path", FREQ_CASES, ids=[os.path.basename(p)[8:-4] for p in FREQ_CASES])
+def test_frequency_error_oracle_matches_reference_fixture(path):
+    from oracle import spectral_ops_port as port
+    (e, m, f), (re, rm, rf) = run_freq_case(port, path)
+    assert e.shape == re.shape and m.shape == rm.shape and f.shape == rf.shape
+    assert vec_rel(e, re) < 2e-6 and vec_rel(m, rm) < 2e-6 and vec_rel(f, rf) < 1e-7
 
 
 @pytest.mark.parametrize("path", CASES, ids=[os.path.basename(p)[8:-4] for p in CASES])

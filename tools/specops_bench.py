@@ -37,3 +37,22 @@ for name, shape, call in cases:
     print(json.dumps({"op": name, "shape": list(shape), "gpu_ms": round(gms, 4), "cpu_ms": round(cms, 3), "cpu_threads": torch.get_num_threads(),
                       "speedup": round(cms / gms, 1), "rel_err_vs_cpu_fp32": float(f"{err:.2e}"),
                       "hbm_frac": round(byts / (gms * 1e-3) / 1e9 / pk["hbm"], 3)}), flush=True)
+
+# frequency-resolved error metrics: Parseval on the device against the reference's mode-by-mode loop
+import resolution_pde_b200.frequency_error as fe
+for name, shape, call in [
+    ("decompose_error_by_frequency_1d (513 modes)", (64, 1, 1024), lambda f, a, b: f.decompose_error_by_frequency_1d(a, b, None)),
+    ("decompose_error_by_frequency_2d (64 bins)", (16, 1, 256, 256), lambda f, a, b: f.decompose_error_by_frequency_2d(a, b, 64)),
+]:
+    torch.manual_seed(1)
+    ah, bh = torch.randn(*shape), torch.randn(*shape)
+    ad, bd = ah.cuda(), bh.cuda()
+    for _ in range(3): got = call(fe, ad, bd)
+    torch.cuda.synchronize(); t0 = time.perf_counter()
+    for _ in range(10): got = call(fe, ad, bd)          # returns numpy: the device sync is inside
+    gms = (time.perf_counter() - t0) / 10 * 1e3
+    t0 = time.perf_counter(); ref = call(port, ah, bh); cms = (time.perf_counter() - t0) * 1e3
+    import numpy as np
+    err = float(np.linalg.norm(got[0] - ref[0]) / np.linalg.norm(ref[0]))
+    print(json.dumps({"op": name, "shape": list(shape), "gpu_ms_wall_incl_sync": round(gms, 4), "cpu_ms": round(cms, 2),
+                      "cpu_threads": torch.get_num_threads(), "speedup": round(cms / gms, 1), "rel_err_vs_cpu_fp32": float(f"{err:.2e}")}), flush=True)
