@@ -158,6 +158,31 @@ int rpde_rel_l2_fwd(const float* x, const float* y, float* acc, float* per_sampl
 int rpde_rel_l2_bwd(const float* x, const float* y, const float* acc, const float* gout, float* dx, int B,
                     long long S, int reduce_mode, rpde_stream_t stream);
 
+/* ---- autoregressive rollout on the device (utils/autoregressive_step.py:284-309 perform_rollout_1d and the
+ * per-step loss loop :170-196).  The state never leaves HBM between steps.
+ * rpde_rollout_renorm: one pass over the model output of step t, pred[b] = S contiguous floats at
+ * pred + b*pred_batch_stride (S = all non-batch elements: N in 1-D, H*W in 2-D; the stride lets the initial
+ * condition trajectories[:, 0] be encoded with y_scale = 1, y_mean = 0 and no gather copy, :155-162).
+ * preds_out + b*preds_batch_stride receives pred[b] unchanged (the reference's cat of normalised predictions;
+ * the caller passes the pointer of step t; NULL = no such store).  next_state (B, S) receives the next
+ * model input: renorm = 1 -> x_normalizer.encode(y_normalizer.decode(pred)) = ((pred*y_scale + y_mean) - x_mean)
+ * / x_scale with y_scale = std_y + eps and x_scale = std_x + eps (SimpleNormalizer, ks_naive_markov.py:396-406;
+ * four separately rounded fp32 operations like the reference's tensor-scalar ops); renorm = 0 -> pred (the
+ * reference's branch when a normaliser is None, :305-306). */
+int rpde_rollout_renorm(const float* pred, float* preds_out, float* next_state, int B, long long S,
+                        long long pred_batch_stride, long long preds_batch_stride, float y_scale, float y_mean,
+                        float x_mean, float x_scale, int renorm, rpde_stream_t stream);
+/* rpde_rollout_loss: every step's RelativeL2Loss(size_average=True) of the decoded rollout against the ground
+ * truth in one launch pair, instead of one loss call and one .item() per step (:192-196).  preds[b,t,:] at
+ * preds + b*preds_batch_stride + t*preds_step_stride, truth likewise (strides in floats: truth may be the view
+ * trajectories[:, 1:T+1] of a (B, T_all, S) tensor).  decode = 1 applies pred*y_scale + y_mean first (:176-181).
+ * acc: 2*B*T floats scratch; step_losses: T floats, step_losses[t] = mean_b ||p-y|| / (||y|| + 1e-8);
+ * batch_loss: 1 float = sum_t step_losses[t] / T.  B*T <= 65535. */
+int rpde_rollout_loss(const float* preds, const float* truth, float* acc, float* step_losses, float* batch_loss, int B,
+                      int T, long long S, long long preds_batch_stride, long long preds_step_stride,
+                      long long truth_batch_stride, long long truth_step_stride, float y_scale, float y_mean,
+                      int decode, rpde_stream_t stream);
+
 /* ---- fused multi-tensor AdamW (torch.optim.AdamW as the reference builds it: main_1d.py:144, main_2d.py:173;
  * SURVEY 8f rank 1).  table: device array of ntensors records {float* p; const float* g; float* m; float* v;
  * int64 n; int64 chunk0} (48 bytes each; chunk0 = index of the tensor's first 1024-element chunk, ascending);

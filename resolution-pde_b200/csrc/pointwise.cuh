@@ -549,6 +549,111 @@ __global__ void rel_l2_bwd_kernel(const float* __restrict__ x, const float* __re
 }
 
 // ----------------------------------------------------------------------------------------------
+// Autoregressive rollout (utils/autoregressive_step.py:284-309, :170-196).
+// rollout_renorm: one pass over the model output of step t.  Stores it into the trajectory of predictions
+// (the reference's torch.cat of `next_state_norm`) and writes the next model input
+//   encode_x(decode_y(p)) = ((p * ys + ym) - xm) / xs ,  ys = std_y + eps, xs = std_x + eps
+// with the reference's four separately rounded fp32 operations (no fma contraction), or a plain copy when the
+// reference skips the re-normalisation (a normaliser is None).
+// ----------------------------------------------------------------------------------------------
+__device__ __forceinline__ float rollout_reencode(float p, float ys, float ym, float xm, float xs) {
+  return __fdiv_rn(__fsub_rn(__fadd_rn(__fmul_rn(p, ys), ym), xm), xs);
+}
+
+template <int VEC>
+__global__ void rollout_renorm_kernel(const float* __restrict__ pred, float* __restrict__ preds_out,
+                                      float* __restrict__ next_state, long long S, long long pred_bs,
+                                      long long preds_bs, float ys, float ym, float xm, float xs, int renorm) {
+  const int b = blockIdx.y;
+  const float* pb = pred + (long long)b * pred_bs;
+  float* ob = preds_out ? preds_out + (long long)b * preds_bs : nullptr;
+  float* nb = next_state + (long long)b * S;
+  const long long n = S / VEC;
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x) {
+    if (VEC == 4) {
+      const float4 v = reinterpret_cast<const float4*>(pb)[e];
+      if (ob) reinterpret_cast<float4*>(ob)[e] = v;
+      float4 r = v;
+      if (renorm) {
+        r.x = rollout_reencode(v.x, ys, ym, xm, xs);
+        r.y = rollout_reencode(v.y, ys, ym, xm, xs);
+        r.z = rollout_reencode(v.z, ys, ym, xm, xs);
+        r.w = rollout_reencode(v.w, ys, ym, xm, xs);
+      }
+      reinterpret_cast<float4*>(nb)[e] = r;
+    } else {
+      const float v = pb[e];
+      if (ob) ob[e] = v;
+      nb[e] = renorm ? rollout_reencode(v, ys, ym, xm, xs) : v;
+    }
+  }
+}
+
+// rollout_loss: acc[(t*B + b)] = {sum (decode_y(pred[b,t]) - truth[b,t])^2, sum truth[b,t]^2} for every step of the
+// rollout in one launch (the reference loops over steps with one RelativeL2Loss + .item() each, :192-196).
+// (zero-filled by the caller; strides in floats, so `truth` can be the view trajectories[:, 1:T+1] with no copy)
+__global__ void rollout_loss_partial_kernel(const float* __restrict__ preds, const float* __restrict__ truth,
+                                            float* __restrict__ acc, int Bn, long long S, long long chunk,
+                                            long long p_bs, long long p_ts, long long t_bs, long long t_ts, float ys,
+                                            float ym, int decode) {
+  const int bt = blockIdx.y, t = bt / Bn, b = bt - t * Bn;
+  const long long e0 = blockIdx.x * chunk, e1 = min(S, e0 + chunk);
+  const float* pb = preds + b * p_bs + t * p_ts;
+  const float* yb = truth + b * t_bs + t * t_ts;
+  float d2 = 0.f, y2 = 0.f;
+  for (long long e = e0 + threadIdx.x; e < e1; e += blockDim.x) {
+    float p = pb[e];
+    if (decode) p = __fadd_rn(__fmul_rn(p, ys), ym);
+    const float yv = yb[e], d = p - yv;
+    d2 = fmaf(d, d, d2);
+    y2 = fmaf(yv, yv, y2);
+  }
+  d2 = warp_sum(d2);
+  y2 = warp_sum(y2);
+  __shared__ float r1[8], r2[8];
+  if ((threadIdx.x & 31) == 0) {
+    r1[threadIdx.x >> 5] = d2;
+    r2[threadIdx.x >> 5] = y2;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = 0.f, c = 0.f;
+    for (int k = 0; k < (int)(blockDim.x >> 5); ++k) {
+      a += r1[k];
+      c += r2[k];
+    }
+    atomicAdd(&acc[2 * bt], a);
+    atomicAdd(&acc[2 * bt + 1], c);
+  }
+}
+
+// step_losses[t] = mean_b sqrt(d2)/(sqrt(y2)+eps)  (RelativeL2Loss(size_average=True), utils/loss.py:31-59);
+// batch_loss[0] = sum_t step_losses[t] / T  (autoregressive_step.py:196).  One warp per step.
+__global__ void rollout_loss_finalize_kernel(const float* __restrict__ acc, float* __restrict__ step_losses,
+                                             float* __restrict__ batch_loss, int Bn, int Tn) {
+  __shared__ float tot[32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  float mine = 0.f;
+  for (int t = warp; t < Tn; t += nwarp) {
+    float s = 0.f;
+    for (int b = lane; b < Bn; b += 32) {
+      const float* a = acc + 2 * ((long long)t * Bn + b);
+      s += sqrtf(a[0]) / (sqrtf(a[1]) + 1e-8f);
+    }
+    s = warp_sum(s) / (float)Bn;
+    if (lane == 0) step_losses[t] = s;
+    mine += s;
+  }
+  if (lane == 0) tot[warp] = mine;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float z = 0.f;
+    for (int k = 0; k < nwarp; ++k) z += tot[k];
+    batch_loss[0] = z / (float)Tn;
+  }
+}
+
+// ----------------------------------------------------------------------------------------------
 // Grid concatenation: out = cat(x, grid...) along channels.  x is channels-first (B, Cin, S0[, S1]);
 // out is channels-first (B, Cin+G, S0, S1) or channels-last (B, S0, S1, Cin+G).  g0 indexes S0, g1 indexes S1.
 // ----------------------------------------------------------------------------------------------

@@ -5,6 +5,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <stdint.h>
 #include <atomic>
 
 #include "../../include/rpde_b200.h"
@@ -879,6 +880,53 @@ int rpde_rel_l2_bwd(const float* x, const float* y, const float* acc, const floa
   if (gx > cap) gx = cap;
   dim3 grid((unsigned)gx, (unsigned)B);
   rel_l2_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, y, acc, gout, dx, S, B, reduce_mode);
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+
+int rpde_rollout_renorm(const float* pred, float* preds_out, float* next_state, int B, long long S,
+                        long long pred_batch_stride, long long preds_batch_stride, float y_scale, float y_mean,
+                        float x_mean, float x_scale, int renorm, rpde_stream_t stream) {
+  if (!pred || !next_state || B <= 0 || S <= 0 || pred_batch_stride < S || (preds_out && preds_batch_stride < S) ||
+      (renorm && x_scale == 0.f))
+    return fail(RPDE_E_INVALID, "rpde_rollout_renorm: bad arguments%s");
+  const bool vec = S % 4 == 0 && pred_batch_stride % 4 == 0 && (!preds_out || preds_batch_stride % 4 == 0) &&
+                   (((uintptr_t)pred | (uintptr_t)preds_out | (uintptr_t)next_state) & 15) == 0;
+  const long long n = vec ? S / 4 : S;
+  long long gx = (n + 255) / 256;
+  const long long cap = (148LL * 8 + B - 1) / B;
+  if (gx > cap) gx = cap;
+  dim3 grid((unsigned)gx, (unsigned)B);
+  if (vec)
+    rollout_renorm_kernel<4><<<grid, 256, 0, (cudaStream_t)stream>>>(pred, preds_out, next_state, S, pred_batch_stride,
+                                                                     preds_batch_stride, y_scale, y_mean, x_mean,
+                                                                     x_scale, renorm);
+  else
+    rollout_renorm_kernel<1><<<grid, 256, 0, (cudaStream_t)stream>>>(pred, preds_out, next_state, S, pred_batch_stride,
+                                                                     preds_batch_stride, y_scale, y_mean, x_mean,
+                                                                     x_scale, renorm);
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+
+int rpde_rollout_loss(const float* preds, const float* truth, float* acc, float* step_losses, float* batch_loss, int B,
+                      int T, long long S, long long preds_batch_stride, long long preds_step_stride,
+                      long long truth_batch_stride, long long truth_step_stride, float y_scale, float y_mean,
+                      int decode, rpde_stream_t stream) {
+  if (!preds || !truth || !acc || !step_losses || !batch_loss || B <= 0 || T <= 0 || S <= 0 ||
+      (long long)B * T > 65535)
+    return fail(RPDE_E_INVALID, "rpde_rollout_loss: bad arguments (B*T must be <= 65535)%s");
+  cudaStream_t s = (cudaStream_t)stream;
+  const long long BT = (long long)B * T;
+  RPDE_CUDA(cudaMemsetAsync(acc, 0, (size_t)2 * BT * sizeof(float), s));
+  long long per = (148LL * 8 + BT - 1) / BT;
+  long long chunk = (S + per - 1) / per;
+  if (chunk < 4096) chunk = 4096;
+  dim3 grid((unsigned)((S + chunk - 1) / chunk), (unsigned)BT);
+  rollout_loss_partial_kernel<<<grid, 256, 0, s>>>(preds, truth, acc, B, S, chunk, preds_batch_stride, preds_step_stride,
+                                                   truth_batch_stride, truth_step_stride, y_scale, y_mean, decode);
+  RPDE_LAUNCH_CHECK();
+  rollout_loss_finalize_kernel<<<1, 256, 0, s>>>(acc, step_losses, batch_loss, B, T);
   RPDE_LAUNCH_CHECK();
   return RPDE_OK;
 }
