@@ -54,6 +54,13 @@ def main():
         x = torch.randn(*shape, generator=g)
         cases[f"resize2d_{'x'.join(map(str, shape))}_to{out[0]}x{out[1]}_p{int(perm)}"] = dict(
             x=x, out=np.array(out), permute=perm, y=ru.resize(x.clone(), out, permute=perm))
+    for shape, n in [((2, 3, 32), 16), ((2, 2, 33), 16), ((3, 32), 15), ((2, 20), 8), ((2, 16), 16), ((1, 2, 16), 32), ((2, 9), 8)]:
+        x = torch.randn(*shape, generator=g)
+        cases[f"downsample1d_{'x'.join(map(str, shape))}_to{n}"] = dict(x=x, out=n, y=ru.downsample_1d(x.numpy().copy(), n))
+    for shape, n in [((2, 3, 32, 32), 16), ((1, 2, 33, 33), 16), ((2, 1, 32, 32), 15), ((1, 1, 20, 20), 8), ((1, 2, 16, 16), 16),
+                     ((1, 1, 9, 9), 4)]:
+        x = torch.randn(*shape, generator=g)
+        cases[f"downsample2d_{'x'.join(map(str, shape))}_to{n}"] = dict(x=x, out=n, y=ru.downsample(x.numpy().copy(), n))
     _stub_plotting()
     fe = _load("ref_frequency_error", "utils/frequency_error.py")
     for shape, nm in [((3, 2, 64), None), ((2, 1, 48), 10), ((2, 2, 33), None), ((1, 1, 32), 100)]:
@@ -64,6 +71,11 @@ def main():
         yh, yt = torch.randn(*shape, generator=g), torch.randn(*shape, generator=g)
         e, m, f = fe.decompose_error_by_frequency_2d(yh.clone(), yt.clone(), nb)
         cases[f"freqerr2d_{'x'.join(map(str, shape))}_b{nb}"] = dict(y_hat=yh, x=yt, num=nb, err=e, mag=m, freqs=f)
+    # odd heights (one more positive than negative row kept, res_utils.py:35-40); drawn last so earlier cases keep their inputs
+    for shape, out in [((1, 2, 15, 16), (8, 8)), ((1, 1, 16, 16), (15, 12)), ((2, 1, 15, 15), (9, 9)), ((1, 1, 9, 12), (15, 16))]:
+        x = torch.randn(*shape, generator=g)
+        cases[f"resize2d_{'x'.join(map(str, shape))}_to{out[0]}x{out[1]}_p0"] = dict(
+            x=x, out=np.array(out), permute=False, y=ru.resize(x.clone(), out, permute=False))
     os.makedirs(OUT, exist_ok=True)
     for name, c in cases.items():
         np.savez_compressed(os.path.join(OUT, f"specops_{name}.npz"),

@@ -62,6 +62,29 @@ def resize(x: torch.Tensor, out_size, permute: bool = False) -> torch.Tensor:
     return y
 
 
+def _select(n_old: int, n: int) -> torch.Tensor:
+    """utils/res_utils.py:21-22, 79-82: fftfreq(n_old, d=1/n_old) within [-n/2, n/2 - 1]"""
+    freqs = torch.fft.fftfreq(n_old, d=1.0 / n_old, dtype=torch.float64)
+    return (freqs >= -n / 2) & (freqs <= n / 2 - 1)
+
+
+def downsample_1d(u: torch.Tensor, n: int) -> torch.Tensor:
+    """utils/res_utils.py:62-91: complex fft (norm='forward') along the last axis, the modes with -n/2 <= k <= n/2 - 1
+    kept in fft order, ifft (norm='forward') of that shorter spectrum, real part.  Output length = number of kept modes
+    (n for even n < n_old, n - 1 for odd n, n_old when nothing is cut)."""
+    sel = _select(u.shape[-1], n)
+    spec = torch.fft.fft(u, dim=-1, norm="forward")[..., sel]
+    return torch.fft.ifft(spec, dim=-1, norm="forward").real
+
+
+def downsample(u: torch.Tensor, n: int) -> torch.Tensor:
+    """utils/res_utils.py:19-27: the same on both axes of (B, C, S, S) fields: fft2 (norm='forward'), rows and
+    columns with -n/2 <= k <= n/2 - 1, ifft2 (norm='forward'), real part."""
+    sel = _select(u.shape[-2], n)
+    spec = torch.fft.fft2(u, norm="forward")[:, :, sel, :][:, :, :, sel]
+    return torch.fft.ifft2(spec, norm="forward").real
+
+
 def decompose_error_by_frequency_1d(y_hat: torch.Tensor, y: torch.Tensor, num_modes=None):
     """utils/frequency_error.py:37-91: for every retained rfft bin, keep only that bin of y_hat and of y, irfft(n=H), and
     take the L2 norm over the whole batch of the difference and of the target part."""

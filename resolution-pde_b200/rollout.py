@@ -215,21 +215,36 @@ class RolloutEvaluator:
         return out
 
 
-def evaluate_rollout(model, trajectory_loader: Iterable[torch.Tensor], rollout_steps: int = 10, x_normalizer=None,
-                     y_normalizer=None, use_graph: bool = True) -> float:
-    """Mean over batches of the per-batch rollout loss, the number `evaluate_1d_rollout_all_resolution` stores per
-    resolution (`autoregressive_step.py:128-131, 197-199, 238-240`); batches too short to roll out are skipped as there.
-    One host sync at the end instead of one per step."""
-    ev = RolloutEvaluator(model, rollout_steps, x_normalizer, y_normalizer, use_graph=use_graph)
-    dev = next(model.parameters()).device
-    total = torch.zeros((), dtype=torch.float32, device=dev)
-    n = 0
+def mean_over_batches(trajectory_loader: Iterable[torch.Tensor], batch_loss, device, distributed: bool = False, group=None) -> float:
+    """total_loss / num_batches of `autoregressive_step.py:128-131, 197-199, 238-240` with the batch losses kept on the
+    device: one host sync at the end instead of one per step.  Batches too short to roll out are skipped as there.
+    distributed=True ("rollout/eval sweeps shard trajectories/batches across ranks"): rank r takes the valid
+    batches r, r + world, ...; one all-reduce of (sum of batch losses, batch count) at the end, so every rank returns the
+    single-process mean.  No collective inside the rollout itself."""
+    import torch.distributed as dist
+    on = distributed and dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+    rank, world = (dist.get_rank(group), dist.get_world_size(group)) if on else (0, 1)
+    acc = torch.zeros(2, dtype=torch.float32, device=device)      # (sum of batch losses, number of batches)
+    i = 0
     for batch in trajectory_loader:
         if batch.shape[1] - 1 <= 0:
             continue
-        loss, _, _ = ev(batch.to(torch.float32))
-        total += loss
-        n += 1
+        if i % world == rank:
+            acc[0] += batch_loss(batch)
+            acc[1] += 1
+        i += 1
+    if on:
+        dist.all_reduce(acc, op=dist.ReduceOp.SUM, group=group)
+    tot, n = acc.tolist()
     if n == 0:
         raise ValueError("evaluate_rollout: no valid batches")
-    return float(total.item()) / n
+    return tot / n
+
+
+def evaluate_rollout(model, trajectory_loader: Iterable[torch.Tensor], rollout_steps: int = 10, x_normalizer=None,
+                     y_normalizer=None, use_graph: bool = True, distributed: bool = False, group=None) -> float:
+    """Mean over batches of the per-batch rollout loss, the number `evaluate_1d_rollout_all_resolution` stores per
+    resolution; every batch is one CUDA-graph replay (`RolloutEvaluator`), see `mean_over_batches` for the multi-GPU split."""
+    ev = RolloutEvaluator(model, rollout_steps, x_normalizer, y_normalizer, use_graph=use_graph)
+    dev = next(model.parameters()).device
+    return mean_over_batches(trajectory_loader, lambda b: ev(b.to(torch.float32))[0], dev, distributed, group)

@@ -91,3 +91,52 @@ def test_shard_batch_partitions():
             assert all(spans[i][1] == spans[i + 1][0] for i in range(world - 1))
             sizes = [hi - lo for lo, hi in spans]
             assert max(sizes) - min(sizes) <= 1
+
+
+# ---------------------------------------------------------------------------------------------------------
+# rollout evaluation sharded over ranks: batches r, r + world, ... per rank, one all-reduce of (sum, count)
+# ---------------------------------------------------------------------------------------------------------
+def _rollout_batches():
+    g = torch.Generator().manual_seed(5)
+    shapes = [(3, 6, 16), (3, 6, 16), (2, 1, 16), (3, 4, 16), (1, 6, 16), (2, 6, 16)]      # one batch too short to roll out
+    return [torch.randn(*s, generator=g) for s in shapes]
+
+
+def _rollout_batch_loss(batch):
+    from oracle import rollout_port as rp                       # the CPU checker stands in for the device evaluator
+    return rp.rollout_batch_loss(lambda x: 0.9 * x.roll(1, -1), batch, 4, (0.1, 1.2, 1e-8), (0.2, 0.8, 1e-8))[0]
+
+
+def _rollout_worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from resolution_pde_b200.rollout import mean_over_batches
+    seen = []
+
+    def loss(b):
+        seen.append(tuple(b.shape))
+        return _rollout_batch_loss(b)
+
+    got = mean_over_batches(_rollout_batches(), loss, "cpu", distributed=True)
+    q.put((rank, got, len(seen)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_rollout_evaluation_sharded_over_ranks_matches_single_process():
+    from resolution_pde_b200.rollout import mean_over_batches
+    want = mean_over_batches(_rollout_batches(), _rollout_batch_loss, "cpu")
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_rollout_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert [r[2] for r in res] == [3, 2]                         # 5 valid batches: ranks take 0,2,4 and 1,3
+    for _, got, _ in res:
+        assert abs(got - want) < 1e-6 * abs(want)

@@ -5,7 +5,7 @@ import os
 import pytest
 import torch
 
-from test_spectral_ops_oracle import CASES, FREQ_CASES, rel, run_case, run_freq_case, vec_rel
+from test_spectral_ops_oracle import CASES, DOWN_CASES, FREQ_CASES, rel, run_case, run_down_case, run_freq_case, vec_rel
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
@@ -39,10 +39,8 @@ def test_cuda_matches_reference_fixture(engine, path):
     assert rel(y, ref) < TOL
 
 
-def test_odd_height_resize_is_refused():
+def test_cpu_tensors_are_refused():
     import resolution_pde_b200.spectral_ops as so
-    with pytest.raises(NotImplementedError):
-        so.resize(torch.randn(1, 1, 15, 16, device=DEV), (8, 8))
     with pytest.raises(ValueError):
         so.lowpass_filter_1d(torch.randn(2, 3, 16), 0.5)            # CPU tensor: no fallback
 
@@ -89,3 +87,24 @@ def test_frequency_error_at_dataset_sizes(engine):
     e, m, f = fe.decompose_error_by_frequency_2d(yh.to(DEV), yt.to(DEV), 32)
     re, rm, rf = port.decompose_error_by_frequency_2d(yh.double(), yt.double(), 32)
     assert vec_rel(e, re) < TOL and vec_rel(m, rm) < TOL and vec_rel(f, rf) < 1e-12
+
+
+@pytest.mark.parametrize("path", DOWN_CASES, ids=lambda p: os.path.basename(p)[8:-4])
+def test_downsample_cuda_matches_reference_fixture(engine, path):
+    import resolution_pde_b200.spectral_ops as so
+    y, ref = run_down_case(so, path, to=DEV)
+    assert tuple(y.shape) == tuple(ref.shape)
+    assert rel(y, ref) < TOL
+
+
+@pytest.mark.parametrize("shape,n", [((4, 2, 256, 256), 64), ((2, 1, 512, 512), 128), ((16, 3, 2048), 256), ((8, 1024), 33)])
+def test_downsample_cuda_matches_fp64_oracle_at_dataset_sizes(engine, shape, n):
+    from oracle import spectral_ops_port as port
+    import resolution_pde_b200.spectral_ops as so
+    x = torch.randn(*shape, generator=torch.Generator().manual_seed(n))
+    if len(shape) == 4:
+        y, ref = so.downsample(x.to(DEV), n), port.downsample(x.double(), n)
+    else:
+        y, ref = so.downsample_1d(x.to(DEV), n), port.downsample_1d(x.double(), n)
+    assert tuple(y.shape) == tuple(ref.shape)
+    assert rel(y, ref) < TOL

@@ -8,7 +8,8 @@ import pytest
 import torch
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "specops")
-CASES = sorted(p for p in glob.glob(os.path.join(GOLDEN, "specops_*.npz")) if "freqerr" not in p)
+CASES = sorted(p for p in glob.glob(os.path.join(GOLDEN, "specops_*.npz")) if "freqerr" not in p and "downsample" not in p)
+DOWN_CASES = sorted(glob.glob(os.path.join(GOLDEN, "specops_downsample*.npz")))
 FREQ_CASES = sorted(glob.glob(os.path.join(GOLDEN, "specops_freqerr*.npz")))
 
 
@@ -34,7 +35,7 @@ def rel(a, b):
 
 
 def test_fixtures_present():
-    assert len(CASES) == 22 and len(FREQ_CASES) == 8
+    assert len(CASES) == 26 and len(FREQ_CASES) == 8 and len(DOWN_CASES) == 13
 
 
 def run_freq_case(mod, path, to=None):
@@ -67,5 +68,23 @@ def test_frequency_error_oracle_matches_reference_fixture(path):
 def test_oracle_matches_reference_fixture(path):
     from oracle import spectral_ops_port as port
     y, ref = run_case(port, path)
+    assert y.shape == ref.shape
+    assert rel(y, ref) < 2e-6
+
+
+def run_down_case(mod, path, to=None, dtype=None):
+    """downsample_1d / downsample (the reference runs scipy on numpy arrays; both ports take tensors)"""
+    d = np.load(path)
+    x = torch.from_numpy(d["x"])
+    x = x.to(dtype) if dtype is not None else x
+    x = x.to(to) if to is not None else x
+    fn = mod.downsample_1d if "downsample1d" in path else mod.downsample
+    return fn(x, int(d["out"])), torch.from_numpy(d["y"])
+
+
+@pytest.mark.parametrize("path", DOWN_CASES, ids=[os.path.basename(p)[8:-4] for p in DOWN_CASES])
+def test_downsample_oracle_matches_reference_fixture(path):
+    from oracle import spectral_ops_port as port
+    y, ref = run_down_case(port, path)
     assert y.shape == ref.shape
     assert rel(y, ref) < 2e-6
