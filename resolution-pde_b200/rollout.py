@@ -242,9 +242,11 @@ def mean_over_batches(trajectory_loader: Iterable[torch.Tensor], batch_loss, dev
 
 
 def evaluate_rollout(model, trajectory_loader: Iterable[torch.Tensor], rollout_steps: int = 10, x_normalizer=None,
-                     y_normalizer=None, use_graph: bool = True, distributed: bool = False, group=None) -> float:
+                     y_normalizer=None, use_graph: bool = True, distributed: bool = False, group=None,
+                     evaluator: Optional[RolloutEvaluator] = None) -> float:
     """Mean over batches of the per-batch rollout loss, the number `evaluate_1d_rollout_all_resolution` stores per
-    resolution; every batch is one CUDA-graph replay (`RolloutEvaluator`), see `mean_over_batches` for the multi-GPU split."""
-    ev = RolloutEvaluator(model, rollout_steps, x_normalizer, y_normalizer, use_graph=use_graph)
+    resolution; every batch is one CUDA-graph replay (`RolloutEvaluator`; pass `evaluator` to reuse its captured graphs across
+    calls), see `mean_over_batches` for the multi-GPU split."""
+    ev = evaluator or RolloutEvaluator(model, rollout_steps, x_normalizer, y_normalizer, use_graph=use_graph)
     dev = next(model.parameters()).device
     return mean_over_batches(trajectory_loader, lambda b: ev(b.to(torch.float32))[0], dev, distributed, group)
