@@ -285,8 +285,21 @@ def main():
     launches = (lib.rpde_launch_count() - l0) if hasattr(lib, "rpde_launch_count") else None
     if launches_per_step is not None:
         launches = launches_per_step * args.steps           # replayed graph nodes (counted once, at capture)
+    loss_val = float(loss.detach()) if torch.is_tensor(loss) else float(loss)
+    extra = 0
+    if rank == 0 and world == 1 and ms < 1500.0:
+        # nvidia-smi samples every 100 ms: a timed region of a few ms would yield none.  Keep the same step running
+        # (untimed) under the sampler until 1.5 s of load have been observed, and say so.
+        t_end = time.perf_counter() + 1.5 - ms / 1e3
+        while time.perf_counter() < t_end:
+            step(xd, yd)
+            extra += 1
+            if extra % 16 == 0:
+                torch.cuda.synchronize()
+        torch.cuda.synchronize()
     clocks = sampler.stop() if rank == 0 else None
-    loss_val = float(loss)
+    if clocks is not None and extra:
+        clocks["note"] = f"timed region {ms:.1f} ms < sampling period: sampled over it and {extra} untimed repetitions of the same step"
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.barrier()
