@@ -67,6 +67,15 @@ size_t rpde_spectral1d_workspace_bytes(int B, int I, int O, int N, int modes);
 int rpde_spectral1d_fwd(const float* x, const float* w, const float* fa, const float* fs, float* spec, float* y,
                         float* z, int B, int I, int O, int N, int modes, int beta, int act, void* ws,
                         size_t ws_bytes, rpde_stream_t stream);
+/* Fused FNOBlock1d forward (models/fno_blocks.py:25-33: activation(spectral_conv(x) + bypass_conv(x)), around
+ * spectral_convolution.py:38-55) in three launches: analysis (one register-resident row per warp), per-mode mixing straight
+ * from the parameter layout, then synthesis + 1x1 bypass conv + bias + activation.  fp32 FMA (engine-independent).  fs4: kind-4 table [2][modes][N]
+ * scale 1/N.  wb (O,I) / bb (O) may be NULL (plain SpectralConv1d).  spec ([mode][re|im][b][i]) and z (pre-activation)
+ * may be NULL when no backward pass follows.  ws: modes*B*2*O floats (+ modes*B*2*I when spec is NULL), each rounded up
+ * to 256 bytes.  Returns RPDE_E_INVALID when N > 2048 or modes*I exceeds the mixing kernel's shared memory (callers then use rpde_conv1x1_fwd + rpde_spectral1d_fwd). */
+int rpde_fno_block1d_fwd(const float* x, const float* w, const float* fa, const float* fs4, const float* wb,
+                         const float* bb, float* spec, float* y, float* z, int B, int I, int O, int N, int modes, int act,
+                         void* ws, size_t ws_bytes, rpde_stream_t stream);
 /* dx (+)= adjoint wrt x ; dw (complex64 (I,O,modes)) = gradient wrt w.  dx may be NULL. */
 int rpde_spectral1d_bwd(const float* dy, const float* w, const float* fa, const float* fs, const float* spec,
                         float* dx, int dx_accumulate, float* dw, int B, int I, int O, int N, int modes, void* ws,

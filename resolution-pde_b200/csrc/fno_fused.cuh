@@ -1,0 +1,207 @@
+// Fused FNOBlock1d forward (fno_blocks.py:25-33 around spectral_convolution.py:38-55): three launches instead of
+// memset + weight pack + three contractions + the bypass conv.  At the reference's sizes (C2: B=16, width 64, N=1024,
+// 16 modes) every one of those contractions is a latency-bound 8..128-tile problem (~10 us each); here the retained
+// spectrum never takes a detour through a packed-weight workspace and x is read from L2 by both kernels.
+//
+//   kernel 1 (analysis), warp = one (b, i) row held in registers:
+//       spec[k][ri][b][i] = sum_n x[b,i,n] fa[(k,ri)][n]                 (kept for the backward pass)
+//   kernel 2 (mode mixing), CTA = (8 output channels, b):
+//       om[k][ro][b][o]   = sum_i spec[k][.][b][i] (*) w[i,o,k]          (complex product, w in the parameter layout)
+//   kernel 3 (synthesis + bypass 1x1 conv + bias + activation), CTA = (tile of TN grid points, b):
+//       y[b,o,n] = act( sum_(k,ro) om[k][ro][b][o] fs[n][(k,ro)] + sum_i wb[o,i] x[b,i,n] + bb[o] )
+//
+// fp32 FMA throughout (no tensor cores: the K dimensions are 2*modes = 32 and width = 64, and the problem is bound by
+// launch latency and L2, not arithmetic), so the result is engine-independent and within 1e-6 of the composed path.
+#pragma once
+#include "common.cuh"
+
+namespace rpde {
+
+constexpr int FNO_TN = 128;    // grid points per CTA in the synthesis kernel
+constexpr int FNO_OB = 64;     // output channels per register-tile pass in the synthesis kernel
+constexpr int FNO_MO = 8;      // output channels per CTA in the mixing kernel
+
+// Analysis: CTA = (8 rows (b, i), chunk of FNO_RC table rows).  Each warp keeps its x row in registers (NPL values per lane,
+// n = lane + 32 j); the table chunk is staged in shared memory by the whole CTA, so every global load of the kernel is
+// issued up front (one L2 round trip), then FNO_RC dot products per warp run out of registers and shared memory.
+constexpr int FNO_RC = 8;
+template <int NPL>
+__global__ void __launch_bounds__(256) fno1d_analysis_kernel(const float* __restrict__ x, const float* __restrict__ fa,
+                                                             float* __restrict__ spec, int Bn, int I, int N, int K) {
+  extern __shared__ float tab[];                                              // [FNO_RC][N]
+  const int lane = threadIdx.x & 31;
+  const long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);      // b * I + i
+  const bool valid = row < (long long)Bn * I;
+  const int r0 = blockIdx.y * FNO_RC, rc = min(FNO_RC, 2 * K - r0);
+  float v[NPL];
+  if (valid) {
+    const float* xr = x + row * N;
+#pragma unroll
+    for (int j = 0; j < NPL; ++j) {
+      const int n = lane + 32 * j;
+      v[j] = n < N ? __ldg(xr + n) : 0.f;
+    }
+  }
+  const float* src = fa + (long long)r0 * N;
+  const int total = rc * N;
+  if ((N & 3) == 0) {
+    for (int e = threadIdx.x * 4; e < total; e += 1024)
+      *reinterpret_cast<float4*>(tab + e) = __ldg(reinterpret_cast<const float4*>(src + e));
+  } else {
+    for (int e = threadIdx.x; e < total; e += 256) tab[e] = __ldg(src + e);
+  }
+  __syncthreads();
+  if (!valid) return;
+  const int b = (int)(row / I), i = (int)(row - (long long)b * I);
+  for (int rr = 0; rr < rc; ++rr) {
+    const float* t = tab + rr * N;
+    float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+    for (int j = 0; j < NPL; j += 2) {
+      const int n = lane + 32 * j;
+      a0 = fmaf(v[j], n < N ? t[n] : 0.f, a0);
+      a1 = fmaf(v[j + 1], n + 32 < N ? t[n + 32] : 0.f, a1);
+    }
+    const float sum = warp_sum(a0 + a1);
+    if (lane == 0) spec[((long long)(r0 + rr) * Bn + b) * I + i] = sum;
+  }
+}
+
+// Mixing: CTA = (block of FNO_MO output channels, b); thread pairs (oo, k).  For a fixed i the weights of the CTA's
+// (o, k) pairs are one contiguous run of the parameter tensor (I, O, K, 2), so the loads coalesce without a packing pass.
+// smem: sp[2K][I + 1]
+__global__ void __launch_bounds__(256) fno1d_mix_kernel(const float* __restrict__ spec, const float* __restrict__ w,
+                                                        float* __restrict__ om, int Bn, int I, int O, int K) {
+  extern __shared__ float sp[];
+  const int b = blockIdx.y, o0 = blockIdx.x * FNO_MO;
+  const int ob = min(FNO_MO, O - o0);
+  const int ld = I + 1;
+  for (int e = threadIdx.x; e < 2 * K * I; e += 256) {
+    const int r = e / I, i = e - r * I;
+    sp[r * ld + i] = spec[((long long)r * Bn + b) * I + i];
+  }
+  __syncthreads();
+  for (int e = threadIdx.x; e < ob * K; e += 256) {
+    const int oo = e / K, k = e - oo * K;
+    const float* sr = sp + (2 * k) * ld;
+    const float* si = sr + ld;
+    const float* wp = w + ((long long)(o0 + oo) * K + k) * 2;
+    float re = 0.f, im = 0.f;
+#pragma unroll 16
+    for (int i = 0; i < I; ++i) {
+      const float2 wv = __ldg(reinterpret_cast<const float2*>(wp + (long long)i * O * K * 2));
+      re = fmaf(sr[i], wv.x, re);
+      re = fmaf(-si[i], wv.y, re);
+      im = fmaf(sr[i], wv.y, im);
+      im = fmaf(si[i], wv.x, im);
+    }
+    om[((long long)(2 * k) * Bn + b) * O + o0 + oo] = re;
+    om[((long long)(2 * k + 1) * Bn + b) * O + o0 + oo] = im;
+  }
+}
+
+// smem: A[KT][FNO_OB] (om slice then wbT slice), Bm[KT][FNO_TN] (fs^T slice then x slice); KT = chunk of the reduction
+constexpr int FNO_KT = 32;
+
+__global__ void __launch_bounds__(256) fno1d_synth_bypass_kernel(const float* __restrict__ x, const float* __restrict__ om,
+                                                                 const float* __restrict__ fs4, const float* __restrict__ wb,
+                                                                 const float* __restrict__ bb, float* __restrict__ y,
+                                                                 float* __restrict__ z, int Bn, int I, int O, int N, int K,
+                                                                 int act) {
+  __shared__ __align__(16) float As[FNO_KT][FNO_OB + 4];
+  __shared__ __align__(16) float Bs[FNO_KT][FNO_TN + 4];
+  const int b = blockIdx.y, n0 = blockIdx.x * FNO_TN;
+  const int tid = threadIdx.x;
+  const int tn = (tid & 15) * 8;        // 8 consecutive grid points
+  const int to = (tid >> 4) * 4;        // 4 consecutive output channels
+  const int R = 2 * K;
+  for (int o0 = 0; o0 < O; o0 += FNO_OB) {
+    float acc[4][8];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+      for (int c = 0; c < 8; ++c) acc[a][c] = 0.f;
+    // reduction index r runs over the 2K spectral rows, then (when there is a bypass conv) over the I input channels
+    const int RT = R + (wb ? I : 0);
+    for (int r0 = 0; r0 < RT; r0 += FNO_KT) {
+      __syncthreads();
+      // every global load of the chunk is issued before the first shared-memory store (one L2 round trip per chunk)
+      float ra[FNO_KT * FNO_OB / 256], rb[FNO_KT * FNO_TN / 256];
+#pragma unroll
+      for (int j = 0; j < FNO_KT * FNO_OB / 256; ++j) {
+        const int e = tid + 256 * j;
+        const int rr = e / FNO_OB, oo = e - rr * FNO_OB;
+        const int r = r0 + rr, o = o0 + oo;
+        const bool ok = r < RT && o < O;
+        const float* p = r < R ? om + ((long long)r * Bn + b) * O + o : wb + (long long)o * I + (r - R);
+        ra[j] = ok ? __ldg(p) : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < FNO_KT * FNO_TN / 256; ++j) {
+        const int e = tid + 256 * j;
+        const int rr = e / FNO_TN, nn = e - rr * FNO_TN;
+        const int r = r0 + rr, n = n0 + nn;
+        const bool ok = r < RT && n < N;      // spectral rows r = (k, ro) come from the plane-major synthesis table fs4[ro][k][n]
+        const float* p = r < R ? fs4 + ((long long)(r & 1) * K + (r >> 1)) * N + n : x + ((long long)b * I + (r - R)) * N + n;
+        rb[j] = ok ? __ldg(p) : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < FNO_KT * FNO_OB / 256; ++j) {
+        const int e = tid + 256 * j;
+        As[e / FNO_OB][e % FNO_OB] = ra[j];
+      }
+#pragma unroll
+      for (int j = 0; j < FNO_KT * FNO_TN / 256; ++j) {
+        const int e = tid + 256 * j;
+        Bs[e / FNO_TN][e % FNO_TN] = rb[j];
+      }
+      __syncthreads();
+#pragma unroll 8
+      for (int rr = 0; rr < FNO_KT; ++rr) {
+        const float4 a = *reinterpret_cast<const float4*>(&As[rr][to]);
+        const float4 p = *reinterpret_cast<const float4*>(&Bs[rr][tn]);
+        const float4 q = *reinterpret_cast<const float4*>(&Bs[rr][tn + 4]);
+        const float av[4] = {a.x, a.y, a.z, a.w};
+        const float bv[8] = {p.x, p.y, p.z, p.w, q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int o = o0 + to + i;
+      if (o >= O) continue;
+      const float bias = bb ? bb[o] : 0.f;
+      const long long row = ((long long)b * O + o) * N;
+      if ((N & 3) == 0 && n0 + tn + 8 <= N) {
+        float pre[8], out[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          pre[j] = acc[i][j] + bias;
+          out[j] = act_f(act, pre[j]);
+        }
+        float4* yp = reinterpret_cast<float4*>(y + row + n0 + tn);
+        yp[0] = make_float4(out[0], out[1], out[2], out[3]);
+        yp[1] = make_float4(out[4], out[5], out[6], out[7]);
+        if (z) {
+          float4* zp = reinterpret_cast<float4*>(z + row + n0 + tn);
+          zp[0] = make_float4(pre[0], pre[1], pre[2], pre[3]);
+          zp[1] = make_float4(pre[4], pre[5], pre[6], pre[7]);
+        }
+        continue;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int n = n0 + tn + j;
+        if (n >= N) continue;
+        const float pre = acc[i][j] + bias;
+        if (z) z[row + n] = pre;
+        y[row + n] = act_f(act, pre);
+      }
+    }
+  }
+}
+
+}  // namespace rpde

@@ -12,6 +12,7 @@
 #include "common.cuh"
 #include "gemm_simt.cuh"
 #include "pointwise.cuh"
+#include "fno_fused.cuh"
 #ifdef RPDE_WITH_TC
 #include "gemm_tc.cuh"
 #endif
@@ -169,6 +170,42 @@ int rpde_spectral1d_fwd(const float* x, const float* w, const float* fa, const f
   g.c = MatDesc{lin(0), lin(N), lin(1)};
   g.beta = beta; g.act = act; g.Z = z;
   RPDE_CUDA(gemm(g, s));
+  return RPDE_OK;
+}
+
+int rpde_fno_block1d_fwd(const float* x, const float* w, const float* fa, const float* fs4, const float* wb,
+                         const float* bb, float* spec, float* y, float* z, int B, int I, int O, int N, int modes, int act,
+                         void* ws, size_t ws_bytes, rpde_stream_t stream) {
+  if (!x || !w || !fa || !fs4 || !y || B <= 0 || I <= 0 || O <= 0 || N <= 0 || modes <= 0 || B > 65535 || (bb && !wb))
+    return fail(RPDE_E_INVALID, "rpde_fno_block1d_fwd: bad arguments%s");
+  if (modes > N / 2 + 1) return fail(RPDE_E_MODES, "SpectralConv1d: modes1 exceeds N//2+1%s");
+  if (N > 2048) return fail(RPDE_E_INVALID, "rpde_fno_block1d_fwd: grid too long for the fused kernels (use rpde_spectral1d_fwd)%s");
+  const size_t smem2 = (size_t)2 * modes * (I + 1) * sizeof(float);
+  if (smem2 > 200 * 1024) return fail(RPDE_E_INVALID, "rpde_fno_block1d_fwd: modes x channels too large for the fused kernels%s");
+  const size_t need = align_up((size_t)modes * B * 2 * O * 4) + (spec ? 0 : align_up((size_t)modes * B * 2 * I * 4));
+  if (!ws || ws_bytes < need) return fail(RPDE_E_WORKSPACE, "rpde_fno_block1d_fwd: workspace too small%s");
+  cudaStream_t s = (cudaStream_t)stream;
+  float* om = (float*)ws;
+  if (!spec) spec = (float*)((char*)ws + align_up((size_t)modes * B * 2 * O * 4));   // inference: spectrum stays in the workspace
+  dim3 g1((unsigned)(((long long)B * I + 7) / 8), (unsigned)((2 * modes + FNO_RC - 1) / FNO_RC));
+  const size_t smem1 = (size_t)FNO_RC * N * sizeof(float);
+  if (smem1 > 48 * 1024)      // N in (1536, 2048]: 64 KB table chunk (the attribute is per device: set it on every call)
+    RPDE_CUDA(cudaFuncSetAttribute(fno1d_analysis_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  if (N <= 256)
+    fno1d_analysis_kernel<8><<<g1, 256, smem1, s>>>(x, fa, spec, B, I, N, modes);
+  else if (N <= 1024)
+    fno1d_analysis_kernel<32><<<g1, 256, smem1, s>>>(x, fa, spec, B, I, N, modes);
+  else
+    fno1d_analysis_kernel<64><<<g1, 256, smem1, s>>>(x, fa, spec, B, I, N, modes);
+  RPDE_LAUNCH_CHECK();
+  if (smem2 > 48 * 1024)
+    RPDE_CUDA(cudaFuncSetAttribute(fno1d_mix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+  dim3 gm((unsigned)((O + FNO_MO - 1) / FNO_MO), (unsigned)B);
+  fno1d_mix_kernel<<<gm, 256, smem2, s>>>(spec, w, om, B, I, O, modes);
+  RPDE_LAUNCH_CHECK();
+  dim3 g2((unsigned)((N + FNO_TN - 1) / FNO_TN), (unsigned)B);
+  fno1d_synth_bypass_kernel<<<g2, 256, 0, s>>>(x, om, fs4, wb, bb, y, z, B, I, O, N, modes, act);
+  RPDE_LAUNCH_CHECK();
   return RPDE_OK;
 }
 

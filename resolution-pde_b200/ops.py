@@ -7,6 +7,7 @@ stream.  No CPU path exists: a non-CUDA tensor raises.
 from __future__ import annotations
 
 import math
+import os
 import threading
 from typing import Optional, Sequence, Tuple
 
@@ -23,6 +24,7 @@ _ACT_BY_NAME = {"identity": ACT_NONE, "none": ACT_NONE, "gelu": ACT_GELU, "relu"
 
 _state = threading.local()
 _default_precision = 0
+_fno_fused = os.environ.get("RPDE_FNO_FUSED", "1") != "0"   # fused FNOBlock1d forward (rpde_fno_block1d_fwd); 0 = composed path
 
 
 def set_precision(name: str) -> None:
@@ -181,6 +183,24 @@ class _FNOSpectralFn(torch.autograd.Function):
         tabs = _spectral_tables(ndim, spatial, modes, x.device)
         nmodes = int(np.prod(modes)) * (2 if ndim == 2 else 1)
         spec = torch.empty(nmodes * B * 2 * I, dtype=torch.float32, device=x.device)
+        fused = ndim == 1 and _fno_fused and spatial[0] <= 2048 and 8 * modes[0] * (I + 1) <= 200 * 1024 and B <= 65535
+        if fused:
+            # FNOBlock1d in three launches (analysis, mixing, synthesis + bypass + bias + activation), fp32 FMA
+            n, k = spatial[0], modes[0]
+            fs4 = dft_table(4, n, k, 0, 1.0 / n, x.device)
+            wbc = wb.detach().reshape(O, I).contiguous() if wb is not None else None
+            if bb is not None and wb is None:
+                raise RuntimeError("fno_spectral: a bias needs the bypass weight")
+            up = lambda v: (v + 255) // 256 * 256
+            nb = up(k * B * 2 * O * 4) + (0 if need_grad else up(k * B * 2 * I * 4))
+            ws = _ws(nb, x.device)
+            with _Ctx(x) as c:
+                _lib.check(c.lib.rpde_fno_block1d_fwd(_p(x), _p(w1r), _p(tabs[0]), _p(fs4), _p(wbc), _p(bb),
+                                                      _p(spec) if need_grad else None, _p(y), _p(z), B, I, O, n, k, act,
+                                                      _p(ws), nb, c.stream), "rpde_fno_block1d_fwd")
+            ctx.save_for_backward(x, w1, w2, wb, spec, z)
+            ctx.cfg = (act, ndim, B, I, O, spatial, modes, S, bb is not None)
+            return y
         with _Ctx(x) as c:
             beta = 0
             if wb is not None:
