@@ -299,7 +299,8 @@ def main():
         torch.cuda.synchronize()
     clocks = sampler.stop() if rank == 0 else None
     if clocks is not None and extra:
-        clocks["note"] = f"timed region {ms:.1f} ms < sampling period: sampled over it and {extra} untimed repetitions of the same step"
+        clocks["note"] = (f"timed region {ms:.1f} ms is short against the 100 ms sampling period: sampled over it and over {extra} "
+                          "untimed repetitions of the same step right after it (1.5 s of load in total)")
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.barrier()

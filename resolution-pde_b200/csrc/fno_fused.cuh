@@ -17,7 +17,6 @@
 
 namespace rpde {
 
-constexpr int FNO_TN = 128;    // grid points per CTA in the synthesis kernel
 constexpr int FNO_OB = 64;     // output channels per register-tile pass in the synthesis kernel
 constexpr int FNO_MO = 8;      // output channels per CTA in the mixing kernel
 
@@ -100,33 +99,37 @@ __global__ void __launch_bounds__(256) fno1d_mix_kernel(const float* __restrict_
   }
 }
 
-// smem: A[KT][FNO_OB] (om slice then wbT slice), Bm[KT][FNO_TN] (fs^T slice then x slice); KT = chunk of the reduction
+// smem: A[KT][FNO_OB] (om slice then wbT slice), Bm[KT][TN] (fs^T slice then x slice); KT = chunk of the reduction
 constexpr int FNO_KT = 32;
 
+// TN = grid points per CTA (128: 4x8 outputs per thread; 64: 4x4 per thread, twice the CTAs -- chosen by the host so that the
+// grid fills the SMs at least twice and neighbouring CTAs overlap their load and FMA phases)
+template <int TN>
 __global__ void __launch_bounds__(256) fno1d_synth_bypass_kernel(const float* __restrict__ x, const float* __restrict__ om,
                                                                  const float* __restrict__ fs4, const float* __restrict__ wb,
                                                                  const float* __restrict__ bb, float* __restrict__ y,
                                                                  float* __restrict__ z, int Bn, int I, int O, int N, int K,
                                                                  int act) {
+  constexpr int NT = TN / 16;            // consecutive grid points per thread (8 or 4)
   __shared__ __align__(16) float As[FNO_KT][FNO_OB + 4];
-  __shared__ __align__(16) float Bs[FNO_KT][FNO_TN + 4];
-  const int b = blockIdx.y, n0 = blockIdx.x * FNO_TN;
+  __shared__ __align__(16) float Bs[FNO_KT][TN + 4];
+  const int b = blockIdx.y, n0 = blockIdx.x * TN;
   const int tid = threadIdx.x;
-  const int tn = (tid & 15) * 8;        // 8 consecutive grid points
+  const int tn = (tid & 15) * NT;
   const int to = (tid >> 4) * 4;        // 4 consecutive output channels
   const int R = 2 * K;
   for (int o0 = 0; o0 < O; o0 += FNO_OB) {
-    float acc[4][8];
+    float acc[4][NT];
 #pragma unroll
     for (int a = 0; a < 4; ++a)
 #pragma unroll
-      for (int c = 0; c < 8; ++c) acc[a][c] = 0.f;
+      for (int c = 0; c < NT; ++c) acc[a][c] = 0.f;
     // reduction index r runs over the 2K spectral rows, then (when there is a bypass conv) over the I input channels
     const int RT = R + (wb ? I : 0);
     for (int r0 = 0; r0 < RT; r0 += FNO_KT) {
       __syncthreads();
       // every global load of the chunk is issued before the first shared-memory store (one L2 round trip per chunk)
-      float ra[FNO_KT * FNO_OB / 256], rb[FNO_KT * FNO_TN / 256];
+      float ra[FNO_KT * FNO_OB / 256], rb[FNO_KT * TN / 256];
 #pragma unroll
       for (int j = 0; j < FNO_KT * FNO_OB / 256; ++j) {
         const int e = tid + 256 * j;
@@ -137,9 +140,9 @@ __global__ void __launch_bounds__(256) fno1d_synth_bypass_kernel(const float* __
         ra[j] = ok ? __ldg(p) : 0.f;
       }
 #pragma unroll
-      for (int j = 0; j < FNO_KT * FNO_TN / 256; ++j) {
+      for (int j = 0; j < FNO_KT * TN / 256; ++j) {
         const int e = tid + 256 * j;
-        const int rr = e / FNO_TN, nn = e - rr * FNO_TN;
+        const int rr = e / TN, nn = e - rr * TN;
         const int r = r0 + rr, n = n0 + nn;
         const bool ok = r < RT && n < N;      // spectral rows r = (k, ro) come from the plane-major synthesis table fs4[ro][k][n]
         const float* p = r < R ? fs4 + ((long long)(r & 1) * K + (r >> 1)) * N + n : x + ((long long)b * I + (r - R)) * N + n;
@@ -151,22 +154,25 @@ __global__ void __launch_bounds__(256) fno1d_synth_bypass_kernel(const float* __
         As[e / FNO_OB][e % FNO_OB] = ra[j];
       }
 #pragma unroll
-      for (int j = 0; j < FNO_KT * FNO_TN / 256; ++j) {
+      for (int j = 0; j < FNO_KT * TN / 256; ++j) {
         const int e = tid + 256 * j;
-        Bs[e / FNO_TN][e % FNO_TN] = rb[j];
+        Bs[e / TN][e % TN] = rb[j];
       }
       __syncthreads();
 #pragma unroll 8
       for (int rr = 0; rr < FNO_KT; ++rr) {
         const float4 a = *reinterpret_cast<const float4*>(&As[rr][to]);
-        const float4 p = *reinterpret_cast<const float4*>(&Bs[rr][tn]);
-        const float4 q = *reinterpret_cast<const float4*>(&Bs[rr][tn + 4]);
         const float av[4] = {a.x, a.y, a.z, a.w};
-        const float bv[8] = {p.x, p.y, p.z, p.w, q.x, q.y, q.z, q.w};
+        float bv[NT];
+#pragma unroll
+        for (int q = 0; q < NT / 4; ++q) {
+          const float4 p = *reinterpret_cast<const float4*>(&Bs[rr][tn + 4 * q]);
+          bv[4 * q] = p.x; bv[4 * q + 1] = p.y; bv[4 * q + 2] = p.z; bv[4 * q + 3] = p.w;
+        }
 #pragma unroll
         for (int i = 0; i < 4; ++i)
 #pragma unroll
-          for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+          for (int j = 0; j < NT; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
       }
     }
 #pragma unroll
@@ -175,25 +181,24 @@ __global__ void __launch_bounds__(256) fno1d_synth_bypass_kernel(const float* __
       if (o >= O) continue;
       const float bias = bb ? bb[o] : 0.f;
       const long long row = ((long long)b * O + o) * N;
-      if ((N & 3) == 0 && n0 + tn + 8 <= N) {
-        float pre[8], out[8];
+      if ((N & 3) == 0 && n0 + tn + NT <= N) {
+        float pre[NT], out[NT];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
+        for (int j = 0; j < NT; ++j) {
           pre[j] = acc[i][j] + bias;
           out[j] = act_f(act, pre[j]);
         }
         float4* yp = reinterpret_cast<float4*>(y + row + n0 + tn);
-        yp[0] = make_float4(out[0], out[1], out[2], out[3]);
-        yp[1] = make_float4(out[4], out[5], out[6], out[7]);
-        if (z) {
-          float4* zp = reinterpret_cast<float4*>(z + row + n0 + tn);
-          zp[0] = make_float4(pre[0], pre[1], pre[2], pre[3]);
-          zp[1] = make_float4(pre[4], pre[5], pre[6], pre[7]);
+        float4* zp = reinterpret_cast<float4*>(z + row + n0 + tn);
+#pragma unroll
+        for (int q = 0; q < NT / 4; ++q) {
+          yp[q] = make_float4(out[4 * q], out[4 * q + 1], out[4 * q + 2], out[4 * q + 3]);
+          if (z) zp[q] = make_float4(pre[4 * q], pre[4 * q + 1], pre[4 * q + 2], pre[4 * q + 3]);
         }
         continue;
       }
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
+      for (int j = 0; j < NT; ++j) {
         const int n = n0 + tn + j;
         if (n >= N) continue;
         const float pre = acc[i][j] + bias;

@@ -203,8 +203,15 @@ int rpde_fno_block1d_fwd(const float* x, const float* w, const float* fa, const 
   dim3 gm((unsigned)((O + FNO_MO - 1) / FNO_MO), (unsigned)B);
   fno1d_mix_kernel<<<gm, 256, smem2, s>>>(spec, w, om, B, I, O, modes);
   RPDE_LAUNCH_CHECK();
-  dim3 g2((unsigned)((N + FNO_TN - 1) / FNO_TN), (unsigned)B);
-  fno1d_synth_bypass_kernel<<<g2, 256, 0, s>>>(x, om, fs4, wb, bb, y, z, B, I, O, N, modes, act);
+  static const int tn_sel = getenv("RPDE_FNO_TN") ? atoi(getenv("RPDE_FNO_TN")) : 0;   // bring-up switch: 64 or 128
+  const bool wide = tn_sel ? tn_sel == 128 : (long long)((N + 127) / 128) * B >= 2 * 148;   // enough 128-point tiles to fill the SMs twice
+  if (wide) {
+    dim3 g2((unsigned)((N + 127) / 128), (unsigned)B);
+    fno1d_synth_bypass_kernel<128><<<g2, 256, 0, s>>>(x, om, fs4, wb, bb, y, z, B, I, O, N, modes, act);
+  } else {
+    dim3 g2((unsigned)((N + 63) / 64), (unsigned)B);
+    fno1d_synth_bypass_kernel<64><<<g2, 256, 0, s>>>(x, om, fs4, wb, bb, y, z, B, I, O, N, modes, act);
+  }
   RPDE_LAUNCH_CHECK();
   return RPDE_OK;
 }
