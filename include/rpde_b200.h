@@ -81,6 +81,15 @@ int rpde_spectral1d_bwd(const float* dy, const float* w, const float* fa, const 
                         float* dx, int dx_accumulate, float* dw, int B, int I, int O, int N, int modes, void* ws,
                         size_t ws_bytes, rpde_stream_t stream);
 
+/* Backward of the fused block: rpde_spectral1d_bwd with a fused prologue.  dpre = dy * act'(z) (written when z != NULL; this
+ * is the gradient the bypass conv's backward consumes) and its projection on the synthesis table come from one launch
+ * instead of rpde_act_bwd + memset + split-K contraction; the rest (weight gradient, mixing adjoint, analysis adjoint) is
+ * rpde_spectral1d_bwd's.  fs4: kind-4 table scale 1/N.  z = dpre = NULL for act == none.  N <= 2048.  Workspace as
+ * rpde_spectral1d_workspace_bytes. */
+int rpde_fno_block1d_bwd(const float* dy, const float* z, int act, const float* w, const float* fa, const float* fs4,
+                         const float* spec, float* dpre, float* dx, int dx_accumulate, float* dw, int B, int I, int O, int N,
+                         int modes, void* ws, size_t ws_bytes, rpde_stream_t stream);
+
 /* ---- FNO SpectralConv2d (models/spectral_convolution.py:61-98), (B,I,H,W) -> (B,O,H,W) ---------------------
  * w1, w2: complex64 (I,O,m1,m2).  fa_y/fs_y: kind 0/4 tables for axis W with k = m2 (scales 1, 1/W);
  * gf/gi: kind 2/3 tables for axis H with j = 2*m1 (scales 1, 1/H).  spec: (2*m1*m2*B*2I floats). */

@@ -32,6 +32,7 @@ SIGNATURES = {
     "rpde_spectral1d_fwd": (I, [P, P, P, P, P, P, P, I, I, I, I, I, I, I, P, Z, S]),
     "rpde_spectral1d_bwd": (I, [P, P, P, P, P, P, I, P, I, I, I, I, I, P, Z, S]),
     "rpde_fno_block1d_fwd": (I, [P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, P, Z, S]),
+    "rpde_fno_block1d_bwd": (I, [P, P, I, P, P, P, P, P, P, I, P, I, I, I, I, I, P, Z, S]),
     "rpde_spectral2d_workspace_bytes": (Z, [I, I, I, I, I, I, I]),
     "rpde_spectral2d_fwd": (I, [P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, P, Z, S]),
     "rpde_spectral2d_bwd": (I, [P, P, P, P, P, P, P, P, P, I, P, P, I, I, I, I, I, I, I, P, Z, S]),

@@ -25,13 +25,29 @@ constexpr int FNO_MO = 8;      // output channels per CTA in the mixing kernel
 // issued up front (one L2 round trip), then FNO_RC dot products per warp run out of registers and shared memory.
 constexpr int FNO_RC = 8;
 template <int NPL>
+// Backward use (adjoint of the synthesis): x = dy, z / act = the block's pre-activation and activation (the row is multiplied
+// by act'(z) on load and written once to xout = dL/d(pre-activation) by the CTAs of the first table chunk), fa = the plane-major
+// synthesis table [ro][k][n] (rowmap = 1: table row t = ro*K + k lands in output row 2k + ro).
 __global__ void __launch_bounds__(256) fno1d_analysis_kernel(const float* __restrict__ x, const float* __restrict__ fa,
-                                                             float* __restrict__ spec, int Bn, int I, int N, int K) {
+                                                             float* __restrict__ spec, int Bn, int I, int N, int K,
+                                                             const float* __restrict__ z, int act, float* __restrict__ xout,
+                                                             int rowmap) {
   extern __shared__ float tab[];                                              // [FNO_RC][N]
   const int lane = threadIdx.x & 31;
   const long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);      // b * I + i
   const bool valid = row < (long long)Bn * I;
   const int r0 = blockIdx.y * FNO_RC, rc = min(FNO_RC, 2 * K - r0);
+  // the table chunk goes to shared memory with cp.async (no register dependency), so it is in flight together with the row loads
+  const float* src = fa + (long long)r0 * N;
+  const int total = rc * N;
+  const bool vec = (N & 3) == 0;
+  if (vec) {
+    for (int e = threadIdx.x * 4; e < total; e += 1024) {
+      const unsigned dst = (unsigned)__cvta_generic_to_shared(tab + e);
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src + e) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
   float v[NPL];
   if (valid) {
     const float* xr = x + row * N;
@@ -40,12 +56,28 @@ __global__ void __launch_bounds__(256) fno1d_analysis_kernel(const float* __rest
       const int n = lane + 32 * j;
       v[j] = n < N ? __ldg(xr + n) : 0.f;
     }
+    if (z) {
+      const float* zr = z + row * N;
+      float zz[NPL];
+#pragma unroll
+      for (int j = 0; j < NPL; ++j) {
+        const int n = lane + 32 * j;
+        zz[j] = n < N ? __ldg(zr + n) : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < NPL; ++j) v[j] *= dact_f(act, zz[j]);
+    }
+    if (xout && blockIdx.y == 0) {
+      float* o = xout + row * N;
+#pragma unroll
+      for (int j = 0; j < NPL; ++j) {
+        const int n = lane + 32 * j;
+        if (n < N) o[n] = v[j];
+      }
+    }
   }
-  const float* src = fa + (long long)r0 * N;
-  const int total = rc * N;
-  if ((N & 3) == 0) {
-    for (int e = threadIdx.x * 4; e < total; e += 1024)
-      *reinterpret_cast<float4*>(tab + e) = __ldg(reinterpret_cast<const float4*>(src + e));
+  if (vec) {
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
   } else {
     for (int e = threadIdx.x; e < total; e += 256) tab[e] = __ldg(src + e);
   }
@@ -62,7 +94,9 @@ __global__ void __launch_bounds__(256) fno1d_analysis_kernel(const float* __rest
       a1 = fmaf(v[j + 1], n + 32 < N ? t[n + 32] : 0.f, a1);
     }
     const float sum = warp_sum(a0 + a1);
-    if (lane == 0) spec[((long long)(r0 + rr) * Bn + b) * I + i] = sum;
+    const int r = r0 + rr;
+    const int orow = rowmap ? 2 * (r % K) + r / K : r;
+    if (lane == 0) spec[((long long)orow * Bn + b) * I + i] = sum;
   }
 }
 

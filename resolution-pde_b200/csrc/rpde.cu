@@ -173,6 +173,23 @@ int rpde_spectral1d_fwd(const float* x, const float* w, const float* fa, const f
   return RPDE_OK;
 }
 
+// analysis launch shared by the fused forward (x -> spec) and the fused backward prologue (dy, z -> dpre, dom)
+static int launch_fno1d_analysis(const float* x, const float* table, float* out, int B, int rows_per_b, int N, int modes,
+                                 const float* z, int act, float* xout, int rowmap, cudaStream_t s) {
+  dim3 g1((unsigned)(((long long)B * rows_per_b + 7) / 8), (unsigned)((2 * modes + FNO_RC - 1) / FNO_RC));
+  const size_t smem1 = (size_t)FNO_RC * N * sizeof(float);
+  if (smem1 > 48 * 1024)      // N in (1536, 2048]: 64 KB table chunk (the attribute is per device: set it on every call)
+    RPDE_CUDA(cudaFuncSetAttribute(fno1d_analysis_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  if (N <= 256)
+    fno1d_analysis_kernel<8><<<g1, 256, smem1, s>>>(x, table, out, B, rows_per_b, N, modes, z, act, xout, rowmap);
+  else if (N <= 1024)
+    fno1d_analysis_kernel<32><<<g1, 256, smem1, s>>>(x, table, out, B, rows_per_b, N, modes, z, act, xout, rowmap);
+  else
+    fno1d_analysis_kernel<64><<<g1, 256, smem1, s>>>(x, table, out, B, rows_per_b, N, modes, z, act, xout, rowmap);
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+
 int rpde_fno_block1d_fwd(const float* x, const float* w, const float* fa, const float* fs4, const float* wb,
                          const float* bb, float* spec, float* y, float* z, int B, int I, int O, int N, int modes, int act,
                          void* ws, size_t ws_bytes, rpde_stream_t stream) {
@@ -187,17 +204,8 @@ int rpde_fno_block1d_fwd(const float* x, const float* w, const float* fa, const 
   cudaStream_t s = (cudaStream_t)stream;
   float* om = (float*)ws;
   if (!spec) spec = (float*)((char*)ws + align_up((size_t)modes * B * 2 * O * 4));   // inference: spectrum stays in the workspace
-  dim3 g1((unsigned)(((long long)B * I + 7) / 8), (unsigned)((2 * modes + FNO_RC - 1) / FNO_RC));
-  const size_t smem1 = (size_t)FNO_RC * N * sizeof(float);
-  if (smem1 > 48 * 1024)      // N in (1536, 2048]: 64 KB table chunk (the attribute is per device: set it on every call)
-    RPDE_CUDA(cudaFuncSetAttribute(fno1d_analysis_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
-  if (N <= 256)
-    fno1d_analysis_kernel<8><<<g1, 256, smem1, s>>>(x, fa, spec, B, I, N, modes);
-  else if (N <= 1024)
-    fno1d_analysis_kernel<32><<<g1, 256, smem1, s>>>(x, fa, spec, B, I, N, modes);
-  else
-    fno1d_analysis_kernel<64><<<g1, 256, smem1, s>>>(x, fa, spec, B, I, N, modes);
-  RPDE_LAUNCH_CHECK();
+  int rc1 = launch_fno1d_analysis(x, fa, spec, B, I, N, modes, nullptr, 0, nullptr, 0, s);
+  if (rc1) return rc1;
   if (smem2 > 48 * 1024)
     RPDE_CUDA(cudaFuncSetAttribute(fno1d_mix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
   dim3 gm((unsigned)((O + FNO_MO - 1) / FNO_MO), (unsigned)B);
@@ -216,10 +224,12 @@ int rpde_fno_block1d_fwd(const float* x, const float* w, const float* fa, const 
   return RPDE_OK;
 }
 
-int rpde_spectral1d_bwd(const float* dy, const float* w, const float* fa, const float* fs, const float* spec,
-                        float* dx, int dx_accumulate, float* dw, int B, int I, int O, int N, int modes, void* ws,
-                        size_t ws_bytes, rpde_stream_t stream) {
-  if (!dy || !w || !fa || !fs || !spec || B <= 0 || I <= 0 || O <= 0 || N <= 0 || modes <= 0)
+// z / act / fs4 / dpre non-NULL select the fused prologue (rpde_fno_block1d_bwd): dpre = dy * act'(z) and its projection on the
+// synthesis table in one launch instead of rpde_act_bwd + memset + split-K contraction
+static int spectral1d_bwd_impl(const float* dy, const float* z, int act, const float* fs4, float* dpre, const float* w,
+                               const float* fa, const float* fs, const float* spec, float* dx, int dx_accumulate, float* dw,
+                               int B, int I, int O, int N, int modes, void* ws, size_t ws_bytes, rpde_stream_t stream) {
+  if (!dy || !w || !fa || !(fs || fs4) || !spec || B <= 0 || I <= 0 || O <= 0 || N <= 0 || modes <= 0)
     return fail(RPDE_E_INVALID, "rpde_spectral1d_bwd: bad arguments%s");
   if (modes > N / 2 + 1) return fail(RPDE_E_MODES, "SpectralConv1d: modes1 exceeds N//2+1%s");
   if (!ws || ws_bytes < rpde_spectral1d_workspace_bytes(B, I, O, N, modes))
@@ -235,15 +245,21 @@ int rpde_spectral1d_bwd(const float* dy, const float* w, const float* fa, const 
   if (rc) return rc;
   const long long BI = (long long)B * I, BO = (long long)B * O;
   // 3'. dom[(k,ro)][(b,o)] = sum_n dy[(b,o)][n] fs[n][(k,ro)]
-  RPDE_CUDA(cudaMemsetAsync(dom, 0, (size_t)K * 2 * BO * sizeof(float), s));
   GemmP g = gemm_default();
-  g.A = dy; g.B = fs; g.C = dom;
-  g.M = B * O; g.N = 2 * K; g.K = N;
-  g.a = MatDesc{lin(0), lin(N), lin(1)};
-  g.b = MatDesc{lin(0), lin(2 * K), lin(1)};
-  g.c = MatDesc{lin(0), lin(1), lin(BO)};
-  g.splitk = 0;
-  RPDE_CUDA(gemm(g, s));
+  if (fs4) {
+    rc = launch_fno1d_analysis(dy, fs4, dom, B, O, N, K, z, act, dpre, 1, s);
+    if (rc) return rc;
+    if (dpre) dy = dpre;
+  } else {
+    RPDE_CUDA(cudaMemsetAsync(dom, 0, (size_t)K * 2 * BO * sizeof(float), s));
+    g.A = dy; g.B = fs; g.C = dom;
+    g.M = B * O; g.N = 2 * K; g.K = N;
+    g.a = MatDesc{lin(0), lin(N), lin(1)};
+    g.b = MatDesc{lin(0), lin(2 * K), lin(1)};
+    g.c = MatDesc{lin(0), lin(1), lin(BO)};
+    g.splitk = 0;
+    RPDE_CUDA(gemm(g, s));
+  }
   if (dw) {
     // dWp[k] = spec[k]^T dom[k]
     RPDE_CUDA(cudaMemsetAsync(P, 0, (size_t)K * 4 * I * O * sizeof(float), s));
@@ -278,6 +294,23 @@ int rpde_spectral1d_bwd(const float* dy, const float* w, const float* fa, const 
     RPDE_CUDA(gemm(g, s));
   }
   return RPDE_OK;
+}
+
+int rpde_spectral1d_bwd(const float* dy, const float* w, const float* fa, const float* fs, const float* spec,
+                        float* dx, int dx_accumulate, float* dw, int B, int I, int O, int N, int modes, void* ws,
+                        size_t ws_bytes, rpde_stream_t stream) {
+  if (!fs) return fail(RPDE_E_INVALID, "rpde_spectral1d_bwd: bad arguments%s");
+  return spectral1d_bwd_impl(dy, nullptr, 0, nullptr, nullptr, w, fa, fs, spec, dx, dx_accumulate, dw, B, I, O, N, modes, ws,
+                             ws_bytes, stream);
+}
+
+int rpde_fno_block1d_bwd(const float* dy, const float* z, int act, const float* w, const float* fa, const float* fs4,
+                         const float* spec, float* dpre, float* dx, int dx_accumulate, float* dw, int B, int I, int O, int N,
+                         int modes, void* ws, size_t ws_bytes, rpde_stream_t stream) {
+  if (!fs4 || N > 2048 || (z && !dpre) || (!z && dpre))
+    return fail(RPDE_E_INVALID, "rpde_fno_block1d_bwd: bad arguments (N <= 2048; z and dpre come together)%s");
+  return spectral1d_bwd_impl(dy, z, act, fs4, dpre, w, fa, nullptr, spec, dx, dx_accumulate, dw, B, I, O, N, modes, ws,
+                             ws_bytes, stream);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -25,6 +25,9 @@ _ACT_BY_NAME = {"identity": ACT_NONE, "none": ACT_NONE, "gelu": ACT_GELU, "relu"
 _state = threading.local()
 _default_precision = 0
 _fno_fused = os.environ.get("RPDE_FNO_FUSED", "1") != "0"   # fused FNOBlock1d forward (rpde_fno_block1d_fwd); 0 = composed path
+# fused backward prologue (rpde_fno_block1d_bwd: act' multiply + synthesis adjoint in one launch).  FNO1d Burgers fwd+bwd:
+# 0.723 ms composed -> 0.679 ms fused forward -> 0.638 ms with this prologue (profiles/README.md r1i); 0 = composed prologue
+_fno_fused_bwd = os.environ.get("RPDE_FNO_FUSED_BWD", "1") != "0"
 
 
 def set_precision(name: str) -> None:
@@ -237,13 +240,28 @@ class _FNOSpectralFn(torch.autograd.Function):
         dw1 = torch.empty_like(w1r)
         dw2 = torch.empty_like(w2r) if w2 is not None else None
         dwb = dbb = None
+        fused = ndim == 1 and _fno_fused and _fno_fused_bwd and spatial[0] <= 2048
         with _Ctx(x) as c:
-            if act != ACT_NONE:
+            if fused:
+                # act' multiply + projection on the synthesis table in one launch, then the spectral backward proper
+                n, k = spatial[0], modes[0]
+                dpre = torch.empty_like(dy) if act != ACT_NONE else None
+                fs4 = dft_table(4, n, k, 0, 1.0 / n, x.device)
+                nb = c.lib.rpde_spectral1d_workspace_bytes(B, I, O, n, k)
+                ws = _ws(nb, x.device)
+                _lib.check(c.lib.rpde_fno_block1d_bwd(_p(dy), _p(z) if dpre is not None else None, act, _p(w1r), _p(tabs[0]), _p(fs4),
+                                                      _p(spec), _p(dpre), _p(dx), 0, _p(dw1), B, I, O, n, k, _p(ws), nb, c.stream),
+                           "rpde_fno_block1d_bwd")
+                if dpre is None:
+                    dpre = dy
+            elif act != ACT_NONE:
                 dpre = torch.empty_like(dy)
                 _lib.check(c.lib.rpde_act_bwd(_p(dy), _p(z), _p(dpre), dy.numel(), act, c.stream), "rpde_act_bwd")
             else:
                 dpre = dy
-            if ndim == 1:
+            if fused:
+                pass
+            elif ndim == 1:
                 nb = c.lib.rpde_spectral1d_workspace_bytes(B, I, O, spatial[0], modes[0])
                 ws = _ws(nb, x.device)
                 _lib.check(c.lib.rpde_spectral1d_bwd(_p(dpre), _p(w1r), _p(tabs[0]), _p(tabs[1]), _p(spec), _p(dx), 0, _p(dw1),

@@ -20,6 +20,15 @@ def engine(request):
     R.set_precision("fp32")
 
 
+@pytest.fixture(autouse=True, params=[False, True], ids=["bwd-composed", "bwd-fused"])
+def _fused_backward(request):
+    """both backward prologues: the composed one (default) and rpde_fno_block1d_bwd (RPDE_FNO_FUSED_BWD=1)"""
+    from resolution_pde_b200 import ops
+    old, ops._fno_fused_bwd = ops._fno_fused_bwd, request.param
+    yield
+    ops._fno_fused_bwd = old
+
+
 @pytest.fixture
 def composed():
     """context: run the composed (unfused) 1-D path"""
