@@ -84,11 +84,14 @@ int rpde_spectral1d_bwd(const float* dy, const float* w, const float* fa, const 
 /* Backward of the fused block: rpde_spectral1d_bwd with a fused prologue.  dpre = dy * act'(z) (written when z != NULL; this
  * is the gradient the bypass conv's backward consumes) and its projection on the synthesis table come from one launch
  * instead of rpde_act_bwd + memset + split-K contraction; the rest (weight gradient, mixing adjoint, analysis adjoint) is
- * rpde_spectral1d_bwd's.  fs4: kind-4 table scale 1/N.  z = dpre = NULL for act == none.  N <= 2048.  Workspace as
+ * rpde_spectral1d_bwd's, except that with dx_accumulate = 0 the input gradient dx = analysis adjoint + wb^T dpre (the bypass
+ * conv's input gradient; wb (O,I) may be NULL) comes from one kernel, so callers must NOT run rpde_conv1x1_bwd_input as well
+ * (RPDE_FNO_FUSED_DX=0 in the environment restores the separate kernels; rpde_fno_block1d_bwd_fuses_dx() tells).  fs4: kind-4 table scale 1/N.  z = dpre = NULL for act == none.  N <= 2048.  Workspace as
  * rpde_spectral1d_workspace_bytes. */
+int rpde_fno_block1d_bwd_fuses_dx(void);
 int rpde_fno_block1d_bwd(const float* dy, const float* z, int act, const float* w, const float* fa, const float* fs4,
-                         const float* spec, float* dpre, float* dx, int dx_accumulate, float* dw, int B, int I, int O, int N,
-                         int modes, void* ws, size_t ws_bytes, rpde_stream_t stream);
+                         const float* spec, const float* wb, float* dpre, float* dx, int dx_accumulate, float* dw, int B, int I,
+                         int O, int N, int modes, void* ws, size_t ws_bytes, rpde_stream_t stream);
 
 /* ---- FNO SpectralConv2d (models/spectral_convolution.py:61-98), (B,I,H,W) -> (B,O,H,W) ---------------------
  * w1, w2: complex64 (I,O,m1,m2).  fa_y/fs_y: kind 0/4 tables for axis W with k = m2 (scales 1, 1/W);

@@ -32,7 +32,8 @@ SIGNATURES = {
     "rpde_spectral1d_fwd": (I, [P, P, P, P, P, P, P, I, I, I, I, I, I, I, P, Z, S]),
     "rpde_spectral1d_bwd": (I, [P, P, P, P, P, P, I, P, I, I, I, I, I, P, Z, S]),
     "rpde_fno_block1d_fwd": (I, [P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, P, Z, S]),
-    "rpde_fno_block1d_bwd": (I, [P, P, I, P, P, P, P, P, P, I, P, I, I, I, I, I, P, Z, S]),
+    "rpde_fno_block1d_bwd_fuses_dx": (I, []),
+    "rpde_fno_block1d_bwd": (I, [P, P, I, P, P, P, P, P, P, P, I, P, I, I, I, I, I, P, Z, S]),
     "rpde_spectral2d_workspace_bytes": (Z, [I, I, I, I, I, I, I]),
     "rpde_spectral2d_fwd": (I, [P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, P, Z, S]),
     "rpde_spectral2d_bwd": (I, [P, P, P, P, P, P, P, P, P, I, P, P, I, I, I, I, I, I, I, P, Z, S]),
@@ -78,6 +79,10 @@ def load() -> ctypes.CDLL:
         raise ExtensionMissing(
             f"{LIB_PATH} not found: build the CUDA extension first (python -c 'import __graft_entry__ as g; g.build()' "
             "or python resolution-pde_b200/build.py).  There is no CPU/PyTorch fallback for this path.")
+    # rpde_fno_block1d_bwd can also produce dx (analysis adjoint + bypass dgrad) in one kernel; parity-green on B200 (277 tests,
+    # profiles/r1j_tests.log) but measured slower than the two separate kernels (0.656 vs 0.638 ms/step, FNO1d Burgers): off
+    # unless the caller sets RPDE_FNO_FUSED_DX=1 before the first call (the library reads it once)
+    os.environ.setdefault("RPDE_FNO_FUSED_DX", "0")
     lib = ctypes.CDLL(LIB_PATH)
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported

@@ -143,7 +143,9 @@ __global__ void __launch_bounds__(256) fno1d_synth_bypass_kernel(const float* __
                                                                  const float* __restrict__ fs4, const float* __restrict__ wb,
                                                                  const float* __restrict__ bb, float* __restrict__ y,
                                                                  float* __restrict__ z, int Bn, int I, int O, int N, int K,
-                                                                 int act) {
+                                                                 int act, int adjoint) {
+  // adjoint = 1 (backward, dx = analysis adjoint of dsp + bypass dgrad): the table is the analysis table fa[(k,ri)][n] (row r
+  // as is) and the bypass weight is read transposed, wb[(reduction channel)][output channel]
   constexpr int NT = TN / 16;            // consecutive grid points per thread (8 or 4)
   __shared__ __align__(16) float As[FNO_KT][FNO_OB + 4];
   __shared__ __align__(16) float Bs[FNO_KT][TN + 4];
@@ -170,7 +172,8 @@ __global__ void __launch_bounds__(256) fno1d_synth_bypass_kernel(const float* __
         const int rr = e / FNO_OB, oo = e - rr * FNO_OB;
         const int r = r0 + rr, o = o0 + oo;
         const bool ok = r < RT && o < O;
-        const float* p = r < R ? om + ((long long)r * Bn + b) * O + o : wb + (long long)o * I + (r - R);
+        const float* p = r < R ? om + ((long long)r * Bn + b) * O + o
+                               : (adjoint ? wb + (long long)(r - R) * O + o : wb + (long long)o * I + (r - R));
         ra[j] = ok ? __ldg(p) : 0.f;
       }
 #pragma unroll
@@ -179,7 +182,8 @@ __global__ void __launch_bounds__(256) fno1d_synth_bypass_kernel(const float* __
         const int rr = e / TN, nn = e - rr * TN;
         const int r = r0 + rr, n = n0 + nn;
         const bool ok = r < RT && n < N;      // spectral rows r = (k, ro) come from the plane-major synthesis table fs4[ro][k][n]
-        const float* p = r < R ? fs4 + ((long long)(r & 1) * K + (r >> 1)) * N + n : x + ((long long)b * I + (r - R)) * N + n;
+        const float* p = r < R ? fs4 + (adjoint ? (long long)r : (long long)(r & 1) * K + (r >> 1)) * N + n
+                               : x + ((long long)b * I + (r - R)) * N + n;
         rb[j] = ok ? __ldg(p) : 0.f;
       }
 #pragma unroll

@@ -173,6 +173,22 @@ int rpde_spectral1d_fwd(const float* x, const float* w, const float* fa, const f
   return RPDE_OK;
 }
 
+// synthesis + bypass launch shared by the fused forward and (adjoint = 1) the fused input gradient
+static int launch_fno1d_synth(const float* x, const float* om, const float* table, const float* wb, const float* bb, float* y,
+                              float* z, int B, int I, int O, int N, int modes, int act, int adjoint, cudaStream_t s) {
+  static const int tn_sel = getenv("RPDE_FNO_TN") ? atoi(getenv("RPDE_FNO_TN")) : 0;   // bring-up switch: 64 or 128
+  const bool wide = tn_sel ? tn_sel == 128 : (long long)((N + 127) / 128) * B >= 2 * 148;   // enough 128-point tiles to fill the SMs twice
+  if (wide) {
+    dim3 g2((unsigned)((N + 127) / 128), (unsigned)B);
+    fno1d_synth_bypass_kernel<128><<<g2, 256, 0, s>>>(x, om, table, wb, bb, y, z, B, I, O, N, modes, act, adjoint);
+  } else {
+    dim3 g2((unsigned)((N + 63) / 64), (unsigned)B);
+    fno1d_synth_bypass_kernel<64><<<g2, 256, 0, s>>>(x, om, table, wb, bb, y, z, B, I, O, N, modes, act, adjoint);
+  }
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+
 // analysis launch shared by the fused forward (x -> spec) and the fused backward prologue (dy, z -> dpre, dom)
 static int launch_fno1d_analysis(const float* x, const float* table, float* out, int B, int rows_per_b, int N, int modes,
                                  const float* z, int act, float* xout, int rowmap, cudaStream_t s) {
@@ -211,22 +227,13 @@ int rpde_fno_block1d_fwd(const float* x, const float* w, const float* fa, const 
   dim3 gm((unsigned)((O + FNO_MO - 1) / FNO_MO), (unsigned)B);
   fno1d_mix_kernel<<<gm, 256, smem2, s>>>(spec, w, om, B, I, O, modes);
   RPDE_LAUNCH_CHECK();
-  static const int tn_sel = getenv("RPDE_FNO_TN") ? atoi(getenv("RPDE_FNO_TN")) : 0;   // bring-up switch: 64 or 128
-  const bool wide = tn_sel ? tn_sel == 128 : (long long)((N + 127) / 128) * B >= 2 * 148;   // enough 128-point tiles to fill the SMs twice
-  if (wide) {
-    dim3 g2((unsigned)((N + 127) / 128), (unsigned)B);
-    fno1d_synth_bypass_kernel<128><<<g2, 256, 0, s>>>(x, om, fs4, wb, bb, y, z, B, I, O, N, modes, act);
-  } else {
-    dim3 g2((unsigned)((N + 63) / 64), (unsigned)B);
-    fno1d_synth_bypass_kernel<64><<<g2, 256, 0, s>>>(x, om, fs4, wb, bb, y, z, B, I, O, N, modes, act);
-  }
-  RPDE_LAUNCH_CHECK();
-  return RPDE_OK;
+  return launch_fno1d_synth(x, om, fs4, wb, bb, y, z, B, I, O, N, modes, act, 0, s);
 }
 
 // z / act / fs4 / dpre non-NULL select the fused prologue (rpde_fno_block1d_bwd): dpre = dy * act'(z) and its projection on the
 // synthesis table in one launch instead of rpde_act_bwd + memset + split-K contraction
-static int spectral1d_bwd_impl(const float* dy, const float* z, int act, const float* fs4, float* dpre, const float* w,
+static int spectral1d_bwd_impl(const float* dy, const float* z, int act, const float* fs4, float* dpre, const float* wb,
+                               int fuse_dx, const float* w,
                                const float* fa, const float* fs, const float* spec, float* dx, int dx_accumulate, float* dw,
                                int B, int I, int O, int N, int modes, void* ws, size_t ws_bytes, rpde_stream_t stream) {
   if (!dy || !w || !fa || !(fs || fs4) || !spec || B <= 0 || I <= 0 || O <= 0 || N <= 0 || modes <= 0)
@@ -284,6 +291,8 @@ static int spectral1d_bwd_impl(const float* dy, const float* z, int act, const f
     g.c = MatDesc{lin(2 * BI), lin(I), two(I, BI, 1)};
     RPDE_CUDA(gemm(g, s));
     // 1'. dx[(b,i)][n] (+)= sum_(k,ri) dsp[(k,ri)][(b,i)] fa[(k,ri)][n]
+    if (fuse_dx && !dx_accumulate)   // (+ the bypass conv's input gradient wb^T dpre in the same kernel; dy == dpre here)
+      return launch_fno1d_synth(dy, dsp, fa, wb, nullptr, dx, nullptr, B, /*reduction channels*/ O, /*outputs*/ I, N, K, ACT_NONE, 1, s);
     g = gemm_default();
     g.A = dsp; g.B = fa; g.C = dx;
     g.M = B * I; g.N = N; g.K = 2 * K;
@@ -300,17 +309,20 @@ int rpde_spectral1d_bwd(const float* dy, const float* w, const float* fa, const 
                         float* dx, int dx_accumulate, float* dw, int B, int I, int O, int N, int modes, void* ws,
                         size_t ws_bytes, rpde_stream_t stream) {
   if (!fs) return fail(RPDE_E_INVALID, "rpde_spectral1d_bwd: bad arguments%s");
-  return spectral1d_bwd_impl(dy, nullptr, 0, nullptr, nullptr, w, fa, fs, spec, dx, dx_accumulate, dw, B, I, O, N, modes, ws,
-                             ws_bytes, stream);
+  return spectral1d_bwd_impl(dy, nullptr, 0, nullptr, nullptr, nullptr, 0, w, fa, fs, spec, dx, dx_accumulate, dw, B, I, O, N,
+                             modes, ws, ws_bytes, stream);
 }
 
+int rpde_fno_block1d_bwd_fuses_dx(void) { return !(getenv("RPDE_FNO_FUSED_DX") && atoi(getenv("RPDE_FNO_FUSED_DX")) == 0); }
+
 int rpde_fno_block1d_bwd(const float* dy, const float* z, int act, const float* w, const float* fa, const float* fs4,
-                         const float* spec, float* dpre, float* dx, int dx_accumulate, float* dw, int B, int I, int O, int N,
-                         int modes, void* ws, size_t ws_bytes, rpde_stream_t stream) {
+                         const float* spec, const float* wb, float* dpre, float* dx, int dx_accumulate, float* dw, int B, int I,
+                         int O, int N, int modes, void* ws, size_t ws_bytes, rpde_stream_t stream) {
   if (!fs4 || N > 2048 || (z && !dpre) || (!z && dpre))
     return fail(RPDE_E_INVALID, "rpde_fno_block1d_bwd: bad arguments (N <= 2048; z and dpre come together)%s");
-  return spectral1d_bwd_impl(dy, z, act, fs4, dpre, w, fa, nullptr, spec, dx, dx_accumulate, dw, B, I, O, N, modes, ws,
-                             ws_bytes, stream);
+  static const bool fuse_dx = !(getenv("RPDE_FNO_FUSED_DX") && atoi(getenv("RPDE_FNO_FUSED_DX")) == 0);
+  return spectral1d_bwd_impl(dy, z, act, fs4, dpre, wb, fuse_dx ? 1 : 0, w, fa, nullptr, spec, dx, dx_accumulate, dw, B, I, O, N,
+                             modes, ws, ws_bytes, stream);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -241,6 +241,7 @@ class _FNOSpectralFn(torch.autograd.Function):
         dw2 = torch.empty_like(w2r) if w2 is not None else None
         dwb = dbb = None
         fused = ndim == 1 and _fno_fused and _fno_fused_bwd and spatial[0] <= 2048
+        dx_done = False
         with _Ctx(x) as c:
             if fused:
                 # act' multiply + projection on the synthesis table in one launch, then the spectral backward proper
@@ -249,9 +250,11 @@ class _FNOSpectralFn(torch.autograd.Function):
                 fs4 = dft_table(4, n, k, 0, 1.0 / n, x.device)
                 nb = c.lib.rpde_spectral1d_workspace_bytes(B, I, O, n, k)
                 ws = _ws(nb, x.device)
+                wbc = wb.detach().reshape(O, I).contiguous() if wb is not None else None
+                dx_done = bool(c.lib.rpde_fno_block1d_bwd_fuses_dx())      # dx then includes the bypass conv's input gradient
                 _lib.check(c.lib.rpde_fno_block1d_bwd(_p(dy), _p(z) if dpre is not None else None, act, _p(w1r), _p(tabs[0]), _p(fs4),
-                                                      _p(spec), _p(dpre), _p(dx), 0, _p(dw1), B, I, O, n, k, _p(ws), nb, c.stream),
-                           "rpde_fno_block1d_bwd")
+                                                      _p(spec), _p(wbc) if dx_done else None, _p(dpre), _p(dx), 0, _p(dw1), B, I, O,
+                                                      n, k, _p(ws), nb, c.stream), "rpde_fno_block1d_bwd")
                 if dpre is None:
                     dpre = dy
             elif act != ACT_NONE:
@@ -275,7 +278,7 @@ class _FNOSpectralFn(torch.autograd.Function):
                                                      modes[0], modes[1], _p(ws), nb, c.stream), "rpde_spectral2d_bwd")
             if wb is not None:
                 wbc = wb.detach().reshape(O, I).contiguous()
-                if need_x:
+                if need_x and not (fused and dx_done):
                     _lib.check(c.lib.rpde_conv1x1_bwd_input(_p(dpre), _p(wbc), None, 0, _p(dx), 1, B, I, O, S, c.stream),
                                "rpde_conv1x1_bwd_input")
                 dwb = torch.empty_like(wb)
