@@ -14,7 +14,7 @@ autograd on the CPU gives oracle gradients for every parameter.
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl
 reference legs may import this module, and only as the checker or the timed CPU
-baseline.  The product path (resolution-pde_b200/) never imports it.
+baseline.  The product path (resolution_pde_b200/) never imports it.
 
 Parity pin: the reference has no tests or golden vectors of its own (SURVEY §4,
 §8c).  The pin is therefore tests/golden/*.npz, produced by oracle/make_golden.py

@@ -1,7 +1,7 @@
 """CPU restatement of the reference's autoregressive rollout and its evaluation loop -- TEST INFRASTRUCTURE.
 
 Only tests/, __graft_entry__.smoke() and the benchmark's CPU legs may import this module, and only as the checker or
-the timed CPU baseline.  The product (resolution-pde_b200/rollout.py) never imports it.
+the timed CPU baseline.  The product (resolution_pde_b200/rollout.py) never imports it.
 
 Follows `utils/autoregressive_step.py`:
   perform_rollout       <- perform_rollout_1d (:284-309); the 2-D case is the same loop on (B, H, W) states (the

@@ -1,12 +1,25 @@
-"""Importable alias of the package directory `resolution-pde_b200/` (a hyphen cannot be imported).
+"""resolution-pde, B200-native spectral path.
 
-`import resolution_pde_b200` executes `resolution-pde_b200/__init__.py` with this module's __path__ pointing
-at that directory, so `resolution_pde_b200.ops`, `.fno`, ... resolve to the files there.
+Drop-in replacements for the reference's spectral layers and the two model families built on them
+(models/spectral_convolution.py, models/fno.py, models/fno_blocks.py, models/ffno.py,
+models/custom_layer.py: FeedForward/WNLinear, utils/loss.py), backed by hand-written sm_100a CUDA kernels
+behind the C ABI in include/rpde_b200.h.
 """
-import os as _os
+from . import _lib, ops
+from .custom_layer import FeedForward, Linear, WNLinear
+from .ffno import FFNO1D, FFNO2D
+from .fno import FNO1d, FNO2d
+from .fno_blocks import FNOBlock1d, FNOBlock2d, MLP1d, MLP2d
+from .loss import RelativeL2Loss
+from .ops import get_precision, set_precision
+from .training import GraphedTrainStep
+from .optim import FusedAdamW
+from .rollout import RolloutEvaluator, SimpleNormalizer, evaluate_rollout, perform_rollout_1d, perform_rollout_2d, rollout_losses
+from .spectral_convolution import FSpectralConv1d, FSpectralConv2d, SpectralConv1d, SpectralConv2d
 
-_real = _os.path.join(_os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))), "resolution-pde_b200")
-__path__ = [_real]
-with open(_os.path.join(_real, "__init__.py")) as _f:
-    exec(compile(_f.read(), _os.path.join(_real, "__init__.py"), "exec"))
-del _f
+__all__ = [
+    "SpectralConv1d", "SpectralConv2d", "FSpectralConv1d", "FSpectralConv2d", "FNOBlock1d", "FNOBlock2d", "MLP1d",
+    "MLP2d", "FNO1d", "FNO2d", "FFNO1D", "FFNO2D", "FeedForward", "WNLinear", "Linear", "RelativeL2Loss",
+    "set_precision", "get_precision", "ops", "GraphedTrainStep", "FusedAdamW", "RolloutEvaluator", "SimpleNormalizer",
+    "evaluate_rollout", "perform_rollout_1d", "perform_rollout_2d", "rollout_losses",
+]

@@ -78,7 +78,7 @@ def load() -> ctypes.CDLL:
     if not os.path.exists(LIB_PATH):
         raise ExtensionMissing(
             f"{LIB_PATH} not found: build the CUDA extension first (python -c 'import __graft_entry__ as g; g.build()' "
-            "or python resolution-pde_b200/build.py).  There is no CPU/PyTorch fallback for this path.")
+            "or python resolution_pde_b200/build.py).  There is no CPU/PyTorch fallback for this path.")
     # rpde_fno_block1d_bwd can also produce dx (analysis adjoint + bypass dgrad) in one kernel; parity-green on B200 (277 tests,
     # profiles/r1j_tests.log) but measured slower than the two separate kernels (0.656 vs 0.638 ms/step, FNO1d Burgers): off
     # unless the caller sets RPDE_FNO_FUSED_DX=1 before the first call (the library reads it once)

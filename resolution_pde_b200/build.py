@@ -1,4 +1,4 @@
-"""Builds librpde_b200.so in-tree with nvcc for sm_100a.  `python resolution-pde_b200/build.py [--force]`."""
+"""Builds librpde_b200.so in-tree with nvcc for sm_100a.  `python resolution_pde_b200/build.py [--force]`."""
 import os
 import subprocess
 import sys

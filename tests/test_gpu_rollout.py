@@ -1,4 +1,4 @@
-"""GPU (-m gpu): the device rollout (resolution-pde_b200/rollout.py: rpde_rollout_renorm / rpde_rollout_loss behind
+"""GPU (-m gpu): the device rollout (resolution_pde_b200/rollout.py: rpde_rollout_renorm / rpde_rollout_loss behind
 perform_rollout_1d/2d, rollout_losses, RolloutEvaluator) against the fixtures generated from the unmodified reference
 (tests/golden/rollout), against the CPU oracle at other sizes, and through size-independent properties at benchmark sizes."""
 import ctypes
