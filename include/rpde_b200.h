@@ -50,6 +50,10 @@ int rpde_get_precision(void);
 unsigned long long rpde_launch_count(void);
 /* ... of which contractions executed by the tcgen05/TMA tensor-core engine (0 under RPDE_PREC_FP32). */
 unsigned long long rpde_tc_launch_count(void);
+/* ... and contractions that ran on the CUDA-core FMA engine (every one under RPDE_PREC_FP32; under the tensor-core
+ * precisions only shapes TMA cannot address or launch-bound ones).  Tests assert on it so that a layout regression
+ * cannot hide as a slowdown. */
+unsigned long long rpde_simt_launch_count(void);
 
 /* Twiddle / truncated-DFT tables, generated on the device in fp64 and rounded once to fp32.
  * Replaces the cuFFT/pocketfft plans behind torch.fft.rfft/irfft/rfft2/irfft2
@@ -84,9 +88,11 @@ int rpde_spectral1d_bwd(const float* dy, const float* w, const float* fa, const 
 /* Backward of the fused block: rpde_spectral1d_bwd with a fused prologue.  dpre = dy * act'(z) (written when z != NULL; this
  * is the gradient the bypass conv's backward consumes) and its projection on the synthesis table come from one launch
  * instead of rpde_act_bwd + memset + split-K contraction; the rest (weight gradient, mixing adjoint, analysis adjoint) is
- * rpde_spectral1d_bwd's, except that with dx_accumulate = 0 the input gradient dx = analysis adjoint + wb^T dpre (the bypass
- * conv's input gradient; wb (O,I) may be NULL) comes from one kernel, so callers must NOT run rpde_conv1x1_bwd_input as well
- * (RPDE_FNO_FUSED_DX=0 in the environment restores the separate kernels; rpde_fno_block1d_bwd_fuses_dx() tells).  fs4: kind-4 table scale 1/N.  z = dpre = NULL for act == none.  N <= 2048.  Workspace as
+ * rpde_spectral1d_bwd's.  wb (O,I) is the explicit switch for the fused input gradient: when it is given (needs dx,
+ * dx_accumulate = 0, B <= 65535, else RPDE_E_INVALID) dx = analysis adjoint + wb^T dpre (the bypass conv's input gradient)
+ * comes from one kernel, so the caller must NOT run rpde_conv1x1_bwd_input as well; with wb = NULL dx is the spectral part
+ * only.  No environment variable is read.  rpde_fno_block1d_bwd_fuses_dx() returns 1 when the library supports the wb
+ * form.  fs4: kind-4 table scale 1/N.  z = dpre = NULL for act == none.  N <= 2048.  Workspace as
  * rpde_spectral1d_workspace_bytes. */
 int rpde_fno_block1d_bwd_fuses_dx(void);
 int rpde_fno_block1d_bwd(const float* dy, const float* z, int act, const float* w, const float* fa, const float* fs4,
@@ -198,7 +204,7 @@ int rpde_rollout_renorm(const float* pred, float* preds_out, float* next_state, 
  * preds + b*preds_batch_stride + t*preds_step_stride, truth likewise (strides in floats: truth may be the view
  * trajectories[:, 1:T+1] of a (B, T_all, S) tensor).  decode = 1 applies pred*y_scale + y_mean first (:176-181).
  * acc: 2*B*T floats scratch; step_losses: T floats, step_losses[t] = mean_b ||p-y|| / (||y|| + 1e-8);
- * batch_loss: 1 float = sum_t step_losses[t] / T.  B*T <= 65535. */
+ * batch_loss: 1 float = sum_t step_losses[t] / T.  B*T < 2^31 (no grid-dimension limit). */
 int rpde_rollout_loss(const float* preds, const float* truth, float* acc, float* step_losses, float* batch_loss, int B,
                       int T, long long S, long long preds_batch_stride, long long preds_step_stride,
                       long long truth_batch_stride, long long truth_step_stride, float y_scale, float y_mean,

@@ -27,6 +27,7 @@ SIGNATURES = {
     "rpde_get_precision": (I, []),
     "rpde_launch_count": (ctypes.c_ulonglong, []),
     "rpde_tc_launch_count": (ctypes.c_ulonglong, []),
+    "rpde_simt_launch_count": (ctypes.c_ulonglong, []),
     "rpde_dft_table": (I, [P, I, I, I, I, c_double, S]),
     "rpde_spectral1d_workspace_bytes": (Z, [I, I, I, I, I]),
     "rpde_spectral1d_fwd": (I, [P, P, P, P, P, P, P, I, I, I, I, I, I, I, P, Z, S]),
@@ -79,10 +80,6 @@ def load() -> ctypes.CDLL:
         raise ExtensionMissing(
             f"{LIB_PATH} not found: build the CUDA extension first (python -c 'import __graft_entry__ as g; g.build()' "
             "or python resolution_pde_b200/build.py).  There is no CPU/PyTorch fallback for this path.")
-    # rpde_fno_block1d_bwd can also produce dx (analysis adjoint + bypass dgrad) in one kernel; parity-green on B200 (277 tests,
-    # profiles/r1j_tests.log) but measured slower than the two separate kernels (0.656 vs 0.638 ms/step, FNO1d Burgers): off
-    # unless the caller sets RPDE_FNO_FUSED_DX=1 before the first call (the library reads it once)
-    os.environ.setdefault("RPDE_FNO_FUSED_DX", "0")
     lib = ctypes.CDLL(LIB_PATH)
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported

@@ -24,6 +24,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <atomic>
 #include <mutex>
 #include <type_traits>
 
@@ -1218,12 +1219,17 @@ template <int BN, bool SPLIT, bool CH>
 static cudaError_t launch_cfg(const TcParams& P, const CUtensorMap& ma, const CUtensorMap& mb, const EpiMaps& em, int sms,
                               cudaStream_t s) {
   using C = Cfg<BN, SPLIT>;
-  static std::once_flag once;
-  static cudaError_t attr_rc = cudaSuccess;
-  std::call_once(once, [] {
-    attr_rc = cudaFuncSetAttribute(gemm_tc_kernel<BN, SPLIT, CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::smem_bytes);
-  });
-  if (attr_rc != cudaSuccess) return attr_rc;
+  // cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device attribute: one flag per device, so a single process that
+  // drives several GPUs (nn.DataParallel: one thread per device) configures the kernel on each of them
+  static std::atomic<unsigned char> attr_done[64];
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64 || !attr_done[dev].load(std::memory_order_acquire)) {
+    const cudaError_t attr_rc =
+        cudaFuncSetAttribute(gemm_tc_kernel<BN, SPLIT, CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::smem_bytes);
+    if (attr_rc != cudaSuccess) return attr_rc;
+    if (dev >= 0 && dev < 64) attr_done[dev].store(1, std::memory_order_release);
+  }
   const int grid = P.total_tiles < sms ? P.total_tiles : sms;
   static const bool pdl = !(getenv("RPDE_TC_PDL") && atoi(getenv("RPDE_TC_PDL")) == 0);
   if (pdl) {

@@ -596,8 +596,9 @@ __global__ void rollout_loss_partial_kernel(const float* __restrict__ preds, con
                                             float* __restrict__ acc, int Bn, long long S, long long chunk,
                                             long long p_bs, long long p_ts, long long t_bs, long long t_ts, float ys,
                                             float ym, int decode) {
-  const int bt = blockIdx.y, t = bt / Bn, b = bt - t * Bn;
-  const long long e0 = blockIdx.x * chunk, e1 = min(S, e0 + chunk);
+  // (b, t) rides in gridDim.x (2^31 - 1 blocks), the chunk of the field in gridDim.y: B*T is unbounded like the reference's loop
+  const int bt = blockIdx.x, t = bt / Bn, b = bt - t * Bn;
+  const long long e0 = blockIdx.y * chunk, e1 = min(S, e0 + chunk);
   const float* pb = preds + b * p_bs + t * p_ts;
   const float* yb = truth + b * t_bs + t * t_ts;
   float d2 = 0.f, y2 = 0.f;

@@ -34,6 +34,7 @@ static int fail(int code, const char* fmt, const char* a = "") {
 // launch statistics only (monotonic counter of kernels this library enqueued; read by bench.py)
 static std::atomic<unsigned long long> g_launches{0};
 static std::atomic<unsigned long long> g_tc_launches{0};  // contractions that ran on the tcgen05 engine
+static std::atomic<unsigned long long> g_simt_launches{0};  // contractions that ran on the CUDA-core FMA engine
 #define RPDE_LAUNCH_CHECK()        \
   do {                             \
     g_launches.fetch_add(1);       \
@@ -57,6 +58,7 @@ static cudaError_t gemm(const GemmP& p, cudaStream_t s) {
     static const bool log = getenv("RPDE_TC_DBG") && atoi(getenv("RPDE_TC_DBG")) == 9;
     if (log) fprintf(stderr, "[rpde simt] M=%d N=%d K=%d batch=%d splitk=%d\n", p.M, p.N, p.K, p.batch, p.splitk);
   }
+  if (p.M > 0 && p.N > 0 && p.batch > 0) g_simt_launches.fetch_add(1);
   return gemm_simt_launch(p, s);
 }
 
@@ -86,6 +88,7 @@ int rpde_set_precision(int prec) {
 int rpde_get_precision(void) { return g_prec; }
 unsigned long long rpde_launch_count(void) { return g_launches.load(); }
 unsigned long long rpde_tc_launch_count(void) { return g_tc_launches.load(); }
+unsigned long long rpde_simt_launch_count(void) { return g_simt_launches.load(); }
 
 // ------------------------------------------------------------------------------------------------
 int rpde_dft_table(float* out, int kind, int n, int k, int m1, double scale, rpde_stream_t stream) {
@@ -313,15 +316,19 @@ int rpde_spectral1d_bwd(const float* dy, const float* w, const float* fa, const 
                              modes, ws, ws_bytes, stream);
 }
 
-int rpde_fno_block1d_bwd_fuses_dx(void) { return !(getenv("RPDE_FNO_FUSED_DX") && atoi(getenv("RPDE_FNO_FUSED_DX")) == 0); }
+// 1: rpde_fno_block1d_bwd produces the complete input gradient (spectral + bypass conv) when it is given wb.
+// The choice is the caller's and is made per call by passing wb or NULL; no environment switch is read here.
+int rpde_fno_block1d_bwd_fuses_dx(void) { return 1; }
 
 int rpde_fno_block1d_bwd(const float* dy, const float* z, int act, const float* w, const float* fa, const float* fs4,
                          const float* spec, const float* wb, float* dpre, float* dx, int dx_accumulate, float* dw, int B, int I,
                          int O, int N, int modes, void* ws, size_t ws_bytes, rpde_stream_t stream) {
   if (!fs4 || N > 2048 || (z && !dpre) || (!z && dpre))
     return fail(RPDE_E_INVALID, "rpde_fno_block1d_bwd: bad arguments (N <= 2048; z and dpre come together)%s");
-  static const bool fuse_dx = !(getenv("RPDE_FNO_FUSED_DX") && atoi(getenv("RPDE_FNO_FUSED_DX")) == 0);
-  return spectral1d_bwd_impl(dy, z, act, fs4, dpre, wb, fuse_dx ? 1 : 0, w, fa, nullptr, spec, dx, dx_accumulate, dw, B, I, O, N,
+  if (wb && (dx_accumulate || !dx))
+    return fail(RPDE_E_INVALID, "rpde_fno_block1d_bwd: wb (fused bypass input gradient) needs dx and dx_accumulate == 0%s");
+  if (wb && B > 65535) return fail(RPDE_E_INVALID, "rpde_fno_block1d_bwd: fused input gradient is limited to B <= 65535%s");
+  return spectral1d_bwd_impl(dy, z, act, fs4, dpre, wb, wb ? 1 : 0, w, fa, nullptr, spec, dx, dx_accumulate, dw, B, I, O, N,
                              modes, ws, ws_bytes, stream);
 }
 
@@ -1003,15 +1010,16 @@ int rpde_rollout_loss(const float* preds, const float* truth, float* acc, float*
                       long long truth_batch_stride, long long truth_step_stride, float y_scale, float y_mean,
                       int decode, rpde_stream_t stream) {
   if (!preds || !truth || !acc || !step_losses || !batch_loss || B <= 0 || T <= 0 || S <= 0 ||
-      (long long)B * T > 65535)
-    return fail(RPDE_E_INVALID, "rpde_rollout_loss: bad arguments (B*T must be <= 65535)%s");
+      (long long)B * T > 0x7fffffffLL)
+    return fail(RPDE_E_INVALID, "rpde_rollout_loss: bad arguments%s");
   cudaStream_t s = (cudaStream_t)stream;
   const long long BT = (long long)B * T;
   RPDE_CUDA(cudaMemsetAsync(acc, 0, (size_t)2 * BT * sizeof(float), s));
   long long per = (148LL * 8 + BT - 1) / BT;
   long long chunk = (S + per - 1) / per;
   if (chunk < 4096) chunk = 4096;
-  dim3 grid((unsigned)((S + chunk - 1) / chunk), (unsigned)BT);
+  if ((S + chunk - 1) / chunk > 65535) chunk = (S + 65534) / 65535;
+  dim3 grid((unsigned)BT, (unsigned)((S + chunk - 1) / chunk));
   rollout_loss_partial_kernel<<<grid, 256, 0, s>>>(preds, truth, acc, B, S, chunk, preds_batch_stride, preds_step_stride,
                                                    truth_batch_stride, truth_step_stride, y_scale, y_mean, decode);
   RPDE_LAUNCH_CHECK();

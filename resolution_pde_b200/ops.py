@@ -28,6 +28,10 @@ _fno_fused = os.environ.get("RPDE_FNO_FUSED", "1") != "0"   # fused FNOBlock1d f
 # fused backward prologue (rpde_fno_block1d_bwd: act' multiply + synthesis adjoint in one launch).  FNO1d Burgers fwd+bwd:
 # 0.723 ms composed -> 0.679 ms fused forward -> 0.638 ms with this prologue (profiles/README.md r1i); 0 = composed prologue
 _fno_fused_bwd = os.environ.get("RPDE_FNO_FUSED_BWD", "1") != "0"
+# rpde_fno_block1d_bwd can also produce dx (analysis adjoint + bypass dgrad) in one kernel when it is handed the bypass
+# weight; parity-green on B200 (profiles/r1j_tests.log) but measured slower than the two separate kernels (0.656 vs 0.638
+# ms/step, FNO1d Burgers), so the wrapper only passes the weight when asked to
+_fno_fused_dx = os.environ.get("RPDE_FNO_FUSED_DX", "0") != "0"
 
 
 def set_precision(name: str) -> None:
@@ -169,7 +173,7 @@ class _FNOSpectralFn(torch.autograd.Function):
     """y = act(spectral(x; weights) [+ conv1x1(x; wb, bb)])   channels-first, 1-D or 2-D."""
 
     @staticmethod
-    def forward(ctx, x, w1, w2, wb, bb, act, ndim):
+    def forward(ctx, x, w1, w2, wb, bb, act, ndim, grad_on=True):
         _need_cuda(x, wb, bb)
         x = x.contiguous()
         B, I = x.shape[0], x.shape[1]
@@ -181,19 +185,19 @@ class _FNOSpectralFn(torch.autograd.Function):
         w2r = torch.view_as_real(w2.detach().contiguous()) if w2 is not None else None
         S = int(np.prod(spatial))
         y = torch.empty((B, O) + spatial, dtype=torch.float32, device=x.device)
-        need_grad = any(ctx.needs_input_grad)
+        need_grad = grad_on and any(ctx.needs_input_grad)
         z = torch.empty_like(y) if (act != ACT_NONE and need_grad) else None
         tabs = _spectral_tables(ndim, spatial, modes, x.device)
         nmodes = int(np.prod(modes)) * (2 if ndim == 2 else 1)
         spec = torch.empty(nmodes * B * 2 * I, dtype=torch.float32, device=x.device)
+        if bb is not None and wb is None:
+            raise RuntimeError("fno_spectral: a bias needs the bypass weight")
         fused = ndim == 1 and _fno_fused and spatial[0] <= 2048 and 8 * modes[0] * (I + 1) <= 200 * 1024 and B <= 65535
         if fused:
             # FNOBlock1d in three launches (analysis, mixing, synthesis + bypass + bias + activation), fp32 FMA
             n, k = spatial[0], modes[0]
             fs4 = dft_table(4, n, k, 0, 1.0 / n, x.device)
             wbc = wb.detach().reshape(O, I).contiguous() if wb is not None else None
-            if bb is not None and wb is None:
-                raise RuntimeError("fno_spectral: a bias needs the bypass weight")
             up = lambda v: (v + 255) // 256 * 256
             nb = up(k * B * 2 * O * 4) + (0 if need_grad else up(k * B * 2 * I * 4))
             ws = _ws(nb, x.device)
@@ -202,7 +206,7 @@ class _FNOSpectralFn(torch.autograd.Function):
                                                       _p(spec) if need_grad else None, _p(y), _p(z), B, I, O, n, k, act,
                                                       _p(ws), nb, c.stream), "rpde_fno_block1d_fwd")
             ctx.save_for_backward(x, w1, w2, wb, spec, z)
-            ctx.cfg = (act, ndim, B, I, O, spatial, modes, S, bb is not None)
+            ctx.cfg = (act, ndim, B, I, O, spatial, modes, S, bb is not None, True)
             return y
         with _Ctx(x) as c:
             beta = 0
@@ -224,13 +228,13 @@ class _FNOSpectralFn(torch.autograd.Function):
                                                      _p(spec), _p(y), _p(z), B, I, O, spatial[0], spatial[1], modes[0],
                                                      modes[1], beta, act, _p(ws), nb, c.stream), "rpde_spectral2d_fwd")
         ctx.save_for_backward(x, w1, w2, wb, spec, z)
-        ctx.cfg = (act, ndim, B, I, O, spatial, modes, S, bb is not None)
+        ctx.cfg = (act, ndim, B, I, O, spatial, modes, S, bb is not None, False)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         x, w1, w2, wb, spec, z = ctx.saved_tensors
-        act, ndim, B, I, O, spatial, modes, S, has_bias = ctx.cfg
+        act, ndim, B, I, O, spatial, modes, S, has_bias, fwd_fused = ctx.cfg
         dy = dy.contiguous()
         need_x = ctx.needs_input_grad[0]
         w1r = torch.view_as_real(w1.detach().contiguous())
@@ -240,7 +244,7 @@ class _FNOSpectralFn(torch.autograd.Function):
         dw1 = torch.empty_like(w1r)
         dw2 = torch.empty_like(w2r) if w2 is not None else None
         dwb = dbb = None
-        fused = ndim == 1 and _fno_fused and _fno_fused_bwd and spatial[0] <= 2048
+        fused = fwd_fused and _fno_fused_bwd          # one decision, taken in forward (same shape limits)
         dx_done = False
         with _Ctx(x) as c:
             if fused:
@@ -251,7 +255,7 @@ class _FNOSpectralFn(torch.autograd.Function):
                 nb = c.lib.rpde_spectral1d_workspace_bytes(B, I, O, n, k)
                 ws = _ws(nb, x.device)
                 wbc = wb.detach().reshape(O, I).contiguous() if wb is not None else None
-                dx_done = bool(c.lib.rpde_fno_block1d_bwd_fuses_dx())      # dx then includes the bypass conv's input gradient
+                dx_done = bool(_fno_fused_dx and wbc is not None and need_x)   # dx then includes the bypass conv's input gradient
                 _lib.check(c.lib.rpde_fno_block1d_bwd(_p(dy), _p(z) if dpre is not None else None, act, _p(w1r), _p(tabs[0]), _p(fs4),
                                                       _p(spec), _p(wbc) if dx_done else None, _p(dpre), _p(dx), 0, _p(dw1), B, I, O,
                                                       n, k, _p(ws), nb, c.stream), "rpde_fno_block1d_bwd")
@@ -286,11 +290,13 @@ class _FNOSpectralFn(torch.autograd.Function):
                 _lib.check(c.lib.rpde_conv1x1_bwd_params(_p(dpre), _p(x), _p(dwb), _p(dbb), B, I, O, S, c.stream),
                            "rpde_conv1x1_bwd_params")
         return (dx, torch.view_as_complex(dw1), torch.view_as_complex(dw2) if dw2 is not None else None, dwb, dbb,
-                None, None)
+                None, None, None)
 
 
 def fno_spectral(x, w1, w2=None, bypass_weight=None, bypass_bias=None, act: int = ACT_NONE):
-    return _FNOSpectralFn.apply(x, w1, w2, bypass_weight, bypass_bias, act, x.dim() - 2)
+    # autograd.Function.forward always runs with grad mode off: sample it here so torch.no_grad() inference
+    # (rollouts, evaluation) saves nothing and keeps the spectrum in the workspace
+    return _FNOSpectralFn.apply(x, w1, w2, bypass_weight, bypass_bias, act, x.dim() - 2, torch.is_grad_enabled())
 
 
 # ---------------------------------------------------------------------------------------------
@@ -300,7 +306,7 @@ class _FFNOFourierFn(torch.autograd.Function):
     """1-D: x (B,N,C), weights (w,).  2-D: x (B,M,N,C), weights (w_y, w_x); result = x-pass + y-pass."""
 
     @staticmethod
-    def forward(ctx, x, n_modes, mix, norm, *weights):
+    def forward(ctx, x, n_modes, mix, norm, grad_on, *weights):
         _need_cuda(x, *weights)
         x = x.contiguous()
         C = x.shape[-1]
@@ -327,7 +333,7 @@ class _FFNOFourierFn(torch.autograd.Function):
                                                     rest, C, k, w.shape[2], mix, _p(ws), nb, c.stream),
                            "rpde_ffno_axis_fwd")
                 specs.append(spec)
-        keep_spec = mix == MIX_FULL and any(ctx.needs_input_grad[4:])
+        keep_spec = grad_on and mix == MIX_FULL and any(ctx.needs_input_grad[5:])
         ctx.save_for_backward(*weights, *(specs if keep_spec else []))
         ctx.cfg = (n_modes, mix, norm, passes, C, len(weights), keep_spec, tuple(x.shape))
         return y
@@ -348,7 +354,7 @@ class _FFNOFourierFn(torch.autograd.Function):
                 fa = dft_table(0, n, k, 0, sf, dy.device)
                 fs = dft_table(1, n, k, 0, si, dy.device)
                 w = weights[wi].detach().contiguous()
-                want_w = keep_spec and ctx.needs_input_grad[4 + wi]
+                want_w = keep_spec and ctx.needs_input_grad[5 + wi]
                 dw = None
                 if want_w:
                     dw = torch.empty_like(w)
@@ -360,12 +366,12 @@ class _FFNOFourierFn(torch.autograd.Function):
                                                     outer, n, rest, C, k, w.shape[2], mix, _p(ws), nb, c.stream),
                            "rpde_ffno_axis_bwd")
         if mix != MIX_FULL:
-            dws = [torch.zeros_like(w) if ctx.needs_input_grad[4 + i] else None for i, w in enumerate(weights)]
-        return (dx, None, None, None, *dws)
+            dws = [torch.zeros_like(w) if ctx.needs_input_grad[5 + i] else None for i, w in enumerate(weights)]
+        return (dx, None, None, None, None, *dws)
 
 
 def ffno_fourier(x, weights: Sequence[torch.Tensor], n_modes: int, mix: int = MIX_FULL, norm: str = "ortho"):
-    return _FFNOFourierFn.apply(x, n_modes, mix, norm, *weights)
+    return _FFNOFourierFn.apply(x, n_modes, mix, norm, torch.is_grad_enabled(), *weights)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -422,7 +428,7 @@ class _FeedForwardFn(torch.autograd.Function):
        u = L_n(gelu(... gelu(L_1(x))));  v = LayerNorm(u) if ln;  y = residual + act(v)."""
 
     @staticmethod
-    def forward(ctx, x, residual, n_layers, use_ln, final_act, eps, *params):
+    def forward(ctx, x, residual, n_layers, use_ln, final_act, eps, grad_on, *params):
         _need_cuda(x, residual, *params)
         x = x.contiguous()
         C_in = x.shape[-1]
@@ -431,7 +437,7 @@ class _FeedForwardFn(torch.autograd.Function):
         bs = [params[2 * i + 1] for i in range(n_layers)]
         gamma = params[2 * n_layers] if use_ln else None
         beta = params[2 * n_layers + 1] if use_ln else None
-        need_grad = any(ctx.needs_input_grad)
+        need_grad = grad_on and any(ctx.needs_input_grad)
         acts, zs = [x], []
         dev = x.device
         res = residual.contiguous() if residual is not None else None
@@ -533,7 +539,7 @@ class _FeedForwardFn(torch.autograd.Function):
                     g = gin
                     if i == 0:
                         dx = gin.reshape(acts[0].shape)
-        return (dx, dres, None, None, None, None, *grads)
+        return (dx, dres, None, None, None, None, None, *grads)
 
 
 def feed_forward(x, residual, weights, biases, ln_weight=None, ln_bias=None, final_act: int = ACT_NONE, eps: float = 1e-5):
@@ -544,7 +550,7 @@ def feed_forward(x, residual, weights, biases, ln_weight=None, ln_bias=None, fin
     use_ln = ln_weight is not None
     if use_ln:
         params += [ln_weight, ln_bias]
-    return _FeedForwardFn.apply(x, residual, n, use_ln, final_act, eps, *params)
+    return _FeedForwardFn.apply(x, residual, n, use_ln, final_act, eps, torch.is_grad_enabled(), *params)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -595,7 +601,7 @@ class _MLPFn(torch.autograd.Function):
     """projection MLP (fno_blocks.py:35-45, 73-83): conv1x1 -> GELU -> conv1x1, GELU fused in both directions."""
 
     @staticmethod
-    def forward(ctx, x, w1, b1, w2, b2):
+    def forward(ctx, x, w1, b1, w2, b2, grad_on=True):
         _need_cuda(x, w1, b1, w2, b2)
         x = x.contiguous()
         B, I = x.shape[0], x.shape[1]
@@ -604,7 +610,7 @@ class _MLPFn(torch.autograd.Function):
         H, O = w1.shape[0], w2.shape[0]
         w1c = w1.detach().reshape(H, I).contiguous()
         w2c = w2.detach().reshape(O, H).contiguous()
-        need_grad = any(ctx.needs_input_grad)
+        need_grad = grad_on and any(ctx.needs_input_grad)
         h = torch.empty((B, H) + spatial, dtype=torch.float32, device=x.device)
         z = torch.empty_like(h) if need_grad else None
         y = torch.empty((B, O) + spatial, dtype=torch.float32, device=x.device)
@@ -642,11 +648,11 @@ class _MLPFn(torch.autograd.Function):
                 dx = torch.empty_like(x)
                 _lib.check(c.lib.rpde_conv1x1_bwd_input(_p(dz), _p(w1c), None, 0, _p(dx), 0, B, I, H, S, c.stream),
                            "rpde_conv1x1_bwd_input")
-        return dx, dw1, db1, dw2, db2
+        return dx, dw1, db1, dw2, db2, None
 
 
 def mlp_gelu(x, w1, b1, w2, b2):
-    return _MLPFn.apply(x, w1, b1, w2, b2)
+    return _MLPFn.apply(x, w1, b1, w2, b2, torch.is_grad_enabled())
 
 
 class _WeightNormFn(torch.autograd.Function):

@@ -1,0 +1,183 @@
+"""GPU (-m gpu): oracle parity at every BASELINE.json configuration AT ITS REAL SHAPE.
+
+The resolution sweeps in test_gpu_parity.py use narrow models; here the model hyper-parameters, grid sizes and (where
+the fp64 CPU oracle finishes in seconds) batch sizes are the ones BASELINE.json / conf/model/*.yaml name:
+
+  C1  FFNO1D  width 128, 64 modes, 4 layers, 3 FF layers, LayerNorm, weight-norm, gelu;  N = 512,  batch 32
+  C2  FNO1d   16 modes, width 64, relu, 4 blocks;                                        N = 1024, batch 16
+  C3  FFNO2D  width 64, 64 modes, 4 layers, 3 FF layers, LayerNorm, weight-norm;         256 x 256, batch 2 (of 16)
+  C4  FNO2d   modes 12/12, width 32, gelu, 4 blocks;                                     64^2, 128^2, 256^2
+  C5  2-D 512^2 and 1024^2 at batch 1, F-FNO 1-D at N = 2048 (the super-resolution sweep's largest grids)
+
+Forward output, loss and EVERY gradient are compared with oracle/reference_port.py evaluated in fp64 on the CPU
+(models/ffno.py:131-237, models/fno.py:24-150, conf/model/ffno_2d/ffno_2d.yaml:4-14), on both fp32-accurate engines at
+the north_star tolerance 1e-5, and on the fast variants (tf32, bf16) at their stated model-level tolerances.
+"""
+import os
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from helpers import TOL, assert_grads_close, rel
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+# stated model-level tolerances of the fast variants: relative L2 per tensor against the fp64 oracle
+FAST_TOL = {"tf32": (1e-3, 4e-3), "bf16": (1e-2, 4e-2)}      # (outputs / loss, gradients)
+
+C1 = dict(kind="FFNO1D", ctor=dict(in_channels=1, out_channels=1, width=128, n_layers=4, n_modes=64, factor=4, ff_weight_norm=True,
+                                   n_ff_layers=3, layer_norm=True, dropout=0.0, activation="gelu"),
+          hyper=dict(n_layers=4, n_modes=64, n_ff_layers=3, layer_norm=True, activation="gelu"))
+C2 = dict(kind="FNO1d", ctor=dict(in_channels=1, out_channels=1, modes=16, width=64), hyper=dict(activation="relu", n_blocks=4))
+C3 = dict(kind="FFNO2D", ctor=dict(in_channels=1, out_channels=1, width=64, n_layers=4, n_modes=64, factor=4, ff_weight_norm=True,
+                                   n_ff_layers=3, layer_norm=True, dropout=0.0),
+          hyper=dict(n_layers=4, n_modes=64, n_ff_layers=3, layer_norm=True, use_grid=True))
+C4 = dict(kind="FNO2d", ctor=dict(in_channels=1, out_channels=1, modes1=12, modes2=12, width=32), hyper=dict(activation="gelu", n_blocks=4))
+
+
+def _fields(shape, seed):
+    """smooth standardised fields (what the model sees in training): low-pass filtered noise"""
+    g = torch.Generator().manual_seed(seed)
+    out = []
+    for _ in range(2):
+        f = torch.randn(*shape, generator=g)
+        if len(shape) == 4:
+            ft = torch.fft.rfft2(f)
+            kx = torch.fft.fftfreq(shape[2], 1.0 / shape[2]).abs().reshape(-1, 1)
+            ky = torch.arange(ft.shape[-1]).reshape(1, -1)
+            ft = ft * (1.0 + kx ** 2 + ky ** 2) ** -0.75
+            f = torch.fft.irfft2(ft, s=shape[2:])
+        else:
+            ft = torch.fft.rfft(f)
+            ft = ft * (1.0 + torch.arange(ft.shape[-1]) ** 2) ** -0.5
+            f = torch.fft.irfft(ft, n=shape[-1])
+        out.append(((f - f.mean()) / f.std()).float().contiguous())
+    return out
+
+
+def _relu_margin(kind, sd, x, y, hyper):
+    """smallest |pre-activation| / rms over every ReLU input of the fp64 oracle (see test_gpu_parity._relu_margin)"""
+    from oracle import reference_port as rp
+    margins = []
+
+    def rec(t, *a, **k):
+        margins.append((t.abs().min() / t.pow(2).mean().sqrt()).item())
+        return F.relu(t, *a, **k)
+
+    rp.step_loss_and_grads(kind, sd, x, y, dtype=torch.float64, **dict(hyper, activation=rec))
+    return min(margins)
+
+
+SKIPPED_DRAWS = []   # (kind, shape, seed, margin): draws whose ReLU mask is a coin toss in fp32; printed by the C2 test
+
+
+def _run(cfg, shape, seed, engine, tol_out=TOL, tol_grad=TOL, scale_spectral=None, relu_guard=0.0):
+    import resolution_pde_b200 as R
+    from oracle import reference_port as rp
+    for attempt in range(12):
+        torch.manual_seed(seed)
+        m = getattr(R, cfg["kind"])(**cfg["ctor"])
+        if scale_spectral:                   # FNO: the reference's init (scale 1/(in*out)) makes the spectral branch tiny
+            with torch.no_grad():
+                for b in m.fno_blocks:
+                    for p in b.spectral_conv.parameters():
+                        p.mul_(scale_spectral)
+        x, y = _fields(shape, seed + 1)
+        sd = {k: v.detach().clone() for k, v in m.state_dict().items()}
+        if not relu_guard:
+            break
+        # With 4 x 10^6 ReLU inputs per step, some draws put a pre-activation within fp32 rounding (~1e-7 rms) of zero: the
+        # mask of that element is then a coin toss in ANY fp32 implementation and flips a gradient entry (measured
+        # 1e-3 relative on the affected weight gradient).  Such a draw cannot be held to 1e-5; it is
+        # recorded (and printed) and the next seed is taken.
+        margin = _relu_margin(cfg["kind"], sd, x, y, cfg["hyper"])
+        if margin > relu_guard:
+            break
+        SKIPPED_DRAWS.append((cfg["kind"], shape, seed, margin))
+        seed += 1000
+    pred_o, loss_o, g_o = rp.step_loss_and_grads(cfg["kind"], sd, x, y, dtype=torch.float64, **cfg["hyper"])
+    R.set_precision(engine)
+    try:
+        m = m.to(DEV)
+        lib = R._lib.load()
+        s0 = lib.rpde_simt_launch_count()
+        out = m(x.to(DEV))
+        loss = R.RelativeL2Loss()(out, y.to(DEV))
+        loss.backward()
+        torch.cuda.synchronize()
+        simt = lib.rpde_simt_launch_count() - s0
+    finally:
+        R.set_precision("fp32")
+    assert rel(out, pred_o) < tol_out, ("output", rel(out, pred_o))
+    assert abs(loss.item() - loss_o.item()) < tol_out * max(1.0, abs(loss_o.item())), (loss.item(), loss_o.item())
+    grads = {k: (p.grad if p.grad is not None else torch.zeros_like(p)) for k, p in m.named_parameters()}
+    assert_grads_close(grads, g_o, tol_grad)
+    return simt
+
+
+ENGINES = [e for e in os.environ.get("RPDE_TEST_PRECISION", "fp32,3xtf32").split(",") if e]
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+def test_c1_ffno1d_ks512_b32(engine):
+    _run(C1, (32, 1, 512), 101, engine)
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+def test_c2_fno1d_burgers1024_b16(engine):
+    _run(C2, (16, 1, 1024), 202, engine, scale_spectral=20.0, relu_guard=5e-7)
+    for rec in SKIPPED_DRAWS:
+        print("ReLU-kink draw skipped (kind, shape, seed, min |z| / rms):", rec)
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+def test_c3_ffno2d_ns256(engine):
+    simt = _run(C3, (2, 1, 256, 256), 303, engine)
+    if engine != "fp32":
+        # Every contraction of the C3 step whose operands TMA can address must run on the tcgen05 engine.  The CUDA-core
+        # engine is left with the 3-channel in_proj / 1-channel out_proj contractions and similar unaligned shapes.
+        assert simt <= 6, f"{simt} CUDA-core contractions in the C3 step: a layout fell off the tensor-core engine"
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+@pytest.mark.parametrize("n", [64, 128, 256])
+def test_c4_fno2d_ns(engine, n):
+    _run(C4, (2 if n == 256 else 4, 1, n, n), 404 + n, engine, scale_spectral=10.0)
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+@pytest.mark.parametrize("n", [512, 1024])
+def test_c5_fno2d_large_grids(engine, n):
+    _run(C4, (1, 1, n, n), 505 + n, engine, scale_spectral=10.0)
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+@pytest.mark.parametrize("n,layers,width", [(512, 2, 64), (1024, 1, 32)])
+def test_c5_ffno2d_large_grids(engine, n, layers, width):
+    cfg = dict(kind="FFNO2D", ctor=dict(C3["ctor"], n_layers=layers, width=width), hyper=dict(C3["hyper"], n_layers=layers))
+    _run(cfg, (1, 1, n, n), 606 + n, engine)
+
+
+@pytest.mark.parametrize("engine", ENGINES)
+def test_c5_ffno1d_n2048(engine):
+    _run(C1, (4, 1, 2048), 707, engine)
+
+
+# ---- fast variants: model-level tolerance, stated and tested (north_star: "stated tolerance for the bf16/TF32 variant")
+@pytest.mark.parametrize("engine", ["tf32", "bf16"])
+@pytest.mark.parametrize("case", ["c1", "c3", "c2", "c4"])
+def test_fast_variant_model_level_tolerance(engine, case):
+    import resolution_pde_b200 as R
+    if engine not in R.ops.PREC:
+        pytest.skip(f"{engine} variant not built")
+    to, tg = FAST_TOL[engine]
+    if case == "c1":
+        _run(C1, (32, 1, 512), 111, engine, to, tg)
+    elif case == "c3":
+        _run(C3, (2, 1, 256, 256), 313, engine, to, tg)
+    elif case == "c2":
+        _run(C2, (16, 1, 1024), 212, engine, to, tg, scale_spectral=20.0, relu_guard=5e-7)
+    else:
+        _run(C4, (2, 1, 128, 128), 414, engine, to, tg, scale_spectral=10.0)
