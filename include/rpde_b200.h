@@ -39,7 +39,8 @@ enum { RPDE_MIX_FULL = 0, RPDE_MIX_LOWPASS = 1 };
 enum { RPDE_DFT_R2C_ANALYSIS = 0, RPDE_DFT_C2R_SYNTHESIS = 1, RPDE_DFT_C2C_ANALYSIS_ROWS = 2, RPDE_DFT_C2C_SYNTHESIS_ROWS = 3,
        RPDE_DFT_C2R_SYNTHESIS_PLANES = 4 };
 /* precision of the contraction engine */
-enum { RPDE_PREC_FP32 = 0, RPDE_PREC_3XTF32 = 1, RPDE_PREC_TF32 = 2 };
+enum { RPDE_PREC_FP32 = 0, RPDE_PREC_3XTF32 = 1, RPDE_PREC_TF32 = 2,
+       RPDE_PREC_BF16 = 3 /* fused BF16 FeedForward (rpde_ff3_*) where it applies, the TF32 engine elsewhere */ };
 
 int rpde_version(void);
 const char* rpde_last_error(void);
@@ -220,6 +221,29 @@ int rpde_rollout_loss(const float* preds, const float* truth, float* acc, float*
  * launch.  Complex parameters ride as their (re, im) fp32 view, as in torch.  Graph-capturable. */
 int rpde_adamw_step(const void* table, int ntensors, long long nchunks, float* hyper, double beta1, double beta2,
                     float eps, float weight_decay, rpde_stream_t stream);
+
+/* ---- fused F-FNO FeedForward layer, BF16 tensor cores (the fast variant; stated tolerance in DESIGN.md) --------------
+ * y = res + LayerNorm(W3 gelu(W2 gelu(W1 x + b1) + b2) + b3) * gamma + beta for C = 64 channels and hidden width 256:
+ * FeedForward with n_layers = 3, factor 4 (models/custom_layer.py:49-68) as FSpectralConv1d/2d call it
+ * (models/spectral_convolution.py:248-254) plus the layer's residual (models/ffno.py:116-118, 228-235), in ONE kernel.
+ * The hidden activations stay in TMEM (accumulator of one layer = BF16 A operand of the next); HBM traffic is
+ * read x (+ res) and write y.  rpde_ff3_supported(C, hidden) tells whether a shape is covered (64, 256).
+ * image: rpde_ff3_weight_image_bytes() bytes, the three weights (nn.Linear layout (out, in), fp32) as the BF16
+ * shared-memory image the kernels load; rebuild it with rpde_ff3_pack_weights whenever a weight changes.
+ * res, gamma/beta may be NULL (no residual / no LayerNorm).  All pointers 16-byte aligned, x/res/y are [T][64]. */
+size_t rpde_ff3_weight_image_bytes(void);
+int rpde_ff3_supported(int channels, int hidden);
+int rpde_ff3_pack_weights(const float* w1, const float* w2, const float* w3, void* image, rpde_stream_t stream);
+int rpde_ff3_fwd(const float* x, const float* res, const void* image, const float* b1, const float* b2, const float* b3,
+                 const float* gamma, const float* beta, float* y, long long T, float eps, rpde_stream_t stream);
+/* Backward of the same layer from x and dy alone: the forward pass is recomputed on chip (nothing but x is saved),
+ * ds = gradient w.r.t. x; dw*, db*, dgamma, dbeta are overwritten.  The weight gradients come from a second kernel
+ * pair over BF16 copies of the per-layer operands held in the workspace (rpde_ff3_bwd_workspace_bytes(T)).  The
+ * gradient w.r.t. res is dy itself and is left to the caller. */
+size_t rpde_ff3_bwd_workspace_bytes(long long T);
+int rpde_ff3_bwd(const float* x, const float* dy, const void* image, const float* b1, const float* b2, const float* b3,
+                 const float* gamma, float* ds, float* dw1, float* db1, float* dw2, float* db2, float* dw3, float* db3,
+                 float* dgamma, float* dbeta, long long T, float eps, void* ws, size_t ws_bytes, rpde_stream_t stream);
 
 /* ---- raw contraction (test hook): C[M,N] = A[M,K] B[K,N], row-major, through the selected engine -------- */
 int rpde_matmul(const float* a, const float* b, float* c, int M, int N, int K, int trans_a, int trans_b,

@@ -60,6 +60,12 @@ SIGNATURES = {
     "rpde_rollout_renorm": (I, [P, P, P, I, L, L, L, c_float, c_float, c_float, c_float, I, S]),
     "rpde_rollout_loss": (I, [P, P, P, P, P, I, I, L, L, L, L, L, c_float, c_float, I, S]),
     "rpde_adamw_step": (I, [P, I, L, P, c_double, c_double, c_float, c_float, S]),
+    "rpde_ff3_weight_image_bytes": (Z, []),
+    "rpde_ff3_supported": (I, [I, I]),
+    "rpde_ff3_pack_weights": (I, [P, P, P, P, S]),
+    "rpde_ff3_fwd": (I, [P, P, P, P, P, P, P, P, P, L, c_float, S]),
+    "rpde_ff3_bwd_workspace_bytes": (Z, [L]),
+    "rpde_ff3_bwd": (I, [P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, L, c_float, P, Z, S]),
     "rpde_matmul": (I, [P, P, P, I, I, I, I, I, S]),
 }
 

@@ -1,0 +1,863 @@
+// Fused F-FNO FeedForward layer for sm_100a, BF16 tensor cores (tcgen05.mma kind::f16, fp32 accumulate in TMEM):
+//
+//     y = res + LayerNorm( W3 gelu( W2 gelu( W1 x + b1 ) + b2 ) + b3 )            models/custom_layer.py:49-68 (FeedForward, 3 layers)
+//                                                                                  models/spectral_convolution.py:248-254 (backcast_ff)
+//                                                                                  models/ffno.py:228-235 (x = x + layer(x))
+//
+// for C = 64 channels and a hidden width of 4C = 256 (conf/model/ffno_2d/ffno_2d.yaml).  The 4C-wide hidden activations
+// never leave the SM: they live in TMEM as the accumulator of one layer and, converted to BF16 in place, as the A
+// operand of the next one (tcgen05.mma with A from TMEM).  HBM traffic of the forward pass is read x + read res + write y.
+//
+// One persistent CTA per SM; the three weight matrices (192 KB as BF16) are loaded once per CTA into shared memory in the
+// K-major SWIZZLE_128B image the UMMA descriptors expect (built once per weight update by ff_pack_weights_kernel), and the
+// same image serves the backward pass as the MN-major (transposed) operand.  Tile = 128 rows (TMEM lanes).
+//
+//   warp 0        UMMA issuer (one lane) + TMEM owner
+//   warp 1        weight image: one cp.async.bulk sequence at kernel start
+//   warps 2-5     x loader: fp32 rows -> BF16 -> swizzled shared-memory A tile (and, backward, the BF16 copy the
+//                 weight-gradient kernel reads)
+//   warps 6-13    epilogues, two warps per TMEM lane quadrant (even / odd 32-column chunks)
+//
+// TMEM (512 columns):   [0,256) D1 = x W1^T  -> gelu -> H1 (BF16 pairs, [0,128))           [256,512) D2 = H1 W2^T -> H2 ([256,384))
+//                       [128,192) D3 = H2 W3^T (read by the LayerNorm epilogue)
+//   backward (same kernel, BWD = true; the forward part is recomputed, nothing but x is saved by the forward pass):
+//                       [192,224) dZ3 (BF16)   [256,512) dH2 = dZ3 W3 -> * gelu'(Z2) -> dZ2 ([256,384))
+//                       [0,256) dH1 = dZ2 W2 -> * gelu'(Z1) -> dZ1 ([0,128))              [256,320) dS = dZ1 W1
+//   gelu'(Z1), gelu'(Z2) wait in a per-CTA scratch (L2-resident, written and re-read by the same thread); H1, H2, dZ1,
+//   dZ2, dZ3 and x leave as BF16 for the weight-gradient kernel (ff_wgrad_kernel below: dW = dZ^T H with K = rows).
+//
+// In-place conversion: the result of 32-column chunk c (16 packed columns) lands in columns that belong to chunk c/2.
+// The two warps of a quadrant own the even and the odd chunks and meet at a 64-thread named barrier after every chunk
+// load, so chunk c/2 has always been read by its owner before it is overwritten.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+
+#include "../../include/rpde_b200.h"
+#include "internal.h"
+#include "common.cuh"
+#include "tc_ptx.cuh"
+
+namespace rpde {
+namespace ff {
+using namespace tc;
+
+constexpr int C = 64, H = 256, TM = 128;
+constexpr uint32_t W1_OFF = 0, W1_BYTES = H * 128;                                    // [256 rows][64 bf16]
+constexpr uint32_t W2_OFF = W1_OFF + W1_BYTES, W2_PLANE = H * 128, W2_BYTES = 4 * W2_PLANE;  // 4 k-planes of [256 rows][64 bf16]
+constexpr uint32_t W3_OFF = W2_OFF + W2_BYTES, W3_PLANE = C * 128, W3_BYTES = 4 * W3_PLANE;  // 4 k-planes of [64 rows][64 bf16]
+constexpr uint32_t WBLOB = W3_OFF + W3_BYTES;                                          // 196608
+constexpr uint32_t X_OFF = WBLOB, X_BYTES = TM * 128;                                  // A tile of layer 1: [128 rows][64 bf16]
+constexpr uint32_t STAT_OFF = X_OFF + X_BYTES;                                         // row statistics exchange: 3 x [2][128] float2
+constexpr uint32_t STAT_BYTES = 3 * 2 * TM * 8;
+constexpr uint32_t BAR_OFF = STAT_OFF + STAT_BYTES;
+constexpr uint32_t SMEM_BYTES = BAR_OFF + 256;
+constexpr int kThreads = 14 * 32;
+// TMEM columns
+constexpr uint32_t D1 = 0, H1 = 0, D3 = 128, DZ3 = 192, D2 = 256, H2 = 256, D4 = 256, DZ2 = 256, D5 = 0, DZ1 = 0, D6 = 256;
+// barriers
+enum { B_WFULL = 0, B_XFULL, B_XEMPTY, B_D1, B_D2, B_D3, B_TILE, B_H1, B_H2 = B_H1 + 4, B_DZ3 = B_H2 + 4, B_D4, B_DZ2,
+       B_D5 = B_DZ2 + 4, B_DZ1, B_D6 = B_DZ1 + 4, B_COUNT };
+static_assert(B_COUNT * 8 + 8 <= 256, "barrier area");
+
+struct Params {
+  const float* x;       // [T][64] FeedForward input (spectral output)
+  const float* res;     // [T][64] residual or NULL (forward)
+  const uint8_t* blob;  // packed BF16 weight image (WBLOB bytes)
+  const float *b1, *b2, *b3, *gamma, *beta;  // gamma == NULL: no LayerNorm
+  float* y;             // forward output
+  long long T;
+  float eps;
+  // backward
+  const float* dy;      // [T][64]
+  float* ds;            // [T][64] gradient w.r.t. x
+  uint16_t *xb, *h1s, *h2s, *dz1s, *dz2s, *dz3s;  // BF16 copies for the weight-gradient kernel
+  uint8_t* gscratch;    // gridDim.x * 2 * 128 * 512 bytes
+  float *db1, *db2, *db3, *dgamma, *dbeta;        // zero-initialised by the caller, accumulated atomically
+};
+
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ float bf16_lo(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf16_hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
+
+__host__ __device__ constexpr uint32_t idesc_bf16(int M, int N, int b_mn_major) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)b_mn_major << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void umma_bf16_ss(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d), "l"(a), "l"(b), "r"(idesc), "r"(acc)
+      : "memory");
+}
+__device__ __forceinline__ void umma_bf16_ts(uint32_t d, uint32_t a_tmem, uint64_t b, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d), "r"(a_tmem), "l"(b), "r"(idesc), "r"(acc)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* v) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+      "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]), "r"(v[10]),
+      "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+      : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+               "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void pair_sync(int quad) { asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory"); }
+__device__ __forceinline__ void stg128(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint4 ldg128(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+
+// lane j receives the sum over the warp's 32 lanes of v[j] (31 shuffles): the column sums of a 32 x 32 block whose rows
+// are the lanes.  v is destroyed.
+__device__ __forceinline__ float colsum32(float (&v)[32], int lane) {
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const bool up = (lane & off) != 0;
+#pragma unroll
+    for (int k = 0; k < off; ++k) {
+      const float send = up ? v[k] : v[k + off];
+      const float keep = up ? v[k + off] : v[k];
+      v[k] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+  return v[0];
+}
+
+// One hidden-layer epilogue over this warp's four 32-column chunks (c = 2j + half), converted in place.
+//   MODE 0: h = gelu(acc + bias)                                         -> BF16 A operand                    (inference / forward)
+//   MODE 1: the same, plus gelu'(acc + bias) -> scratch and h -> spill                                        (backward: recompute)
+//   MODE 2: dz = acc * gelu' (from scratch) -> BF16 A operand, dz -> spill, column sums of dz (bias gradient)  (backward)
+template <int MODE>
+__device__ __forceinline__ void hidden_epi(uint32_t tlane, uint32_t src_col, uint32_t dst_col, int half, int quad, int lane,
+                                           uint32_t ready_bar0, const float* __restrict__ bias, bool valid,
+                                           uint16_t* spill_row, uint8_t* scratch_row, float (&cs)[4]) {
+#pragma unroll 1
+  for (int j = 0; j < 4; ++j) {
+    const int c = 2 * j + half;
+    uint32_t r[32];
+    tmem_ld32(tlane + src_col + 32 * c, r);
+    uint4 g4[4];
+    if (MODE == 2) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) g4[q] = ldg128(scratch_row + c * 64 + q * 16);
+    }
+    tmem_ld_wait();
+    tc_fence_before_sync();
+    pair_sync(quad);   // both warps of the quadrant have read their chunk 2j / 2j + 1: columns of chunk j may be overwritten
+    tc_fence_after_sync();
+    uint32_t p[16];
+    if (MODE != 2) {
+      float v[32];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const float4 b4 = __ldg(reinterpret_cast<const float4*>(bias + 32 * c) + q);
+        v[4 * q] = __uint_as_float(r[4 * q]) + b4.x;
+        v[4 * q + 1] = __uint_as_float(r[4 * q + 1]) + b4.y;
+        v[4 * q + 2] = __uint_as_float(r[4 * q + 2]) + b4.z;
+        v[4 * q + 3] = __uint_as_float(r[4 * q + 3]) + b4.w;
+      }
+      uint32_t gp[16];
+#pragma unroll
+      for (int k = 0; k < 32; k += 2) {
+        float h0, h1, g0, g1;
+        gelu_both2(v[k], v[k + 1], h0, h1, g0, g1);
+        p[k >> 1] = pack_bf16(h0, h1);
+        if (MODE == 1) gp[k >> 1] = pack_bf16(g0, g1);
+      }
+      tmem_st16(tlane + dst_col + 16 * c, p);
+      if (MODE == 1) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) stg128(scratch_row + c * 64 + q * 16, gp[4 * q], gp[4 * q + 1], gp[4 * q + 2], gp[4 * q + 3]);
+        if (valid) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) stg128(spill_row + c * 32 + q * 8, p[4 * q], p[4 * q + 1], p[4 * q + 2], p[4 * q + 3]);
+        }
+      }
+    } else {
+      float v[32];
+      const uint32_t* gw = reinterpret_cast<const uint32_t*>(g4);
+#pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        v[2 * k] = __uint_as_float(r[2 * k]) * bf16_lo(gw[k]);
+        v[2 * k + 1] = __uint_as_float(r[2 * k + 1]) * bf16_hi(gw[k]);
+        p[k] = pack_bf16(v[2 * k], v[2 * k + 1]);
+      }
+      tmem_st16(tlane + dst_col + 16 * c, p);
+      if (valid) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) stg128(spill_row + c * 32 + q * 8, p[4 * q], p[4 * q + 1], p[4 * q + 2], p[4 * q + 3]);
+      }
+      cs[j] += colsum32(v, lane);
+    }
+    tmem_st_wait();
+    tc_fence_before_sync();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(ready_bar0 + 8 * j);
+  }
+}
+
+template <bool BWD>
+__global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant__ Params P) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t sbase = smem_u32(smem_raw);
+  const uint32_t w1s = sbase + W1_OFF, w2s = sbase + W2_OFF, w3s = sbase + W3_OFF, xs = sbase + X_OFF;
+  const uint32_t bars = sbase + BAR_OFF;
+  auto bar = [&](int i) { return bars + 8u * (uint32_t)i; };
+  const uint32_t tmem_slot = bars + 8u * B_COUNT;
+  float2* stat = reinterpret_cast<float2*>(smem_raw + STAT_OFF);   // [3][2][128]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long ntiles = (P.T + TM - 1) / TM;
+
+  if (threadIdx.x == 0) {
+    mbar_init(bar(B_WFULL), 1);
+    mbar_init(bar(B_XFULL), 4);
+    mbar_init(bar(B_XEMPTY), 1);
+    mbar_init(bar(B_D1), 1);
+    mbar_init(bar(B_D2), 1);
+    mbar_init(bar(B_D3), 1);
+    mbar_init(bar(B_TILE), 8);
+    for (int j = 0; j < 4; ++j) {
+      mbar_init(bar(B_H1 + j), 8);
+      mbar_init(bar(B_H2 + j), 8);
+      mbar_init(bar(B_DZ2 + j), 8);
+      mbar_init(bar(B_DZ1 + j), 8);
+    }
+    mbar_init(bar(B_DZ3), 8);
+    mbar_init(bar(B_D4), 1);
+    mbar_init(bar(B_D5), 1);
+    mbar_init(bar(B_D6), 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) tmem_alloc(tmem_slot, 512);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  uint32_t tmem;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem) : "r"(tmem_slot));
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------------------------------------ UMMA issuer
+    if (lane == 0) {
+      constexpr uint32_t I256 = idesc_bf16(128, 256, 0), I64 = idesc_bf16(128, 64, 0);
+      constexpr uint32_t I256T = idesc_bf16(128, 256, 1), I64T = idesc_bf16(128, 64, 1);
+      const uint64_t dK = umma_desc(0, 16, 1024, UMMA_LAYOUT_SW128);                  // K-major, 8-row groups 1024 B apart
+      const uint64_t dT3 = umma_desc(0, W3_PLANE, 1024, UMMA_LAYOUT_SW128);           // MN-major views of the same images:
+      const uint64_t dT2 = umma_desc(0, W2_PLANE, 1024, UMMA_LAYOUT_SW128);           //   64-column groups one plane apart,
+      const uint64_t dT1 = umma_desc(0, W1_BYTES, 1024, UMMA_LAYOUT_SW128);           //   8-k-row groups 1024 B apart
+      mbar_wait(bar(B_WFULL), 0);
+      uint32_t it = 0;
+      for (long long t = blockIdx.x; t < ntiles; t += gridDim.x, ++it) {
+        const uint32_t ph = it & 1;
+        mbar_wait(bar(B_XFULL), ph);
+        if (it > 0) mbar_wait(bar(B_TILE), ph ^ 1);   // the last epilogue of the previous tile has left TMEM
+        tc_fence_after_sync();
+#pragma unroll
+        for (int s = 0; s < 4; ++s)
+          umma_bf16_ss(tmem + D1, dK + ((xs + 32u * s) >> 4), dK + ((w1s + 32u * s) >> 4), I256, s > 0);
+        umma_commit(bar(B_XEMPTY));
+        umma_commit(bar(B_D1));
+        for (int j = 0; j < 4; ++j) {
+          mbar_wait(bar(B_H1 + j), ph);
+          tc_fence_after_sync();
+#pragma unroll
+          for (int s = 0; s < 4; ++s)
+            umma_bf16_ts(tmem + D2, tmem + H1 + 32 * j + 8 * s, dK + ((w2s + j * W2_PLANE + 32u * s) >> 4), I256, (j | s) > 0);
+        }
+        umma_commit(bar(B_D2));
+        for (int j = 0; j < 4; ++j) {
+          mbar_wait(bar(B_H2 + j), ph);
+          tc_fence_after_sync();
+#pragma unroll
+          for (int s = 0; s < 4; ++s)
+            umma_bf16_ts(tmem + D3, tmem + H2 + 32 * j + 8 * s, dK + ((w3s + j * W3_PLANE + 32u * s) >> 4), I64, (j | s) > 0);
+        }
+        umma_commit(bar(B_D3));
+        if (BWD) {
+          mbar_wait(bar(B_DZ3), ph);
+          tc_fence_after_sync();
+#pragma unroll
+          for (int s = 0; s < 4; ++s)   // dH2 = dZ3 W3: K = 64 output features of layer 3 (rows of the W3 image)
+            umma_bf16_ts(tmem + D4, tmem + DZ3 + 8 * s, dT3 + ((w3s + 2048u * s) >> 4), I256T, s > 0);
+          umma_commit(bar(B_D4));
+          for (int j = 0; j < 4; ++j) {   // dH1 = dZ2 W2: K = 256 output features of layer 2
+            mbar_wait(bar(B_DZ2 + j), ph);
+            tc_fence_after_sync();
+#pragma unroll
+            for (int s = 0; s < 4; ++s)
+              umma_bf16_ts(tmem + D5, tmem + DZ2 + 32 * j + 8 * s, dT2 + ((w2s + 8192u * j + 2048u * s) >> 4), I256T, (j | s) > 0);
+          }
+          umma_commit(bar(B_D5));
+          for (int j = 0; j < 4; ++j) {   // dS = dZ1 W1
+            mbar_wait(bar(B_DZ1 + j), ph);
+            tc_fence_after_sync();
+#pragma unroll
+            for (int s = 0; s < 4; ++s)
+              umma_bf16_ts(tmem + D6, tmem + DZ1 + 32 * j + 8 * s, dT1 + ((w1s + 8192u * j + 2048u * s) >> 4), I64T, (j | s) > 0);
+          }
+          umma_commit(bar(B_D6));
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------------------------------------ weight image
+    if (lane == 0) {
+      mbar_arrive_expect_tx(bar(B_WFULL), WBLOB);
+      for (uint32_t o = 0; o < WBLOB; o += 32768) bulk_g2s(sbase + o, P.blob + o, 32768, bar(B_WFULL));
+    }
+  } else if (warp < 6) {
+    // ------------------------------------------------------------------------------------------------ x loader
+    const int lw = warp - 2, hl = lane >> 4, q = lane & 15;
+    uint32_t it = 0;
+    for (long long t = blockIdx.x; t < ntiles; t += gridDim.x, ++it) {
+      float4 v[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const long long row = t * TM + lw * 32 + 2 * i + hl;
+        v[i] = row < P.T ? __ldg(reinterpret_cast<const float4*>(P.x + row * C) + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      mbar_wait(bar(B_XEMPTY), (it & 1) ^ 1);   // layer 1 of the previous tile has consumed the buffer
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const int r = lw * 32 + 2 * i + hl;
+        const uint32_t lo = pack_bf16(v[i].x, v[i].y), hi = pack_bf16(v[i].z, v[i].w);
+        const uint32_t a = xs + r * 128 + ((((uint32_t)q >> 1) ^ ((uint32_t)r & 7u)) << 4) + ((uint32_t)q & 1u) * 8u;
+        asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(a), "r"(lo), "r"(hi) : "memory");
+        if (BWD) {
+          const long long row = t * TM + r;
+          if (row < P.T) asm volatile("st.global.v2.b32 [%0], {%1, %2};" ::"l"(P.xb + row * C + 4 * q), "r"(lo), "r"(hi) : "memory");
+        }
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(B_XFULL));
+    }
+  } else {
+    // ------------------------------------------------------------------------------------------------ epilogues
+    const int ew = warp - 6, quad = warp & 3, half = ew >> 2;
+    const uint32_t tlane = tmem + ((uint32_t)(quad * 32) << 16);
+    const int rl = quad * 32 + lane;                       // row of the tile = TMEM lane
+    const bool ln = P.gamma != nullptr;
+    float cs1[4] = {0.f, 0.f, 0.f, 0.f}, cs2[4] = {0.f, 0.f, 0.f, 0.f}, cs3 = 0.f, csg = 0.f, csb = 0.f;
+    uint8_t* scr = BWD ? P.gscratch + (size_t)blockIdx.x * (2 * TM * 512) + (size_t)rl * 512 : nullptr;
+    float dummy[4];
+    uint32_t it = 0;
+    for (long long t = blockIdx.x; t < ntiles; t += gridDim.x, ++it) {
+      const uint32_t ph = it & 1;
+      const long long row = t * TM + rl;
+      const bool valid = row < P.T;
+      // ---- layer 1 and 2: bias + GELU, converted in place into the next layer's A operand
+      mbar_wait(bar(B_D1), ph);
+      tc_fence_after_sync();
+      hidden_epi<BWD ? 1 : 0>(tlane, D1, H1, half, quad, lane, bar(B_H1), P.b1, valid, BWD ? P.h1s + row * H : nullptr, scr, dummy);
+      mbar_wait(bar(B_D2), ph);
+      tc_fence_after_sync();
+      hidden_epi<BWD ? 1 : 0>(tlane, D2, H2, half, quad, lane, bar(B_H2), P.b2, valid, BWD ? P.h2s + row * H : nullptr,
+                              BWD ? scr + TM * 512 : nullptr, dummy);
+      // ---- layer 3: bias, LayerNorm (row statistics shared by the two warps of the quadrant through shared memory)
+      float4 in4[8];   // forward: residual; backward: dy
+      {
+        const float* src = BWD ? P.dy : P.res;
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+          in4[q] = (src && valid) ? __ldg(reinterpret_cast<const float4*>(src + row * C + 32 * half) + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      mbar_wait(bar(B_D3), ph);
+      tc_fence_after_sync();
+      float v[32];
+      {
+        uint32_t r[32];
+        tmem_ld32(tlane + D3 + 32 * half, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const float4 b4 = __ldg(reinterpret_cast<const float4*>(P.b3 + 32 * half) + q);
+          v[4 * q] = __uint_as_float(r[4 * q]) + b4.x;
+          v[4 * q + 1] = __uint_as_float(r[4 * q + 1]) + b4.y;
+          v[4 * q + 2] = __uint_as_float(r[4 * q + 2]) + b4.z;
+          v[4 * q + 3] = __uint_as_float(r[4 * q + 3]) + b4.w;
+        }
+      }
+      if (!BWD) {   // the accumulator has been read: the next tile may start
+        tc_fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(B_TILE));
+      }
+      float mean = 0.f, rstd = 1.f;
+      if (ln) {
+        float s = 0.f;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) s += v[k];
+        stat[(0 * 2 + half) * TM + rl].x = s;
+        pair_sync(quad);
+        mean = (s + stat[(0 * 2 + (half ^ 1)) * TM + rl].x) * (1.0f / C);
+        float qv = 0.f;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+          const float d = v[k] - mean;
+          qv = fmaf(d, d, qv);
+        }
+        stat[(1 * 2 + half) * TM + rl].x = qv;
+        pair_sync(quad);
+        const float var = (qv + stat[(1 * 2 + (half ^ 1)) * TM + rl].x) * (1.0f / C);
+        rstd = 1.0f / sqrtf(var + P.eps);
+      }
+      if (!BWD) {
+        float* yo = P.y + row * C + 32 * half;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          float4 o = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+          if (ln) {
+            const float4 g4 = __ldg(reinterpret_cast<const float4*>(P.gamma + 32 * half) + q);
+            const float4 b4 = __ldg(reinterpret_cast<const float4*>(P.beta + 32 * half) + q);
+            o.x = (o.x - mean) * rstd * g4.x + b4.x;
+            o.y = (o.y - mean) * rstd * g4.y + b4.y;
+            o.z = (o.z - mean) * rstd * g4.z + b4.z;
+            o.w = (o.w - mean) * rstd * g4.w + b4.w;
+          }
+          o.x += in4[q].x; o.y += in4[q].y; o.z += in4[q].z; o.w += in4[q].w;
+          if (valid) *reinterpret_cast<float4*>(yo + 4 * q) = o;
+        }
+      } else {
+        // ---- LayerNorm backward: dz3 = rstd (g - mean(g) - xhat mean(g xhat)), g = dy gamma
+        float dz[32];
+        const float* dyv = reinterpret_cast<const float*>(in4);
+        if (ln) {
+          float s1 = 0.f, s2 = 0.f;
+          float gx[32];
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const float4 g4 = __ldg(reinterpret_cast<const float4*>(P.gamma + 32 * half) + q);
+            const float gg[4] = {g4.x, g4.y, g4.z, g4.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int k = 4 * q + e;
+              const float xh = (v[k] - mean) * rstd;
+              const float g = dyv[k] * gg[e];
+              s1 += g;
+              s2 = fmaf(g, xh, s2);
+              dz[k] = g;
+              v[k] = xh;
+              gx[k] = dyv[k] * xh;
+            }
+          }
+          stat[(2 * 2 + half) * TM + rl] = make_float2(s1, s2);
+          pair_sync(quad);
+          const float2 o = stat[(2 * 2 + (half ^ 1)) * TM + rl];
+          s1 = (s1 + o.x) * (1.0f / C);
+          s2 = (s2 + o.y) * (1.0f / C);
+#pragma unroll
+          for (int k = 0; k < 32; ++k) dz[k] = rstd * (dz[k] - s1 - v[k] * s2);
+          csg += colsum32(gx, lane);
+          float dyc[32];
+#pragma unroll
+          for (int k = 0; k < 32; ++k) dyc[k] = dyv[k];
+          csb += colsum32(dyc, lane);
+        } else {
+#pragma unroll
+          for (int k = 0; k < 32; ++k) dz[k] = dyv[k];
+        }
+        uint32_t p[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) p[k] = pack_bf16(dz[2 * k], dz[2 * k + 1]);
+        tmem_st16(tlane + DZ3 + 16 * half, p);
+        if (valid) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) stg128(P.dz3s + row * C + 32 * half + q * 8, p[4 * q], p[4 * q + 1], p[4 * q + 2], p[4 * q + 3]);
+        }
+        cs3 += colsum32(dz, lane);
+        tmem_st_wait();
+        tc_fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(B_DZ3));
+        // ---- dZ2 = dH2 * gelu'(Z2), dZ1 = dH1 * gelu'(Z1)
+        mbar_wait(bar(B_D4), ph);
+        tc_fence_after_sync();
+        hidden_epi<2>(tlane, D4, DZ2, half, quad, lane, bar(B_DZ2), nullptr, valid, P.dz2s + row * H, scr + TM * 512, cs2);
+        mbar_wait(bar(B_D5), ph);
+        tc_fence_after_sync();
+        hidden_epi<2>(tlane, D5, DZ1, half, quad, lane, bar(B_DZ1), nullptr, valid, P.dz1s + row * H, scr, cs1);
+        // ---- dS
+        mbar_wait(bar(B_D6), ph);
+        tc_fence_after_sync();
+        uint32_t r[32];
+        tmem_ld32(tlane + D6 + 32 * half, r);
+        tmem_ld_wait();
+        tc_fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(B_TILE));
+        if (valid) {
+          float* o = P.ds + row * C + 32 * half;
+#pragma unroll
+          for (int q = 0; q < 8; ++q) stg128(o + 4 * q, r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3]);
+        }
+      }
+    }
+    if (BWD) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        atomicAdd(P.db1 + 32 * (2 * j + half) + lane, cs1[j]);
+        atomicAdd(P.db2 + 32 * (2 * j + half) + lane, cs2[j]);
+      }
+      atomicAdd(P.db3 + 32 * half + lane, cs3);
+      if (ln) {
+        atomicAdd(P.dgamma + 32 * half + lane, csg);
+        atomicAdd(P.dbeta + 32 * half + lane, csb);
+      }
+    }
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after_sync();
+    tmem_dealloc(tmem, 512);
+  }
+}
+
+// fp32 weights (out, in) row-major -> the BF16 shared-memory image: K-major rows of 128 bytes (64 input features), the
+// 16-byte chunk c of row r stored at chunk c ^ (r & 7) (SWIZZLE_128B), one 1024-byte-aligned plane per 64 input features
+__global__ void ff_pack_weights_kernel(const float* __restrict__ w1, const float* __restrict__ w2, const float* __restrict__ w3,
+                                       uint8_t* __restrict__ blob) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;   // one 16-byte chunk (8 elements) per thread
+  if (i >= (int)(WBLOB / 16)) return;
+  const uint32_t off = (uint32_t)i * 16u;
+  const float* w;
+  int rows, in, local;
+  if (off < W2_OFF) { w = w1; rows = H; in = C; local = off; }
+  else if (off < W3_OFF) { w = w2; rows = H; in = H; local = off - W2_OFF; }
+  else { w = w3; rows = C; in = H; local = off - W3_OFF; }
+  const int plane = local / (rows * 128), rem = local % (rows * 128);
+  const int r = rem / 128, cpos = (rem % 128) / 16;
+  const int c = cpos ^ (r & 7);
+  const float* src = w + (size_t)r * in + plane * 64 + c * 8;
+  uint4 o;
+  o.x = pack_bf16(src[0], src[1]);
+  o.y = pack_bf16(src[2], src[3]);
+  o.z = pack_bf16(src[4], src[5]);
+  o.w = pack_bf16(src[6], src[7]);
+  *reinterpret_cast<uint4*>(blob + off) = o;
+}
+
+// ====================================================================================================================
+// Weight gradients of the fused layer: dW2 = dZ2^T H1 (job 0) and dW1 = dZ1^T Xb, dW3^T = H2^T dZ3 (job 1), K = rows.
+// Both operands are BF16 row-major [T][features] in global memory = MN-major operands: one TMA box of 64 rows x 64
+// features lands as a SWIZZLE_128B atom stack ([k rows][128 B]).  Each CTA owns a contiguous slab of 64-row k-blocks,
+// accumulates in TMEM (fp32) and adds its partial result to the zero-initialised gradient with red.global.add.
+//   warp 0: TMA producer, warp 1: UMMA issuer + TMEM owner, warps 2-5: final TMEM -> global reduction.
+// ====================================================================================================================
+constexpr int WG_THREADS = 6 * 32;
+constexpr uint32_t WG_BOX = 64 * 128;   // one 64 x 64 BF16 box
+
+template <int JOB>
+struct WgCfg {
+  // job 0: A = dZ2 (4 boxes), B = H1 (4 boxes)               -> D[2 x 128 lanes][256 cols] = 512 TMEM columns
+  // job 1: A0 = dZ1 (4 boxes), B0 = Xb (1 box) -> cols [0,128);  A1 = H2 (4 boxes), B1 = dZ3 (1 box) -> cols [128,256)
+  static constexpr int boxes = JOB == 0 ? 8 : 10;
+  static constexpr uint32_t stage_bytes = boxes * WG_BOX;
+  static constexpr int stages = JOB == 0 ? 3 : 2;
+  static constexpr uint32_t smem_bytes = stages * stage_bytes + 1024 + 256;
+  static constexpr int tmem_cols = JOB == 0 ? 512 : 256;
+};
+
+struct WgParams {
+  long long T;
+  float *dw1, *dw2, *dw3;   // (256,64), (256,256), (64,256) fp32, zero-initialised
+};
+
+template <int JOB>
+__global__ void __launch_bounds__(WG_THREADS, 1)
+ff_wgrad_kernel(const __grid_constant__ WgParams P, const __grid_constant__ CUtensorMap mA0, const __grid_constant__ CUtensorMap mB0,
+                const __grid_constant__ CUtensorMap mA1, const __grid_constant__ CUtensorMap mB1) {
+  using G = WgCfg<JOB>;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bars = sbase + G::stages * G::stage_bytes;
+  auto full = [&](int s) { return bars + 8u * s; };
+  auto empty = [&](int s) { return bars + 8u * (G::stages + s); };
+  const uint32_t done = bars + 8u * (2 * G::stages), tmem_slot = done + 8;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long kblocks = (P.T + 63) / 64;
+  const long long per = (kblocks + gridDim.x - 1) / gridDim.x;
+  const long long kb0 = (long long)blockIdx.x * per, kb1 = kb0 + per < kblocks ? kb0 + per : kblocks;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&mA0);
+    tma_prefetch_desc(&mB0);
+    for (int s = 0; s < G::stages; ++s) {
+      mbar_init(full(s), 1);
+      mbar_init(empty(s), 1);
+    }
+    mbar_init(done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, G::tmem_cols);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  uint32_t tmem;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem) : "r"(tmem_slot));
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      for (long long kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(empty(s), ph ^ 1);
+        mbar_arrive_expect_tx(full(s), G::stage_bytes);
+        const uint32_t st = sbase + s * G::stage_bytes;
+        const int row = (int)(kb * 64);
+        if (JOB == 0) {
+          for (int b = 0; b < 4; ++b) {
+            const int c[2] = {b * 64, row};
+            tma_load(st + b * WG_BOX, &mA0, full(s), 2, c);
+            tma_load(st + (4 + b) * WG_BOX, &mB0, full(s), 2, c);
+          }
+        } else {
+          for (int b = 0; b < 4; ++b) {
+            const int c[2] = {b * 64, row};
+            tma_load(st + b * WG_BOX, &mA0, full(s), 2, c);
+            tma_load(st + (5 + b) * WG_BOX, &mA1, full(s), 2, c);
+          }
+          const int c0[2] = {0, row};
+          tma_load(st + 4 * WG_BOX, &mB0, full(s), 2, c0);
+          tma_load(st + 9 * WG_BOX, &mB1, full(s), 2, c0);
+        }
+        if (++s == G::stages) { s = 0; ph ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // both operands MN-major: 64-feature groups one box (8192 B) apart, 8-k-row groups 1024 B apart, a k-step of 16
+      // rows advances the start address by 2048 B
+      const uint64_t dMN = umma_desc(0, WG_BOX, 1024, UMMA_LAYOUT_SW128);
+      constexpr uint32_t IA = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(128 >> 4) << 24);
+      constexpr uint32_t I256 = IA | ((uint32_t)(256 >> 3) << 17), I64 = IA | ((uint32_t)(64 >> 3) << 17);
+      int s = 0;
+      uint32_t ph = 0;
+      for (long long kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(full(s), ph);
+        tc_fence_after_sync();
+        const uint32_t st = sbase + s * G::stage_bytes;
+        const uint32_t acc0 = kb > kb0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint32_t acc = acc0 | (k > 0);
+          if (JOB == 0) {
+            const uint64_t b = dMN + ((st + 4 * WG_BOX + 2048u * k) >> 4);
+            umma_bf16_ss(tmem, dMN + ((st + 2048u * k) >> 4), b, I256, acc);                       // output features 0..127
+            umma_bf16_ss(tmem + 256, dMN + ((st + 2 * WG_BOX + 2048u * k) >> 4), b, I256, acc);    // 128..255
+          } else {
+            const uint64_t b0 = dMN + ((st + 4 * WG_BOX + 2048u * k) >> 4), b1 = dMN + ((st + 9 * WG_BOX + 2048u * k) >> 4);
+            umma_bf16_ss(tmem, dMN + ((st + 2048u * k) >> 4), b0, I64, acc);
+            umma_bf16_ss(tmem + 64, dMN + ((st + 2 * WG_BOX + 2048u * k) >> 4), b0, I64, acc);
+            umma_bf16_ss(tmem + 128, dMN + ((st + 5 * WG_BOX + 2048u * k) >> 4), b1, I64, acc);
+            umma_bf16_ss(tmem + 192, dMN + ((st + 7 * WG_BOX + 2048u * k) >> 4), b1, I64, acc);
+          }
+        }
+        umma_commit(empty(s));
+        if (++s == G::stages) { s = 0; ph ^= 1; }
+      }
+      umma_commit(done);
+    }
+  } else if (kb1 > kb0) {
+    // TMEM lane quadrant = warp % 4: warps 2..5 cover quadrants 2, 3, 0, 1.  Lane = feature m within the 128-row block.
+    const int quad = warp & 3;
+    const uint32_t tlane = tmem + ((uint32_t)(quad * 32) << 16);
+    const int m = quad * 32 + lane;
+    mbar_wait(done, 0);
+    tc_fence_after_sync();
+    constexpr int NCH = G::tmem_cols / 32;
+#pragma unroll 1
+    for (int ch = 0; ch < NCH; ++ch) {
+      uint32_t r[32];
+      tmem_ld32(tlane + 32 * ch, r);
+      tmem_ld_wait();
+      float* dst;
+      int stride = 1;
+      if (JOB == 0) {
+        // columns [0,256): dW2[m][n]; [256,512): dW2[128 + m][n]
+        const int blk = ch >> 3, n0 = (ch & 7) * 32;
+        dst = P.dw2 + (size_t)(blk * 128 + m) * H + n0;
+      } else if (ch < 4) {
+        // [0,64): dW1[m][i]; [64,128): dW1[128 + m][i]
+        const int blk = ch >> 1, n0 = (ch & 1) * 32;
+        dst = P.dw1 + (size_t)(blk * 128 + m) * C + n0;
+      } else {
+        // [128,192): dW3^T[m][o]; [192,256): dW3^T[128 + m][o]  ->  dW3[o][blk * 128 + m]
+        const int blk = (ch - 4) >> 1, n0 = ((ch - 4) & 1) * 32;
+        dst = P.dw3 + (size_t)n0 * H + blk * 128 + m;
+        stride = H;
+      }
+#pragma unroll
+      for (int k = 0; k < 32; ++k) atomicAdd(dst + (size_t)k * stride, __uint_as_float(r[k]));
+    }
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after_sync();
+    tmem_dealloc(tmem, G::tmem_cols);
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess) p = nullptr;
+    return (EncodeTiledFn)p;
+  }();
+  return fn;
+}
+// [T][cols] BF16 row-major, boxes of 64 rows x 64 columns, 128B swizzle, rows beyond T read as zero
+static bool bf16_map(CUtensorMap* m, const void* base, long long T, int cols) {
+  EncodeTiledFn enc = encode_fn();
+  if (!enc) return false;
+  const cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)T};
+  const cuuint64_t gstr[1] = {(cuuint64_t)cols * 2};
+  const cuuint32_t box[2] = {64, 64}, estr[2] = {1, 1};
+  return enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <typename K>
+static cudaError_t set_smem(K kernel, int bytes) {
+  // per-device attribute: set on every call (cheap) so that a process driving several GPUs configures each of them
+  return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+}
+
+}  // namespace ff
+}  // namespace rpde
+
+using namespace rpde;
+using namespace rpde::ff;
+
+static inline size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
+static int sm_count() {
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  return sms;
+}
+#define FF_CUDA(expr)                                                                  \
+  do {                                                                                 \
+    cudaError_t _e = (expr);                                                           \
+    if (_e != cudaSuccess) return rpde_internal_fail(RPDE_E_CUDA, cudaGetErrorString(_e)); \
+  } while (0)
+
+extern "C" {
+
+size_t rpde_ff3_weight_image_bytes(void) { return WBLOB; }
+
+int rpde_ff3_supported(int c, int hidden) { return c == C && hidden == H; }
+
+int rpde_ff3_pack_weights(const float* w1, const float* w2, const float* w3, void* image, rpde_stream_t stream) {
+  if (!w1 || !w2 || !w3 || !image || (reinterpret_cast<uintptr_t>(image) & 15))
+    return rpde_internal_fail(RPDE_E_INVALID, "rpde_ff3_pack_weights: bad arguments");
+  ff_pack_weights_kernel<<<(WBLOB / 16 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(w1, w2, w3, (uint8_t*)image);
+  rpde_internal_count_launch(0);
+  FF_CUDA(cudaGetLastError());
+  return RPDE_OK;
+}
+
+int rpde_ff3_fwd(const float* x, const float* res, const void* image, const float* b1, const float* b2, const float* b3,
+                 const float* gamma, const float* beta, float* y, long long T, float eps, rpde_stream_t stream) {
+  auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  if (!x || !image || !b1 || !b2 || !b3 || !y || T <= 0 || (gamma && !beta) || !al(x) || !al(res) || !al(image) || !al(b1) || !al(b2) ||
+      !al(b3) || !al(gamma) || !al(beta) || !al(y))
+    return rpde_internal_fail(RPDE_E_INVALID, "rpde_ff3_fwd: bad arguments (NULL or not 16-byte aligned)");
+  Params P{};
+  P.x = x; P.res = res; P.blob = (const uint8_t*)image; P.b1 = b1; P.b2 = b2; P.b3 = b3; P.gamma = gamma; P.beta = beta;
+  P.y = y; P.T = T; P.eps = eps;
+  FF_CUDA(set_smem(ff3_kernel<false>, SMEM_BYTES));
+  const long long tiles = (T + TM - 1) / TM;
+  const int sms = sm_count();
+  const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
+  ff3_kernel<false><<<grid, kThreads, SMEM_BYTES, (cudaStream_t)stream>>>(P);
+  rpde_internal_count_launch(1);
+  FF_CUDA(cudaGetLastError());
+  return RPDE_OK;
+}
+
+size_t rpde_ff3_bwd_workspace_bytes(long long T) {
+  const size_t t = (size_t)T;
+  return up256(t * C * 2) * 2 + up256(t * H * 2) * 4 + up256((size_t)256 * 2 * TM * 512);
+}
+
+int rpde_ff3_bwd(const float* x, const float* dy, const void* image, const float* b1, const float* b2, const float* b3,
+                 const float* gamma, float* ds, float* dw1, float* db1, float* dw2, float* db2, float* dw3, float* db3,
+                 float* dgamma, float* dbeta, long long T, float eps, void* ws, size_t ws_bytes, rpde_stream_t stream) {
+  auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  if (!x || !dy || !image || !b1 || !b2 || !b3 || !ds || !dw1 || !db1 || !dw2 || !db2 || !dw3 || !db3 || T <= 0 || T > 0x7fffffffLL ||
+      (gamma && (!dgamma || !dbeta)) || !al(x) || !al(dy) || !al(image) || !al(b1) || !al(b2) || !al(b3) || !al(gamma) || !al(ds) || !al(ws))
+    return rpde_internal_fail(RPDE_E_INVALID, "rpde_ff3_bwd: bad arguments (NULL or not 16-byte aligned)");
+  if (!ws || ws_bytes < rpde_ff3_bwd_workspace_bytes(T)) return rpde_internal_fail(RPDE_E_WORKSPACE, "rpde_ff3_bwd: workspace too small");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int sms = sm_count();
+  if (sms > 256) return rpde_internal_fail(RPDE_E_INVALID, "rpde_ff3_bwd: more than 256 SMs");
+  const size_t t = (size_t)T;
+  uint8_t* w = (uint8_t*)ws;
+  Params P{};
+  P.x = x; P.dy = dy; P.blob = (const uint8_t*)image; P.b1 = b1; P.b2 = b2; P.b3 = b3; P.gamma = gamma; P.ds = ds; P.T = T; P.eps = eps;
+  P.xb = (uint16_t*)w;   w += up256(t * C * 2);
+  P.dz3s = (uint16_t*)w; w += up256(t * C * 2);
+  P.h1s = (uint16_t*)w;  w += up256(t * H * 2);
+  P.h2s = (uint16_t*)w;  w += up256(t * H * 2);
+  P.dz1s = (uint16_t*)w; w += up256(t * H * 2);
+  P.dz2s = (uint16_t*)w; w += up256(t * H * 2);
+  P.gscratch = w;
+  P.db1 = db1; P.db2 = db2; P.db3 = db3; P.dgamma = dgamma; P.dbeta = dbeta;
+  FF_CUDA(cudaMemsetAsync(db1, 0, H * sizeof(float), s));
+  FF_CUDA(cudaMemsetAsync(db2, 0, H * sizeof(float), s));
+  FF_CUDA(cudaMemsetAsync(db3, 0, C * sizeof(float), s));
+  if (gamma) {
+    FF_CUDA(cudaMemsetAsync(dgamma, 0, C * sizeof(float), s));
+    FF_CUDA(cudaMemsetAsync(dbeta, 0, C * sizeof(float), s));
+  }
+  FF_CUDA(cudaMemsetAsync(dw1, 0, (size_t)H * C * sizeof(float), s));
+  FF_CUDA(cudaMemsetAsync(dw2, 0, (size_t)H * H * sizeof(float), s));
+  FF_CUDA(cudaMemsetAsync(dw3, 0, (size_t)C * H * sizeof(float), s));
+  FF_CUDA(set_smem(ff3_kernel<true>, SMEM_BYTES));
+  const long long tiles = (T + TM - 1) / TM;
+  const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
+  ff3_kernel<true><<<grid, kThreads, SMEM_BYTES, s>>>(P);
+  rpde_internal_count_launch(1);
+  FF_CUDA(cudaGetLastError());
+  // weight gradients from the BF16 copies
+  CUtensorMap mdz2, mh1, mdz1, mxb, mh2, mdz3;
+  if (!bf16_map(&mdz2, P.dz2s, T, H) || !bf16_map(&mh1, P.h1s, T, H) || !bf16_map(&mdz1, P.dz1s, T, H) || !bf16_map(&mxb, P.xb, T, C) ||
+      !bf16_map(&mh2, P.h2s, T, H) || !bf16_map(&mdz3, P.dz3s, T, C))
+    return rpde_internal_fail(RPDE_E_CUDA, "rpde_ff3_bwd: cuTensorMapEncodeTiled failed");
+  WgParams W{T, dw1, dw2, dw3};
+  const long long kblocks = (T + 63) / 64;
+  const unsigned wgrid = (unsigned)(kblocks < sms ? kblocks : sms);
+  FF_CUDA(set_smem(ff_wgrad_kernel<0>, WgCfg<0>::smem_bytes));
+  ff_wgrad_kernel<0><<<wgrid, WG_THREADS, WgCfg<0>::smem_bytes, s>>>(W, mdz2, mh1, mdz2, mh1);
+  rpde_internal_count_launch(1);
+  FF_CUDA(cudaGetLastError());
+  FF_CUDA(set_smem(ff_wgrad_kernel<1>, WgCfg<1>::smem_bytes));
+  ff_wgrad_kernel<1><<<wgrid, WG_THREADS, WgCfg<1>::smem_bytes, s>>>(W, mdz1, mxb, mh2, mdz3);
+  rpde_internal_count_launch(1);
+  FF_CUDA(cudaGetLastError());
+  return RPDE_OK;
+}
+
+}  // extern "C"

@@ -19,7 +19,7 @@ from . import _lib
 ACT_NONE, ACT_GELU, ACT_RELU = 0, 1, 2
 ACT_SAVE_GRAD, DACT_SAVED = 0x100, 3   # forward stores act'(z); backward multiplies by the stored factor
 MIX_FULL, MIX_LOWPASS = 0, 1
-PREC = {"fp32": 0, "3xtf32": 1, "tf32": 2}
+PREC = {"fp32": 0, "3xtf32": 1, "tf32": 2, "bf16": 3}
 _ACT_BY_NAME = {"identity": ACT_NONE, "none": ACT_NONE, "gelu": ACT_GELU, "relu": ACT_RELU}
 
 _state = threading.local()
@@ -35,7 +35,8 @@ _fno_fused_dx = os.environ.get("RPDE_FNO_FUSED_DX", "0") != "0"
 
 
 def set_precision(name: str) -> None:
-    """'fp32' (CUDA-core FMA, default), '3xtf32' (tcgen05, fp32-accurate) or 'tf32' (tcgen05, ~5e-4)."""
+    """'fp32' (CUDA-core FMA, default), '3xtf32' (tcgen05, fp32-accurate), 'tf32' (tcgen05, ~5e-4) or 'bf16' (fused BF16
+    FeedForward kernels where the shape allows, the TF32 engine elsewhere; model-level tolerance 1e-2 / 4e-2)."""
     global _default_precision
     _default_precision = PREC[name]
 
@@ -423,6 +424,79 @@ def linear(x, w, b=None, channels_first_out: Optional[Tuple[int, ...]] = None):
     return _LinearFn.apply(x, w, b, channels_first_out)
 
 
+_ff3_images = {}
+
+
+def _ff3_image(c, Ws, cache: bool) -> torch.Tensor:
+    """BF16 shared-memory image of the three FeedForward weights (rpde_ff3_pack_weights).  Under no_grad (constant
+    weights: rollouts, evaluation) the image is cached on the parameters' storage and version counters."""
+    key = tuple((w.data_ptr(), w._version) for w in Ws) if cache else None
+    if key is not None:
+        hit = _ff3_images.get(key[0][0])
+        if hit is not None and hit[0] == key:
+            return hit[1]
+    img = torch.empty(int(c.lib.rpde_ff3_weight_image_bytes()), dtype=torch.uint8, device=Ws[0].device)
+    _lib.check(c.lib.rpde_ff3_pack_weights(_p(Ws[0]), _p(Ws[1]), _p(Ws[2]), _p(img), c.stream), "rpde_ff3_pack_weights")
+    if key is not None:
+        _ff3_images[key[0][0]] = (key, img)
+    return img
+
+
+class _FusedFF3Fn(torch.autograd.Function):
+    """y = residual + LayerNorm(FeedForward_3(x)) in one BF16 tcgen05 kernel (rpde_ff3_fwd); the backward pass recomputes
+    the hidden activations on chip from x (rpde_ff3_bwd) - nothing but x is kept between the two."""
+
+    @staticmethod
+    def forward(ctx, x, residual, use_ln, eps, grad_on, w1, b1, w2, b2, w3, b3, gamma, beta):
+        _need_cuda(x, residual, w1, b1, w2, b2, w3, b3, gamma, beta)
+        x = x.contiguous()
+        T = x.numel() // x.shape[-1]
+        res = residual.contiguous() if residual is not None else None
+        Ws = [w1.contiguous(), w2.contiguous(), w3.contiguous()]
+        bs = [b1.contiguous(), b2.contiguous(), b3.contiguous()]
+        g = gamma.contiguous() if use_ln else None
+        bt = beta.contiguous() if use_ln else None
+        y = torch.empty_like(x)
+        need_grad = grad_on and any(ctx.needs_input_grad)
+        with _Ctx(x) as c:
+            img = _ff3_image(c, Ws, cache=not need_grad)
+            _lib.check(c.lib.rpde_ff3_fwd(_p(x), _p(res), _p(img), _p(bs[0]), _p(bs[1]), _p(bs[2]), _p(g), _p(bt), _p(y), T,
+                                          float(eps), c.stream), "rpde_ff3_fwd")
+        if need_grad:
+            ctx.save_for_backward(x, img, *bs, g)
+            ctx.cfg = (T, use_ln, float(eps), residual is not None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, img, b1, b2, b3, g = ctx.saved_tensors
+        T, use_ln, eps, has_res = ctx.cfg
+        dy = dy.contiguous()
+        dev = dy.device
+        f = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
+        ds = torch.empty_like(x)
+        dw1, dw2, dw3 = f(256, 64), f(256, 256), f(64, 256)
+        db1, db2, db3 = f(256), f(256), f(64)
+        dg, dbt = (f(64), f(64)) if use_ln else (None, None)
+        with _Ctx(dy) as c:
+            nb = int(c.lib.rpde_ff3_bwd_workspace_bytes(T))
+            ws = _ws(nb, dev)
+            _lib.check(c.lib.rpde_ff3_bwd(_p(x), _p(dy), _p(img), _p(b1), _p(b2), _p(b3), _p(g), _p(ds), _p(dw1), _p(db1),
+                                          _p(dw2), _p(db2), _p(dw3), _p(db3), _p(dg), _p(dbt), T, eps, _p(ws), nb, c.stream),
+                       "rpde_ff3_bwd")
+        return (ds if ctx.needs_input_grad[0] else None, dy if has_res else None, None, None, None,
+                dw1, db1, dw2, db2, dw3, db3, dg, dbt)
+
+
+def _ff3_applies(x, weights, biases, final_act) -> bool:
+    if _default_precision != PREC["bf16"] or len(weights) != 3 or final_act != ACT_NONE or any(b is None for b in biases):
+        return False
+    c = x.shape[-1]
+    h = weights[0].shape[0]
+    return (tuple(weights[0].shape) == (h, c) and tuple(weights[1].shape) == (h, h) and tuple(weights[2].shape) == (c, h)
+            and bool(_lib.load().rpde_ff3_supported(c, h)))
+
+
 class _FeedForwardFn(torch.autograd.Function):
     """FeedForward (custom_layer.py:49-68, dropout 0) fused with what follows it in the F-FNO layer:
        u = L_n(gelu(... gelu(L_1(x))));  v = LayerNorm(u) if ln;  y = residual + act(v)."""
@@ -544,6 +618,9 @@ class _FeedForwardFn(torch.autograd.Function):
 
 def feed_forward(x, residual, weights, biases, ln_weight=None, ln_bias=None, final_act: int = ACT_NONE, eps: float = 1e-5):
     n = len(weights)
+    if _ff3_applies(x, weights, biases, final_act):
+        return _FusedFF3Fn.apply(x, residual, ln_weight is not None, eps, torch.is_grad_enabled(), weights[0], biases[0],
+                                 weights[1], biases[1], weights[2], biases[2], ln_weight, ln_bias)
     params = []
     for w, b in zip(weights, biases):
         params += [w, b]
