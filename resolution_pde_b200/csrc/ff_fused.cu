@@ -34,6 +34,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
 
 #include "../../include/rpde_b200.h"
 #include "internal.h"
@@ -50,13 +51,17 @@ constexpr uint32_t W2_OFF = W1_OFF + W1_BYTES, W2_PLANE = H * 128, W2_BYTES = 4 
 constexpr uint32_t W3_OFF = W2_OFF + W2_BYTES, W3_PLANE = C * 128, W3_BYTES = 4 * W3_PLANE;  // 4 k-planes of [64 rows][64 bf16]
 constexpr uint32_t WBLOB = W3_OFF + W3_BYTES;                                          // 196608
 constexpr uint32_t X_OFF = WBLOB, X_BYTES = TM * 128;                                  // A tile of layer 1: [128 rows][64 bf16]
-constexpr uint32_t STAT_OFF = X_OFF + X_BYTES;                                         // row statistics exchange: 3 x [2][128] float2
-constexpr uint32_t STAT_BYTES = 3 * 2 * TM * 8;
-constexpr uint32_t BAR_OFF = STAT_OFF + STAT_BYTES;
+constexpr uint32_t STG_OFF = X_OFF + X_BYTES;                                          // 8 epilogue warps x 2 KB staging box (TMA stores)
+constexpr uint32_t STG_BYTES = 8 * 2048;
+constexpr uint32_t PAR_OFF = STG_OFF + STG_BYTES;                                      // b1[256] b2[256] b3[64] gamma[64] beta[64]
+constexpr uint32_t PAR_BYTES = (2 * H + 3 * C) * 4;
+constexpr uint32_t BAR_OFF = PAR_OFF + PAR_BYTES;
 constexpr uint32_t SMEM_BYTES = BAR_OFF + 256;
+static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 constexpr int kThreads = 14 * 32;
 // TMEM columns
 constexpr uint32_t D1 = 0, H1 = 0, D3 = 128, DZ3 = 192, D2 = 256, H2 = 256, D4 = 256, DZ2 = 256, D5 = 0, DZ1 = 0, D6 = 256;
+constexpr uint32_t ST_A = 224, ST_B = 226, ST_C = 228;   // row-statistic exchange between the two warps of a quadrant
 // barriers
 enum { B_WFULL = 0, B_XFULL, B_XEMPTY, B_D1, B_D2, B_D3, B_TILE, B_H1, B_H2 = B_H1 + 4, B_DZ3 = B_H2 + 4, B_D4, B_DZ2,
        B_D5 = B_DZ2 + 4, B_DZ1, B_D6 = B_DZ1 + 4, B_COUNT };
@@ -67,15 +72,17 @@ struct Params {
   const float* res;     // [T][64] residual or NULL (forward)
   const uint8_t* blob;  // packed BF16 weight image (WBLOB bytes)
   const float *b1, *b2, *b3, *gamma, *beta;  // gamma == NULL: no LayerNorm
-  float* y;             // forward output
   long long T;
   float eps;
-  // backward
-  const float* dy;      // [T][64]
-  float* ds;            // [T][64] gradient w.r.t. x
-  uint16_t *xb, *h1s, *h2s, *dz1s, *dz2s, *dz3s;  // BF16 copies for the weight-gradient kernel
-  uint8_t* gscratch;    // gridDim.x * 2 * 128 * 512 bytes
+  const float* dy;      // backward: [T][64]
+  uint16_t* xb;         // backward: BF16 copy of x for the weight-gradient kernel
+  uint8_t* gscratch;    // backward: gridDim.x * 128 KB
   float *db1, *db2, *db3, *dgamma, *dbeta;        // zero-initialised by the caller, accumulated atomically
+};
+// TMA maps of everything the epilogue warps store: boxes of 32 rows x 64 bytes, SWIZZLE_64B
+struct Maps {
+  CUtensorMap out;                     // forward: y; backward: ds   ([T][64] fp32, box 16 x 32)
+  CUtensorMap h1, h2, dz1, dz2, dz3;   // backward: BF16 copies ([T][256] / [T][64], box 32 x 32)
 };
 
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
@@ -108,6 +115,12 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* v) {
       "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
       : "memory");
 }
+__device__ __forceinline__ void tmem_st2(uint32_t taddr, float a, float b) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};" ::"r"(taddr), "f"(a), "f"(b) : "memory");
+}
+__device__ __forceinline__ void tmem_ld2(uint32_t taddr, float& a, float& b) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=f"(a), "=f"(b) : "r"(taddr) : "memory");
+}
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
                "r"(bytes), "r"(bar)
@@ -122,6 +135,51 @@ __device__ __forceinline__ uint4 ldg128(const void* p) {
   asm volatile("ld.global.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ float4 lds_f4(uint32_t a) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+  return v;
+}
+
+// The two warps of a quadrant exchange one pair of per-row values through two spare TMEM columns each (both warps may
+// access the quadrant's lanes): write mine, barrier, read the other's.
+__device__ __forceinline__ void pair_exchange(uint32_t tlane, uint32_t col, int half, int quad, float a, float b, float& oa, float& ob) {
+  tmem_st2(tlane + col + 2 * half, a, b);
+  tmem_st_wait();
+  tc_fence_before_sync();
+  pair_sync(quad);
+  tc_fence_after_sync();
+  tmem_ld2(tlane + col + 2 * (half ^ 1), oa, ob);
+  tmem_ld_wait();
+}
+
+// per-warp staging box for bulk tensor stores: 32 rows (lanes) of 64 bytes, 16-byte chunk q of row r at q ^ ((r >> 1) & 3)
+// (SWIZZLE_64B: the warp's four 128-bit stores are bank-conflict free)
+struct Stage {
+  uint32_t base;
+  int lane;
+  __device__ __forceinline__ void wait_free() const {   // the previous bulk store has finished reading the box
+    if (lane == 0) bulk_wait_read0();
+    __syncwarp();
+  }
+  __device__ __forceinline__ void write(const uint32_t* p) const {
+    const uint32_t row = base + (uint32_t)lane * 64u, sw = ((uint32_t)lane >> 1) & 3u;
+#pragma unroll
+    for (uint32_t q = 0; q < 4; ++q)
+      asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(row + ((q ^ sw) << 4)), "r"(p[4 * q]), "r"(p[4 * q + 1]),
+                   "r"(p[4 * q + 2]), "r"(p[4 * q + 3])
+                   : "memory");
+  }
+  __device__ __forceinline__ void store(const CUtensorMap* m, int col, int row) const {
+    fence_proxy_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+      const int c[2] = {col, row};
+      tma_store(base, m, 2, c, false);
+      bulk_commit();
+    }
+  }
+};
 
 // lane j receives the sum over the warp's 32 lanes of v[j] (31 shuffles): the column sums of a 32 x 32 block whose rows
 // are the lanes.  v is destroyed.
@@ -143,19 +201,33 @@ __device__ __forceinline__ float colsum32(float (&v)[32], int lane) {
 //   MODE 0: h = gelu(acc + bias)                                         -> BF16 A operand                    (inference / forward)
 //   MODE 1: the same, plus gelu'(acc + bias) -> scratch and h -> spill                                        (backward: recompute)
 //   MODE 2: dz = acc * gelu' (from scratch) -> BF16 A operand, dz -> spill, column sums of dz (bias gradient)  (backward)
+// scratch: this warp's private 8 KB for the layer, laid out [j][q][lane] in 16-byte units (coalesced, same thread reads back)
 template <int MODE>
 __device__ __forceinline__ void hidden_epi(uint32_t tlane, uint32_t src_col, uint32_t dst_col, int half, int quad, int lane,
-                                           uint32_t ready_bar0, const float* __restrict__ bias, bool valid,
-                                           uint16_t* spill_row, uint8_t* scratch_row, float (&cs)[4]) {
+                                           uint32_t ready_bar0, uint32_t bias_smem, const Stage& stg, const CUtensorMap* spill_map,
+                                           int row0, uint8_t* scratch, float (&cs)[4]) {
+  uint4 g4[4];
+  if (MODE == 2) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) g4[q] = ldg128(scratch + ((0 * 4 + q) * 32 + lane) * 16);
+  }
 #pragma unroll 1
   for (int j = 0; j < 4; ++j) {
     const int c = 2 * j + half;
     uint32_t r[32];
     tmem_ld32(tlane + src_col + 32 * c, r);
-    uint4 g4[4];
-    if (MODE == 2) {
+    uint4 gn[4];
+    if (MODE == 2 && j < 3) {   // the next chunk's gelu' is in flight while this one is processed
 #pragma unroll
-      for (int q = 0; q < 4; ++q) g4[q] = ldg128(scratch_row + c * 64 + q * 16);
+      for (int q = 0; q < 4; ++q) gn[q] = ldg128(scratch + (((j + 1) * 4 + q) * 32 + lane) * 16);
+    }
+    float v[32];
+    if (MODE != 2) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const float4 b4 = lds_f4(bias_smem + (32 * c + 4 * q) * 4);
+        v[4 * q] = b4.x; v[4 * q + 1] = b4.y; v[4 * q + 2] = b4.z; v[4 * q + 3] = b4.w;
+      }
     }
     tmem_ld_wait();
     tc_fence_before_sync();
@@ -163,34 +235,20 @@ __device__ __forceinline__ void hidden_epi(uint32_t tlane, uint32_t src_col, uin
     tc_fence_after_sync();
     uint32_t p[16];
     if (MODE != 2) {
-      float v[32];
-#pragma unroll
-      for (int q = 0; q < 8; ++q) {
-        const float4 b4 = __ldg(reinterpret_cast<const float4*>(bias + 32 * c) + q);
-        v[4 * q] = __uint_as_float(r[4 * q]) + b4.x;
-        v[4 * q + 1] = __uint_as_float(r[4 * q + 1]) + b4.y;
-        v[4 * q + 2] = __uint_as_float(r[4 * q + 2]) + b4.z;
-        v[4 * q + 3] = __uint_as_float(r[4 * q + 3]) + b4.w;
-      }
       uint32_t gp[16];
 #pragma unroll
       for (int k = 0; k < 32; k += 2) {
         float h0, h1, g0, g1;
-        gelu_both2(v[k], v[k + 1], h0, h1, g0, g1);
+        gelu_both2(__uint_as_float(r[k]) + v[k], __uint_as_float(r[k + 1]) + v[k + 1], h0, h1, g0, g1);
         p[k >> 1] = pack_bf16(h0, h1);
         if (MODE == 1) gp[k >> 1] = pack_bf16(g0, g1);
       }
       tmem_st16(tlane + dst_col + 16 * c, p);
       if (MODE == 1) {
 #pragma unroll
-        for (int q = 0; q < 4; ++q) stg128(scratch_row + c * 64 + q * 16, gp[4 * q], gp[4 * q + 1], gp[4 * q + 2], gp[4 * q + 3]);
-        if (valid) {
-#pragma unroll
-          for (int q = 0; q < 4; ++q) stg128(spill_row + c * 32 + q * 8, p[4 * q], p[4 * q + 1], p[4 * q + 2], p[4 * q + 3]);
-        }
+        for (int q = 0; q < 4; ++q) stg128(scratch + ((j * 4 + q) * 32 + lane) * 16, gp[4 * q], gp[4 * q + 1], gp[4 * q + 2], gp[4 * q + 3]);
       }
     } else {
-      float v[32];
       const uint32_t* gw = reinterpret_cast<const uint32_t*>(g4);
 #pragma unroll
       for (int k = 0; k < 16; ++k) {
@@ -199,11 +257,18 @@ __device__ __forceinline__ void hidden_epi(uint32_t tlane, uint32_t src_col, uin
         p[k] = pack_bf16(v[2 * k], v[2 * k + 1]);
       }
       tmem_st16(tlane + dst_col + 16 * c, p);
-      if (valid) {
-#pragma unroll
-        for (int q = 0; q < 4; ++q) stg128(spill_row + c * 32 + q * 8, p[4 * q], p[4 * q + 1], p[4 * q + 2], p[4 * q + 3]);
-      }
+    }
+    if (MODE != 0) {   // BF16 copy for the weight-gradient kernel: staged, then one bulk tensor store per chunk
+      stg.wait_free();
+      stg.write(p);
+      stg.store(spill_map, 32 * c, row0);
+    }
+    if (MODE == 2) {
       cs[j] += colsum32(v, lane);
+      if (j < 3) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) g4[q] = gn[q];
+      }
     }
     tmem_st_wait();
     tc_fence_before_sync();
@@ -213,18 +278,33 @@ __device__ __forceinline__ void hidden_epi(uint32_t tlane, uint32_t src_col, uin
 }
 
 template <bool BWD>
-__global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant__ Params P) {
+__global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant__ Params P, const __grid_constant__ Maps M) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t sbase = smem_u32(smem_raw);
   const uint32_t w1s = sbase + W1_OFF, w2s = sbase + W2_OFF, w3s = sbase + W3_OFF, xs = sbase + X_OFF;
+  const uint32_t par = sbase + PAR_OFF;
+  const uint32_t pb1 = par, pb2 = par + H * 4, pb3 = par + 2 * H * 4, pgam = pb3 + C * 4, pbet = pgam + C * 4;
   const uint32_t bars = sbase + BAR_OFF;
   auto bar = [&](int i) { return bars + 8u * (uint32_t)i; };
   const uint32_t tmem_slot = bars + 8u * B_COUNT;
-  float2* stat = reinterpret_cast<float2*>(smem_raw + STAT_OFF);   // [3][2][128]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long ntiles = (P.T + TM - 1) / TM;
+  const bool ln = P.gamma != nullptr;
 
+  {   // biases / LayerNorm parameters -> shared memory
+    float* pf = reinterpret_cast<float*>(smem_raw + PAR_OFF);
+    for (int i = threadIdx.x; i < 2 * H + 3 * C; i += kThreads) {
+      float v;
+      if (i < H) v = P.b1[i];
+      else if (i < 2 * H) v = P.b2[i - H];
+      else if (i < 2 * H + C) v = P.b3[i - 2 * H];
+      else if (i < 2 * H + 2 * C) v = ln ? P.gamma[i - 2 * H - C] : 1.f;
+      else v = (ln && P.beta) ? P.beta[i - 2 * H - 2 * C] : 0.f;
+      pf[i] = v;
+    }
+  }
   if (threadIdx.x == 0) {
+    tma_prefetch_desc(&M.out);
     mbar_init(bar(B_WFULL), 1);
     mbar_init(bar(B_XFULL), 4);
     mbar_init(bar(B_XEMPTY), 1);
@@ -352,30 +432,32 @@ __global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant_
     const int ew = warp - 6, quad = warp & 3, half = ew >> 2;
     const uint32_t tlane = tmem + ((uint32_t)(quad * 32) << 16);
     const int rl = quad * 32 + lane;                       // row of the tile = TMEM lane
-    const bool ln = P.gamma != nullptr;
+    const Stage stg{sbase + STG_OFF + (uint32_t)ew * 2048u, lane};
     float cs1[4] = {0.f, 0.f, 0.f, 0.f}, cs2[4] = {0.f, 0.f, 0.f, 0.f}, cs3 = 0.f, csg = 0.f, csb = 0.f;
-    uint8_t* scr = BWD ? P.gscratch + (size_t)blockIdx.x * (2 * TM * 512) + (size_t)rl * 512 : nullptr;
+    uint8_t* scr = BWD ? P.gscratch + ((size_t)blockIdx.x * 8 + ew) * 16384 : nullptr;   // [layer][8 KB] per warp
     float dummy[4];
     uint32_t it = 0;
     for (long long t = blockIdx.x; t < ntiles; t += gridDim.x, ++it) {
       const uint32_t ph = it & 1;
       const long long row = t * TM + rl;
+      const int row0 = (int)(t * TM) + quad * 32;
       const bool valid = row < P.T;
       // ---- layer 1 and 2: bias + GELU, converted in place into the next layer's A operand
       mbar_wait(bar(B_D1), ph);
       tc_fence_after_sync();
-      hidden_epi<BWD ? 1 : 0>(tlane, D1, H1, half, quad, lane, bar(B_H1), P.b1, valid, BWD ? P.h1s + row * H : nullptr, scr, dummy);
+      hidden_epi<BWD ? 1 : 0>(tlane, D1, H1, half, quad, lane, bar(B_H1), pb1, stg, &M.h1, row0, scr, dummy);
       mbar_wait(bar(B_D2), ph);
       tc_fence_after_sync();
-      hidden_epi<BWD ? 1 : 0>(tlane, D2, H2, half, quad, lane, bar(B_H2), P.b2, valid, BWD ? P.h2s + row * H : nullptr,
-                              BWD ? scr + TM * 512 : nullptr, dummy);
-      // ---- layer 3: bias, LayerNorm (row statistics shared by the two warps of the quadrant through shared memory)
-      float4 in4[8];   // forward: residual; backward: dy
+      hidden_epi<BWD ? 1 : 0>(tlane, D2, H2, half, quad, lane, bar(B_H2), pb2, stg, &M.h2, row0, BWD ? scr + 8192 : nullptr, dummy);
+      // ---- layer 3: bias, LayerNorm (row statistics shared by the two warps of the quadrant)
+      float in[32];   // forward: residual; backward: dy
       {
         const float* src = BWD ? P.dy : P.res;
 #pragma unroll
-        for (int q = 0; q < 8; ++q)
-          in4[q] = (src && valid) ? __ldg(reinterpret_cast<const float4*>(src + row * C + 32 * half) + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int q = 0; q < 8; ++q) {
+          const float4 a = (src && valid) ? __ldg(reinterpret_cast<const float4*>(src + row * C + 32 * half) + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+          in[4 * q] = a.x; in[4 * q + 1] = a.y; in[4 * q + 2] = a.z; in[4 * q + 3] = a.w;
+        }
       }
       mbar_wait(bar(B_D3), ph);
       tc_fence_after_sync();
@@ -386,100 +468,92 @@ __global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant_
         tmem_ld_wait();
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
-          const float4 b4 = __ldg(reinterpret_cast<const float4*>(P.b3 + 32 * half) + q);
+          const float4 b4 = lds_f4(pb3 + (32 * half + 4 * q) * 4);
           v[4 * q] = __uint_as_float(r[4 * q]) + b4.x;
           v[4 * q + 1] = __uint_as_float(r[4 * q + 1]) + b4.y;
           v[4 * q + 2] = __uint_as_float(r[4 * q + 2]) + b4.z;
           v[4 * q + 3] = __uint_as_float(r[4 * q + 3]) + b4.w;
         }
       }
-      if (!BWD) {   // the accumulator has been read: the next tile may start
-        tc_fence_before_sync();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bar(B_TILE));
-      }
       float mean = 0.f, rstd = 1.f;
       if (ln) {
-        float s = 0.f;
+        float s = 0.f, o, o2;
 #pragma unroll
         for (int k = 0; k < 32; ++k) s += v[k];
-        stat[(0 * 2 + half) * TM + rl].x = s;
-        pair_sync(quad);
-        mean = (s + stat[(0 * 2 + (half ^ 1)) * TM + rl].x) * (1.0f / C);
+        pair_exchange(tlane, ST_A, half, quad, s, 0.f, o, o2);
+        mean = (s + o) * (1.0f / C);
         float qv = 0.f;
 #pragma unroll
         for (int k = 0; k < 32; ++k) {
           const float d = v[k] - mean;
           qv = fmaf(d, d, qv);
         }
-        stat[(1 * 2 + half) * TM + rl].x = qv;
-        pair_sync(quad);
-        const float var = (qv + stat[(1 * 2 + (half ^ 1)) * TM + rl].x) * (1.0f / C);
-        rstd = 1.0f / sqrtf(var + P.eps);
+        pair_exchange(tlane, ST_B, half, quad, qv, 0.f, o, o2);
+        rstd = 1.0f / sqrtf((qv + o) * (1.0f / C) + P.eps);
       }
       if (!BWD) {
-        float* yo = P.y + row * C + 32 * half;
+        // every TMEM access of this tile is done: the next tile may start
+        tc_fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(B_TILE));
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
-          float4 o = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+          const float4 g4 = lds_f4(pgam + (32 * half + 4 * q) * 4), b4 = lds_f4(pbet + (32 * half + 4 * q) * 4);
           if (ln) {
-            const float4 g4 = __ldg(reinterpret_cast<const float4*>(P.gamma + 32 * half) + q);
-            const float4 b4 = __ldg(reinterpret_cast<const float4*>(P.beta + 32 * half) + q);
-            o.x = (o.x - mean) * rstd * g4.x + b4.x;
-            o.y = (o.y - mean) * rstd * g4.y + b4.y;
-            o.z = (o.z - mean) * rstd * g4.z + b4.z;
-            o.w = (o.w - mean) * rstd * g4.w + b4.w;
+            v[4 * q] = (v[4 * q] - mean) * rstd * g4.x + b4.x;
+            v[4 * q + 1] = (v[4 * q + 1] - mean) * rstd * g4.y + b4.y;
+            v[4 * q + 2] = (v[4 * q + 2] - mean) * rstd * g4.z + b4.z;
+            v[4 * q + 3] = (v[4 * q + 3] - mean) * rstd * g4.w + b4.w;
           }
-          o.x += in4[q].x; o.y += in4[q].y; o.z += in4[q].z; o.w += in4[q].w;
-          if (valid) *reinterpret_cast<float4*>(yo + 4 * q) = o;
+          v[4 * q] += in[4 * q]; v[4 * q + 1] += in[4 * q + 1]; v[4 * q + 2] += in[4 * q + 2]; v[4 * q + 3] += in[4 * q + 3];
+        }
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {   // two boxes of 16 fp32 columns
+          stg.wait_free();
+          stg.write(reinterpret_cast<const uint32_t*>(v) + 16 * hh);
+          stg.store(&M.out, 32 * half + 16 * hh, row0);
         }
       } else {
         // ---- LayerNorm backward: dz3 = rstd (g - mean(g) - xhat mean(g xhat)), g = dy gamma
         float dz[32];
-        const float* dyv = reinterpret_cast<const float*>(in4);
         if (ln) {
-          float s1 = 0.f, s2 = 0.f;
-          float gx[32];
+          float s1 = 0.f, s2 = 0.f, o1, o2;
 #pragma unroll
           for (int q = 0; q < 8; ++q) {
-            const float4 g4 = __ldg(reinterpret_cast<const float4*>(P.gamma + 32 * half) + q);
+            const float4 g4 = lds_f4(pgam + (32 * half + 4 * q) * 4);
             const float gg[4] = {g4.x, g4.y, g4.z, g4.w};
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
               const int k = 4 * q + e;
               const float xh = (v[k] - mean) * rstd;
-              const float g = dyv[k] * gg[e];
+              const float g = in[k] * gg[e];
               s1 += g;
               s2 = fmaf(g, xh, s2);
               dz[k] = g;
               v[k] = xh;
-              gx[k] = dyv[k] * xh;
             }
           }
-          stat[(2 * 2 + half) * TM + rl] = make_float2(s1, s2);
-          pair_sync(quad);
-          const float2 o = stat[(2 * 2 + (half ^ 1)) * TM + rl];
-          s1 = (s1 + o.x) * (1.0f / C);
-          s2 = (s2 + o.y) * (1.0f / C);
+          pair_exchange(tlane, ST_C, half, quad, s1, s2, o1, o2);
+          s1 = (s1 + o1) * (1.0f / C);
+          s2 = (s2 + o2) * (1.0f / C);
 #pragma unroll
-          for (int k = 0; k < 32; ++k) dz[k] = rstd * (dz[k] - s1 - v[k] * s2);
-          csg += colsum32(gx, lane);
-          float dyc[32];
-#pragma unroll
-          for (int k = 0; k < 32; ++k) dyc[k] = dyv[k];
-          csb += colsum32(dyc, lane);
+          for (int k = 0; k < 32; ++k) {
+            dz[k] = rstd * (dz[k] - s1 - v[k] * s2);
+            v[k] *= in[k];           // dy * xhat: dgamma
+          }
+          csg += colsum32(v, lane);
         } else {
 #pragma unroll
-          for (int k = 0; k < 32; ++k) dz[k] = dyv[k];
+          for (int k = 0; k < 32; ++k) dz[k] = in[k];
         }
         uint32_t p[16];
 #pragma unroll
         for (int k = 0; k < 16; ++k) p[k] = pack_bf16(dz[2 * k], dz[2 * k + 1]);
         tmem_st16(tlane + DZ3 + 16 * half, p);
-        if (valid) {
-#pragma unroll
-          for (int q = 0; q < 4; ++q) stg128(P.dz3s + row * C + 32 * half + q * 8, p[4 * q], p[4 * q + 1], p[4 * q + 2], p[4 * q + 3]);
-        }
+        stg.wait_free();
+        stg.write(p);
+        stg.store(&M.dz3, 32 * half, row0);
+        if (ln) csb += colsum32(in, lane);
         cs3 += colsum32(dz, lane);
         tmem_st_wait();
         tc_fence_before_sync();
@@ -488,10 +562,10 @@ __global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant_
         // ---- dZ2 = dH2 * gelu'(Z2), dZ1 = dH1 * gelu'(Z1)
         mbar_wait(bar(B_D4), ph);
         tc_fence_after_sync();
-        hidden_epi<2>(tlane, D4, DZ2, half, quad, lane, bar(B_DZ2), nullptr, valid, P.dz2s + row * H, scr + TM * 512, cs2);
+        hidden_epi<2>(tlane, D4, DZ2, half, quad, lane, bar(B_DZ2), 0, stg, &M.dz2, row0, scr + 8192, cs2);
         mbar_wait(bar(B_D5), ph);
         tc_fence_after_sync();
-        hidden_epi<2>(tlane, D5, DZ1, half, quad, lane, bar(B_DZ1), nullptr, valid, P.dz1s + row * H, scr, cs1);
+        hidden_epi<2>(tlane, D5, DZ1, half, quad, lane, bar(B_DZ1), 0, stg, &M.dz1, row0, scr, cs1);
         // ---- dS
         mbar_wait(bar(B_D6), ph);
         tc_fence_after_sync();
@@ -501,10 +575,11 @@ __global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant_
         tc_fence_before_sync();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar(B_TILE));
-        if (valid) {
-          float* o = P.ds + row * C + 32 * half;
 #pragma unroll
-          for (int q = 0; q < 8; ++q) stg128(o + 4 * q, r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3]);
+        for (int hh = 0; hh < 2; ++hh) {
+          stg.wait_free();
+          stg.write(r + 16 * hh);
+          stg.store(&M.out, 32 * half + 16 * hh, row0);
         }
       }
     }
@@ -520,6 +595,8 @@ __global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant_
         atomicAdd(P.dbeta + 32 * half + lane, csb);
       }
     }
+    if (lane == 0) bulk_wait0();   // the staging box must outlive the bulk stores that read it
+    __syncwarp();
   }
   tc_fence_before_sync();
   __syncthreads();
@@ -738,6 +815,18 @@ static bool bf16_map(CUtensorMap* m, const void* base, long long T, int cols) {
              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// [T][cols] row-major (elem_bytes per element), boxes of 32 rows x 64 bytes, 64B swizzle: the epilogue warps' staging boxes
+static bool stage_map(CUtensorMap* m, const void* base, long long T, int cols, int elem_bytes) {
+  EncodeTiledFn enc = encode_fn();
+  if (!enc) return false;
+  const cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)T};
+  const cuuint64_t gstr[1] = {(cuuint64_t)cols * elem_bytes};
+  const cuuint32_t box[2] = {(cuuint32_t)(64 / elem_bytes), 32}, estr[2] = {1, 1};
+  return enc(m, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), gdim,
+             gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 template <typename K>
 static cudaError_t set_smem(K kernel, int bytes) {
   // per-device attribute: set on every call (cheap) so that a process driving several GPUs configures each of them
@@ -784,14 +873,18 @@ int rpde_ff3_fwd(const float* x, const float* res, const void* image, const floa
   if (!x || !image || !b1 || !b2 || !b3 || !y || T <= 0 || (gamma && !beta) || !al(x) || !al(res) || !al(image) || !al(b1) || !al(b2) ||
       !al(b3) || !al(gamma) || !al(beta) || !al(y))
     return rpde_internal_fail(RPDE_E_INVALID, "rpde_ff3_fwd: bad arguments (NULL or not 16-byte aligned)");
+  if (T > 0x7fffffffLL) return rpde_internal_fail(RPDE_E_INVALID, "rpde_ff3_fwd: T too large");
   Params P{};
   P.x = x; P.res = res; P.blob = (const uint8_t*)image; P.b1 = b1; P.b2 = b2; P.b3 = b3; P.gamma = gamma; P.beta = beta;
-  P.y = y; P.T = T; P.eps = eps;
+  P.T = T; P.eps = eps;
+  Maps M;
+  memset(&M, 0, sizeof(M));
+  if (!stage_map(&M.out, y, T, C, 4)) return rpde_internal_fail(RPDE_E_CUDA, "rpde_ff3_fwd: cuTensorMapEncodeTiled failed");
   FF_CUDA(set_smem(ff3_kernel<false>, SMEM_BYTES));
   const long long tiles = (T + TM - 1) / TM;
   const int sms = sm_count();
   const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
-  ff3_kernel<false><<<grid, kThreads, SMEM_BYTES, (cudaStream_t)stream>>>(P);
+  ff3_kernel<false><<<grid, kThreads, SMEM_BYTES, (cudaStream_t)stream>>>(P, M);
   rpde_internal_count_launch(1);
   FF_CUDA(cudaGetLastError());
   return RPDE_OK;
@@ -816,14 +909,20 @@ int rpde_ff3_bwd(const float* x, const float* dy, const void* image, const float
   const size_t t = (size_t)T;
   uint8_t* w = (uint8_t*)ws;
   Params P{};
-  P.x = x; P.dy = dy; P.blob = (const uint8_t*)image; P.b1 = b1; P.b2 = b2; P.b3 = b3; P.gamma = gamma; P.ds = ds; P.T = T; P.eps = eps;
-  P.xb = (uint16_t*)w;   w += up256(t * C * 2);
-  P.dz3s = (uint16_t*)w; w += up256(t * C * 2);
-  P.h1s = (uint16_t*)w;  w += up256(t * H * 2);
-  P.h2s = (uint16_t*)w;  w += up256(t * H * 2);
-  P.dz1s = (uint16_t*)w; w += up256(t * H * 2);
-  P.dz2s = (uint16_t*)w; w += up256(t * H * 2);
+  P.x = x; P.dy = dy; P.blob = (const uint8_t*)image; P.b1 = b1; P.b2 = b2; P.b3 = b3; P.gamma = gamma; P.T = T; P.eps = eps;
+  uint16_t *dz3s, *h1s, *h2s, *dz1s, *dz2s;
+  P.xb = (uint16_t*)w; w += up256(t * C * 2);
+  dz3s = (uint16_t*)w; w += up256(t * C * 2);
+  h1s = (uint16_t*)w;  w += up256(t * H * 2);
+  h2s = (uint16_t*)w;  w += up256(t * H * 2);
+  dz1s = (uint16_t*)w; w += up256(t * H * 2);
+  dz2s = (uint16_t*)w; w += up256(t * H * 2);
   P.gscratch = w;
+  Maps M;
+  memset(&M, 0, sizeof(M));
+  if (!stage_map(&M.out, ds, T, C, 4) || !stage_map(&M.h1, h1s, T, H, 2) || !stage_map(&M.h2, h2s, T, H, 2) ||
+      !stage_map(&M.dz1, dz1s, T, H, 2) || !stage_map(&M.dz2, dz2s, T, H, 2) || !stage_map(&M.dz3, dz3s, T, C, 2))
+    return rpde_internal_fail(RPDE_E_CUDA, "rpde_ff3_bwd: cuTensorMapEncodeTiled failed");
   P.db1 = db1; P.db2 = db2; P.db3 = db3; P.dgamma = dgamma; P.dbeta = dbeta;
   FF_CUDA(cudaMemsetAsync(db1, 0, H * sizeof(float), s));
   FF_CUDA(cudaMemsetAsync(db2, 0, H * sizeof(float), s));
@@ -838,13 +937,13 @@ int rpde_ff3_bwd(const float* x, const float* dy, const void* image, const float
   FF_CUDA(set_smem(ff3_kernel<true>, SMEM_BYTES));
   const long long tiles = (T + TM - 1) / TM;
   const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
-  ff3_kernel<true><<<grid, kThreads, SMEM_BYTES, s>>>(P);
+  ff3_kernel<true><<<grid, kThreads, SMEM_BYTES, s>>>(P, M);
   rpde_internal_count_launch(1);
   FF_CUDA(cudaGetLastError());
   // weight gradients from the BF16 copies
   CUtensorMap mdz2, mh1, mdz1, mxb, mh2, mdz3;
-  if (!bf16_map(&mdz2, P.dz2s, T, H) || !bf16_map(&mh1, P.h1s, T, H) || !bf16_map(&mdz1, P.dz1s, T, H) || !bf16_map(&mxb, P.xb, T, C) ||
-      !bf16_map(&mh2, P.h2s, T, H) || !bf16_map(&mdz3, P.dz3s, T, C))
+  if (!bf16_map(&mdz2, dz2s, T, H) || !bf16_map(&mh1, h1s, T, H) || !bf16_map(&mdz1, dz1s, T, H) || !bf16_map(&mxb, P.xb, T, C) ||
+      !bf16_map(&mh2, h2s, T, H) || !bf16_map(&mdz3, dz3s, T, C))
     return rpde_internal_fail(RPDE_E_CUDA, "rpde_ff3_bwd: cuTensorMapEncodeTiled failed");
   WgParams W{T, dw1, dw2, dw3};
   const long long kblocks = (T + 63) / 64;
