@@ -77,7 +77,7 @@ struct Params {
   const float* dy;      // backward: [T][64]
   uint16_t* xb;         // backward: BF16 copy of x for the weight-gradient kernel
   uint8_t* gscratch;    // backward: gridDim.x * 128 KB
-  float *db1, *db2, *db3, *dgamma, *dbeta;        // zero-initialised by the caller, accumulated atomically
+  float *dgamma, *dbeta;   // zero-initialised by the caller, accumulated atomically
 };
 // TMA maps of everything the epilogue warps store: boxes of 32 rows x 64 bytes, SWIZZLE_64B
 struct Maps {
@@ -141,6 +141,35 @@ __device__ __forceinline__ float4 lds_f4(uint32_t a) {
   return v;
 }
 
+// GELU and its derivative for the BF16 variant, two elements at a time on the packed fp32x2 pipe, ONE special-function
+// instruction per element:  Phi(x) = 1/2 + 1/2 tanh(x (a0 + a1 x^2 + a2 x^4)),  the odd polynomial fitted to
+// atanh(erf(x / sqrt 2)) on [0, 6]: |gelu error| < 3e-5, |gelu' error| < 1.3e-4 in exact arithmetic, plus tanh.approx
+// (2^-11 relative) -- an order of magnitude below the BF16 rounding (2^-9) applied to the result right after.
+//   gelu(x) = x Phi(x),   gelu'(x) = Phi + x/2 (1 - t^2)(a0 + 3 a1 x^2 + 5 a2 x^4).
+// The exact erf form (common.cuh: gelu_both2, two MUFU + 11.5 FP instructions per element) stays with the fp32-parity
+// and TF32 engines; this kernel's epilogues are instruction-issue bound.
+template <bool WITH_G>
+__device__ __forceinline__ void gelu_tanh2(float x0, float x1, float& h0, float& h1, float& g0, float& g1) {
+  constexpr float A0 = 7.97458471e-01f, A1 = 3.70503451e-02f, A2 = -3.58732361e-04f;
+  x0 = fminf(fmaxf(x0, -8.f), 8.f);   // beyond +-8 the fitted polynomial turns over; gelu is x or 0 there to 1e-15
+  x1 = fminf(fmaxf(x1, -8.f), 8.f);
+  const f32x2_t x = f2_pack(x0, x1), u = f2_mul(x, x);
+  f32x2_t q = f2_fma(u, f2_c(A2), f2_c(A1));
+  q = f2_fma(q, u, f2_c(A0));
+  float p0, p1, t0, t1;
+  f2_unpack(f2_mul(q, x), p0, p1);
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t0) : "f"(p0));
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t1) : "f"(p1));
+  const f32x2_t t = f2_pack(t0, t1), cdf = f2_fma(t, f2_c(0.5f), f2_c(0.5f));
+  f2_unpack(f2_mul(x, cdf), h0, h1);
+  if (WITH_G) {
+    f32x2_t dq = f2_fma(u, f2_c(5.f * A2), f2_c(3.f * A1));
+    dq = f2_fma(dq, u, f2_c(A0));
+    const f32x2_t s = f2_fma(t, f2_mul(t, f2_c(-1.f)), f2_c(1.f));      // 1 - t^2
+    f2_unpack(f2_fma(f2_mul(f2_mul(x, dq), s), f2_c(0.5f), cdf), g0, g1);
+  }
+}
+
 // The two warps of a quadrant exchange one pair of per-row values through two spare TMEM columns each (both warps may
 // access the quadrant's lanes): write mine, barrier, read the other's.
 __device__ __forceinline__ void pair_exchange(uint32_t tlane, uint32_t col, int half, int quad, float a, float b, float& oa, float& ob) {
@@ -200,12 +229,12 @@ __device__ __forceinline__ float colsum32(float (&v)[32], int lane) {
 // One hidden-layer epilogue over this warp's four 32-column chunks (c = 2j + half), converted in place.
 //   MODE 0: h = gelu(acc + bias)                                         -> BF16 A operand                    (inference / forward)
 //   MODE 1: the same, plus gelu'(acc + bias) -> scratch and h -> spill                                        (backward: recompute)
-//   MODE 2: dz = acc * gelu' (from scratch) -> BF16 A operand, dz -> spill, column sums of dz (bias gradient)  (backward)
+//   MODE 2: dz = acc * gelu' (from scratch) -> BF16 A operand, dz -> spill                                     (backward)
 // scratch: this warp's private 8 KB for the layer, laid out [j][q][lane] in 16-byte units (coalesced, same thread reads back)
 template <int MODE>
 __device__ __forceinline__ void hidden_epi(uint32_t tlane, uint32_t src_col, uint32_t dst_col, int half, int quad, int lane,
                                            uint32_t ready_bar0, uint32_t bias_smem, const Stage& stg, const CUtensorMap* spill_map,
-                                           int row0, uint8_t* scratch, float (&cs)[4]) {
+                                           int row0, uint8_t* scratch) {
   uint4 g4[4];
   if (MODE == 2) {
 #pragma unroll
@@ -239,7 +268,7 @@ __device__ __forceinline__ void hidden_epi(uint32_t tlane, uint32_t src_col, uin
 #pragma unroll
       for (int k = 0; k < 32; k += 2) {
         float h0, h1, g0, g1;
-        gelu_both2(__uint_as_float(r[k]) + v[k], __uint_as_float(r[k + 1]) + v[k + 1], h0, h1, g0, g1);
+        gelu_tanh2<MODE == 1>(__uint_as_float(r[k]) + v[k], __uint_as_float(r[k + 1]) + v[k + 1], h0, h1, g0, g1);
         p[k >> 1] = pack_bf16(h0, h1);
         if (MODE == 1) gp[k >> 1] = pack_bf16(g0, g1);
       }
@@ -264,7 +293,6 @@ __device__ __forceinline__ void hidden_epi(uint32_t tlane, uint32_t src_col, uin
       stg.store(spill_map, 32 * c, row0);
     }
     if (MODE == 2) {
-      cs[j] += colsum32(v, lane);
       if (j < 3) {
 #pragma unroll
         for (int q = 0; q < 4; ++q) g4[q] = gn[q];
@@ -433,9 +461,8 @@ __global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant_
     const uint32_t tlane = tmem + ((uint32_t)(quad * 32) << 16);
     const int rl = quad * 32 + lane;                       // row of the tile = TMEM lane
     const Stage stg{sbase + STG_OFF + (uint32_t)ew * 2048u, lane};
-    float cs1[4] = {0.f, 0.f, 0.f, 0.f}, cs2[4] = {0.f, 0.f, 0.f, 0.f}, cs3 = 0.f, csg = 0.f, csb = 0.f;
+    float csg = 0.f, csb = 0.f;   // dgamma / dbeta column sums (the bias gradients come from the weight-gradient kernel)
     uint8_t* scr = BWD ? P.gscratch + ((size_t)blockIdx.x * 8 + ew) * 16384 : nullptr;   // [layer][8 KB] per warp
-    float dummy[4];
     uint32_t it = 0;
     for (long long t = blockIdx.x; t < ntiles; t += gridDim.x, ++it) {
       const uint32_t ph = it & 1;
@@ -445,10 +472,10 @@ __global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant_
       // ---- layer 1 and 2: bias + GELU, converted in place into the next layer's A operand
       mbar_wait(bar(B_D1), ph);
       tc_fence_after_sync();
-      hidden_epi<BWD ? 1 : 0>(tlane, D1, H1, half, quad, lane, bar(B_H1), pb1, stg, &M.h1, row0, scr, dummy);
+      hidden_epi<BWD ? 1 : 0>(tlane, D1, H1, half, quad, lane, bar(B_H1), pb1, stg, &M.h1, row0, scr);
       mbar_wait(bar(B_D2), ph);
       tc_fence_after_sync();
-      hidden_epi<BWD ? 1 : 0>(tlane, D2, H2, half, quad, lane, bar(B_H2), pb2, stg, &M.h2, row0, BWD ? scr + 8192 : nullptr, dummy);
+      hidden_epi<BWD ? 1 : 0>(tlane, D2, H2, half, quad, lane, bar(B_H2), pb2, stg, &M.h2, row0, BWD ? scr + 8192 : nullptr);
       // ---- layer 3: bias, LayerNorm (row statistics shared by the two warps of the quadrant)
       float in[32];   // forward: residual; backward: dy
       {
@@ -554,7 +581,6 @@ __global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant_
         stg.write(p);
         stg.store(&M.dz3, 32 * half, row0);
         if (ln) csb += colsum32(in, lane);
-        cs3 += colsum32(dz, lane);
         tmem_st_wait();
         tc_fence_before_sync();
         __syncwarp();
@@ -562,10 +588,10 @@ __global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant_
         // ---- dZ2 = dH2 * gelu'(Z2), dZ1 = dH1 * gelu'(Z1)
         mbar_wait(bar(B_D4), ph);
         tc_fence_after_sync();
-        hidden_epi<2>(tlane, D4, DZ2, half, quad, lane, bar(B_DZ2), 0, stg, &M.dz2, row0, scr + 8192, cs2);
+        hidden_epi<2>(tlane, D4, DZ2, half, quad, lane, bar(B_DZ2), 0, stg, &M.dz2, row0, scr + 8192);
         mbar_wait(bar(B_D5), ph);
         tc_fence_after_sync();
-        hidden_epi<2>(tlane, D5, DZ1, half, quad, lane, bar(B_DZ1), 0, stg, &M.dz1, row0, scr, cs1);
+        hidden_epi<2>(tlane, D5, DZ1, half, quad, lane, bar(B_DZ1), 0, stg, &M.dz1, row0, scr);
         // ---- dS
         mbar_wait(bar(B_D6), ph);
         tc_fence_after_sync();
@@ -584,12 +610,6 @@ __global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant_
       }
     }
     if (BWD) {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        atomicAdd(P.db1 + 32 * (2 * j + half) + lane, cs1[j]);
-        atomicAdd(P.db2 + 32 * (2 * j + half) + lane, cs2[j]);
-      }
-      atomicAdd(P.db3 + 32 * half + lane, cs3);
       if (ln) {
         atomicAdd(P.dgamma + 32 * half + lane, csg);
         atomicAdd(P.dbeta + 32 * half + lane, csb);
@@ -635,7 +655,8 @@ __global__ void ff_pack_weights_kernel(const float* __restrict__ w1, const float
 // Both operands are BF16 row-major [T][features] in global memory = MN-major operands: one TMA box of 64 rows x 64
 // features lands as a SWIZZLE_128B atom stack ([k rows][128 B]).  Each CTA owns a contiguous slab of 64-row k-blocks,
 // accumulates in TMEM (fp32) and adds its partial result to the zero-initialised gradient with red.global.add.
-//   warp 0: TMA producer, warp 1: UMMA issuer + TMEM owner, warps 2-5: final TMEM -> global reduction.
+//   warp 0: TMA producer, warp 1: UMMA issuer + TMEM owner, warps 2-5: column sums of the dZ tiles while they sit in
+//   shared memory (the bias gradients), then the final TMEM -> global reduction.
 // ====================================================================================================================
 constexpr int WG_THREADS = 6 * 32;
 constexpr uint32_t WG_BOX = 64 * 128;   // one 64 x 64 BF16 box
@@ -654,6 +675,7 @@ struct WgCfg {
 struct WgParams {
   long long T;
   float *dw1, *dw2, *dw3;   // (256,64), (256,256), (64,256) fp32, zero-initialised
+  float *db1, *db2, *db3;   // bias gradients = column sums of dZ1 / dZ2 / dZ3, zero-initialised
 };
 
 template <int JOB>
@@ -677,7 +699,7 @@ ff_wgrad_kernel(const __grid_constant__ WgParams P, const __grid_constant__ CUte
     tma_prefetch_desc(&mB0);
     for (int s = 0; s < G::stages; ++s) {
       mbar_init(full(s), 1);
-      mbar_init(empty(s), 1);
+      mbar_init(empty(s), 5);   // the UMMA commit + the four column-sum warps
     }
     mbar_init(done, 1);
     fence_barrier_init();
@@ -752,6 +774,46 @@ ff_wgrad_kernel(const __grid_constant__ WgParams P, const __grid_constant__ CUte
       umma_commit(done);
     }
   } else if (kb1 > kb0) {
+    {
+      // bias gradients: thread (box b = warp - 2, word w = lane) owns features 64 b + 2 w, + 1 of the 256-wide dZ operand
+      // (boxes 0..3 of the stage); the 16-byte chunk c of k-row k sits at c ^ (k & 7) (SWIZZLE_128B)
+      const int b = warp - 2;
+      float a0 = 0.f, a1 = 0.f, c0 = 0.f, c1 = 0.f;
+      int s = 0;
+      uint32_t ph = 0;
+      for (long long kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(full(s), ph);
+        const uint32_t box = sbase + s * G::stage_bytes + b * WG_BOX + (((uint32_t)lane & 3u) << 2);
+        const uint32_t chunk = (uint32_t)lane >> 2;
+#pragma unroll 8
+        for (uint32_t k = 0; k < 64; ++k) {
+          uint32_t w;
+          asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(box + k * 128u + ((chunk ^ (k & 7u)) << 4)));
+          a0 += bf16_lo(w);
+          a1 += bf16_hi(w);
+        }
+        if (JOB == 1 && b == 0) {   // dZ3 (box 9, 64 features)
+          const uint32_t box3 = sbase + s * G::stage_bytes + 9 * WG_BOX + (((uint32_t)lane & 3u) << 2);
+#pragma unroll 8
+          for (uint32_t k = 0; k < 64; ++k) {
+            uint32_t w;
+            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(box3 + k * 128u + ((chunk ^ (k & 7u)) << 4)));
+            c0 += bf16_lo(w);
+            c1 += bf16_hi(w);
+          }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty(s));
+        if (++s == G::stages) { s = 0; ph ^= 1; }
+      }
+      float* db = JOB == 0 ? P.db2 : P.db1;
+      atomicAdd(db + 64 * b + 2 * lane, a0);
+      atomicAdd(db + 64 * b + 2 * lane + 1, a1);
+      if (JOB == 1 && b == 0) {
+        atomicAdd(P.db3 + 2 * lane, c0);
+        atomicAdd(P.db3 + 2 * lane + 1, c1);
+      }
+    }
     // TMEM lane quadrant = warp % 4: warps 2..5 cover quadrants 2, 3, 0, 1.  Lane = feature m within the 128-row block.
     const int quad = warp & 3;
     const uint32_t tlane = tmem + ((uint32_t)(quad * 32) << 16);
@@ -923,7 +985,7 @@ int rpde_ff3_bwd(const float* x, const float* dy, const void* image, const float
   if (!stage_map(&M.out, ds, T, C, 4) || !stage_map(&M.h1, h1s, T, H, 2) || !stage_map(&M.h2, h2s, T, H, 2) ||
       !stage_map(&M.dz1, dz1s, T, H, 2) || !stage_map(&M.dz2, dz2s, T, H, 2) || !stage_map(&M.dz3, dz3s, T, C, 2))
     return rpde_internal_fail(RPDE_E_CUDA, "rpde_ff3_bwd: cuTensorMapEncodeTiled failed");
-  P.db1 = db1; P.db2 = db2; P.db3 = db3; P.dgamma = dgamma; P.dbeta = dbeta;
+  P.dgamma = dgamma; P.dbeta = dbeta;
   FF_CUDA(cudaMemsetAsync(db1, 0, H * sizeof(float), s));
   FF_CUDA(cudaMemsetAsync(db2, 0, H * sizeof(float), s));
   FF_CUDA(cudaMemsetAsync(db3, 0, C * sizeof(float), s));
@@ -945,7 +1007,7 @@ int rpde_ff3_bwd(const float* x, const float* dy, const void* image, const float
   if (!bf16_map(&mdz2, dz2s, T, H) || !bf16_map(&mh1, h1s, T, H) || !bf16_map(&mdz1, dz1s, T, H) || !bf16_map(&mxb, P.xb, T, C) ||
       !bf16_map(&mh2, h2s, T, H) || !bf16_map(&mdz3, dz3s, T, C))
     return rpde_internal_fail(RPDE_E_CUDA, "rpde_ff3_bwd: cuTensorMapEncodeTiled failed");
-  WgParams W{T, dw1, dw2, dw3};
+  WgParams W{T, dw1, dw2, dw3, db1, db2, db3};
   const long long kblocks = (T + 63) / 64;
   const unsigned wgrid = (unsigned)(kblocks < sms ? kblocks : sms);
   FF_CUDA(set_smem(ff_wgrad_kernel<0>, WgCfg<0>::smem_bytes));
