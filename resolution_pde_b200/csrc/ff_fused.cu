@@ -14,9 +14,10 @@
 //
 //   warp 0        UMMA issuer (one lane) + TMEM owner
 //   warp 1        weight image: one cp.async.bulk sequence at kernel start
-//   warps 2-5     x loader: fp32 rows -> BF16 -> swizzled shared-memory A tile (and, backward, the BF16 copy the
+//   warps 4-7     x loader: fp32 rows -> BF16 -> swizzled shared-memory A tile (and, backward, the BF16 copy the
 //                 weight-gradient kernel reads)
-//   warps 6-13    epilogues, two warps per TMEM lane quadrant (even / odd 32-column chunks)
+//   warps 8-23    epilogues, four warps per TMEM lane quadrant (16-column chunks c = 4j + sub): the epilogues are
+//                 latency- and issue-bound CUDA-core work, four warps per scheduler hide each other's waits
 //
 // TMEM (512 columns):   [0,256) D1 = x W1^T  -> gelu -> H1 (BF16 pairs, [0,128))           [256,512) D2 = H1 W2^T -> H2 ([256,384))
 //                       [128,192) D3 = H2 W3^T (read by the LayerNorm epilogue)
@@ -26,9 +27,9 @@
 //   gelu'(Z1), gelu'(Z2) wait in a per-CTA scratch (L2-resident, written and re-read by the same thread); H1, H2, dZ1,
 //   dZ2, dZ3 and x leave as BF16 for the weight-gradient kernel (ff_wgrad_kernel below: dW = dZ^T H with K = rows).
 //
-// In-place conversion: the result of 32-column chunk c (16 packed columns) lands in columns that belong to chunk c/2.
-// The two warps of a quadrant own the even and the odd chunks and meet at a 64-thread named barrier after every chunk
-// load, so chunk c/2 has always been read by its owner before it is overwritten.
+// In-place conversion: the result of 16-column chunk c (8 packed columns) lands in columns that belong to chunk c/2.
+// The four warps of a quadrant own chunks 4j + sub and meet at a 128-thread named barrier after every chunk load, so
+// chunk c/2 <= 2j + 1 has always been read by its owner before it is overwritten.
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -51,17 +52,18 @@ constexpr uint32_t W2_OFF = W1_OFF + W1_BYTES, W2_PLANE = H * 128, W2_BYTES = 4 
 constexpr uint32_t W3_OFF = W2_OFF + W2_BYTES, W3_PLANE = C * 128, W3_BYTES = 4 * W3_PLANE;  // 4 k-planes of [64 rows][64 bf16]
 constexpr uint32_t WBLOB = W3_OFF + W3_BYTES;                                          // 196608
 constexpr uint32_t X_OFF = WBLOB, X_BYTES = TM * 128;                                  // A tile of layer 1: [128 rows][64 bf16]
-constexpr uint32_t STG_OFF = X_OFF + X_BYTES;                                          // 8 epilogue warps x 2 KB staging box (TMA stores)
-constexpr uint32_t STG_BYTES = 8 * 2048;
+constexpr int kEpiWarps = 16;                                                          // four per TMEM lane quadrant
+constexpr uint32_t STG_OFF = X_OFF + X_BYTES;                                          // one 1 KB staging box per epilogue warp (TMA stores)
+constexpr uint32_t STG_BYTES = kEpiWarps * 1024;
 constexpr uint32_t PAR_OFF = STG_OFF + STG_BYTES;                                      // b1[256] b2[256] b3[64] gamma[64] beta[64]
 constexpr uint32_t PAR_BYTES = (2 * H + 3 * C) * 4;
 constexpr uint32_t BAR_OFF = PAR_OFF + PAR_BYTES;
 constexpr uint32_t SMEM_BYTES = BAR_OFF + 256;
 static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
-constexpr int kThreads = 14 * 32;
+constexpr int kThreads = (8 + kEpiWarps) * 32;   // warp 0 UMMA, 1 weights, 2-3 idle, 4-7 x loaders, 8-23 epilogues
 // TMEM columns
 constexpr uint32_t D1 = 0, H1 = 0, D3 = 128, DZ3 = 192, D2 = 256, H2 = 256, D4 = 256, DZ2 = 256, D5 = 0, DZ1 = 0, D6 = 256;
-constexpr uint32_t ST_A = 224, ST_B = 226, ST_C = 228;   // row-statistic exchange between the two warps of a quadrant
+constexpr uint32_t ST_A = 224, ST_B = 232, ST_C = 240;   // row-statistic exchange between the four warps of a quadrant
 // barriers
 enum { B_WFULL = 0, B_XFULL, B_XEMPTY, B_D1, B_D2, B_D3, B_TILE, B_H1, B_H2 = B_H1 + 4, B_DZ3 = B_H2 + 4, B_D4, B_DZ2,
        B_D5 = B_DZ2 + 4, B_DZ1, B_D6 = B_DZ1 + 4, B_COUNT };
@@ -76,13 +78,13 @@ struct Params {
   float eps;
   const float* dy;      // backward: [T][64]
   uint16_t* xb;         // backward: BF16 copy of x for the weight-gradient kernel
-  uint8_t* gscratch;    // backward: gridDim.x * 128 KB
+  uint8_t* gscratch;    // backward: gridDim.x * 128 KB (8 KB per epilogue warp)
   float *dgamma, *dbeta;   // zero-initialised by the caller, accumulated atomically
 };
-// TMA maps of everything the epilogue warps store: boxes of 32 rows x 64 bytes, SWIZZLE_64B
+// TMA maps of everything the epilogue warps store: boxes of 32 rows x 32 bytes, SWIZZLE_32B
 struct Maps {
-  CUtensorMap out;                     // forward: y; backward: ds   ([T][64] fp32, box 16 x 32)
-  CUtensorMap h1, h2, dz1, dz2, dz3;   // backward: BF16 copies ([T][256] / [T][64], box 32 x 32)
+  CUtensorMap out;                     // forward: y; backward: ds   ([T][64] fp32, box 8 x 32)
+  CUtensorMap h1, h2, dz1, dz2, dz3;   // backward: BF16 copies ([T][256] / [T][64], box 16 x 32)
 };
 
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
@@ -151,9 +153,12 @@ __device__ __forceinline__ float4 lds_f4(uint32_t a) {
 template <bool WITH_G>
 __device__ __forceinline__ void gelu_tanh2(float x0, float x1, float& h0, float& h1, float& g0, float& g1) {
   constexpr float A0 = 7.97458471e-01f, A1 = 3.70503451e-02f, A2 = -3.58732361e-04f;
-  x0 = fminf(fmaxf(x0, -8.f), 8.f);   // beyond +-8 the fitted polynomial turns over; gelu is x or 0 there to 1e-15
-  x1 = fminf(fmaxf(x1, -8.f), 8.f);
-  const f32x2_t x = f2_pack(x0, x1), u = f2_mul(x, x);
+  const f32x2_t x = f2_pack(x0, x1);
+  float u0, u1;
+  f2_unpack(f2_mul(x, x), u0, u1);
+  // beyond |x| = 8 the fitted polynomial would turn over: freeze its argument there (q(64) = 1.70 > 0, so x q stays
+  // monotone and tanh saturates; gelu is x or 0 to 1e-15 out there)
+  const f32x2_t u = f2_pack(fminf(u0, 64.f), fminf(u1, 64.f));
   f32x2_t q = f2_fma(u, f2_c(A2), f2_c(A1));
   q = f2_fma(q, u, f2_c(A0));
   float p0, p1, t0, t1;
@@ -170,20 +175,45 @@ __device__ __forceinline__ void gelu_tanh2(float x0, float x1, float& h0, float&
   }
 }
 
-// The two warps of a quadrant exchange one pair of per-row values through two spare TMEM columns each (both warps may
-// access the quadrant's lanes): write mine, barrier, read the other's.
-__device__ __forceinline__ void pair_exchange(uint32_t tlane, uint32_t col, int half, int quad, float a, float b, float& oa, float& ob) {
-  tmem_st2(tlane + col + 2 * half, a, b);
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* v) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+        "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t* v) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+               : "r"(taddr)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t* v) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr), "r"(v[0]), "r"(v[1]),
+               "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+               : "memory");
+}
+// the four epilogue warps of a TMEM lane quadrant
+__device__ __forceinline__ void quad_sync(int quad) { asm volatile("bar.sync %0, 128;" ::"r"(1 + quad) : "memory"); }
+
+// The four warps of a quadrant share per-row partial sums through eight spare TMEM columns (every warp of the quadrant
+// may access its lanes): write mine, barrier, read all four pairs and add them in a fixed order.
+__device__ __forceinline__ void quad_exchange(uint32_t tlane, uint32_t col, int sub, int quad, float a, float b, float& sa, float& sb) {
+  tmem_st2(tlane + col + 2 * sub, a, b);
   tmem_st_wait();
   tc_fence_before_sync();
-  pair_sync(quad);
+  quad_sync(quad);
   tc_fence_after_sync();
-  tmem_ld2(tlane + col + 2 * (half ^ 1), oa, ob);
+  uint32_t r[8];
+  tmem_ld8(tlane + col, r);
   tmem_ld_wait();
+  sa = (__uint_as_float(r[0]) + __uint_as_float(r[2])) + (__uint_as_float(r[4]) + __uint_as_float(r[6]));
+  sb = (__uint_as_float(r[1]) + __uint_as_float(r[3])) + (__uint_as_float(r[5]) + __uint_as_float(r[7]));
 }
 
-// per-warp staging box for bulk tensor stores: 32 rows (lanes) of 64 bytes, 16-byte chunk q of row r at q ^ ((r >> 1) & 3)
-// (SWIZZLE_64B: the warp's four 128-bit stores are bank-conflict free)
+// per-warp staging box for bulk tensor stores: 32 rows (lanes) of 32 bytes, 16-byte chunk q of row r at q ^ ((r >> 2) & 1)
+// (SWIZZLE_32B: the warp's two 128-bit stores are bank-conflict free)
 struct Stage {
   uint32_t base;
   int lane;
@@ -191,10 +221,10 @@ struct Stage {
     if (lane == 0) bulk_wait_read0();
     __syncwarp();
   }
-  __device__ __forceinline__ void write(const uint32_t* p) const {
-    const uint32_t row = base + (uint32_t)lane * 64u, sw = ((uint32_t)lane >> 1) & 3u;
+  __device__ __forceinline__ void write(const uint32_t* p) const {   // 8 words = this lane's 32-byte row
+    const uint32_t row = base + (uint32_t)lane * 32u, sw = ((uint32_t)lane >> 2) & 1u;
 #pragma unroll
-    for (uint32_t q = 0; q < 4; ++q)
+    for (uint32_t q = 0; q < 2; ++q)
       asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(row + ((q ^ sw) << 4)), "r"(p[4 * q]), "r"(p[4 * q + 1]),
                    "r"(p[4 * q + 2]), "r"(p[4 * q + 3])
                    : "memory");
@@ -210,11 +240,11 @@ struct Stage {
   }
 };
 
-// lane j receives the sum over the warp's 32 lanes of v[j] (31 shuffles): the column sums of a 32 x 32 block whose rows
-// are the lanes.  v is destroyed.
-__device__ __forceinline__ float colsum32(float (&v)[32], int lane) {
+// lanes l and l + 16 receive the sum over the warp's 32 lanes of v[l & 15] (16 shuffles): the column sums of a 32 x 16
+// block whose rows are the lanes.  v is destroyed.
+__device__ __forceinline__ float colsum16(float (&v)[16], int lane) {
 #pragma unroll
-  for (int off = 16; off >= 1; off >>= 1) {
+  for (int off = 8; off >= 1; off >>= 1) {
     const bool up = (lane & off) != 0;
 #pragma unroll
     for (int k = 0; k < off; ++k) {
@@ -223,80 +253,77 @@ __device__ __forceinline__ float colsum32(float (&v)[32], int lane) {
       v[k] = keep + __shfl_xor_sync(0xffffffffu, send, off);
     }
   }
-  return v[0];
+  return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 16);
 }
 
-// One hidden-layer epilogue over this warp's four 32-column chunks (c = 2j + half), converted in place.
+// One hidden-layer epilogue over this warp's four 16-column chunks (c = 4j + sub), converted in place.
 //   MODE 0: h = gelu(acc + bias)                                         -> BF16 A operand                    (inference / forward)
 //   MODE 1: the same, plus gelu'(acc + bias) -> scratch and h -> spill                                        (backward: recompute)
 //   MODE 2: dz = acc * gelu' (from scratch) -> BF16 A operand, dz -> spill                                     (backward)
-// scratch: this warp's private 8 KB for the layer, laid out [j][q][lane] in 16-byte units (coalesced, same thread reads back)
+// scratch: this warp's private 4 KB for the layer, laid out [j][q][lane] in 16-byte units (coalesced, same thread reads back)
 template <int MODE>
-__device__ __forceinline__ void hidden_epi(uint32_t tlane, uint32_t src_col, uint32_t dst_col, int half, int quad, int lane,
+__device__ __forceinline__ void hidden_epi(uint32_t tlane, uint32_t src_col, uint32_t dst_col, int sub, int quad, int lane,
                                            uint32_t ready_bar0, uint32_t bias_smem, const Stage& stg, const CUtensorMap* spill_map,
                                            int row0, uint8_t* scratch) {
-  uint4 g4[4];
+  uint4 g4[2];
   if (MODE == 2) {
 #pragma unroll
-    for (int q = 0; q < 4; ++q) g4[q] = ldg128(scratch + ((0 * 4 + q) * 32 + lane) * 16);
+    for (int q = 0; q < 2; ++q) g4[q] = ldg128(scratch + ((0 * 2 + q) * 32 + lane) * 16);
   }
 #pragma unroll 1
   for (int j = 0; j < 4; ++j) {
-    const int c = 2 * j + half;
-    uint32_t r[32];
-    tmem_ld32(tlane + src_col + 32 * c, r);
-    uint4 gn[4];
+    const int c = 4 * j + sub;
+    uint32_t r[16];
+    tmem_ld16(tlane + src_col + 16 * c, r);
+    uint4 gn[2];
     if (MODE == 2 && j < 3) {   // the next chunk's gelu' is in flight while this one is processed
 #pragma unroll
-      for (int q = 0; q < 4; ++q) gn[q] = ldg128(scratch + (((j + 1) * 4 + q) * 32 + lane) * 16);
+      for (int q = 0; q < 2; ++q) gn[q] = ldg128(scratch + (((j + 1) * 2 + q) * 32 + lane) * 16);
     }
-    float v[32];
+    float v[16];
     if (MODE != 2) {
 #pragma unroll
-      for (int q = 0; q < 8; ++q) {
-        const float4 b4 = lds_f4(bias_smem + (32 * c + 4 * q) * 4);
+      for (int q = 0; q < 4; ++q) {
+        const float4 b4 = lds_f4(bias_smem + (16 * c + 4 * q) * 4);
         v[4 * q] = b4.x; v[4 * q + 1] = b4.y; v[4 * q + 2] = b4.z; v[4 * q + 3] = b4.w;
       }
     }
     tmem_ld_wait();
     tc_fence_before_sync();
-    pair_sync(quad);   // both warps of the quadrant have read their chunk 2j / 2j + 1: columns of chunk j may be overwritten
+    quad_sync(quad);   // the four warps of the quadrant have read chunks 4j .. 4j + 3: columns of chunks <= 2j + 1 may be overwritten
     tc_fence_after_sync();
-    uint32_t p[16];
+    uint32_t p[8];
     if (MODE != 2) {
-      uint32_t gp[16];
+      uint32_t gp[8];
 #pragma unroll
-      for (int k = 0; k < 32; k += 2) {
+      for (int k = 0; k < 16; k += 2) {
         float h0, h1, g0, g1;
-        gelu_tanh2<MODE == 1>(__uint_as_float(r[k]) + v[k], __uint_as_float(r[k + 1]) + v[k + 1], h0, h1, g0, g1);
+        float z0, z1;   // accumulator + bias on the packed pipe
+        f2_unpack(f2_add(f2_pack(__uint_as_float(r[k]), __uint_as_float(r[k + 1])), f2_pack(v[k], v[k + 1])), z0, z1);
+        gelu_tanh2<MODE == 1>(z0, z1, h0, h1, g0, g1);
         p[k >> 1] = pack_bf16(h0, h1);
         if (MODE == 1) gp[k >> 1] = pack_bf16(g0, g1);
       }
-      tmem_st16(tlane + dst_col + 16 * c, p);
+      tmem_st8(tlane + dst_col + 8 * c, p);
       if (MODE == 1) {
 #pragma unroll
-        for (int q = 0; q < 4; ++q) stg128(scratch + ((j * 4 + q) * 32 + lane) * 16, gp[4 * q], gp[4 * q + 1], gp[4 * q + 2], gp[4 * q + 3]);
+        for (int q = 0; q < 2; ++q) stg128(scratch + ((j * 2 + q) * 32 + lane) * 16, gp[4 * q], gp[4 * q + 1], gp[4 * q + 2], gp[4 * q + 3]);
       }
     } else {
       const uint32_t* gw = reinterpret_cast<const uint32_t*>(g4);
 #pragma unroll
-      for (int k = 0; k < 16; ++k) {
-        v[2 * k] = __uint_as_float(r[2 * k]) * bf16_lo(gw[k]);
-        v[2 * k + 1] = __uint_as_float(r[2 * k + 1]) * bf16_hi(gw[k]);
-        p[k] = pack_bf16(v[2 * k], v[2 * k + 1]);
-      }
-      tmem_st16(tlane + dst_col + 16 * c, p);
+      for (int k = 0; k < 8; ++k)
+        p[k] = pack_bf16(__uint_as_float(r[2 * k]) * bf16_lo(gw[k]), __uint_as_float(r[2 * k + 1]) * bf16_hi(gw[k]));
+      tmem_st8(tlane + dst_col + 8 * c, p);
     }
     if (MODE != 0) {   // BF16 copy for the weight-gradient kernel: staged, then one bulk tensor store per chunk
       stg.wait_free();
       stg.write(p);
-      stg.store(spill_map, 32 * c, row0);
+      stg.store(spill_map, 16 * c, row0);
     }
-    if (MODE == 2) {
-      if (j < 3) {
-#pragma unroll
-        for (int q = 0; q < 4; ++q) g4[q] = gn[q];
-      }
+    if (MODE == 2 && j < 3) {
+      g4[0] = gn[0];
+      g4[1] = gn[1];
     }
     tmem_st_wait();
     tc_fence_before_sync();
@@ -339,14 +366,14 @@ __global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant_
     mbar_init(bar(B_D1), 1);
     mbar_init(bar(B_D2), 1);
     mbar_init(bar(B_D3), 1);
-    mbar_init(bar(B_TILE), 8);
+    mbar_init(bar(B_TILE), kEpiWarps);
     for (int j = 0; j < 4; ++j) {
-      mbar_init(bar(B_H1 + j), 8);
-      mbar_init(bar(B_H2 + j), 8);
-      mbar_init(bar(B_DZ2 + j), 8);
-      mbar_init(bar(B_DZ1 + j), 8);
+      mbar_init(bar(B_H1 + j), kEpiWarps);
+      mbar_init(bar(B_H2 + j), kEpiWarps);
+      mbar_init(bar(B_DZ2 + j), kEpiWarps);
+      mbar_init(bar(B_DZ1 + j), kEpiWarps);
     }
-    mbar_init(bar(B_DZ3), 8);
+    mbar_init(bar(B_DZ3), kEpiWarps);
     mbar_init(bar(B_D4), 1);
     mbar_init(bar(B_D5), 1);
     mbar_init(bar(B_D6), 1);
@@ -428,41 +455,44 @@ __global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant_
       mbar_arrive_expect_tx(bar(B_WFULL), WBLOB);
       for (uint32_t o = 0; o < WBLOB; o += 32768) bulk_g2s(sbase + o, P.blob + o, 32768, bar(B_WFULL));
     }
-  } else if (warp < 6) {
+  } else if (warp >= 4 && warp < 8) {
     // ------------------------------------------------------------------------------------------------ x loader
-    const int lw = warp - 2, hl = lane >> 4, q = lane & 15;
+    const int lw = warp - 4, hl = lane >> 4, q = lane & 15;
     uint32_t it = 0;
     for (long long t = blockIdx.x; t < ntiles; t += gridDim.x, ++it) {
-      float4 v[16];
+#pragma unroll 1
+      for (int pass = 0; pass < 2; ++pass) {
+        float4 v[8];
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const long long row = t * TM + lw * 32 + 2 * i + hl;
-        v[i] = row < P.T ? __ldg(reinterpret_cast<const float4*>(P.x + row * C) + q) : make_float4(0.f, 0.f, 0.f, 0.f);
-      }
-      mbar_wait(bar(B_XEMPTY), (it & 1) ^ 1);   // layer 1 of the previous tile has consumed the buffer
+        for (int i = 0; i < 8; ++i) {
+          const long long row = t * TM + lw * 32 + 16 * pass + 2 * i + hl;
+          v[i] = row < P.T ? __ldg(reinterpret_cast<const float4*>(P.x + row * C) + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        if (pass == 0) mbar_wait(bar(B_XEMPTY), (it & 1) ^ 1);   // layer 1 of the previous tile has consumed the buffer
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const int r = lw * 32 + 2 * i + hl;
-        const uint32_t lo = pack_bf16(v[i].x, v[i].y), hi = pack_bf16(v[i].z, v[i].w);
-        const uint32_t a = xs + r * 128 + ((((uint32_t)q >> 1) ^ ((uint32_t)r & 7u)) << 4) + ((uint32_t)q & 1u) * 8u;
-        asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(a), "r"(lo), "r"(hi) : "memory");
-        if (BWD) {
-          const long long row = t * TM + r;
-          if (row < P.T) asm volatile("st.global.v2.b32 [%0], {%1, %2};" ::"l"(P.xb + row * C + 4 * q), "r"(lo), "r"(hi) : "memory");
+        for (int i = 0; i < 8; ++i) {
+          const int r = lw * 32 + 16 * pass + 2 * i + hl;
+          const uint32_t lo = pack_bf16(v[i].x, v[i].y), hi = pack_bf16(v[i].z, v[i].w);
+          const uint32_t a = xs + r * 128 + ((((uint32_t)q >> 1) ^ ((uint32_t)r & 7u)) << 4) + ((uint32_t)q & 1u) * 8u;
+          asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(a), "r"(lo), "r"(hi) : "memory");
+          if (BWD) {
+            const long long row = t * TM + r;
+            if (row < P.T) asm volatile("st.global.v2.b32 [%0], {%1, %2};" ::"l"(P.xb + row * C + 4 * q), "r"(lo), "r"(hi) : "memory");
+          }
         }
       }
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(B_XFULL));
     }
-  } else {
+  } else if (warp >= 8) {
     // ------------------------------------------------------------------------------------------------ epilogues
-    const int ew = warp - 6, quad = warp & 3, half = ew >> 2;
+    const int ew = warp - 8, quad = warp & 3, sub = ew >> 2;
     const uint32_t tlane = tmem + ((uint32_t)(quad * 32) << 16);
     const int rl = quad * 32 + lane;                       // row of the tile = TMEM lane
-    const Stage stg{sbase + STG_OFF + (uint32_t)ew * 2048u, lane};
+    const Stage stg{sbase + STG_OFF + (uint32_t)ew * 1024u, lane};
     float csg = 0.f, csb = 0.f;   // dgamma / dbeta column sums (the bias gradients come from the weight-gradient kernel)
-    uint8_t* scr = BWD ? P.gscratch + ((size_t)blockIdx.x * 8 + ew) * 16384 : nullptr;   // [layer][8 KB] per warp
+    uint8_t* scr = BWD ? P.gscratch + ((size_t)blockIdx.x * kEpiWarps + ew) * 8192 : nullptr;   // [layer][4 KB] per warp
     uint32_t it = 0;
     for (long long t = blockIdx.x; t < ntiles; t += gridDim.x, ++it) {
       const uint32_t ph = it & 1;
@@ -472,30 +502,30 @@ __global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant_
       // ---- layer 1 and 2: bias + GELU, converted in place into the next layer's A operand
       mbar_wait(bar(B_D1), ph);
       tc_fence_after_sync();
-      hidden_epi<BWD ? 1 : 0>(tlane, D1, H1, half, quad, lane, bar(B_H1), pb1, stg, &M.h1, row0, scr);
+      hidden_epi<BWD ? 1 : 0>(tlane, D1, H1, sub, quad, lane, bar(B_H1), pb1, stg, &M.h1, row0, scr);
       mbar_wait(bar(B_D2), ph);
       tc_fence_after_sync();
-      hidden_epi<BWD ? 1 : 0>(tlane, D2, H2, half, quad, lane, bar(B_H2), pb2, stg, &M.h2, row0, BWD ? scr + 8192 : nullptr);
-      // ---- layer 3: bias, LayerNorm (row statistics shared by the two warps of the quadrant)
-      float in[32];   // forward: residual; backward: dy
+      hidden_epi<BWD ? 1 : 0>(tlane, D2, H2, sub, quad, lane, bar(B_H2), pb2, stg, &M.h2, row0, BWD ? scr + 4096 : nullptr);
+      // ---- layer 3: bias, LayerNorm (row statistics shared by the four warps of the quadrant), 16 columns per warp
+      float in[16];   // forward: residual; backward: dy
       {
         const float* src = BWD ? P.dy : P.res;
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          const float4 a = (src && valid) ? __ldg(reinterpret_cast<const float4*>(src + row * C + 32 * half) + q) : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int q = 0; q < 4; ++q) {
+          const float4 a = (src && valid) ? __ldg(reinterpret_cast<const float4*>(src + row * C + 16 * sub) + q) : make_float4(0.f, 0.f, 0.f, 0.f);
           in[4 * q] = a.x; in[4 * q + 1] = a.y; in[4 * q + 2] = a.z; in[4 * q + 3] = a.w;
         }
       }
       mbar_wait(bar(B_D3), ph);
       tc_fence_after_sync();
-      float v[32];
+      float v[16];
       {
-        uint32_t r[32];
-        tmem_ld32(tlane + D3 + 32 * half, r);
+        uint32_t r[16];
+        tmem_ld16(tlane + D3 + 16 * sub, r);
         tmem_ld_wait();
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          const float4 b4 = lds_f4(pb3 + (32 * half + 4 * q) * 4);
+        for (int q = 0; q < 4; ++q) {
+          const float4 b4 = lds_f4(pb3 + (16 * sub + 4 * q) * 4);
           v[4 * q] = __uint_as_float(r[4 * q]) + b4.x;
           v[4 * q + 1] = __uint_as_float(r[4 * q + 1]) + b4.y;
           v[4 * q + 2] = __uint_as_float(r[4 * q + 2]) + b4.z;
@@ -504,19 +534,19 @@ __global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant_
       }
       float mean = 0.f, rstd = 1.f;
       if (ln) {
-        float s = 0.f, o, o2;
+        float s = 0.f, tot, unused;
 #pragma unroll
-        for (int k = 0; k < 32; ++k) s += v[k];
-        pair_exchange(tlane, ST_A, half, quad, s, 0.f, o, o2);
-        mean = (s + o) * (1.0f / C);
+        for (int k = 0; k < 16; ++k) s += v[k];
+        quad_exchange(tlane, ST_A, sub, quad, s, 0.f, tot, unused);
+        mean = tot * (1.0f / C);
         float qv = 0.f;
 #pragma unroll
-        for (int k = 0; k < 32; ++k) {
+        for (int k = 0; k < 16; ++k) {
           const float d = v[k] - mean;
           qv = fmaf(d, d, qv);
         }
-        pair_exchange(tlane, ST_B, half, quad, qv, 0.f, o, o2);
-        rstd = 1.0f / sqrtf((qv + o) * (1.0f / C) + P.eps);
+        quad_exchange(tlane, ST_B, sub, quad, qv, 0.f, tot, unused);
+        rstd = 1.0f / sqrtf(tot * (1.0f / C) + P.eps);
       }
       if (!BWD) {
         // every TMEM access of this tile is done: the next tile may start
@@ -524,8 +554,8 @@ __global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant_
         __syncwarp();
         if (lane == 0) mbar_arrive(bar(B_TILE));
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          const float4 g4 = lds_f4(pgam + (32 * half + 4 * q) * 4), b4 = lds_f4(pbet + (32 * half + 4 * q) * 4);
+        for (int q = 0; q < 4; ++q) {
+          const float4 g4 = lds_f4(pgam + (16 * sub + 4 * q) * 4), b4 = lds_f4(pbet + (16 * sub + 4 * q) * 4);
           if (ln) {
             v[4 * q] = (v[4 * q] - mean) * rstd * g4.x + b4.x;
             v[4 * q + 1] = (v[4 * q + 1] - mean) * rstd * g4.y + b4.y;
@@ -535,19 +565,19 @@ __global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant_
           v[4 * q] += in[4 * q]; v[4 * q + 1] += in[4 * q + 1]; v[4 * q + 2] += in[4 * q + 2]; v[4 * q + 3] += in[4 * q + 3];
         }
 #pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {   // two boxes of 16 fp32 columns
+        for (int hh = 0; hh < 2; ++hh) {   // two boxes of 8 fp32 columns
           stg.wait_free();
-          stg.write(reinterpret_cast<const uint32_t*>(v) + 16 * hh);
-          stg.store(&M.out, 32 * half + 16 * hh, row0);
+          stg.write(reinterpret_cast<const uint32_t*>(v) + 8 * hh);
+          stg.store(&M.out, 16 * sub + 8 * hh, row0);
         }
       } else {
         // ---- LayerNorm backward: dz3 = rstd (g - mean(g) - xhat mean(g xhat)), g = dy gamma
-        float dz[32];
+        float dz[16];
         if (ln) {
-          float s1 = 0.f, s2 = 0.f, o1, o2;
+          float s1 = 0.f, s2 = 0.f, t1, t2;
 #pragma unroll
-          for (int q = 0; q < 8; ++q) {
-            const float4 g4 = lds_f4(pgam + (32 * half + 4 * q) * 4);
+          for (int q = 0; q < 4; ++q) {
+            const float4 g4 = lds_f4(pgam + (16 * sub + 4 * q) * 4);
             const float gg[4] = {g4.x, g4.y, g4.z, g4.w};
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
@@ -560,27 +590,27 @@ __global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant_
               v[k] = xh;
             }
           }
-          pair_exchange(tlane, ST_C, half, quad, s1, s2, o1, o2);
-          s1 = (s1 + o1) * (1.0f / C);
-          s2 = (s2 + o2) * (1.0f / C);
+          quad_exchange(tlane, ST_C, sub, quad, s1, s2, t1, t2);
+          s1 = t1 * (1.0f / C);
+          s2 = t2 * (1.0f / C);
 #pragma unroll
-          for (int k = 0; k < 32; ++k) {
+          for (int k = 0; k < 16; ++k) {
             dz[k] = rstd * (dz[k] - s1 - v[k] * s2);
             v[k] *= in[k];           // dy * xhat: dgamma
           }
-          csg += colsum32(v, lane);
+          csg += colsum16(v, lane);
         } else {
 #pragma unroll
-          for (int k = 0; k < 32; ++k) dz[k] = in[k];
+          for (int k = 0; k < 16; ++k) dz[k] = in[k];
         }
-        uint32_t p[16];
+        uint32_t p[8];
 #pragma unroll
-        for (int k = 0; k < 16; ++k) p[k] = pack_bf16(dz[2 * k], dz[2 * k + 1]);
-        tmem_st16(tlane + DZ3 + 16 * half, p);
+        for (int k = 0; k < 8; ++k) p[k] = pack_bf16(dz[2 * k], dz[2 * k + 1]);
+        tmem_st8(tlane + DZ3 + 8 * sub, p);
         stg.wait_free();
         stg.write(p);
-        stg.store(&M.dz3, 32 * half, row0);
-        if (ln) csb += colsum32(in, lane);
+        stg.store(&M.dz3, 16 * sub, row0);
+        if (ln) csb += colsum16(in, lane);
         tmem_st_wait();
         tc_fence_before_sync();
         __syncwarp();
@@ -588,15 +618,15 @@ __global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant_
         // ---- dZ2 = dH2 * gelu'(Z2), dZ1 = dH1 * gelu'(Z1)
         mbar_wait(bar(B_D4), ph);
         tc_fence_after_sync();
-        hidden_epi<2>(tlane, D4, DZ2, half, quad, lane, bar(B_DZ2), 0, stg, &M.dz2, row0, scr + 8192);
+        hidden_epi<2>(tlane, D4, DZ2, sub, quad, lane, bar(B_DZ2), 0, stg, &M.dz2, row0, scr + 4096);
         mbar_wait(bar(B_D5), ph);
         tc_fence_after_sync();
-        hidden_epi<2>(tlane, D5, DZ1, half, quad, lane, bar(B_DZ1), 0, stg, &M.dz1, row0, scr);
+        hidden_epi<2>(tlane, D5, DZ1, sub, quad, lane, bar(B_DZ1), 0, stg, &M.dz1, row0, scr);
         // ---- dS
         mbar_wait(bar(B_D6), ph);
         tc_fence_after_sync();
-        uint32_t r[32];
-        tmem_ld32(tlane + D6 + 32 * half, r);
+        uint32_t r[16];
+        tmem_ld16(tlane + D6 + 16 * sub, r);
         tmem_ld_wait();
         tc_fence_before_sync();
         __syncwarp();
@@ -604,16 +634,14 @@ __global__ void __launch_bounds__(kThreads, 1) ff3_kernel(const __grid_constant_
 #pragma unroll
         for (int hh = 0; hh < 2; ++hh) {
           stg.wait_free();
-          stg.write(r + 16 * hh);
-          stg.store(&M.out, 32 * half + 16 * hh, row0);
+          stg.write(r + 8 * hh);
+          stg.store(&M.out, 16 * sub + 8 * hh, row0);
         }
       }
     }
-    if (BWD) {
-      if (ln) {
-        atomicAdd(P.dgamma + 32 * half + lane, csg);
-        atomicAdd(P.dbeta + 32 * half + lane, csb);
-      }
+    if (BWD && ln && lane < 16) {
+      atomicAdd(P.dgamma + 16 * sub + lane, csg);
+      atomicAdd(P.dbeta + 16 * sub + lane, csb);
     }
     if (lane == 0) bulk_wait0();   // the staging box must outlive the bulk stores that read it
     __syncwarp();
@@ -877,15 +905,15 @@ static bool bf16_map(CUtensorMap* m, const void* base, long long T, int cols) {
              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-// [T][cols] row-major (elem_bytes per element), boxes of 32 rows x 64 bytes, 64B swizzle: the epilogue warps' staging boxes
+// [T][cols] row-major (elem_bytes per element), boxes of 32 rows x 32 bytes, 32B swizzle: the epilogue warps' staging boxes
 static bool stage_map(CUtensorMap* m, const void* base, long long T, int cols, int elem_bytes) {
   EncodeTiledFn enc = encode_fn();
   if (!enc) return false;
   const cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)T};
   const cuuint64_t gstr[1] = {(cuuint64_t)cols * elem_bytes};
-  const cuuint32_t box[2] = {(cuuint32_t)(64 / elem_bytes), 32}, estr[2] = {1, 1};
+  const cuuint32_t box[2] = {(cuuint32_t)(32 / elem_bytes), 32}, estr[2] = {1, 1};
   return enc(m, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), gdim,
-             gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+             gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
