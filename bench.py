@@ -1,20 +1,31 @@
 #!/usr/bin/env python
 """Benchmark of the spectral-convolution hot path: fwd + RelativeL2 + bwd samples/s of the FNO / F-FNO models.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload ffno2d_ns256|fno1d_burgers1024|ffno1d_ks512|fno2d_ns{64,128,256}]
-                  [--precision fp32|3xtf32|tf32] [--impl reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME|all] [--precision fp32|3xtf32|tf32|bf16]
+                  [--impl reference] [--no-variants] [--no-kernels] [--no-cpu-baseline] [--no-e2e] [--no-graph]
 
-Prints ONE JSON line (rank 0).  `value` is whole-job samples/s with the inputs resident in HBM; `e2e` is the same
-step driven from pinned host buffers (H2D of x and y, D2H of the loss every step).  `--impl reference` times the
-CPU restatement of the reference (oracle/reference_port.py; the reference is Python and cannot travel to the GPU
-box) on the host cores with the same config/metric.  Multi-GPU (torchrun): batch-sharded weak scaling, one flat
-NCCL all-reduce of the gradients inside the timed step.
+Prints ONE JSON line (rank 0).
+  value        whole-job samples/s with the inputs resident in HBM (CUDA-event timing, max over ranks)
+  e2e          the same step driven from pinned host buffers (H2D of x and y, D2H of the loss every step)
+  roofline     the dominant kernel of the step, timed IN SITU (torch.profiler / CUPTI over one eager step joined with the
+               library's launch trace for the shapes): algorithmic FLOPs (or bytes) of its launches / their summed duration
+  roofline_step  the whole step against the measured peaks (algorithmic FLOPs of SURVEY 8d / step time, and the HBM floor)
+  kernels      the in-situ table (name, shape, launches, average duration, share); the shares sum to ~1
+  variants     the same workload under the other precision variants (each with its stated, tested model-level tolerance)
+  cpu_baseline the oracle port of the reference (oracle/reference_port.py; the reference is Python and cannot travel to the
+               GPU box) on the host cores at the SAME batch, with a check of this run's loss against the oracle's loss
+`--impl reference` times that CPU arm alone with the same config / metric.  Multi-GPU (torchrun): batch-sharded weak
+scaling, one flat NCCL all-reduce of the gradients inside the timed step.
 """
 from __future__ import annotations
 
 import argparse
+import collections
+import ctypes
+import gc
 import json
 import os
+import re
 import statistics
 import subprocess
 import sys
@@ -52,18 +63,23 @@ WORKLOADS = {
                         ctor=dict(in_channels=1, out_channels=1, modes1=12, modes2=12, width=32), hyper=dict(activation="gelu", n_blocks=4)),
 }
 DEFAULT = "ffno2d_ns256"
+# stated model-level tolerances (relative L2 per tensor vs the fp64 oracle: outputs, gradients), tests/test_gpu_baseline_configs.py
+TOLERANCE = {"fp32": (1e-5, 1e-5), "3xtf32": (1e-5, 1e-5), "tf32": (5e-3, 1.5e-2), "bf16": (1e-2, 4e-2)}
+# tensor peak of a variant relative to the measured dense BF16 peak: kind::tf32 UMMA issues at half the kind::f16 rate,
+# 3xTF32 issues three UMMAs per credited product
+VARIANT_DIV = {"bf16": 1.0, "tf32": 2.0, "3xtf32": 6.0}
 
 
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
         d = json.load(open(p))
-        return dict(hbm=d["hbm_gbs"], tensor=d["bf16_tflops_sustained"], tensor_burst=d["bf16_tflops"], src="measured")
-    return dict(hbm=6650.0, tensor=1400.0, tensor_burst=1590.0, src="fallback")
+        return dict(hbm=d["hbm_gbs"], tensor=d["bf16_tflops_sustained"], tensor_burst=d["bf16_tflops"], src="measured (MEASURED_PEAKS.json)")
+    return dict(hbm=6650.0, tensor=1400.0, tensor_burst=1590.0, src="fallback (B200_PROFILING.md)")
 
 
 def synth_fields(batch, shape, seed):
-    """Band-limited Gaussian random fields, standardised (SURVEY §8d): NS-like (4 pi^2 |k|^2 + 49)^-1.25 in 2-D,
+    """Band-limited Gaussian random fields, standardised (SURVEY 8d): NS-like (4 pi^2 |k|^2 + 49)^-1.25 in 2-D,
     exp(-(k/32)^2) (KS) / k^-1 (Burgers) in 1-D.  Built on the CPU with a seeded generator."""
     g = torch.Generator().manual_seed(seed)
     out = []
@@ -128,20 +144,24 @@ class ClockSampler:
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def run_reference(args, wl, name):
-    """CPU arm: the oracle port of the reference on the host cores, one bounded sample (1 field) per step."""
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return
+# ------------------------------------------------------------------------------------------------------------ CPU arm
+def _oracle_setup(wl):
     from oracle import reference_port as rp
     import resolution_pde_b200 as R
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     torch.manual_seed(0)
-    model = getattr(R, wl["kind"])(**wl["ctor"])            # parameters only (reference initialisers' shapes); never run
+    model = getattr(R, wl["kind"])(**wl["ctor"])            # parameters only (the reference initialisers' shapes); never run
     sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
-    sample_batch = 1 if len(wl["shape"]) == 3 else 4
-    x, y = synth_fields(sample_batch, wl["shape"], 1234)
+    x, y = synth_fields(wl["batch"], wl["shape"], 1234)     # the GPU arm's rank-0 batch: same fields, same weights
+    return rp, sd, x, y, cores
+
+
+def run_reference(args, wl, name):
+    """CPU arm: the oracle port of the reference on all host cores, every step the workload's full per-GPU batch."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    rp, sd, x, y, cores = _oracle_setup(wl)
     times = []
     for i in range(args.warmup + args.steps):
         t0 = time.perf_counter()
@@ -150,29 +170,22 @@ def run_reference(args, wl, name):
         if i >= args.warmup:
             times.append(dt)
     total = sum(times)
-    value = sample_batch * len(times) / total
+    B = wl["batch"]
+    value = B * len(times) / total
     line = {"impl": "reference", "metric": "fwd+bwd samples/s", "value": value, "unit": "samples/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": name, "model": wl["kind"], "per_gpu_batch": wl["batch"], "grid": list(wl["shape"][1:]),
-                       "sample": f"{sample_batch} field(s) per step"},
+            "config": {"workload": name, "model": wl["kind"], "per_gpu_batch": B, "global_batch": B, "grid": list(wl["shape"][1:]),
+                       "step": "zero_grad + forward + RelativeL2 + backward"},
             "cpu_baseline": {"value": value, "unit": "samples/s", "cores": cores, "kind": "port",
-                             "sample": f"{len(times)} step(s) of {sample_batch} field(s), torch {torch.__version__} CPU, {cores} threads"},
+                             "sample": f"{len(times)} step(s) of the full batch of {B} field(s), oracle port of the reference, torch {torch.__version__} CPU, {cores} threads"},
             "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
 
 def cpu_baseline(wl, budget_s=25.0):
-    from oracle import reference_port as rp
-    import resolution_pde_b200 as R
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    torch.manual_seed(0)
-    model = getattr(R, wl["kind"])(**wl["ctor"])
-    sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
-    nb = 1 if len(wl["shape"]) == 3 else 4
-    x, y = synth_fields(nb, wl["shape"], 1234)
-    rp.step_loss_and_grads(wl["kind"], sd, x, y, dtype=torch.float32, **wl["hyper"])  # warm-up
+    rp, sd, x, y, cores = _oracle_setup(wl)
+    _, loss, _ = rp.step_loss_and_grads(wl["kind"], sd, x, y, dtype=torch.float32, **wl["hyper"])  # warm-up
     t0, n = time.perf_counter(), 0
     while True:
         rp.step_loss_and_grads(wl["kind"], sd, x, y, dtype=torch.float32, **wl["hyper"])
@@ -180,49 +193,119 @@ def cpu_baseline(wl, budget_s=25.0):
         el = time.perf_counter() - t0
         if el > budget_s or n >= 20:
             break
-    return {"value": nb * n / el, "unit": "samples/s", "cores": cores, "kind": "port",
-            "sample": f"{n} fwd+bwd step(s) of {nb} field(s) ({el:.1f} s), oracle port of the reference, torch CPU {cores} threads"}
+    B = wl["batch"]
+    return {"value": B * n / el, "unit": "samples/s", "cores": cores, "kind": "port", "loss": float(loss),
+            "sample": f"{n} fwd+bwd step(s) of the full batch of {B} field(s) ({el:.1f} s), oracle port of the reference, torch CPU {cores} threads"}
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default=DEFAULT, choices=sorted(WORKLOADS))
-    ap.add_argument("--precision", default=os.environ.get("RPDE_PRECISION", "auto"))
-    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch override")
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--no-graph", action="store_true", help="launch every op eagerly instead of replaying the captured step")
-    args = ap.parse_args()
-    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
-    name = args.workload
-    wl = dict(WORKLOADS[name])
-    if args.batch:
-        wl["flops"] *= args.batch / wl["batch"]
-        wl["bytes"] *= args.batch / wl["batch"]
-        wl["batch"] = args.batch
-    if args.impl == "reference":
-        return run_reference(args, wl, name)
+# ------------------------------------------------------------------------------------------------------------ GPU arm
+def _short(name):
+    name = re.sub(r"^void ", "", name)
+    name = name.replace("rpde::", "").replace("tc::", "").replace("ff::", "")
+    m = re.match(r"([A-Za-z0-9_:]+(?:<[^>(]*>)?)", name)
+    return (m.group(1) if m else name)[:60]
 
+
+def insitu_kernels(step_fn, lib, T_rows):
+    """One eager step under torch.profiler (CUPTI kernel records, no serialisation) joined with the library's launch trace:
+    per (kernel, shape) launches, summed duration and algorithmic FLOPs."""
+    from torch.profiler import ProfilerActivity, profile
+    for _ in range(2):
+        step_fn()
+    torch.cuda.synchronize()
+    lib.rpde_trace_enable(1)
+    with profile(activities=[ProfilerActivity.CUDA]) as prof:
+        step_fn()
+        torch.cuda.synchronize()
+    n = lib.rpde_trace_count()
+    buf = (ctypes.c_longlong * 8)()
+    trace = []
+    for i in range(n):
+        lib.rpde_trace_get(i, buf)
+        trace.append(tuple(buf))
+    lib.rpde_trace_enable(0)
+    evs = sorted((e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA), key=lambda e: e.time_range.start)
+    gemm_evs = [e for e in evs if "gemm_tc_kernel" in e.name or "gemm_simt_kernel" in e.name]
+    joined = len(gemm_evs) == len(trace)
+    ti = 0
+    agg = collections.OrderedDict()
+    total = 0.0
+    for e in evs:
+        nm, shape, flops = _short(e.name), "", 0.0
+        if e in gemm_evs and joined:
+            M, N, K, b, sk, eng, fl, _ = trace[ti]
+            ti += 1
+            shape = f"M={M} N={N} K={K} b={b}" + (f" sk={sk}" if sk > 1 else "")
+            flops = 2.0 * M * N * K * b
+        elif "ff3_kernel" in e.name:
+            shape, flops = f"T={T_rows} C=64 H=256", 2.0 * T_rows * (64 * 256 + 256 * 256 + 256 * 64)   # fwd: 3 layers; bwd: the dgrad chain
+        elif "ff_wgrad_kernel<0>" in e.name or "ff_wgrad_kernel<(int)0>" in e.name:
+            shape, flops = f"T={T_rows} dW2", 2.0 * T_rows * 256 * 256
+        elif "ff_wgrad_kernel" in e.name:
+            shape, flops = f"T={T_rows} dW1,dW3", 2.0 * T_rows * 2 * 64 * 256
+        a = agg.setdefault((nm, shape), [0, 0.0, 0.0])
+        a[0] += 1
+        a[1] += e.device_time
+        a[2] += flops
+        total += e.device_time
+    rows = [{"name": k[0], "shape": k[1], "n": v[0], "avg_us": v[1] / v[0], "total_ms": v[1] / 1e3, "share": v[1] / total,
+             "tflops": (v[2] / (v[1] * 1e-6) / 1e12) if v[2] else None} for k, v in agg.items()]
+    rows.sort(key=lambda r: -r["total_ms"])
+    return rows, total / 1e3, len(evs), joined
+
+
+def ncu_traffic(kernel_name, shape, prec):
+    """DRAM bytes per launch of a kernel from the committed ncu --set full summaries (profiles/r2_ncu_traffic.json), or None"""
+    p = os.path.join(ROOT, "profiles", "r2_ncu_traffic.json")
+    if not os.path.exists(p):
+        return None, None
+    for rec in json.load(open(p)):
+        if rec["kernel"] in kernel_name and rec.get("precision", prec) == prec and rec.get("shape", shape) == shape:
+            return rec["dram_bytes_per_launch"], rec["source"]
+    return None, None
+
+
+def measure_tf32_peak(dev):
+    """torch.matmul 8192^3 with allow_tf32 (cuBLAS), best of 10 and a 2 s back-to-back loop"""
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        a, b = torch.randn(8192, 8192, device=dev), torch.randn(8192, 8192, device=dev)
+        for _ in range(3):
+            a @ b
+        best = 1e9
+        for _ in range(10):
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            a @ b
+            e.record()
+            torch.cuda.synchronize()
+            best = min(best, s.elapsed_time(e))
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n, t0 = 0, time.perf_counter()
+        s.record()
+        while time.perf_counter() - t0 < 2.0:
+            for _ in range(20):
+                a @ b
+            n += 20
+            torch.cuda.synchronize()
+        e.record()
+        torch.cuda.synchronize()
+        fl = 2.0 * 8192 ** 3
+        return {"tf32_tflops_burst": fl / (best * 1e-3) / 1e12, "tf32_tflops_sustained": fl * n / (s.elapsed_time(e) * 1e-3) / 1e12,
+                "how": "torch.matmul fp32 8192^3 with allow_tf32=True (cuBLAS): best of 10, and back to back for 2 s"}
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old
+
+
+def run_workload(name, wl, args, prec, dev, world, rank, local, full):
+    """Times one workload under one precision.  full: also e2e, clocks, in-situ kernels."""
     import torch.distributed as dist
     import resolution_pde_b200 as R
     from resolution_pde_b200.distributed import GradBucket
+    from resolution_pde_b200.training import GraphedTrainStep
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    prec = args.precision
-    if prec == "auto":
-        prec = "3xtf32" if R._lib.load().rpde_set_precision(1) == 0 else "fp32"
     R.set_precision(prec)
-
     torch.manual_seed(0)                                   # identical weights on every rank
     model = getattr(R, wl["kind"])(**wl["ctor"]).to(dev)
     loss_fn = R.RelativeL2Loss()
@@ -234,14 +317,21 @@ def main():
     lib = R._lib.load()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev) if wl["bytes"] / 4 < 200e6 else None
 
-    from resolution_pde_b200.training import GraphedTrainStep
     gstep = None if args.no_graph else GraphedTrainStep(model, loss_fn)
     launches_per_step = None
     if gstep is not None:
         c0 = lib.rpde_launch_count()
         gstep(xd, yd)                                       # warm-up + capture (one captured step = one count)
         launches_per_step = (lib.rpde_launch_count() - c0) // (gstep.warmup + 1)
-        xd, yd = gstep.static_inputs(xd.shape, yd.shape)    # device-resident arm feeds the graph's own buffers
+        xs, ys = gstep.static_inputs(xd.shape, yd.shape)    # device-resident arm feeds the graph's own buffers
+    else:
+        xs, ys = xd, yd
+
+    def eager_step():
+        model.zero_grad(set_to_none=True)
+        loss = loss_fn(model(xd), yd)
+        loss.backward()
+        return loss
 
     def step(x, y):
         if gstep is not None:
@@ -267,47 +357,50 @@ def main():
                 else:
                     last = step(xh.to(dev, non_blocking=True), yh.to(dev, non_blocking=True)).item()
             else:
-                last = step(xd, yd)
+                last = step(xs, ys)
             e.record()
         torch.cuda.synchronize()
         return sum(s.elapsed_time(e) for s, e in ev), last
 
     for _ in range(args.warmup):
-        step(xd, yd)
+        step(xs, ys)
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     sampler = ClockSampler(local)
-    if rank == 0:
+    if rank == 0 and full:
         sampler.start()
-    l0 = lib.rpde_launch_count() if hasattr(lib, "rpde_launch_count") else 0
+    l0 = lib.rpde_launch_count()
     ms, loss = timed(args.steps, False)
-    launches = (lib.rpde_launch_count() - l0) if hasattr(lib, "rpde_launch_count") else None
+    launches = lib.rpde_launch_count() - l0
     if launches_per_step is not None:
         launches = launches_per_step * args.steps           # replayed graph nodes (counted once, at capture)
     loss_val = float(loss.detach()) if torch.is_tensor(loss) else float(loss)
     extra = 0
-    if rank == 0 and world == 1 and ms < 1500.0:
-        # nvidia-smi samples every 100 ms: a timed region of a few ms would yield none.  Keep the same step running
-        # (untimed) under the sampler until 1.5 s of load have been observed, and say so.
-        t_end = time.perf_counter() + 1.5 - ms / 1e3
-        while time.perf_counter() < t_end:
-            step(xd, yd)
-            extra += 1
-            if extra % 16 == 0:
-                torch.cuda.synchronize()
-        torch.cuda.synchronize()
-    clocks = sampler.stop() if rank == 0 else None
-    if clocks is not None and extra:
-        clocks["note"] = (f"timed region {ms:.1f} ms is short against the 100 ms sampling period: sampled over it and over {extra} "
-                          "untimed repetitions of the same step right after it (1.5 s of load in total)")
+    clocks = None
+    if rank == 0 and full:
+        if world == 1 and ms < 1500.0:
+            # nvidia-smi samples every 100 ms: a timed region of a few ms would yield none.  Keep the same step running
+            # (untimed) under the sampler until 1.5 s of load have been observed, and say so.
+            t_end = time.perf_counter() + 1.5 - ms / 1e3
+            while time.perf_counter() < t_end:
+                step(xs, ys)
+                extra += 1
+                if extra % 16 == 0:
+                    torch.cuda.synchronize()
+            torch.cuda.synchronize()
+        clocks = sampler.stop()
+        if extra:
+            clocks["note"] = (f"timed region {ms:.1f} ms is short against the 100 ms sampling period: sampled over it and over {extra} "
+                              "untimed repetitions of the same step right after it (1.5 s of load in total)")
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.barrier()
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = t.item()
-    e2e = None
-    if not args.no_e2e:
+    res = {"ms": ms, "loss": loss_val, "launches": launches, "clocks": clocks, "B": B, "grad_bytes": bucket.nbytes,
+           "flush": flush is not None, "graph": gstep is not None}
+    if full and not args.no_e2e:
         timed(1, True)
         if world > 1:
             dist.barrier()
@@ -315,61 +408,160 @@ def main():
         t = torch.tensor([ms_e], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e = {"value": world * B * args.steps / (t.item() / 1e3), "unit": "samples/s",
-               "h2d_bytes_per_step": int(xh.numel() * 4 + yh.numel() * 4), "d2h_bytes_per_step": 4}
+        res["e2e"] = {"value": world * B * args.steps / (t.item() / 1e3), "unit": "samples/s",
+                      "h2d_bytes_per_step": int(xh.numel() * 4 + yh.numel() * 4), "d2h_bytes_per_step": 4}
+    if full and rank == 0 and not args.no_kernels:
+        T_rows = B * int(torch.tensor(wl["shape"][1:]).prod())
+        try:
+            res["kernels"] = insitu_kernels(eager_step, lib, T_rows)
+        except Exception as ex:  # the profiler is diagnostics: never lose the timing line over it
+            res["kernels_error"] = repr(ex)
+    del gstep, model, bucket, flush
+    gc.collect()
+    torch.cuda.empty_cache()
+    return res
 
-    # dominant kernel, timed alone with CUDA events: the FeedForward hidden GEMM (F-FNO) / the block synthesis GEMM (FNO)
-    pk = peaks()
+
+def make_line(name, wl, args, prec, world, r, pk, full):
+    B = r["B"]
+    step_s = r["ms"] / args.steps * 1e-3
+    line = {"metric": "fwd+bwd samples/s", "value": world * B / step_s, "unit": "samples/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": {"bf16": "bf16 (FeedForward) / tf32", "tf32": "tf32", "3xtf32": "f32 (3xTF32)"}.get(prec, "f32"),
+            "data": "synthetic",
+            "config": {"workload": name, "model": wl["kind"], "per_gpu_batch": B, "global_batch": B * world,
+                       "grid": list(wl["shape"][1:]), "precision_engine": prec,
+                       "tolerance": {"outputs": TOLERANCE[prec][0], "gradients": TOLERANCE[prec][1],
+                                     "what": "relative L2 per tensor vs the fp64 oracle, tests/test_gpu_baseline_configs.py"},
+                       "parallelism": f"dp{world}",
+                       "l2": "L2 flushed between timed steps" if r["flush"] else "working set >> L2 (no flush)",
+                       "step": "zero_grad + forward + RelativeL2 + backward" + (" + flat NCCL grad all-reduce" if world > 1 else ""),
+                       "launch": "CUDA graph replay (one graph per input shape)" if r["graph"] else "eager",
+                       "grad_bytes": r["grad_bytes"]},
+            "loss": r["loss"], "gpu_launches": r["launches"]}
+    vdiv = VARIANT_DIV.get(prec)
+    rs = {"flops_achieved_tflops": wl["flops"] / step_s / 1e12, "tensor_peak_tflops": pk["tensor"],
+          "frac_tensor": wl["flops"] / step_s / 1e12 / pk["tensor"],
+          "hbm_achieved_gbs": wl["bytes"] / step_s / 1e9, "hbm_peak_gbs": pk["hbm"], "frac_hbm": wl["bytes"] / step_s / 1e9 / pk["hbm"],
+          "bound": wl["bound"], "peak_source": pk["src"] + ", sustained bf16",
+          "note": "algorithmic FLOPs (dense truncated-DFT formulation, SURVEY 8d) and ideal-fusion floor bytes of the whole fwd+bwd step / step time"}
+    if vdiv:
+        rs["frac_variant_peak"] = wl["flops"] / step_s / 1e12 / (pk["tensor"] / vdiv)
+        rs["variant_peak_tflops"] = pk["tensor"] / vdiv
+    rs["frac"] = rs["frac_tensor"] if wl["bound"] == "tensor" else rs["frac_hbm"]
+    line["roofline_step"] = rs
+    if not full:
+        return line
+    line["clocks"] = r["clocks"]
+    line["e2e"] = r.get("e2e")
     roof = None
-    if rank == 0:
+    if "kernels" in r:
+        rows, tot_ms, nk, joined = r["kernels"]
+        line["kernels"] = {"source": "torch.profiler (CUPTI) over one eager step + rpde_trace shapes" + ("" if joined else " (trace length mismatch: shapes omitted)"),
+                           "launches": nk, "sum_ms": tot_ms,
+                           "top": [{k: (round(v, 4) if isinstance(v, float) else v) for k, v in row.items()} for row in rows[:12]]}
+        top = rows[0]
+        if wl["bound"] == "tensor" and top["tflops"]:
+            traffic, src = ncu_traffic(top["name"], top["shape"], prec)
+            roof = {"bound": "tensor", "achieved": top["tflops"], "peak": pk["tensor"], "unit": "TFLOP/s", "frac": top["tflops"] / pk["tensor"],
+                    "traffic": traffic, "traffic_source": src,
+                    "kernel": f"{top['name']} {top['shape']}", "launches_per_step": top["n"], "avg_us_in_situ": top["avg_us"],
+                    "share_of_step": top["share"], "peak_source": pk["src"] + ", sustained bf16 (kernel timed inside the step)",
+                    "how": "algorithmic FLOPs of the kernel's launches in one step / their summed in-situ duration"}
+            if vdiv:
+                roof["frac_variant_peak"] = top["tflops"] / (pk["tensor"] / vdiv)
+    if roof is None:
         if wl["bound"] == "tensor":
-            T = B * int(torch.tensor(wl["shape"][1:]).prod())
-            d = wl["ctor"]["width"] * wl["ctor"]["factor"]
-            a = torch.randn(T, d, device=dev)
-            w = torch.randn(d, d, device=dev)
-            for _ in range(2):
-                R.ops.matmul(a, w, False, True)
-            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            s.record()
-            reps = 5
-            for _ in range(reps):
-                R.ops.matmul(a, w, False, True)
-            e.record()
-            torch.cuda.synchronize()
-            kms = s.elapsed_time(e) / reps
-            ach = 2.0 * T * d * d / (kms * 1e-3) / 1e12
-            # DRAM bytes per launch of this kernel from the ncu --set full capture (profiles/r1f_ncu_full_ffgemm_3xtf32.csv:
-            # dram__bytes_read.sum + dram__bytes_write.sum); only known for the captured shape / engine
-            traffic = 2.1020e9 if (name == "ffno2d_ns256" and B == 16 and prec == "3xtf32") else None
-            vdiv = {"3xtf32": 6.0, "tf32": 2.0}.get(prec)
-            roof = {"bound": "tensor", "achieved": ach, "peak": pk["tensor_burst"], "unit": "TFLOP/s", "frac": ach / pk["tensor_burst"],
-                    "traffic": traffic, "kernel": f"contraction engine ({prec}), FeedForward hidden GEMM {T}x{d}x{d}", "kernel_ms": kms,
-                    "algorithmic_bytes": 4.0 * (2 * T * d + d * d), "hbm_frac": 4.0 * (2 * T * d + d * d) / (kms * 1e-3) / 1e9 / pk["hbm"],
-                    "peak_variant": ({"engine": prec, "peak": pk["tensor_burst"] / vdiv, "frac": ach / (pk["tensor_burst"] / vdiv),
-                                      "note": "kind::tf32 UMMA runs at half the bf16 rate; 3xTF32 issues three UMMAs per credited product"}
-                                     if vdiv else None),
-                    "peak_source": pk["src"] + " bf16 burst (kernel timed alone)",
-                    "step": {"achieved": wl["flops"] / (ms / args.steps * 1e-3) / 1e12, "peak": pk["tensor"], "unit": "TFLOP/s",
-                             "frac": wl["flops"] / (ms / args.steps * 1e-3) / 1e12 / pk["tensor"],
-                             "hbm_frac": wl["bytes"] / (ms / args.steps * 1e-3) / 1e9 / pk["hbm"],
-                             "note": "algorithmic FLOPs (dense truncated-DFT formulation) of the whole fwd+bwd step / step time, vs sustained bf16"}}
+            roof = {"bound": "tensor", "achieved": rs["flops_achieved_tflops"], "peak": pk["tensor"], "unit": "TFLOP/s", "frac": rs["frac_tensor"],
+                    "traffic": None, "kernel": "whole fwd+bwd step (no in-situ table)", "peak_source": pk["src"]}
         else:
-            ach = wl["bytes"] / (ms / args.steps * 1e-3) / 1e9
-            roof = {"bound": "hbm", "achieved": ach, "peak": pk["hbm"], "unit": "GB/s", "frac": ach / pk["hbm"], "traffic": None,
-                    "kernel": "whole fwd+bwd step (ideal-fusion floor bytes / step time)", "peak_source": pk["src"]}
+            roof = {"bound": "hbm", "achieved": rs["hbm_achieved_gbs"], "peak": pk["hbm"], "unit": "GB/s", "frac": rs["frac_hbm"], "traffic": None,
+                    "kernel": "whole fwd+bwd step (ideal-fusion floor bytes / step time): launch-bound, no single dominant kernel",
+                    "peak_source": pk["src"]}
+    roof["step_frac"] = rs["frac"]
+    line["roofline"] = roof
+    return line
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=DEFAULT, choices=sorted(WORKLOADS) + ["all"])
+    ap.add_argument("--precision", default=os.environ.get("RPDE_PRECISION", "auto"))
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch override")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-variants", action="store_true", help="skip the tf32 / bf16 variant timings of the same workload")
+    ap.add_argument("--no-kernels", action="store_true", help="skip the in-situ kernel table (torch.profiler pass)")
+    ap.add_argument("--no-graph", action="store_true", help="launch every op eagerly instead of replaying the captured step")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    name = DEFAULT if args.workload == "all" else args.workload
+    wl = dict(WORKLOADS[name])
+    if args.batch:
+        wl["flops"] *= args.batch / wl["batch"]
+        wl["bytes"] *= args.batch / wl["batch"]
+        wl["batch"] = args.batch
+    if args.impl == "reference":
+        return run_reference(args, wl, name)
+
+    import torch.distributed as dist
+    import resolution_pde_b200 as R
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    prec = args.precision
+    if prec == "auto":
+        prec = "3xtf32" if R._lib.load().rpde_set_precision(1) == 0 else "fp32"
+    pk = peaks()
+
+    r = run_workload(name, wl, args, prec, dev, world, rank, local, full=True)
+    line = make_line(name, wl, args, prec, world, r, pk, full=True) if rank == 0 else None
+
+    # the other precision variants of the same workload (same steps / warm-up; their own stated tolerances)
+    if not args.no_variants and world == 1:
+        variants = {}
+        for vp in ("tf32", "bf16"):
+            if vp == prec:
+                continue
+            rv = run_workload(name, wl, args, vp, dev, world, rank, local, full=False)
+            lv = make_line(name, wl, args, vp, world, rv, pk, full=False)
+            variants[vp] = {"value": lv["value"], "ms_per_step": lv["ms_per_step"], "loss": lv["loss"], "gpu_launches": lv["gpu_launches"],
+                            "tolerance": lv["config"]["tolerance"], "roofline_step": lv["roofline_step"], "dtype": lv["dtype"]}
+        line["variants"] = variants
+    if args.workload == "all" and world == 1:
+        extra = []
+        for other in sorted(WORKLOADS):
+            if other == name:
+                continue
+            wo = dict(WORKLOADS[other])
+            ro = run_workload(other, wo, args, prec, dev, world, rank, local, full=False)
+            extra.append(make_line(other, wo, args, prec, world, ro, pk, full=False))
+        line["extra"] = extra
+    if rank == 0 and world == 1 and wl["bound"] == "tensor" and not args.no_variants:
+        try:
+            line["peaks_measured_in_run"] = measure_tf32_peak(dev)
+        except Exception as ex:
+            line["peaks_measured_in_run"] = {"error": repr(ex)}
     if rank == 0:
-        line = {"metric": "fwd+bwd samples/s", "value": world * B * args.steps / (ms / 1e3), "unit": "samples/s", "n_gpus": world,
-                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": name, "model": wl["kind"], "per_gpu_batch": B, "global_batch": B * world,
-                           "grid": list(wl["shape"][1:]), "precision_engine": prec, "parallelism": f"dp{world}",
-                           "l2": "L2 flushed between timed steps" if flush is not None else "working set >> L2 (no flush)",
-                           "step": "zero_grad + forward + RelativeL2 + backward" + (" + flat NCCL grad all-reduce" if world > 1 else ""),
-                           "launch": "eager" if gstep is None else "CUDA graph replay (one graph per input shape)",
-                           "grad_bytes": bucket.nbytes},
-                "loss": loss_val, "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roof}
         if not args.no_cpu_baseline and world == 1:
-            line["cpu_baseline"] = cpu_baseline(wl)
+            cb = cpu_baseline(wl)
+            tol = TOLERANCE[prec][0]
+            err = abs(line["loss"] - cb["loss"])
+            line["loss_check"] = {"oracle_loss_fp32_cpu": cb["loss"], "abs_err": err, "tolerance": tol * max(1.0, abs(cb["loss"])),
+                                  "ok": bool(err < tol * max(1.0, abs(cb["loss"]))),
+                                  "what": "this run's loss vs the oracle's loss on the same batch and weights"}
+            if not line["loss_check"]["ok"]:
+                print(f"bench.py: LOSS CHECK FAILED: {line['loss']} vs oracle {cb['loss']}", file=sys.stderr)
+            line["cpu_baseline"] = cb
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -56,6 +56,13 @@ unsigned long long rpde_tc_launch_count(void);
  * cannot hide as a slowdown. */
 unsigned long long rpde_simt_launch_count(void);
 
+/* Launch trace (bench.py's in-situ kernel table): while enabled, every contraction records {M, N, K, batch, split-K,
+ * engine (0 CUDA-core FMA, 1 tcgen05), epilogue flags (1 beta, 2 act, 4 dact, 8 Z, 16 colsum, 32 bias), 0} in launch order.
+ * rpde_trace_enable(on) clears the list.  Host-side bookkeeping only; nothing is recorded while it is off. */
+int rpde_trace_enable(int on);
+int rpde_trace_count(void);
+int rpde_trace_get(int i, long long* out8);
+
 /* Twiddle / truncated-DFT tables, generated on the device in fp64 and rounded once to fp32.
  * Replaces the cuFFT/pocketfft plans behind torch.fft.rfft/irfft/rfft2/irfft2
  * (models/spectral_convolution.py:41,54,82,97,165,198,265,284,289,308).

@@ -28,6 +28,9 @@ SIGNATURES = {
     "rpde_launch_count": (ctypes.c_ulonglong, []),
     "rpde_tc_launch_count": (ctypes.c_ulonglong, []),
     "rpde_simt_launch_count": (ctypes.c_ulonglong, []),
+    "rpde_trace_enable": (I, [I]),
+    "rpde_trace_count": (I, []),
+    "rpde_trace_get": (I, [I, P]),
     "rpde_dft_table": (I, [P, I, I, I, I, c_double, S]),
     "rpde_spectral1d_workspace_bytes": (Z, [I, I, I, I, I]),
     "rpde_spectral1d_fwd": (I, [P, P, P, P, P, P, P, I, I, I, I, I, I, I, P, Z, S]),

@@ -7,6 +7,8 @@
 #include <string.h>
 #include <stdint.h>
 #include <atomic>
+#include <mutex>
+#include <vector>
 
 #include "../../include/rpde_b200.h"
 #include "internal.h"
@@ -42,6 +44,21 @@ static std::atomic<unsigned long long> g_simt_launches{0};  // contractions that
     RPDE_CUDA(cudaGetLastError()); \
   } while (0)
 
+// Optional launch trace (rpde_trace_*): shape and engine of every contraction in launch order, so that a profiler's kernel
+// list (names only) can be joined with the shapes.  Off by default; a mutex-protected host vector, touched only when enabled.
+struct TraceRec {
+  long long v[8];   // M, N, K, batch, split-K, engine (0 CUDA-core, 1 tcgen05), epilogue flags, 0
+};
+static std::mutex g_trace_mu;
+static std::vector<TraceRec> g_trace;
+static std::atomic<int> g_trace_on{0};
+static void trace_gemm(const GemmP& p, int engine) {
+  if (!g_trace_on.load(std::memory_order_relaxed)) return;
+  const long long flags = (p.beta ? 1 : 0) | (p.act ? 2 : 0) | (p.dact ? 4 : 0) | (p.Z ? 8 : 0) | (p.colsum ? 16 : 0) | (p.bias_mode ? 32 : 0);
+  std::lock_guard<std::mutex> lk(g_trace_mu);
+  g_trace.push_back(TraceRec{{p.M, p.N, p.K, p.batch, p.splitk, engine, flags, 0}});
+}
+
 static cudaError_t gemm(const GemmP& p, cudaStream_t s) {
   if (p.M > 0 && p.N > 0 && p.batch > 0) g_launches.fetch_add(1);
 #ifdef RPDE_WITH_TC
@@ -51,6 +68,7 @@ static cudaError_t gemm(const GemmP& p, cudaStream_t s) {
     if (rc != cudaSuccess) return rc;
     if (launched) {
       g_tc_launches.fetch_add(1);
+      trace_gemm(p, 1);
       return cudaSuccess;
     }
   }
@@ -59,7 +77,10 @@ static cudaError_t gemm(const GemmP& p, cudaStream_t s) {
     static const bool log = getenv("RPDE_TC_DBG") && atoi(getenv("RPDE_TC_DBG")) == 9;
     if (log) fprintf(stderr, "[rpde simt] M=%d N=%d K=%d batch=%d splitk=%d\n", p.M, p.N, p.K, p.batch, p.splitk);
   }
-  if (p.M > 0 && p.N > 0 && p.batch > 0) g_simt_launches.fetch_add(1);
+  if (p.M > 0 && p.N > 0 && p.batch > 0) {
+    g_simt_launches.fetch_add(1);
+    trace_gemm(p, 0);
+  }
   return gemm_simt_launch(p, s);
 }
 
@@ -97,6 +118,22 @@ int rpde_get_precision(void) { return g_prec; }
 unsigned long long rpde_launch_count(void) { return g_launches.load(); }
 unsigned long long rpde_tc_launch_count(void) { return g_tc_launches.load(); }
 unsigned long long rpde_simt_launch_count(void) { return g_simt_launches.load(); }
+int rpde_trace_enable(int on) {
+  std::lock_guard<std::mutex> lk(g_trace_mu);
+  g_trace.clear();
+  g_trace_on.store(on ? 1 : 0);
+  return RPDE_OK;
+}
+int rpde_trace_count(void) {
+  std::lock_guard<std::mutex> lk(g_trace_mu);
+  return (int)g_trace.size();
+}
+int rpde_trace_get(int i, long long* out8) {
+  std::lock_guard<std::mutex> lk(g_trace_mu);
+  if (!out8 || i < 0 || i >= (int)g_trace.size()) return fail(RPDE_E_INVALID, "rpde_trace_get: bad index%s");
+  for (int k = 0; k < 8; ++k) out8[k] = g_trace[i].v[k];
+  return RPDE_OK;
+}
 
 // ------------------------------------------------------------------------------------------------
 int rpde_dft_table(float* out, int kind, int n, int k, int m1, double scale, rpde_stream_t stream) {
