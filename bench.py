@@ -317,7 +317,8 @@ def run_workload(name, wl, args, prec, dev, world, rank, local, full):
     lib = R._lib.load()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev) if wl["bytes"] / 4 < 200e6 else None
 
-    gstep = None if args.no_graph else GraphedTrainStep(model, loss_fn)
+    in_graph_reduce = world > 1 and not args.no_graph and os.environ.get("RPDE_BENCH_EAGER_ALLREDUCE", "0") == "0"
+    gstep = None if args.no_graph else GraphedTrainStep(model, loss_fn, bucket=bucket if in_graph_reduce else None)
     launches_per_step = None
     if gstep is not None:
         c0 = lib.rpde_launch_count()
@@ -340,7 +341,7 @@ def run_workload(name, wl, args, prec, dev, world, rank, local, full):
             model.zero_grad(set_to_none=True)
             loss = loss_fn(model(x), y)
             loss.backward()
-        if world > 1:
+        if world > 1 and not in_graph_reduce:
             bucket.allreduce_mean()
         return loss
 
@@ -399,7 +400,7 @@ def run_workload(name, wl, args, prec, dev, world, rank, local, full):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = t.item()
     res = {"ms": ms, "loss": loss_val, "launches": launches, "clocks": clocks, "B": B, "grad_bytes": bucket.nbytes,
-           "flush": flush is not None, "graph": gstep is not None}
+           "flush": flush is not None, "graph": gstep is not None, "in_graph_reduce": in_graph_reduce}
     if full and not args.no_e2e:
         timed(1, True)
         if world > 1:
@@ -435,7 +436,8 @@ def make_line(name, wl, args, prec, world, r, pk, full):
                                      "what": "relative L2 per tensor vs the fp64 oracle, tests/test_gpu_baseline_configs.py"},
                        "parallelism": f"dp{world}",
                        "l2": "L2 flushed between timed steps" if r["flush"] else "working set >> L2 (no flush)",
-                       "step": "zero_grad + forward + RelativeL2 + backward" + (" + flat NCCL grad all-reduce" if world > 1 else ""),
+                       "step": "zero_grad + forward + RelativeL2 + backward" + (
+                           (" + flat NCCL grad all-reduce" + (" (captured in the step graph)" if r.get("in_graph_reduce") else " (eager)")) if world > 1 else ""),
                        "launch": "CUDA graph replay (one graph per input shape)" if r["graph"] else "eager",
                        "grad_bytes": r["grad_bytes"]},
             "loss": r["loss"], "gpu_launches": r["launches"]}

@@ -21,15 +21,28 @@ import torch
 class GraphedTrainStep:
     """step(x, y) -> loss (0-dim device tensor).  x, y may live on the device or in pinned host memory."""
 
-    def __init__(self, model: torch.nn.Module, loss_fn: Callable, warmup: int = 2, optimizer=None):
+    def __init__(self, model: torch.nn.Module, loss_fn: Callable, warmup: int = 2, optimizer=None, bucket=None,
+                 max_graphs: int = 16):
         """optimizer: an optional `optim.FusedAdamW`; its update is then captured too (a second graph replayed right
         after the first: its device table needs the gradient pointers the first capture creates) and `step(x, y)`
-        becomes zero_grad + forward + loss + backward + AdamW with no host work besides the two replays."""
+        becomes zero_grad + forward + loss + backward + AdamW with no host work besides the two replays.
+        bucket: an optional `distributed.GradBucket`; when a process group with more than one rank is initialised its
+        pack -> NCCL all-reduce -> scaled unpack is captured INTO the step's graph right after the backward pass, so the
+        data-parallel step is still one replay with no eager tail (the collective is enqueued by the graph on the
+        capture stream; every rank replays the same sequence).
+        max_graphs: ragged tail batches of a resolution-grouped epoch (train/mres_training.py:108-128) create one extra
+        graph per (shape, batch) pair; the least recently used graph is dropped beyond this bound."""
         self.model = model
         self.loss_fn = loss_fn
         self.warmup = warmup
         self.optimizer = optimizer
+        self.bucket = bucket
+        self.max_graphs = max_graphs
         self._graphs: Dict[Tuple, Tuple] = {}
+
+    def _reduce(self):
+        if self.bucket is not None:
+            self.bucket.allreduce_mean()
 
     def _capture(self, x: torch.Tensor, y: torch.Tensor):
         dev = next(self.model.parameters()).device
@@ -43,6 +56,7 @@ class GraphedTrainStep:
             for _ in range(self.warmup):
                 self.model.zero_grad(set_to_none=True)
                 self.loss_fn(self.model(sx), sy).backward()
+                self._reduce()
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
         self.model.zero_grad(set_to_none=True)  # grads are (re)created inside the capture, in the graph's pool
@@ -50,6 +64,7 @@ class GraphedTrainStep:
         with torch.cuda.graph(g):
             loss = self.loss_fn(self.model(sx), sy)
             loss.backward()
+            self._reduce()
         # the gradient tensors written by this graph (its pool owns them); re-attached to the parameters after a replay
         params = [q for q in self.model.parameters() if q.grad is not None]
         grads = [q.grad for q in params]
@@ -64,18 +79,21 @@ class GraphedTrainStep:
 
     def __call__(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
         key = (tuple(x.shape), tuple(y.shape))
-        ent = self._graphs.get(key)
+        ent = self._graphs.pop(key, None)
         if ent is None:
+            while len(self._graphs) >= self.max_graphs:        # bounded cache: drop the least recently used graph
+                self._graphs.pop(next(iter(self._graphs)))
             ent = self._capture(x, y)
-            self._graphs[key] = ent
+        self._graphs[key] = ent                                 # (re)insert as most recently used
         g, sx, sy, loss, params, grads, g_opt = ent
         if x.data_ptr() != sx.data_ptr():
             sx.copy_(x, non_blocking=True)
         if y.data_ptr() != sy.data_ptr():
             sy.copy_(y, non_blocking=True)
         g.replay()
-        for q, gr in zip(params, grads):
-            q.grad = gr
+        if params and (params[0].grad is not grads[0] or params[-1].grad is not grads[-1]):
+            for q, gr in zip(params, grads):   # only after a zero_grad(set_to_none=True) or a switch between graphs
+                q.grad = gr
         if g_opt is not None:
             self.optimizer.sync_lr()
             g_opt.replay()
