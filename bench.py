@@ -417,6 +417,8 @@ def run_workload(name, wl, args, prec, dev, world, rank, local, full):
             res["kernels"] = insitu_kernels(eager_step, lib, T_rows)
         except Exception as ex:  # the profiler is diagnostics: never lose the timing line over it
             res["kernels_error"] = repr(ex)
+    if gstep is not None:
+        gstep.release()     # captured NCCL kernels must be gone before the process group is destroyed
     del gstep, model, bucket, flush
     gc.collect()
     torch.cuda.empty_cache()

@@ -99,6 +99,16 @@ class GraphedTrainStep:
             g_opt.replay()
         return loss
 
+    def release(self) -> None:
+        """Drops every captured graph (and the memory pools they own).  With a `bucket` the graphs hold captured NCCL
+        kernels: call this BEFORE torch.distributed.destroy_process_group() -- tearing the communicator down under a
+        live graph blocks (measured on B200 / NCCL 2.28, tools/dp_check.py)."""
+        self._graphs.clear()
+        import gc
+        gc.collect()
+        if torch.cuda.is_available():
+            torch.cuda.synchronize()
+
     def static_inputs(self, x_shape, y_shape) -> Optional[Tuple[torch.Tensor, torch.Tensor]]:
         ent = self._graphs.get((tuple(x_shape), tuple(y_shape)))
         return (ent[1], ent[2]) if ent else None

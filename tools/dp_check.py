@@ -51,5 +51,15 @@ loss_fn(model(x.to(dev)), y.to(dev)).backward()
 torch.cuda.synchronize()
 worst = max(((got[k] - p.grad).norm() / p.grad.norm().clamp_min(1e-30)).item() for k, p in model.named_parameters() if p.grad.abs().max() > 1e-8)
 log(f"mode={mode} case={case} engine={engine} worst relative gradient difference vs one-rank global batch: {worst:.3e}")
+t = torch.ones(1, device=dev)
+dist.all_reduce(t)
+torch.cuda.synchronize()
+log("eager collective after the replays ok", t.item())
+if mode == "graph":
+    step.release()
+    log("graph released")
 dist.barrier()
+torch.cuda.synchronize()
+log("barrier ok")
 dist.destroy_process_group()
+log("process group destroyed")
