@@ -62,6 +62,12 @@ WORKLOADS = {
     "fno2d_ns256": dict(kind="FNO2d", batch=16, shape=(1, 256, 256), bound="hbm", flops=99.3e9, bytes=2.71e9,
                         ctor=dict(in_channels=1, out_channels=1, modes1=12, modes2=12, width=32), hyper=dict(activation="gelu", n_blocks=4)),
 }
+# BASELINE.json configs[3] as it is meant: ONE run over a true multi-resolution mix, batches grouped by resolution the way
+# ResolutionGroupedDataLoader does (train/mres_training.py:75-131), ragged tail included.  Per GPU and "step" (= one pass):
+# 48 fields at 64^2, 32 at 128^2, 24 at 256^2, batch 16 -> batches of 16,16,16 / 16,16 / 16,8.
+MIX = dict(kind="FNO2d", batch=16, groups=((64, 48), (128, 32), (256, 24)),
+           ctor=dict(in_channels=1, out_channels=1, modes1=12, modes2=12, width=32), hyper=dict(activation="gelu", n_blocks=4),
+           bytes_per_sample={64: 169e6 / 16, 128: 677e6 / 16, 256: 2.71e9 / 16}, flops_per_sample={64: 7.99e9 / 16, 128: 27.0e9 / 16, 256: 99.3e9 / 16})
 DEFAULT = "ffno2d_ns256"
 # stated model-level tolerances (relative L2 per tensor vs the fp64 oracle: outputs, gradients), tests/test_gpu_baseline_configs.py
 TOLERANCE = {"fp32": (1e-5, 1e-5), "3xtf32": (1e-5, 1e-5), "tf32": (5e-3, 1.5e-2), "bf16": (1e-2, 4e-2)}
@@ -425,6 +431,110 @@ def run_workload(name, wl, args, prec, dev, world, rank, local, full):
     return res
 
 
+def mix_dataset(rank, scale=1.0):
+    data = []
+    for n, cnt in MIX["groups"]:
+        x, y = synth_fields(max(1, int(cnt * scale)), (1, n, n), 4321 + n + 1000 * rank)
+        data += [(x[i], y[i]) for i in range(x.shape[0])]
+    return data
+
+
+def run_mix(args, prec, dev, world, rank):
+    """one pass over the mixed-resolution set per step, every batch through GraphedTrainStep (one graph per (shape, batch))"""
+    import torch.distributed as dist
+    import resolution_pde_b200 as R
+    from resolution_pde_b200.distributed import GradBucket
+    R.set_precision(prec)
+    torch.manual_seed(0)
+    model = R.FNO2d(**MIX["ctor"]).to(dev)
+    loss_fn = R.RelativeL2Loss()
+    batches = list(R.ResolutionGroupedBatches(mix_dataset(rank), MIX["batch"], shuffle=False, device=dev))
+    bucket = GradBucket(model.parameters())
+    step = R.GraphedTrainStep(model, loss_fn, bucket=bucket if world > 1 else None)
+    lib = R._lib.load()
+
+    def epoch():
+        tot = None
+        for x, y in batches:
+            l = step(x, y)
+            tot = l if tot is None else tot + l
+        return tot
+
+    l0 = lib.rpde_launch_count()
+    epoch()
+    per_epoch = (lib.rpde_launch_count() - l0) // (step.warmup + 1)
+    for _ in range(max(args.warmup - 1, 0)):
+        epoch()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(args.steps):
+        tot = epoch()
+    e.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([s.elapsed_time(e)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.barrier()
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = t.item()
+    n_samples = sum(c for _, c in MIX["groups"])
+    nbytes = sum(MIX["bytes_per_sample"][n] * c for n, c in MIX["groups"])
+    loss = float(tot) / len(batches)
+    step.release()
+    if rank != 0:
+        return None
+    pk = peaks()
+    step_s = ms / args.steps * 1e-3
+    ach = nbytes / step_s / 1e9
+    return {"metric": "fwd+bwd samples/s", "value": world * n_samples / step_s, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32 (3xTF32)" if prec == "3xtf32" else prec, "data": "synthetic",
+            "config": {"workload": "fno2d_ns_mix", "model": "FNO2d", "per_gpu_batch": MIX["batch"], "precision_engine": prec,
+                       "mix": {str(n): c for n, c in MIX["groups"]}, "batches_per_step": [int(x.shape[0]) for x, _ in batches],
+                       "step": "one pass over the resolution-grouped mix: zero_grad + forward + RelativeL2 + backward per batch"
+                               + (" + flat NCCL grad all-reduce in the graph" if world > 1 else ""),
+                       "launch": "CUDA graph replay, one graph per (resolution, batch size) pair", "parallelism": f"dp{world}"},
+            "loss": loss, "gpu_launches": per_epoch * args.steps,
+            "roofline": {"bound": "hbm", "achieved": ach, "peak": pk["hbm"], "unit": "GB/s", "frac": ach / pk["hbm"], "traffic": None,
+                         "kernel": "whole pass (ideal-fusion floor bytes of every sample / time): launch-bound", "peak_source": pk["src"]}}
+
+
+def run_reference_mix(args):
+    """CPU arm of the mix: the oracle port over resolution-grouped batches, a bounded sample (4 fields per resolution) per step"""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    from oracle import mres_port, reference_port as rp
+    import resolution_pde_b200 as R
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    torch.manual_seed(0)
+    model = R.FNO2d(**MIX["ctor"])
+    sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    data = []
+    for n, _ in MIX["groups"]:
+        x, y = synth_fields(4, (1, n, n), 4321 + n)
+        data += [(x[i], y[i]) for i in range(4)]
+    batches = mres_port.grouped_batches(data, MIX["batch"])
+    times = []
+    for i in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        for x, y in batches:
+            rp.step_loss_and_grads("FNO2d", sd, x, y, dtype=torch.float32, **MIX["hyper"])
+        if i >= args.warmup:
+            times.append(time.perf_counter() - t0)
+    value = len(data) * len(times) / sum(times)
+    print(json.dumps({"impl": "reference", "metric": "fwd+bwd samples/s", "value": value, "unit": "samples/s", "n_gpus": args.gpus,
+                      "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(times) / len(times), "higher_is_better": True,
+                      "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                      "config": {"workload": "fno2d_ns_mix", "model": "FNO2d", "per_gpu_batch": MIX["batch"],
+                                 "mix": {str(n): c for n, c in MIX["groups"]}},
+                      "cpu_baseline": {"value": value, "unit": "samples/s", "cores": cores, "kind": "port",
+                                       "sample": f"{len(times)} pass(es) over 4 fields per resolution (64^2, 128^2, 256^2), grouped by resolution, oracle port, torch CPU {cores} threads"},
+                      "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
 def make_line(name, wl, args, prec, world, r, pk, full):
     B = r["B"]
     step_s = r["ms"] / args.steps * 1e-3
@@ -493,7 +603,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default=DEFAULT, choices=sorted(WORKLOADS) + ["all"])
+    ap.add_argument("--workload", default=DEFAULT, choices=sorted(WORKLOADS) + ["fno2d_ns_mix", "all"])
     ap.add_argument("--precision", default=os.environ.get("RPDE_PRECISION", "auto"))
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch override")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -503,7 +613,9 @@ def main():
     ap.add_argument("--no-graph", action="store_true", help="launch every op eagerly instead of replaying the captured step")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
-    name = DEFAULT if args.workload == "all" else args.workload
+    if args.workload == "fno2d_ns_mix" and args.impl == "reference":
+        return run_reference_mix(args)
+    name = DEFAULT if args.workload in ("all", "fno2d_ns_mix") else args.workload
     wl = dict(WORKLOADS[name])
     if args.batch:
         wl["flops"] *= args.batch / wl["batch"]
@@ -526,6 +638,13 @@ def main():
     if prec == "auto":
         prec = "3xtf32" if R._lib.load().rpde_set_precision(1) == 0 else "fp32"
     pk = peaks()
+    if args.workload == "fno2d_ns_mix":
+        line = run_mix(args, prec, dev, world, rank)
+        if rank == 0:
+            print(json.dumps(line))
+        if world > 1:
+            dist.destroy_process_group()
+        return
 
     r = run_workload(name, wl, args, prec, dev, world, rank, local, full=True)
     line = make_line(name, wl, args, prec, world, r, pk, full=True) if rank == 0 else None
@@ -549,6 +668,7 @@ def main():
             wo = dict(WORKLOADS[other])
             ro = run_workload(other, wo, args, prec, dev, world, rank, local, full=False)
             extra.append(make_line(other, wo, args, prec, world, ro, pk, full=False))
+        extra.append(run_mix(args, prec, dev, world, rank))
         line["extra"] = extra
     if rank == 0 and world == 1 and wl["bound"] == "tensor" and not args.no_variants:
         try:

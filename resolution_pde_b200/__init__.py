@@ -12,7 +12,7 @@ from .fno import FNO1d, FNO2d
 from .fno_blocks import FNOBlock1d, FNOBlock2d, MLP1d, MLP2d
 from .loss import RelativeL2Loss
 from .ops import get_precision, set_precision
-from .training import GraphedTrainStep
+from .training import GraphedTrainStep, ResolutionGroupedBatches
 from .optim import FusedAdamW
 from .rollout import RolloutEvaluator, SimpleNormalizer, evaluate_rollout, perform_rollout_1d, perform_rollout_2d, rollout_losses
 from .spectral_convolution import FSpectralConv1d, FSpectralConv2d, SpectralConv1d, SpectralConv2d
@@ -20,6 +20,6 @@ from .spectral_convolution import FSpectralConv1d, FSpectralConv2d, SpectralConv
 __all__ = [
     "SpectralConv1d", "SpectralConv2d", "FSpectralConv1d", "FSpectralConv2d", "FNOBlock1d", "FNOBlock2d", "MLP1d",
     "MLP2d", "FNO1d", "FNO2d", "FFNO1D", "FFNO2D", "FeedForward", "WNLinear", "Linear", "RelativeL2Loss",
-    "set_precision", "get_precision", "ops", "GraphedTrainStep", "FusedAdamW", "RolloutEvaluator", "SimpleNormalizer",
+    "set_precision", "get_precision", "ops", "GraphedTrainStep", "ResolutionGroupedBatches", "FusedAdamW", "RolloutEvaluator", "SimpleNormalizer",
     "evaluate_rollout", "perform_rollout_1d", "perform_rollout_2d", "rollout_losses",
 ]

@@ -112,3 +112,66 @@ class GraphedTrainStep:
     def static_inputs(self, x_shape, y_shape) -> Optional[Tuple[torch.Tensor, torch.Tensor]]:
         ent = self._graphs.get((tuple(x_shape), tuple(y_shape)))
         return (ent[1], ent[2]) if ent else None
+
+
+class ResolutionGroupedBatches:
+    """Device-resident counterpart of the reference's ResolutionGroupedDataLoader (train/mres_training.py:75-131; SURVEY
+    section 8f rank 1).  Same grouping rule (the samples' LAST dimension, :87-90), same batches (consecutive runs of
+    `batch_size` inside a group, ragged tail kept), same order (groups in order of first appearance, then
+    `random.shuffle` of the batch list when shuffle=True, :108-128) -- but every group is stacked ONCE into one device
+    tensor, so an epoch does no per-step collation or H2D copy: a batch is a view of the group's tensor.
+
+    rank / world: the data-parallel split of SURVEY section 8e -- every rank iterates the SAME batch sequence (same resolution
+    in the same step) and takes its `shard_batch` slice of each batch; `weights()` gives the per-batch (local, global)
+    sample counts for the weighted gradient all-reduce of ragged shards."""
+
+    def __init__(self, dataset, batch_size: int, shuffle: bool = True, device=None, rank: int = 0, world: int = 1):
+        from collections import OrderedDict
+        from .distributed import shard_batch
+        self.batch_size, self.shuffle, self.rank, self.world = batch_size, shuffle, rank, world
+        groups = OrderedDict()
+        for i in range(len(dataset)):
+            x, y = dataset[i]
+            groups.setdefault(int(x.shape[-1]), []).append((x, y))
+        self.groups = OrderedDict()
+        for res, items in groups.items():
+            gx = torch.stack([torch.as_tensor(a) for a, _ in items]).to(device=device, dtype=torch.float32)
+            gy = torch.stack([torch.as_tensor(b) for _, b in items]).to(device=device, dtype=torch.float32)
+            self.groups[res] = (gx, gy)
+        self._shard = shard_batch
+
+    def _plan(self):
+        import random
+        plan = []
+        for res, (gx, _) in self.groups.items():
+            n = gx.shape[0]
+            perm = torch.randperm(n).tolist() if self.shuffle else None     # DataLoader(shuffle=True) inside each group
+            for i in range(0, n, self.batch_size):
+                plan.append((res, i, min(n, i + self.batch_size), perm))
+        if self.shuffle:
+            random.shuffle(plan)
+        return plan
+
+    def __iter__(self):
+        for res, lo, hi, perm in self._plan():
+            gx, gy = self.groups[res]
+            a, b = self._shard(hi - lo, self.rank, self.world)
+            if perm is None:
+                yield gx[lo + a:lo + b], gy[lo + a:lo + b]
+            else:
+                idx = torch.as_tensor(perm[lo + a:lo + b], device=gx.device, dtype=torch.long)
+                yield gx.index_select(0, idx), gy.index_select(0, idx)
+
+    def weights(self):
+        """(local, global) sample counts of every batch of one UNSHUFFLED pass, for GradBucket.allreduce_mean(weight=...)"""
+        out = []
+        for res, (gx, _) in self.groups.items():
+            n = gx.shape[0]
+            for i in range(0, n, self.batch_size):
+                g = min(n, i + self.batch_size) - i
+                a, b = self._shard(g, self.rank, self.world)
+                out.append((b - a, g))
+        return out
+
+    def __len__(self):
+        return sum((gx.shape[0] + self.batch_size - 1) // self.batch_size for gx, _ in self.groups.values())
