@@ -481,7 +481,7 @@ def run_mix(args, prec, dev, world, rank):
     ms = t.item()
     n_samples = sum(c for _, c in MIX["groups"])
     nbytes = sum(MIX["bytes_per_sample"][n] * c for n, c in MIX["groups"])
-    loss = float(tot) / len(batches)
+    loss = float(tot.detach()) / len(batches)
     step.release()
     if rank != 0:
         return None
