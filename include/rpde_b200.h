@@ -218,6 +218,20 @@ int rpde_rollout_loss(const float* preds, const float* truth, float* acc, float*
                       long long truth_batch_stride, long long truth_step_stride, float y_scale, float y_mean,
                       int decode, rpde_stream_t stream);
 
+/* ---- data preparation that is not a contraction -------------------------------------------------
+ * rpde_moments_accumulate: acc3 = {count, sum, sum of squares} (fp64, zero-initialised by the caller) += over n floats;
+ * rpde_moments_finalize: mean_std = {mean, unbiased std} as torch's .mean() / .std() -- the reference's global normaliser
+ * statistics, which it computes from a Python list of every scalar (dataloaders/ks_naive_markov.py:377-390,
+ * dataloaders/ns_naive_true_multires.py:513-525).
+ * rpde_stride_downsample: y[o][i][j][c] = x[o][i*fh][j*fw][c] (x: outer x H x W x C, y: outer x ceil(H/fh) x ceil(W/fw) x C),
+ * the naive down-sampling data[:, :, ::f, ::f, :] of dataloaders/ns_naive_true_multires.py:363-366 (1-D: H = fh = 1).
+ * rpde_binned_sums_f64: out[r][b] = sum_j p[r][j] [bin[j] == b] in fp64 (radial-band totals of utils/frequency_error.py:115-150;
+ * bin = -1 selects nothing). */
+int rpde_moments_accumulate(const float* x, long long n, double* acc3, rpde_stream_t stream);
+int rpde_moments_finalize(const double* acc3, float* mean_std, rpde_stream_t stream);
+int rpde_stride_downsample(const float* x, float* y, long long outer, int H, int W, int C, int fh, int fw, rpde_stream_t stream);
+int rpde_binned_sums_f64(const double* p, const int* bin, double* out, int rows, int nbins, long long n, rpde_stream_t stream);
+
 /* ---- fused multi-tensor AdamW (torch.optim.AdamW as the reference builds it: main_1d.py:144, main_2d.py:173;
  * SURVEY 8f rank 1).  table: device array of ntensors records {float* p; const float* g; float* m; float* v;
  * int64 n; int64 chunk0} (48 bytes each; chunk0 = index of the tensor's first 1024-element chunk, ascending);

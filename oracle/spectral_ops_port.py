@@ -121,3 +121,23 @@ def decompose_error_by_frequency_2d(y_hat: torch.Tensor, y: torch.Tensor, num_ra
         err[i] = torch.norm(sh - st).item()
         mag[i] = torch.norm(st).item()
     return err, mag, (edges[:-1] + edges[1:]) / 2
+
+
+def global_mean_std(samples):
+    """dataloaders/ks_naive_markov.py:377-390 (= ns_naive_true_multires.py:513-525), transcribed: every value of every sample
+    goes through a Python list into one float32 tensor; mean() and the unbiased std() of that tensor.  (Inline code of a
+    dataloader factory that needs h5py files: not importable, hence transcribed rather than called.)"""
+    values = []
+    for t in samples:
+        values.extend(t.flatten().tolist())
+    v = torch.tensor(values)
+    return float(v.mean()), float(v.std())
+
+
+def stride_downsample(x, factor: int, spatial_dims: int = 2, channels_last: bool = False):
+    """dataloaders/ns_naive_true_multires.py:363-366: data[:, :, ::f, ::f, :] (and x[..., ::f] in the 1-D loaders)"""
+    sl = [slice(None)] * x.dim()
+    last = x.dim() - (1 if channels_last else 0)
+    for d in range(last - spatial_dims, last):
+        sl[d] = slice(None, None, factor)
+    return x[tuple(sl)]

@@ -62,6 +62,10 @@ SIGNATURES = {
     "rpde_rel_l2_bwd": (I, [P, P, P, P, P, I, L, I, S]),
     "rpde_rollout_renorm": (I, [P, P, P, I, L, L, L, c_float, c_float, c_float, c_float, I, S]),
     "rpde_rollout_loss": (I, [P, P, P, P, P, I, I, L, L, L, L, L, c_float, c_float, I, S]),
+    "rpde_moments_accumulate": (I, [P, L, P, S]),
+    "rpde_moments_finalize": (I, [P, P, S]),
+    "rpde_stride_downsample": (I, [P, P, L, I, I, I, I, I, S]),
+    "rpde_binned_sums_f64": (I, [P, P, P, I, I, L, S]),
     "rpde_adamw_step": (I, [P, I, L, P, c_double, c_double, c_float, c_float, S]),
     "rpde_ff3_weight_image_bytes": (Z, []),
     "rpde_ff3_supported": (I, [I, I]),

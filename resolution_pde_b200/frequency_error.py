@@ -16,7 +16,7 @@ from __future__ import annotations
 import numpy as np
 import torch
 
-from . import ops
+from . import _lib, ops
 
 _masks = {}
 
@@ -46,7 +46,8 @@ def decompose_error_by_frequency_1d(y_hat: torch.Tensor, y: torch.Tensor, num_mo
     return out[0], out[1], freqs[:k]
 
 
-def _radial_masks(H: int, W: int, bins: int, device):
+def _radial_bins(H: int, W: int, bins: int, device):
+    """bin index of every (ky, kx) point of the half spectrum, -1 where the reference's masks select nothing"""
     key = (H, W, bins, str(device))
     m = _masks.get(key)
     if m is None:
@@ -55,7 +56,10 @@ def _radial_masks(H: int, W: int, bins: int, device):
         fx = torch.fft.rfftfreq(W).view(1, -1)
         radial = torch.sqrt(fy ** 2 + fx ** 2)
         edges = np.linspace(0, 0.5, bins + 1)
-        m = torch.stack([((radial >= edges[i]) & (radial < edges[i + 1])).reshape(-1) for i in range(bins)]).double().to(device)
+        idx = torch.full(radial.shape, -1, dtype=torch.int32)
+        for i in range(bins):
+            idx[(radial >= edges[i]) & (radial < edges[i + 1])] = i
+        m = idx.reshape(-1).contiguous().to(device)
         _masks[key] = m
     return m
 
@@ -82,7 +86,12 @@ def decompose_error_by_frequency_2d(y_hat: torch.Tensor, y: torch.Tensor, num_ra
     if W % 2 == 0:
         w[-1] = 1.0
     power = (power * w / (H * W)).permute(1, 0, 2).reshape(2, H * kx)               # (which, (ky, kx)); row j is ky in fft order
-    bins = _radial_masks(H, W, int(num_radial_bins), dev)                            # (bins, H*kx)
-    out = (power @ bins.t()).sqrt().cpu().numpy()
+    bins = _radial_bins(H, W, int(num_radial_bins), dev)                             # (H*kx,) band index of every mode
+    power = power.contiguous()
+    sums = torch.empty((2, int(num_radial_bins)), dtype=torch.float64, device=dev)
+    with ops._Ctx(power) as c:                                                       # band totals: one library kernel (fp64)
+        _lib.check(c.lib.rpde_binned_sums_f64(power.data_ptr(), bins.data_ptr(), sums.data_ptr(), 2, int(num_radial_bins),
+                                              power.shape[1], c.stream), "rpde_binned_sums_f64")
+    out = sums.sqrt().cpu().numpy()
     edges = np.linspace(0, 0.5, int(num_radial_bins) + 1)
     return out[0], out[1], (edges[:-1] + edges[1:]) / 2

@@ -12,12 +12,14 @@ shapes follow the reference; inputs must be CUDA fp32 tensors (no CPU fallback).
     resize_1d(x, out_size)                     utils/res_utils.py:93-125
     resize(x, out_size, permute=False)         utils/res_utils.py:29-50
     downsample_1d(u, N), downsample(u, N)      utils/res_utils.py:62-91, 19-27 (scipy on numpy there; CUDA tensors here)
+    stride_downsample(x, factor, dims)         dataloaders/ns_naive_true_multires.py:363-366 (data[:, :, ::f, ::f, :])
+    global_mean_std(tensors)                   dataloaders/ks_naive_markov.py:377-390, ns_naive_true_multires.py:513-525
 """
 from __future__ import annotations
 
 import torch
 
-from . import ops
+from . import _lib, ops
 
 
 def _axis_last(x2d: torch.Tensor, n_out: int, k: int, scale: float) -> torch.Tensor:
@@ -204,3 +206,50 @@ def downsample(u: torch.Tensor, N: int) -> torch.Tensor:
     sign = 1.0 - 2.0 * (torch.arange(ne, device=dev) & 1).to(torch.float32)
     w -= c.view(B, 1, 1) * (sign.view(ne, 1) * sign.view(1, ne))
     return w.view(*u.shape[:-2], ne, ne)
+
+
+def stride_downsample(x: torch.Tensor, factor: int, spatial_dims: int = 2, channels_last: bool = False) -> torch.Tensor:
+    """Naive down-sampling: every `factor`-th grid point along the last `spatial_dims` axes (before a trailing channel axis
+    when channels_last), i.e. x[..., ::f, ::f] / x[..., ::f, ::f, :] as dataloaders/ns_naive_true_multires.py:363-366 and the 1-D
+    loaders' x[..., ::f] do on the host.  One strided-gather kernel on the device."""
+    _check(x)
+    if factor < 1 or spatial_dims not in (1, 2):
+        raise ValueError("stride_downsample: factor >= 1, one or two spatial axes")
+    x = x.contiguous()
+    C = x.shape[-1] if channels_last else 1
+    sp = x.shape[-spatial_dims - (1 if channels_last else 0):x.dim() - (1 if channels_last else 0)]
+    H, W = (1, sp[0]) if spatial_dims == 1 else (sp[0], sp[1])
+    lead = x.shape[:x.dim() - spatial_dims - (1 if channels_last else 0)]
+    outer = 1
+    for d in lead:
+        outer *= d
+    fh = 1 if spatial_dims == 1 else factor
+    Ho, Wo = (H + fh - 1) // fh, (W + factor - 1) // factor
+    out_sp = (Wo,) if spatial_dims == 1 else (Ho, Wo)
+    y = torch.empty(tuple(lead) + out_sp + ((C,) if channels_last else ()), dtype=torch.float32, device=x.device)
+    with ops._Ctx(x) as c:
+        _lib.check(c.lib.rpde_stride_downsample(x.data_ptr(), y.data_ptr(), outer, H, W, C, fh, factor, c.stream), "rpde_stride_downsample")
+    return y
+
+
+def global_mean_std(tensors):
+    """(mean, std) over every element of every tensor of an iterable -- the reference's 'simple global normalization'
+    statistics (it extends a Python list with x.flatten().tolist() for every sample and calls torch.tensor(...).mean() and
+    .std(), unbiased: dataloaders/ks_naive_markov.py:377-390, ns_naive_true_multires.py:513-525).  One streaming pass per tensor,
+    fp64 accumulators on the device, one host read at the end.  Tensors may differ in shape (mixed resolutions)."""
+    acc = None
+    out = None
+    for t in ([tensors] if isinstance(tensors, torch.Tensor) else tensors):
+        _check(t)
+        t = t.contiguous()
+        if acc is None:
+            acc = torch.zeros(3, dtype=torch.float64, device=t.device)
+            out = torch.empty(2, dtype=torch.float32, device=t.device)
+        with ops._Ctx(t) as c:
+            _lib.check(c.lib.rpde_moments_accumulate(t.data_ptr(), t.numel(), acc.data_ptr(), c.stream), "rpde_moments_accumulate")
+    if acc is None:
+        raise ValueError("global_mean_std: no tensors")
+    with ops._Ctx(out) as c:
+        _lib.check(c.lib.rpde_moments_finalize(acc.data_ptr(), out.data_ptr(), c.stream), "rpde_moments_finalize")
+    m, s = out.tolist()
+    return m, s
