@@ -672,7 +672,19 @@ def main():
         line["extra"] = extra
     if rank == 0 and world == 1 and wl["bound"] == "tensor" and not args.no_variants:
         try:
-            line["peaks_measured_in_run"] = measure_tf32_peak(dev)
+            pm = measure_tf32_peak(dev)
+            line["peaks_measured_in_run"] = pm
+
+            def against_measured(rs, p):
+                # the variant's tensor peak as MEASURED on this box in this run (cuBLAS TF32, sustained; a 3xTF32 product
+                # issues three TF32 UMMAs), beside the figure derived from the BF16 peak
+                div = {"tf32": 1.0, "3xtf32": 3.0}.get(p)
+                if div:
+                    rs["variant_peak_measured_tflops"] = pm["tf32_tflops_sustained"] / div
+                    rs["frac_variant_peak_measured"] = rs["flops_achieved_tflops"] / rs["variant_peak_measured_tflops"]
+            against_measured(line["roofline_step"], prec)
+            for vp, v in line.get("variants", {}).items():
+                against_measured(v["roofline_step"], vp)
         except Exception as ex:
             line["peaks_measured_in_run"] = {"error": repr(ex)}
     if rank == 0:
