@@ -41,6 +41,10 @@ SIGNATURES = {
     "rpde_spectral2d_workspace_bytes": (Z, [I, I, I, I, I, I, I]),
     "rpde_spectral2d_fwd": (I, [P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, P, Z, S]),
     "rpde_spectral2d_bwd": (I, [P, P, P, P, P, P, P, P, P, I, P, P, I, I, I, I, I, I, I, P, Z, S]),
+    "rpde_fno_block2d_supported": (I, [I, I, I, I, I, I, I]),
+    "rpde_fno_block2d_workspace_bytes": (Z, [I, I, I, I, I, I, I]),
+    "rpde_fno_block2d_fwd": (I, [P] * 12 + [I] * 8 + [P, Z, S]),
+    "rpde_fno_block2d_bwd": (I, [P, P, I] + [P] * 12 + [I] * 7 + [P, Z, S]),
     "rpde_ffno_axis_workspace_bytes": (Z, [L, I, L, I, I]),
     "rpde_ffno_axis_fwd": (I, [P, P, P, P, P, P, I, L, I, L, I, I, I, I, P, Z, S]),
     "rpde_ffno_axis_bwd": (I, [P, P, P, P, P, P, I, P, I, L, I, L, I, I, I, I, P, Z, S]),

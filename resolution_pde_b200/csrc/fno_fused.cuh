@@ -143,13 +143,16 @@ __global__ void __launch_bounds__(256) fno1d_synth_bypass_kernel(const float* __
                                                                  const float* __restrict__ fs4, const float* __restrict__ wb,
                                                                  const float* __restrict__ bb, float* __restrict__ y,
                                                                  float* __restrict__ z, int Bn, int I, int O, int N, int K,
-                                                                 int act, int adjoint) {
+                                                                 int act, int adjoint, int Hd) {
+  // Hd > 1 (FNOBlock2d, fno2d_fused.cuh): the "batch" index is an image row (b, h) of a (B, C, Hd, N) tensor, Bn = B * Hd:
+  // spectral rows are indexed by (b, h), the rows of x / y / z by ((b * C + c) * Hd + h)
   // adjoint = 1 (backward, dx = analysis adjoint of dsp + bypass dgrad): the table is the analysis table fa[(k,ri)][n] (row r
   // as is) and the bypass weight is read transposed, wb[(reduction channel)][output channel]
   constexpr int NT = TN / 16;            // consecutive grid points per thread (8 or 4)
   __shared__ __align__(16) float As[FNO_KT][FNO_OB + 4];
   __shared__ __align__(16) float Bs[FNO_KT][TN + 4];
   const int b = blockIdx.y, n0 = blockIdx.x * TN;
+  const int bh = b / Hd, hh = b - bh * Hd;
   const int tid = threadIdx.x;
   const int tn = (tid & 15) * NT;
   const int to = (tid >> 4) * 4;        // 4 consecutive output channels
@@ -183,7 +186,7 @@ __global__ void __launch_bounds__(256) fno1d_synth_bypass_kernel(const float* __
         const int r = r0 + rr, n = n0 + nn;
         const bool ok = r < RT && n < N;      // spectral rows r = (k, ro) come from the plane-major synthesis table fs4[ro][k][n]
         const float* p = r < R ? fs4 + (adjoint ? (long long)r : (long long)(r & 1) * K + (r >> 1)) * N + n
-                               : x + ((long long)b * I + (r - R)) * N + n;
+                               : x + (((long long)bh * I + (r - R)) * Hd + hh) * N + n;
         rb[j] = ok ? __ldg(p) : 0.f;
       }
 #pragma unroll
@@ -218,7 +221,7 @@ __global__ void __launch_bounds__(256) fno1d_synth_bypass_kernel(const float* __
       const int o = o0 + to + i;
       if (o >= O) continue;
       const float bias = bb ? bb[o] : 0.f;
-      const long long row = ((long long)b * O + o) * N;
+      const long long row = (((long long)bh * O + o) * Hd + hh) * N;
       if ((N & 3) == 0 && n0 + tn + NT <= N) {
         float pre[NT], out[NT];
 #pragma unroll

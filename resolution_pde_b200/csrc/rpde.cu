@@ -16,6 +16,7 @@
 #include "gemm_simt.cuh"
 #include "pointwise.cuh"
 #include "fno_fused.cuh"
+#include "fno2d_fused.cuh"
 #ifdef RPDE_WITH_TC
 #include "gemm_tc.cuh"
 #endif
@@ -223,15 +224,15 @@ int rpde_spectral1d_fwd(const float* x, const float* w, const float* fa, const f
 
 // synthesis + bypass launch shared by the fused forward and (adjoint = 1) the fused input gradient
 static int launch_fno1d_synth(const float* x, const float* om, const float* table, const float* wb, const float* bb, float* y,
-                              float* z, int B, int I, int O, int N, int modes, int act, int adjoint, cudaStream_t s) {
+                              float* z, int B, int I, int O, int N, int modes, int act, int adjoint, cudaStream_t s, int Hd = 1) {
   static const int tn_sel = getenv("RPDE_FNO_TN") ? atoi(getenv("RPDE_FNO_TN")) : 0;   // bring-up switch: 64 or 128
   const bool wide = tn_sel ? tn_sel == 128 : (long long)((N + 127) / 128) * B >= 2 * 148;   // enough 128-point tiles to fill the SMs twice
   if (wide) {
     dim3 g2((unsigned)((N + 127) / 128), (unsigned)B);
-    fno1d_synth_bypass_kernel<128><<<g2, 256, 0, s>>>(x, om, table, wb, bb, y, z, B, I, O, N, modes, act, adjoint);
+    fno1d_synth_bypass_kernel<128><<<g2, 256, 0, s>>>(x, om, table, wb, bb, y, z, B, I, O, N, modes, act, adjoint, Hd);
   } else {
     dim3 g2((unsigned)((N + 63) / 64), (unsigned)B);
-    fno1d_synth_bypass_kernel<64><<<g2, 256, 0, s>>>(x, om, table, wb, bb, y, z, B, I, O, N, modes, act, adjoint);
+    fno1d_synth_bypass_kernel<64><<<g2, 256, 0, s>>>(x, om, table, wb, bb, y, z, B, I, O, N, modes, act, adjoint, Hd);
   }
   RPDE_LAUNCH_CHECK();
   return RPDE_OK;
@@ -375,6 +376,121 @@ int rpde_fno_block1d_bwd(const float* dy, const float* z, int act, const float* 
   if (wb && B > 65535) return fail(RPDE_E_INVALID, "rpde_fno_block1d_bwd: fused input gradient is limited to B <= 65535%s");
   return spectral1d_bwd_impl(dy, z, act, fs4, dpre, wb, wb ? 1 : 0, w, fa, nullptr, spec, dx, dx_accumulate, dw, B, I, O, N,
                              modes, ws, ws_bytes, stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Fused FNOBlock2d (fno2d_fused.cuh)
+// ------------------------------------------------------------------------------------------------
+static bool fno2d_fused_ok(int B, int I, int O, int H, int W, int m1, int m2) {
+  return (long long)B * H <= 65535 && W <= 2048 && 4LL * m1 * m2 <= 1024 && (long long)B * (I > O ? I : O) * H <= 0x7fffffffLL / 4;
+}
+int rpde_fno_block2d_supported(int B, int I, int O, int H, int W, int m1, int m2) { return fno2d_fused_ok(B, I, O, H, W, m1, m2) ? 1 : 0; }
+
+size_t rpde_fno_block2d_workspace_bytes(int B, int I, int O, int H, int W, int m1, int m2) {
+  (void)W;
+  const size_t C = (size_t)(I > O ? I : O), J = 2 * (size_t)m1, Ky = m2;
+  size_t f = 0;
+  f += align_up(2 * Ky * (size_t)B * C * H * 4);   // W-axis half transform T / its adjoint
+  f += align_up((size_t)B * C * 2 * J * Ky * 4);   // mixed spectrum om / dom
+  f += align_up((size_t)B * C * 2 * J * Ky * 4);   // dspec, or the input spectrum when the caller keeps none
+  f += align_up(2 * Ky * (size_t)B * H * C * 4);   // Z: the H-axis synthesis per image row
+  return f;
+}
+
+static int launch_fno2d_rows(const float* in, const float* tab, float* out, long long planes, int H, int Ky, int A, cudaStream_t s) {
+  const size_t smem = (size_t)2 * Ky * (F2_HC + 1) * sizeof(float);
+  if (smem > 48 * 1024) RPDE_CUDA(cudaFuncSetAttribute(fno2d_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  fno2d_rows_kernel<<<(unsigned)planes, 256, smem, s>>>(in, tab, out, planes, H, Ky, A);
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+static int launch_fno2d_expand(const float* in, const float* tab, float* Z, int B, int C, int H, int Ky, int A, cudaStream_t s) {
+  dim3 g((unsigned)((H + 7) / 8), (unsigned)B);
+  if (Ky <= 4) fno2d_expand_kernel<4><<<g, 256, 0, s>>>(in, tab, Z, B, C, H, Ky, A);
+  else if (Ky <= 8) fno2d_expand_kernel<8><<<g, 256, 0, s>>>(in, tab, Z, B, C, H, Ky, A);
+  else fno2d_expand_kernel<12><<<g, 256, 0, s>>>(in, tab, Z, B, C, H, Ky, A);
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+
+int rpde_fno_block2d_fwd(const float* x, const float* w1, const float* w2, const float* fa_y, const float* fs4_y, const float* g2,
+                         const float* g3, const float* wb, const float* bb, float* spec, float* y, float* z, int B, int I, int O,
+                         int H, int W, int m1, int m2, int act, void* ws, size_t ws_bytes, rpde_stream_t stream) {
+  if (!x || !w1 || !w2 || !fa_y || !fs4_y || !g2 || !g3 || !y || B <= 0 || I <= 0 || O <= 0 || H <= 0 || W <= 0 || m1 <= 0 ||
+      m2 <= 0 || (bb && !wb))
+    return fail(RPDE_E_INVALID, "rpde_fno_block2d_fwd: bad arguments%s");
+  if (m2 > W / 2 + 1 || m1 > H) return fail(RPDE_E_MODES, "SpectralConv2d: modes exceed the available spectrum%s");
+  if (!fno2d_fused_ok(B, I, O, H, W, m1, m2))
+    return fail(RPDE_E_INVALID, "rpde_fno_block2d_fwd: shape outside the fused kernels (use rpde_conv1x1_fwd + rpde_spectral2d_fwd)%s");
+  if (!ws || ws_bytes < rpde_fno_block2d_workspace_bytes(B, I, O, H, W, m1, m2))
+    return fail(RPDE_E_WORKSPACE, "rpde_fno_block2d_fwd: workspace too small%s");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int J = 2 * m1, Ky = m2;
+  const size_t C = (size_t)(I > O ? I : O);
+  Carver cv{(char*)ws, 0, ws_bytes};
+  float* T = cv.take(2 * (size_t)Ky * B * C * H);
+  float* om = cv.take((size_t)B * C * 2 * J * Ky);
+  float* sp_ws = cv.take((size_t)B * C * 2 * J * Ky);
+  float* Z = cv.take(2 * (size_t)Ky * B * H * C);
+  if (!spec) spec = sp_ws;   // inference: the spectrum stays in the workspace
+  int rc = launch_fno1d_analysis(x, fa_y, T, B * I * H, 1, W, Ky, nullptr, 0, nullptr, 0, s);
+  if (rc) return rc;
+  rc = launch_fno2d_rows(T, g2, spec, (long long)B * I, H, Ky, 2 * J, s);
+  if (rc) return rc;
+  {
+    const long long total = (long long)B * O * J * Ky;
+    fno2d_mix_kernel<<<grid_for(total), 256, 0, s>>>(spec, w1, w2, om, B, I, O, m1, Ky, 0);
+    RPDE_LAUNCH_CHECK();
+  }
+  rc = launch_fno2d_expand(om, g3, Z, B, O, H, Ky, 2 * J, s);
+  if (rc) return rc;
+  return launch_fno1d_synth(x, Z, fs4_y, wb, bb, y, z, B * H, I, O, W, Ky, act, 0, s, H);
+}
+
+// g3t = the kind-3 table transposed to [(j,ri)][(ro,h)], g2t = the kind-2 table transposed to [(h,ri)][(j,ro)] (the adjoints of
+// steps 4 and 2).  dpre (= dy * act'(z), written when z != NULL) is what the bypass conv's parameter gradient consumes; dx
+// receives the complete input gradient (spectral adjoint + wb^T dpre when wb is given).
+int rpde_fno_block2d_bwd(const float* dy, const float* z, int act, const float* w1, const float* w2, const float* fa_y,
+                         const float* fs4_y, const float* g3t, const float* g2t, const float* spec, const float* wb, float* dpre,
+                         float* dx, float* dw1, float* dw2, int B, int I, int O, int H, int W, int m1, int m2, void* ws,
+                         size_t ws_bytes, rpde_stream_t stream) {
+  if (!dy || !w1 || !w2 || !fa_y || !fs4_y || !g3t || !g2t || !spec || B <= 0 || I <= 0 || O <= 0 || H <= 0 || W <= 0 || m1 <= 0 ||
+      m2 <= 0 || (z && !dpre) || (!z && dpre))
+    return fail(RPDE_E_INVALID, "rpde_fno_block2d_bwd: bad arguments (z and dpre come together)%s");
+  if (!fno2d_fused_ok(B, I, O, H, W, m1, m2)) return fail(RPDE_E_INVALID, "rpde_fno_block2d_bwd: shape outside the fused kernels%s");
+  if (!ws || ws_bytes < rpde_fno_block2d_workspace_bytes(B, I, O, H, W, m1, m2))
+    return fail(RPDE_E_WORKSPACE, "rpde_fno_block2d_bwd: workspace too small%s");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int J = 2 * m1, Ky = m2;
+  const size_t C = (size_t)(I > O ? I : O);
+  Carver cv{(char*)ws, 0, ws_bytes};
+  float* T = cv.take(2 * (size_t)Ky * B * C * H);
+  float* dom = cv.take((size_t)B * C * 2 * J * Ky);
+  float* dsp = cv.take((size_t)B * C * 2 * J * Ky);
+  float* U = cv.take(2 * (size_t)Ky * B * H * C);
+  // 5'. dpre = dy * act'(z); T[(ky,ro)][(b,o,h)] = sum_w dpre fs[(ky,ro)][w]
+  int rc = launch_fno1d_analysis(dy, fs4_y, T, B * O * H, 1, W, Ky, z, act, dpre, 1, s);
+  if (rc) return rc;
+  const float* g = dpre ? dpre : dy;
+  // 4'. dom[(b,o)][(j,ri)][ky] = sum_(ro,h) g3[(h,ro)][(j,ri)] T[(ky,ro)][(b,o,h)]
+  rc = launch_fno2d_rows(T, g3t, dom, (long long)B * O, H, Ky, 2 * J, s);
+  if (rc) return rc;
+  if (dw1 && dw2) {
+    const long long total = (long long)I * O * J * Ky;
+    fno2d_wgrad_kernel<<<grid_for(total), 256, 0, s>>>(spec, dom, dw1, dw2, B, I, O, m1, Ky);
+    RPDE_LAUNCH_CHECK();
+  }
+  if (dx) {
+    const long long total = (long long)B * I * J * Ky;
+    fno2d_mix_kernel<<<grid_for(total), 256, 0, s>>>(dom, w1, w2, dsp, B, I, O, m1, Ky, 1);
+    RPDE_LAUNCH_CHECK();
+    // 2'. U[(ky,ri)][(b,h)][i] = sum_(j,ro) g2[(j,ro)][(ri,h)] dspec[(b,i)][(j,ro)][ky]
+    rc = launch_fno2d_expand(dsp, g2t, U, B, I, H, Ky, 2 * J, s);
+    if (rc) return rc;
+    // 1'. dx[b,i,h,w] = sum_(ky,ri) U fa[(ky,ri)][w] + sum_o wb[o,i] dpre[b,o,h,w]
+    return launch_fno1d_synth(g, U, fa_y, wb, nullptr, dx, nullptr, B * H, /*reduction channels*/ O, /*outputs*/ I, W, Ky, ACT_NONE, 1, s, H);
+  }
+  return RPDE_OK;
 }
 
 // ------------------------------------------------------------------------------------------------

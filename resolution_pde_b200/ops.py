@@ -161,6 +161,21 @@ def _spectral_tables(ndim, shape, modes, device):
             dft_table(2, h, 2 * m1, m1, 1.0, device), dft_table(3, h, 2 * m1, m1, 1.0 / h, device))
 
 
+def _transposed_tables_2d(h, m1, device):
+    """adjoint tables of the fused FNOBlock2d backward: kind 3 as [(j,ri)][(ro,h)], kind 2 as [(h,ri)][(j,ro)]"""
+    key = ("fno2d_t", h, m1, str(device))
+    t = _tables.get(key)
+    if t is None:
+        j = 2 * m1
+        g2 = dft_table(2, h, j, m1, 1.0, device)
+        g3 = dft_table(3, h, j, m1, 1.0 / h, device)
+        g3t = g3.view(h, 2, j, 2).permute(2, 3, 1, 0).reshape(2 * j, 2 * h).contiguous()
+        g2t = g2.view(j, 2, 2, h).permute(3, 2, 0, 1).reshape(2 * h, 2 * j).contiguous()
+        t = (g3t, g2t)
+        _tables[key] = t
+    return t
+
+
 def _check_modes(ndim, spatial, modes):
     if ndim == 1:
         if modes[0] > spatial[0] // 2 + 1:
@@ -209,6 +224,20 @@ class _FNOSpectralFn(torch.autograd.Function):
             ctx.save_for_backward(x, w1, w2, wb, spec, z)
             ctx.cfg = (act, ndim, B, I, O, spatial, modes, S, bb is not None, True)
             return y
+        if ndim == 2 and _fno_fused and w2 is not None:
+            with _Ctx(x) as c:
+                if c.lib.rpde_fno_block2d_supported(B, I, O, spatial[0], spatial[1], modes[0], modes[1]):
+                    # FNOBlock2d in five fp32-FMA launches (csrc/fno2d_fused.cuh), engine-independent
+                    wbc = wb.detach().reshape(O, I).contiguous() if wb is not None else None
+                    nb = c.lib.rpde_fno_block2d_workspace_bytes(B, I, O, spatial[0], spatial[1], modes[0], modes[1])
+                    ws = _ws(nb, x.device)
+                    _lib.check(c.lib.rpde_fno_block2d_fwd(_p(x), _p(w1r), _p(w2r), _p(tabs[0]), _p(tabs[1]), _p(tabs[2]), _p(tabs[3]),
+                                                          _p(wbc), _p(bb), _p(spec) if need_grad else None, _p(y), _p(z), B, I, O,
+                                                          spatial[0], spatial[1], modes[0], modes[1], act, _p(ws), nb, c.stream),
+                               "rpde_fno_block2d_fwd")
+                    ctx.save_for_backward(x, w1, w2, wb, spec, z)
+                    ctx.cfg = (act, ndim, B, I, O, spatial, modes, S, bb is not None, True)
+                    return y
         with _Ctx(x) as c:
             beta = 0
             if wb is not None:
@@ -247,6 +276,25 @@ class _FNOSpectralFn(torch.autograd.Function):
         dwb = dbb = None
         fused = fwd_fused and _fno_fused_bwd          # one decision, taken in forward (same shape limits)
         dx_done = False
+        if fwd_fused and ndim == 2:
+            g3t, g2t = _transposed_tables_2d(spatial[0], modes[0], x.device)
+            dpre = torch.empty_like(dy) if act != ACT_NONE else None
+            wbc = wb.detach().reshape(O, I).contiguous() if wb is not None else None
+            with _Ctx(x) as c:
+                nb = c.lib.rpde_fno_block2d_workspace_bytes(B, I, O, spatial[0], spatial[1], modes[0], modes[1])
+                ws = _ws(nb, x.device)
+                _lib.check(c.lib.rpde_fno_block2d_bwd(_p(dy), _p(z) if dpre is not None else None, act, _p(w1r), _p(w2r), _p(tabs[0]),
+                                                      _p(tabs[1]), _p(g3t), _p(g2t), _p(spec), _p(wbc), _p(dpre), _p(dx), _p(dw1),
+                                                      _p(dw2), B, I, O, spatial[0], spatial[1], modes[0], modes[1], _p(ws), nb,
+                                                      c.stream), "rpde_fno_block2d_bwd")
+                if dpre is None:
+                    dpre = dy
+                if wb is not None:
+                    dwb = torch.empty_like(wb)
+                    dbb = torch.empty(O, dtype=torch.float32, device=x.device) if has_bias else None
+                    _lib.check(c.lib.rpde_conv1x1_bwd_params(_p(dpre), _p(x), _p(dwb), _p(dbb), B, I, O, S, c.stream),
+                               "rpde_conv1x1_bwd_params")
+            return (dx, torch.view_as_complex(dw1), torch.view_as_complex(dw2), dwb, dbb, None, None, None)
         with _Ctx(x) as c:
             if fused:
                 # act' multiply + projection on the synthesis table in one launch, then the spectral backward proper
