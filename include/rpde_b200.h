@@ -124,21 +124,21 @@ int rpde_spectral2d_bwd(const float* dy, const float* w1, const float* w2, const
  * conv(x) + bias) as five fp32-FMA launches (W-axis analysis over the image rows, H-axis analysis per plane, per-mode mixing
  * straight from the complex (I,O,m1,m2) parameters, H-axis synthesis, W-axis synthesis + bypass + bias + activation); only the
  * W-axis half transform (2*m2 floats per image row) and the J x m2 K-space tiles pass through the workspace.
- * fa_y: kind-0 table of W with m2 modes (scale 1); fs4_y: kind-4 table (scale 1/W); g2 / g3: kind-2 / kind-3 tables of H with
- * 2*m1 rows (scales 1, 1/H).  spec (B*I*4*m1*m2 floats, [(b,i)][(j,re|im)][ky]) and z (pre-activation) may be NULL when no
+ * fa_y: kind-0 table of W with m2 modes (scale 1); fs4_y: kind-4 table (scale 1/W); g2t: the kind-2 table of H with 2*m1 rows
+ * (scale 1) transposed to [(h,ri)][(j,ro)]; g3: the kind-3 table (scale 1/H, [(h,ro)][(j,ri)] as generated).  spec (B*I*4*m1*m2 floats, [(b,i)][(j,re|im)][ky]) and z (pre-activation) may be NULL when no
  * backward pass follows; wb (O,I) / bb (O) may be NULL.  rpde_fno_block2d_supported() tells whether a shape is covered
- * (B*H <= 65535, W <= 2048, 4*m1*m2 <= 1024); otherwise callers compose rpde_conv1x1_fwd + rpde_spectral2d_fwd.
- * Backward: g3t = the kind-3 table transposed to [(j,ri)][(ro,h)], g2t = the kind-2 table transposed to [(h,ri)][(j,ro)].
+ * (B*H <= 65535, W <= 1024, m2 <= 16, m1 <= 64 with 4*m1*ceil(m2/4) <= 256); otherwise callers compose rpde_conv1x1_fwd +
+ * rpde_spectral2d_fwd.  Backward: the same two H-axis tables, used by the adjoint kernels the other way round.
  * dpre = dy * act'(z) (z = dpre = NULL for act none) is what the bypass conv's parameter gradient consumes; dx = the COMPLETE
  * input gradient (spectral adjoint + wb^T dpre when wb is given: do not run rpde_conv1x1_bwd_input as well); dw1 / dw2 are
  * written in the complex parameter layout.  Workspace: rpde_fno_block2d_workspace_bytes for both directions. */
 int rpde_fno_block2d_supported(int B, int I, int O, int H, int W, int m1, int m2);
 size_t rpde_fno_block2d_workspace_bytes(int B, int I, int O, int H, int W, int m1, int m2);
-int rpde_fno_block2d_fwd(const float* x, const float* w1, const float* w2, const float* fa_y, const float* fs4_y, const float* g2,
+int rpde_fno_block2d_fwd(const float* x, const float* w1, const float* w2, const float* fa_y, const float* fs4_y, const float* g2t,
                          const float* g3, const float* wb, const float* bb, float* spec, float* y, float* z, int B, int I, int O,
                          int H, int W, int m1, int m2, int act, void* ws, size_t ws_bytes, rpde_stream_t stream);
 int rpde_fno_block2d_bwd(const float* dy, const float* z, int act, const float* w1, const float* w2, const float* fa_y,
-                         const float* fs4_y, const float* g3t, const float* g2t, const float* spec, const float* wb, float* dpre,
+                         const float* fs4_y, const float* g3, const float* g2t, const float* spec, const float* wb, float* dpre,
                          float* dx, float* dw1, float* dw2, int B, int I, int O, int H, int W, int m1, int m2, void* ws,
                          size_t ws_bytes, rpde_stream_t stream);
 

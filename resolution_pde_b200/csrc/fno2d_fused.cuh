@@ -5,8 +5,8 @@
 // 24 x 12), so nothing but the W-axis half transform (2 m2 floats per image row, 9 % of the activation) and that tile ever
 // leaves the SM between the read of x and the write of y:
 //
-//   1. fno1d_analysis_kernel (fno_fused.cuh) over the B*C*H image rows:      T[(ky,ri)][(b,c,h)] = sum_w x[b,c,h,w] fa[(ky,ri)][w]
-//   2. fno2d_rows_kernel, CTA = one (b, c) plane:                            spec[(b,c)][(j,ro)][ky] = sum_(ri,h) g2[(j,ro)][(ri,h)] T[(ky,ri)][(b,c,h)]
+//   1. fno2d_waxis_kernel over the B*C*H image rows (persistent, table in smem): T[(b,c,h)][(ky,ri)] = sum_w x[b,c,h,w] fa[(ky,ri)][w]
+//   2. fno2d_rows_kernel, CTA = one (b, c) plane:                            spec[(b,c)][(j,ro)][ky] = sum_(h,ri) g2[(j,ro)][(ri,h)] T[(b,c,h)][(ky,ri)]
 //   3. fno2d_mix_kernel, thread = (b, o, j, ky):                             om[(b,o)][(j,ro)][ky] = sum_i spec[(b,i)] (*) w[i,o,j,ky]   (weights1 | weights2)
 //   4. fno2d_expand_kernel, thread = (b, h, o):                              Z[(ky,ro)][(b,h)][o] = sum_(j,ri) g3[(h,ro)][(j,ri)] om[(b,o)][(j,ri)][ky]
 //   5. fno1d_synth_bypass_kernel with one "batch" per image row (b, h):      y[b,o,h,w] = act( sum_(ky,ro) Z fs[(ky,ro)][w] + sum_i wb[o,i] x[b,i,h,w] + bb[o] )
@@ -21,47 +21,123 @@ namespace rpde {
 
 constexpr int F2_HC = 256;   // image rows per shared-memory chunk of the H-axis kernels
 
-// out[p][a][ky] = sum_{c = (r, h)} tab[a][r * H + h] * in[(2 ky + r)][p * H + h]      a < A (= 2J), r in {0, 1}
-// CTA = one plane p; the plane's half transform (2 Ky rows of H values) is staged through shared memory in chunks of F2_HC rows.
-__global__ void __launch_bounds__(256) fno2d_rows_kernel(const float* __restrict__ in, const float* __restrict__ tab,
-                                                         float* __restrict__ out, long long planes, int H, int Ky, int A) {
-  extern __shared__ float tile[];                      // [2 Ky][F2_HC + 1]
+// lane j receives the sum over the warp's lanes of v[j] (31 shuffles instead of 32 x 5); v is destroyed
+__device__ __forceinline__ float f2_colsum32(float (&v)[32], int lane) {
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const bool up = (lane & off) != 0;
+#pragma unroll
+    for (int k = 0; k < off; ++k) {
+      const float send = up ? v[k] : v[k + off];
+      const float keep = up ? v[k + off] : v[k];
+      v[k] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+  return v[0];
+}
+
+// W-axis pass over image rows:  T[row][r] = sum_w x[row][w] * tab[r][w]   for r < R = 2 Ky <= 32.
+// Persistent CTAs: the whole table sits in shared memory (loaded once per CTA), every warp takes two image rows at a time
+// (each table value read from shared memory feeds two FMAs), keeps 2 x R partial sums per lane and reduces them with one
+// 31-shuffle transpose-reduction per row; the R results of a row leave as one coalesced store.
+// Backward use (adjoint of the W-axis synthesis): z / act = pre-activation and activation of the block, the row is multiplied by
+// act'(z) on load and written once to xout; kplanes > 0: the table is the plane-major synthesis table [ro][k][w] (kind 4) and
+// table row ro * K + k feeds output r = 2 k + ro.
+template <int NPL>
+__global__ void __launch_bounds__(256) fno2d_waxis_kernel(const float* __restrict__ x, const float* __restrict__ tab, float* __restrict__ T,
+                                                          long long rows, int N, int R, const float* __restrict__ z, int act,
+                                                          float* __restrict__ xout, int kplanes) {
+  extern __shared__ float st[];                         // [R][N]
+  for (int e = threadIdx.x; e < R * N; e += 256) {
+    const int r = e / N, n = e - r * N;
+    const int tr = kplanes ? (r & 1) * kplanes + (r >> 1) : r;
+    st[e] = __ldg(tab + (long long)tr * N + n);
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (long long r0 = ((long long)blockIdx.x * 8 + warp) * 2; r0 < rows; r0 += (long long)gridDim.x * 16) {
+    float v[2][NPL];
+#pragma unroll
+    for (int s = 0; s < 2; ++s) {
+      const long long row = r0 + s;
+      const bool ok = row < rows;
+#pragma unroll
+      for (int j = 0; j < NPL; ++j) {
+        const int n = lane + 32 * j;
+        v[s][j] = (ok && n < N) ? __ldg(x + row * N + n) : 0.f;
+      }
+      if (z) {
+#pragma unroll
+        for (int j = 0; j < NPL; ++j) {
+          const int n = lane + 32 * j;
+          if (ok && n < N) {
+            v[s][j] *= dact_f(act, __ldg(z + row * N + n));
+            if (xout) xout[row * N + n] = v[s][j];
+          }
+        }
+      }
+    }
+    float p0[32], p1[32];
+#pragma unroll
+    for (int r = 0; r < 32; ++r) {
+      p0[r] = p1[r] = 0.f;
+      if (r < R) {
+        const float* t = st + r * N + lane;
+#pragma unroll
+        for (int j = 0; j < NPL; ++j) {
+          const float tv = (lane + 32 * j < N) ? t[32 * j] : 0.f;
+          p0[r] = fmaf(v[0][j], tv, p0[r]);
+          p1[r] = fmaf(v[1][j], tv, p1[r]);
+        }
+      }
+    }
+    const float s0 = f2_colsum32(p0, lane), s1 = f2_colsum32(p1, lane);
+    if (lane < R) {
+      T[r0 * R + lane] = s0;
+      if (r0 + 1 < rows) T[(r0 + 1) * R + lane] = s1;
+    }
+  }
+}
+
+// H-axis contraction per plane:  out[p][a][ky] = sum_{h, r} tab[(h * 2 + r)][a] * T[(p * H + h)][2 ky + r]      a < A (= 2J)
+// CTA = one plane p; its half transform (H rows of 2 Ky floats, contiguous) is staged through shared memory; thread = (a, group
+// of KG ky values) with a fastest, so the table loads coalesce and the staged values are warp-wide broadcasts.
+template <int KG>
+__global__ void __launch_bounds__(256) fno2d_rows_kernel(const float* __restrict__ T, const float* __restrict__ tab,
+                                                         float* __restrict__ out, int H, int Ky, int A) {
+  extern __shared__ float tile[];                      // [F2_HC][2 Ky]
   const long long p = blockIdx.x;
-  const int ld = F2_HC + 1;
-  const int items = A * Ky;
-  const long long rows = planes * H;
-  // every thread owns up to 4 (a, ky) outputs (A * Ky <= 1024)
-  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  const int R = 2 * Ky;
+  const int ngroups = (Ky + KG - 1) / KG;
+  const int a = threadIdx.x % A, g = threadIdx.x / A;   // A <= 256
+  const bool active = g < ngroups;                      // requires A * ngroups <= 256 (checked on the host)
+  const int k0 = g * KG;
+  float acc[KG];
+#pragma unroll
+  for (int k = 0; k < KG; ++k) acc[k] = 0.f;
   for (int h0 = 0; h0 < H; h0 += F2_HC) {
     const int hc = min(F2_HC, H - h0);
     __syncthreads();
-    for (int e = threadIdx.x; e < 2 * Ky * hc; e += 256) {
-      const int r = e / hc, h = e - r * hc;
-      tile[r * ld + h] = __ldg(in + (long long)r * rows + p * H + h0 + h);
-    }
+    const float* src = T + (p * H + h0) * R;
+    for (int e = threadIdx.x; e < hc * R; e += 256) tile[e] = __ldg(src + e);
     __syncthreads();
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const int item = threadIdx.x + 256 * q;
-      if (item >= items) break;
-      const int a = item / Ky, ky = item - a * Ky;
-      const float* t0 = tab + (long long)a * 2 * H + h0;      // r = 0 half of the table row
-      const float* t1 = t0 + H;                                // r = 1
-      const float* s0 = tile + (2 * ky) * ld;
-      const float* s1 = s0 + ld;
-      float x0 = 0.f, x1 = 0.f;
+    if (active) {
+      const float* t = tab + (long long)(h0 * 2) * A + a;
 #pragma unroll 4
       for (int h = 0; h < hc; ++h) {
-        x0 = fmaf(__ldg(t0 + h), s0[h], x0);
-        x1 = fmaf(__ldg(t1 + h), s1[h], x1);
+        const float u0 = __ldg(t + (long long)(2 * h) * A), u1 = __ldg(t + (long long)(2 * h + 1) * A);
+        const float* s = tile + h * R + 2 * k0;
+#pragma unroll
+        for (int k = 0; k < KG; ++k) {
+          if (k0 + k < Ky) acc[k] = fmaf(u0, s[2 * k], fmaf(u1, s[2 * k + 1], acc[k]));
+        }
       }
-      acc[q] += x0 + x1;
     }
   }
+  if (active) {
 #pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    const int item = threadIdx.x + 256 * q;
-    if (item < items) out[p * items + item] = acc[q];
+    for (int k = 0; k < KG; ++k)
+      if (k0 + k < Ky) out[(p * A + a) * Ky + k0 + k] = acc[k];
   }
 }
 
@@ -134,37 +210,67 @@ __global__ void __launch_bounds__(256) fno2d_wgrad_kernel(const float* __restric
 }
 
 // Z[(2 ky + r)][b * H + h][c] = sum_{a} tab[(h * 2 + r)][a] * in[(b, c)][a][ky]         a < A (= 2J), r in {0, 1}
-// grid (ceil(H / 8), B), 256 threads = 8 image rows x 32 channels (channels beyond 32 are looped); KYT = ky values per pass
+// grid (ceil(H / 32), B), 256 threads = 8 image rows x 32 channels, four row groups per CTA; the plane tiles in[(b, c)] are
+// staged through shared memory transposed to [a][ky][c] in chunks of F2_AC values of a, so the inner loop reads
+// conflict-free shared memory (channel = lane) and the results leave as coalesced 128-byte stores.
+constexpr int F2_AC = 16;
 template <int KYT>
 __global__ void __launch_bounds__(256) fno2d_expand_kernel(const float* __restrict__ in, const float* __restrict__ tab,
                                                            float* __restrict__ Z, int Bn, int C, int H, int Ky, int A) {
+  __shared__ float sm[F2_AC * KYT * 32];               // [a][ky][c]
   const int b = blockIdx.y;
-  const int h = blockIdx.x * 8 + (threadIdx.x >> 5);
-  if (h >= H) return;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const long long BH = (long long)Bn * H;
-  const float* t0 = tab + (long long)(h * 2) * A;
-  const float* t1 = t0 + A;
-  for (int c = threadIdx.x & 31; c < C; c += 32) {
-    const float* src = in + ((long long)b * C + c) * A * Ky;
+  for (int c0 = 0; c0 < C; c0 += 32) {
+    const int c = c0 + lane;
     for (int k0 = 0; k0 < Ky; k0 += KYT) {
-      float a0[KYT], a1[KYT];
+      float a0[4][KYT], a1[4][KYT];
 #pragma unroll
-      for (int k = 0; k < KYT; ++k) a0[k] = a1[k] = 0.f;
-      for (int a = 0; a < A; ++a) {
-        const float u0 = __ldg(t0 + a), u1 = __ldg(t1 + a);
-        const float* s = src + (long long)a * Ky + k0;
+      for (int q = 0; q < 4; ++q)
 #pragma unroll
-        for (int k = 0; k < KYT; ++k) {
-          const float v = (k0 + k < Ky) ? __ldg(s + k) : 0.f;
-          a0[k] = fmaf(u0, v, a0[k]);
-          a1[k] = fmaf(u1, v, a1[k]);
+        for (int k = 0; k < KYT; ++k) a0[q][k] = a1[q][k] = 0.f;
+      for (int ac = 0; ac < A; ac += F2_AC) {
+        const int na = min(F2_AC, A - ac);
+        __syncthreads();
+        // in[(b, c)][a][ky]: for a fixed channel the (a, ky) block is contiguous; transpose to [a][ky][c]
+        for (int e = threadIdx.x; e < na * KYT * 32; e += 256) {
+          const int cc = e / (na * KYT), rem = e - cc * (na * KYT);
+          const int aa = rem / KYT, k = rem - aa * KYT;
+          float v = 0.f;
+          if (c0 + cc < C && k0 + k < Ky) v = __ldg(in + (((long long)b * C + c0 + cc) * A + ac + aa) * Ky + k0 + k);
+          sm[(aa * KYT + k) * 32 + cc] = v;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int h = blockIdx.x * 32 + q * 8 + warp;
+          if (h >= H) continue;
+          const float* t0 = tab + (long long)(h * 2) * A + ac;
+          const float* t1 = t0 + A;
+          for (int aa = 0; aa < na; ++aa) {
+            const float u0 = __ldg(t0 + aa), u1 = __ldg(t1 + aa);
+            const float* s = sm + aa * KYT * 32 + lane;
+#pragma unroll
+            for (int k = 0; k < KYT; ++k) {
+              const float v = s[k * 32];
+              a0[q][k] = fmaf(u0, v, a0[q][k]);
+              a1[q][k] = fmaf(u1, v, a1[q][k]);
+            }
+          }
         }
       }
+      if (c < C) {
 #pragma unroll
-      for (int k = 0; k < KYT; ++k) {
-        if (k0 + k >= Ky) break;
-        Z[((long long)(2 * (k0 + k)) * BH + (long long)b * H + h) * C + c] = a0[k];
-        Z[((long long)(2 * (k0 + k) + 1) * BH + (long long)b * H + h) * C + c] = a1[k];
+        for (int q = 0; q < 4; ++q) {
+          const int h = blockIdx.x * 32 + q * 8 + warp;
+          if (h >= H) continue;
+#pragma unroll
+          for (int k = 0; k < KYT; ++k) {
+            if (k0 + k >= Ky) break;
+            Z[((long long)(2 * (k0 + k)) * BH + (long long)b * H + h) * C + c] = a0[q][k];
+            Z[((long long)(2 * (k0 + k) + 1) * BH + (long long)b * H + h) * C + c] = a1[q][k];
+          }
+        }
       }
     }
   }

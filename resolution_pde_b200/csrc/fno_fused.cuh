@@ -138,7 +138,9 @@ constexpr int FNO_KT = 32;
 
 // TN = grid points per CTA (128: 4x8 outputs per thread; 64: 4x4 per thread, twice the CTAs -- chosen by the host so that the
 // grid fills the SMs at least twice and neighbouring CTAs overlap their load and FMA phases)
-template <int TN>
+// OB = output channels per register-tile pass (64: 4 x NT outputs per thread over 16 x 16 threads; 32: 8 x 32 threads, for
+// layers with at most 32 channels, where a 64-wide tile would spend half of its FMAs on padding)
+template <int TN, int OB = FNO_OB>
 __global__ void __launch_bounds__(256) fno1d_synth_bypass_kernel(const float* __restrict__ x, const float* __restrict__ om,
                                                                  const float* __restrict__ fs4, const float* __restrict__ wb,
                                                                  const float* __restrict__ bb, float* __restrict__ y,
@@ -148,16 +150,18 @@ __global__ void __launch_bounds__(256) fno1d_synth_bypass_kernel(const float* __
   // spectral rows are indexed by (b, h), the rows of x / y / z by ((b * C + c) * Hd + h)
   // adjoint = 1 (backward, dx = analysis adjoint of dsp + bypass dgrad): the table is the analysis table fa[(k,ri)][n] (row r
   // as is) and the bypass weight is read transposed, wb[(reduction channel)][output channel]
-  constexpr int NT = TN / 16;            // consecutive grid points per thread (8 or 4)
-  __shared__ __align__(16) float As[FNO_KT][FNO_OB + 4];
+  constexpr int OG = OB / 4, NG = 256 / OG;
+  constexpr int NT = TN / NG;            // consecutive grid points per thread (8 or 4)
+  static_assert(NT % 4 == 0, "float4 stores");
+  __shared__ __align__(16) float As[FNO_KT][OB + 4];
   __shared__ __align__(16) float Bs[FNO_KT][TN + 4];
   const int b = blockIdx.y, n0 = blockIdx.x * TN;
   const int bh = b / Hd, hh = b - bh * Hd;
   const int tid = threadIdx.x;
-  const int tn = (tid & 15) * NT;
-  const int to = (tid >> 4) * 4;        // 4 consecutive output channels
+  const int tn = (tid % NG) * NT;
+  const int to = (tid / NG) * 4;        // 4 consecutive output channels
   const int R = 2 * K;
-  for (int o0 = 0; o0 < O; o0 += FNO_OB) {
+  for (int o0 = 0; o0 < O; o0 += OB) {
     float acc[4][NT];
 #pragma unroll
     for (int a = 0; a < 4; ++a)
@@ -168,11 +172,11 @@ __global__ void __launch_bounds__(256) fno1d_synth_bypass_kernel(const float* __
     for (int r0 = 0; r0 < RT; r0 += FNO_KT) {
       __syncthreads();
       // every global load of the chunk is issued before the first shared-memory store (one L2 round trip per chunk)
-      float ra[FNO_KT * FNO_OB / 256], rb[FNO_KT * TN / 256];
+      float ra[FNO_KT * OB / 256], rb[FNO_KT * TN / 256];
 #pragma unroll
-      for (int j = 0; j < FNO_KT * FNO_OB / 256; ++j) {
+      for (int j = 0; j < FNO_KT * OB / 256; ++j) {
         const int e = tid + 256 * j;
-        const int rr = e / FNO_OB, oo = e - rr * FNO_OB;
+        const int rr = e / OB, oo = e - rr * OB;
         const int r = r0 + rr, o = o0 + oo;
         const bool ok = r < RT && o < O;
         const float* p = r < R ? om + ((long long)r * Bn + b) * O + o
@@ -190,9 +194,9 @@ __global__ void __launch_bounds__(256) fno1d_synth_bypass_kernel(const float* __
         rb[j] = ok ? __ldg(p) : 0.f;
       }
 #pragma unroll
-      for (int j = 0; j < FNO_KT * FNO_OB / 256; ++j) {
+      for (int j = 0; j < FNO_KT * OB / 256; ++j) {
         const int e = tid + 256 * j;
-        As[e / FNO_OB][e % FNO_OB] = ra[j];
+        As[e / OB][e % OB] = ra[j];
       }
 #pragma unroll
       for (int j = 0; j < FNO_KT * TN / 256; ++j) {

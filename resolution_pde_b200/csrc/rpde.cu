@@ -227,7 +227,10 @@ static int launch_fno1d_synth(const float* x, const float* om, const float* tabl
                               float* z, int B, int I, int O, int N, int modes, int act, int adjoint, cudaStream_t s, int Hd = 1) {
   static const int tn_sel = getenv("RPDE_FNO_TN") ? atoi(getenv("RPDE_FNO_TN")) : 0;   // bring-up switch: 64 or 128
   const bool wide = tn_sel ? tn_sel == 128 : (long long)((N + 127) / 128) * B >= 2 * 148;   // enough 128-point tiles to fill the SMs twice
-  if (wide) {
+  if (O <= 32 && (wide || Hd > 1)) {     // narrow layers (FNO2d width 32): a 32-channel register tile, no padded FMAs
+    dim3 g2((unsigned)((N + 127) / 128), (unsigned)B);
+    fno1d_synth_bypass_kernel<128, 32><<<g2, 256, 0, s>>>(x, om, table, wb, bb, y, z, B, I, O, N, modes, act, adjoint, Hd);
+  } else if (wide) {
     dim3 g2((unsigned)((N + 127) / 128), (unsigned)B);
     fno1d_synth_bypass_kernel<128><<<g2, 256, 0, s>>>(x, om, table, wb, bb, y, z, B, I, O, N, modes, act, adjoint, Hd);
   } else {
@@ -382,7 +385,10 @@ int rpde_fno_block1d_bwd(const float* dy, const float* z, int act, const float* 
 // Fused FNOBlock2d (fno2d_fused.cuh)
 // ------------------------------------------------------------------------------------------------
 static bool fno2d_fused_ok(int B, int I, int O, int H, int W, int m1, int m2) {
-  return (long long)B * H <= 65535 && W <= 2048 && 4LL * m1 * m2 <= 1024 && (long long)B * (I > O ? I : O) * H <= 0x7fffffffLL / 4;
+  // image rows as the synthesis kernel's grid.y, W-axis rows in registers (W <= 1024), 2 m2 <= 32 table rows, and the H-axis
+  // kernel's thread = (a, ky group) mapping: 4 m1 <= 256 values of a, (4 m1) * ceil(m2 / 4) <= 256 threads
+  return (long long)B * H <= 65535 && W <= 1024 && 2 * m2 <= 32 && 4 * m1 <= 256 && 4LL * m1 * ((m2 + 3) / 4) <= 256 &&
+         (long long)B * (I > O ? I : O) * H <= 0x7fffffffLL / 4;
 }
 int rpde_fno_block2d_supported(int B, int I, int O, int H, int W, int m1, int m2) { return fno2d_fused_ok(B, I, O, H, W, m1, m2) ? 1 : 0; }
 
@@ -397,15 +403,35 @@ size_t rpde_fno_block2d_workspace_bytes(int B, int I, int O, int H, int W, int m
   return f;
 }
 
-static int launch_fno2d_rows(const float* in, const float* tab, float* out, long long planes, int H, int Ky, int A, cudaStream_t s) {
-  const size_t smem = (size_t)2 * Ky * (F2_HC + 1) * sizeof(float);
-  if (smem > 48 * 1024) RPDE_CUDA(cudaFuncSetAttribute(fno2d_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  fno2d_rows_kernel<<<(unsigned)planes, 256, smem, s>>>(in, tab, out, planes, H, Ky, A);
+static int launch_fno2d_waxis(const float* x, const float* tab, float* T, long long rows, int N, int R, const float* z, int act,
+                              float* xout, int kplanes, cudaStream_t s) {
+  const size_t smem = (size_t)R * N * sizeof(float);
+  long long blocks = (rows + 15) / 16;
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  const unsigned g = (unsigned)blocks;
+#define RPDE_WAXIS(NPL)                                                                                                      \
+  do {                                                                                                                       \
+    if (smem > 48 * 1024)                                                                                                    \
+      RPDE_CUDA(cudaFuncSetAttribute(fno2d_waxis_kernel<NPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));      \
+    fno2d_waxis_kernel<NPL><<<g, 256, smem, s>>>(x, tab, T, rows, N, R, z, act, xout, kplanes);                            \
+  } while (0)
+  if (N <= 64) RPDE_WAXIS(2);
+  else if (N <= 128) RPDE_WAXIS(4);
+  else if (N <= 256) RPDE_WAXIS(8);
+  else if (N <= 512) RPDE_WAXIS(16);
+  else RPDE_WAXIS(32);
+#undef RPDE_WAXIS
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+static int launch_fno2d_rows(const float* T, const float* tab, float* out, long long planes, int H, int Ky, int A, cudaStream_t s) {
+  const size_t smem = (size_t)F2_HC * 2 * Ky * sizeof(float);    // <= 32 KB
+  fno2d_rows_kernel<4><<<(unsigned)planes, 256, smem, s>>>(T, tab, out, H, Ky, A);
   RPDE_LAUNCH_CHECK();
   return RPDE_OK;
 }
 static int launch_fno2d_expand(const float* in, const float* tab, float* Z, int B, int C, int H, int Ky, int A, cudaStream_t s) {
-  dim3 g((unsigned)((H + 7) / 8), (unsigned)B);
+  dim3 g((unsigned)((H + 31) / 32), (unsigned)B);
   if (Ky <= 4) fno2d_expand_kernel<4><<<g, 256, 0, s>>>(in, tab, Z, B, C, H, Ky, A);
   else if (Ky <= 8) fno2d_expand_kernel<8><<<g, 256, 0, s>>>(in, tab, Z, B, C, H, Ky, A);
   else fno2d_expand_kernel<12><<<g, 256, 0, s>>>(in, tab, Z, B, C, H, Ky, A);
@@ -413,10 +439,10 @@ static int launch_fno2d_expand(const float* in, const float* tab, float* Z, int 
   return RPDE_OK;
 }
 
-int rpde_fno_block2d_fwd(const float* x, const float* w1, const float* w2, const float* fa_y, const float* fs4_y, const float* g2,
+int rpde_fno_block2d_fwd(const float* x, const float* w1, const float* w2, const float* fa_y, const float* fs4_y, const float* g2t,
                          const float* g3, const float* wb, const float* bb, float* spec, float* y, float* z, int B, int I, int O,
                          int H, int W, int m1, int m2, int act, void* ws, size_t ws_bytes, rpde_stream_t stream) {
-  if (!x || !w1 || !w2 || !fa_y || !fs4_y || !g2 || !g3 || !y || B <= 0 || I <= 0 || O <= 0 || H <= 0 || W <= 0 || m1 <= 0 ||
+  if (!x || !w1 || !w2 || !fa_y || !fs4_y || !g2t || !g3 || !y || B <= 0 || I <= 0 || O <= 0 || H <= 0 || W <= 0 || m1 <= 0 ||
       m2 <= 0 || (bb && !wb))
     return fail(RPDE_E_INVALID, "rpde_fno_block2d_fwd: bad arguments%s");
   if (m2 > W / 2 + 1 || m1 > H) return fail(RPDE_E_MODES, "SpectralConv2d: modes exceed the available spectrum%s");
@@ -433,9 +459,9 @@ int rpde_fno_block2d_fwd(const float* x, const float* w1, const float* w2, const
   float* sp_ws = cv.take((size_t)B * C * 2 * J * Ky);
   float* Z = cv.take(2 * (size_t)Ky * B * H * C);
   if (!spec) spec = sp_ws;   // inference: the spectrum stays in the workspace
-  int rc = launch_fno1d_analysis(x, fa_y, T, B * I * H, 1, W, Ky, nullptr, 0, nullptr, 0, s);
+  int rc = launch_fno2d_waxis(x, fa_y, T, (long long)B * I * H, W, 2 * Ky, nullptr, 0, nullptr, 0, s);
   if (rc) return rc;
-  rc = launch_fno2d_rows(T, g2, spec, (long long)B * I, H, Ky, 2 * J, s);
+  rc = launch_fno2d_rows(T, g2t, spec, (long long)B * I, H, Ky, 2 * J, s);
   if (rc) return rc;
   {
     const long long total = (long long)B * O * J * Ky;
@@ -447,14 +473,14 @@ int rpde_fno_block2d_fwd(const float* x, const float* w1, const float* w2, const
   return launch_fno1d_synth(x, Z, fs4_y, wb, bb, y, z, B * H, I, O, W, Ky, act, 0, s, H);
 }
 
-// g3t = the kind-3 table transposed to [(j,ri)][(ro,h)], g2t = the kind-2 table transposed to [(h,ri)][(j,ro)] (the adjoints of
-// steps 4 and 2).  dpre (= dy * act'(z), written when z != NULL) is what the bypass conv's parameter gradient consumes; dx
+// Both H-axis kernels read their table as [(h, r)][a]: forward 2 uses g2t (the kind-2 table transposed to [(h,ri)][(j,ro)]) and
+// 4 uses g3 (kind 3 as generated); the adjoints swap them.  dpre (= dy * act'(z), written when z != NULL) is what the bypass conv's parameter gradient consumes; dx
 // receives the complete input gradient (spectral adjoint + wb^T dpre when wb is given).
 int rpde_fno_block2d_bwd(const float* dy, const float* z, int act, const float* w1, const float* w2, const float* fa_y,
-                         const float* fs4_y, const float* g3t, const float* g2t, const float* spec, const float* wb, float* dpre,
+                         const float* fs4_y, const float* g3, const float* g2t, const float* spec, const float* wb, float* dpre,
                          float* dx, float* dw1, float* dw2, int B, int I, int O, int H, int W, int m1, int m2, void* ws,
                          size_t ws_bytes, rpde_stream_t stream) {
-  if (!dy || !w1 || !w2 || !fa_y || !fs4_y || !g3t || !g2t || !spec || B <= 0 || I <= 0 || O <= 0 || H <= 0 || W <= 0 || m1 <= 0 ||
+  if (!dy || !w1 || !w2 || !fa_y || !fs4_y || !g3 || !g2t || !spec || B <= 0 || I <= 0 || O <= 0 || H <= 0 || W <= 0 || m1 <= 0 ||
       m2 <= 0 || (z && !dpre) || (!z && dpre))
     return fail(RPDE_E_INVALID, "rpde_fno_block2d_bwd: bad arguments (z and dpre come together)%s");
   if (!fno2d_fused_ok(B, I, O, H, W, m1, m2)) return fail(RPDE_E_INVALID, "rpde_fno_block2d_bwd: shape outside the fused kernels%s");
@@ -469,11 +495,11 @@ int rpde_fno_block2d_bwd(const float* dy, const float* z, int act, const float* 
   float* dsp = cv.take((size_t)B * C * 2 * J * Ky);
   float* U = cv.take(2 * (size_t)Ky * B * H * C);
   // 5'. dpre = dy * act'(z); T[(ky,ro)][(b,o,h)] = sum_w dpre fs[(ky,ro)][w]
-  int rc = launch_fno1d_analysis(dy, fs4_y, T, B * O * H, 1, W, Ky, z, act, dpre, 1, s);
+  int rc = launch_fno2d_waxis(dy, fs4_y, T, (long long)B * O * H, W, 2 * Ky, z, act, dpre, Ky, s);
   if (rc) return rc;
   const float* g = dpre ? dpre : dy;
-  // 4'. dom[(b,o)][(j,ri)][ky] = sum_(ro,h) g3[(h,ro)][(j,ri)] T[(ky,ro)][(b,o,h)]
-  rc = launch_fno2d_rows(T, g3t, dom, (long long)B * O, H, Ky, 2 * J, s);
+  // 4'. dom[(b,o)][(j,ri)][ky] = sum_(h,ro) g3[(h,ro)][(j,ri)] T[(b,o,h)][(ky,ro)]
+  rc = launch_fno2d_rows(T, g3, dom, (long long)B * O, H, Ky, 2 * J, s);
   if (rc) return rc;
   if (dw1 && dw2) {
     const long long total = (long long)I * O * J * Ky;

@@ -161,17 +161,15 @@ def _spectral_tables(ndim, shape, modes, device):
             dft_table(2, h, 2 * m1, m1, 1.0, device), dft_table(3, h, 2 * m1, m1, 1.0 / h, device))
 
 
-def _transposed_tables_2d(h, m1, device):
-    """adjoint tables of the fused FNOBlock2d backward: kind 3 as [(j,ri)][(ro,h)], kind 2 as [(h,ri)][(j,ro)]"""
-    key = ("fno2d_t", h, m1, str(device))
+def _g2t_table(h, m1, device):
+    """the H-axis analysis table (kind 2, [(j,ro)][(ri,h)]) transposed to [(h,ri)][(j,ro)]: both H-axis kernels of the fused
+    FNOBlock2d read their table as [(h, r)][a], the kind-3 table has that layout as generated"""
+    key = ("fno2d_g2t", h, m1, str(device))
     t = _tables.get(key)
     if t is None:
         j = 2 * m1
         g2 = dft_table(2, h, j, m1, 1.0, device)
-        g3 = dft_table(3, h, j, m1, 1.0 / h, device)
-        g3t = g3.view(h, 2, j, 2).permute(2, 3, 1, 0).reshape(2 * j, 2 * h).contiguous()
-        g2t = g2.view(j, 2, 2, h).permute(3, 2, 0, 1).reshape(2 * h, 2 * j).contiguous()
-        t = (g3t, g2t)
+        t = g2.view(j, 2, 2, h).permute(3, 2, 0, 1).reshape(2 * h, 2 * j).contiguous()
         _tables[key] = t
     return t
 
@@ -231,7 +229,8 @@ class _FNOSpectralFn(torch.autograd.Function):
                     wbc = wb.detach().reshape(O, I).contiguous() if wb is not None else None
                     nb = c.lib.rpde_fno_block2d_workspace_bytes(B, I, O, spatial[0], spatial[1], modes[0], modes[1])
                     ws = _ws(nb, x.device)
-                    _lib.check(c.lib.rpde_fno_block2d_fwd(_p(x), _p(w1r), _p(w2r), _p(tabs[0]), _p(tabs[1]), _p(tabs[2]), _p(tabs[3]),
+                    g2t = _g2t_table(spatial[0], modes[0], x.device)
+                    _lib.check(c.lib.rpde_fno_block2d_fwd(_p(x), _p(w1r), _p(w2r), _p(tabs[0]), _p(tabs[1]), _p(g2t), _p(tabs[3]),
                                                           _p(wbc), _p(bb), _p(spec) if need_grad else None, _p(y), _p(z), B, I, O,
                                                           spatial[0], spatial[1], modes[0], modes[1], act, _p(ws), nb, c.stream),
                                "rpde_fno_block2d_fwd")
@@ -277,14 +276,14 @@ class _FNOSpectralFn(torch.autograd.Function):
         fused = fwd_fused and _fno_fused_bwd          # one decision, taken in forward (same shape limits)
         dx_done = False
         if fwd_fused and ndim == 2:
-            g3t, g2t = _transposed_tables_2d(spatial[0], modes[0], x.device)
+            g2t = _g2t_table(spatial[0], modes[0], x.device)
             dpre = torch.empty_like(dy) if act != ACT_NONE else None
             wbc = wb.detach().reshape(O, I).contiguous() if wb is not None else None
             with _Ctx(x) as c:
                 nb = c.lib.rpde_fno_block2d_workspace_bytes(B, I, O, spatial[0], spatial[1], modes[0], modes[1])
                 ws = _ws(nb, x.device)
                 _lib.check(c.lib.rpde_fno_block2d_bwd(_p(dy), _p(z) if dpre is not None else None, act, _p(w1r), _p(w2r), _p(tabs[0]),
-                                                      _p(tabs[1]), _p(g3t), _p(g2t), _p(spec), _p(wbc), _p(dpre), _p(dx), _p(dw1),
+                                                      _p(tabs[1]), _p(tabs[3]), _p(g2t), _p(spec), _p(wbc), _p(dpre), _p(dx), _p(dw1),
                                                       _p(dw2), B, I, O, spatial[0], spatial[1], modes[0], modes[1], _p(ws), nb,
                                                       c.stream), "rpde_fno_block2d_bwd")
                 if dpre is None:
