@@ -19,12 +19,10 @@
 
 namespace rpde {
 
-constexpr int F2_HC = 256;   // image rows per shared-memory chunk of the H-axis kernels
-
-// lane j receives the sum over the warp's lanes of v[j] (31 shuffles instead of 32 x 5); v is destroyed
-__device__ __forceinline__ float f2_colsum32(float (&v)[32], int lane) {
+// lanes l and l + 16 receive the sum over the warp's 32 lanes of v[l & 15] (16 shuffles instead of 16 x 5); v is destroyed
+__device__ __forceinline__ float f2_colsum16(float (&v)[16], int lane) {
 #pragma unroll
-  for (int off = 16; off >= 1; off >>= 1) {
+  for (int off = 8; off >= 1; off >>= 1) {
     const bool up = (lane & off) != 0;
 #pragma unroll
     for (int k = 0; k < off; ++k) {
@@ -33,25 +31,26 @@ __device__ __forceinline__ float f2_colsum32(float (&v)[32], int lane) {
       v[k] = keep + __shfl_xor_sync(0xffffffffu, send, off);
     }
   }
-  return v[0];
+  return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 16);
 }
 
 // W-axis pass over image rows:  T[row][r] = sum_w x[row][w] * tab[r][w]   for r < R = 2 Ky <= 32.
 // Persistent CTAs: the whole table sits in shared memory (loaded once per CTA), every warp takes two image rows at a time
-// (each table value read from shared memory feeds two FMAs), keeps 2 x R partial sums per lane and reduces them with one
-// 31-shuffle transpose-reduction per row; the R results of a row leave as one coalesced store.
+// (each table value read from shared memory feeds two FMAs) and walks the table rows in groups of eight: 2 x 8 partial
+// sums per lane, reduced by one 16-shuffle transpose-reduction per group.
 // Backward use (adjoint of the W-axis synthesis): z / act = pre-activation and activation of the block, the row is multiplied by
 // act'(z) on load and written once to xout; kplanes > 0: the table is the plane-major synthesis table [ro][k][w] (kind 4) and
 // table row ro * K + k feeds output r = 2 k + ro.
 template <int NPL>
-__global__ void __launch_bounds__(256) fno2d_waxis_kernel(const float* __restrict__ x, const float* __restrict__ tab, float* __restrict__ T,
-                                                          long long rows, int N, int R, const float* __restrict__ z, int act,
-                                                          float* __restrict__ xout, int kplanes) {
-  extern __shared__ float st[];                         // [R][N]
-  for (int e = threadIdx.x; e < R * N; e += 256) {
+__global__ void __launch_bounds__(256, (NPL <= 8 ? 4 : (NPL <= 16 ? 2 : 1))) fno2d_waxis_kernel(const float* __restrict__ x, const float* __restrict__ tab, float* __restrict__ T,
+                                                             long long rows, int N, int R, const float* __restrict__ z, int act,
+                                                             float* __restrict__ xout, int kplanes) {
+  extern __shared__ float st[];                         // [ceil(R / 8) * 8][N], rows beyond R zero
+  const int R8 = (R + 7) & ~7;
+  for (int e = threadIdx.x; e < R8 * N; e += 256) {
     const int r = e / N, n = e - r * N;
     const int tr = kplanes ? (r & 1) * kplanes + (r >> 1) : r;
-    st[e] = __ldg(tab + (long long)tr * N + n);
+    st[e] = r < R ? __ldg(tab + (long long)tr * N + n) : 0.f;
   }
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -67,47 +66,55 @@ __global__ void __launch_bounds__(256) fno2d_waxis_kernel(const float* __restric
         v[s][j] = (ok && n < N) ? __ldg(x + row * N + n) : 0.f;
       }
       if (z) {
+        float zz[NPL];
 #pragma unroll
         for (int j = 0; j < NPL; ++j) {
           const int n = lane + 32 * j;
-          if (ok && n < N) {
-            v[s][j] *= dact_f(act, __ldg(z + row * N + n));
-            if (xout) xout[row * N + n] = v[s][j];
-          }
+          zz[j] = (ok && n < N) ? __ldg(z + row * N + n) : 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < NPL; ++j) {
+          const int n = lane + 32 * j;
+          v[s][j] *= dact_f(act, zz[j]);
+          if (xout && ok && n < N) xout[row * N + n] = v[s][j];
         }
       }
     }
-    float p0[32], p1[32];
+    for (int g = 0; g < R8; g += 8) {
+      float p[16];
 #pragma unroll
-    for (int r = 0; r < 32; ++r) {
-      p0[r] = p1[r] = 0.f;
-      if (r < R) {
-        const float* t = st + r * N + lane;
+      for (int r = 0; r < 8; ++r) {
+        const float* t = st + (g + r) * N + lane;
+        float a0 = 0.f, a1 = 0.f;
 #pragma unroll
         for (int j = 0; j < NPL; ++j) {
           const float tv = (lane + 32 * j < N) ? t[32 * j] : 0.f;
-          p0[r] = fmaf(v[0][j], tv, p0[r]);
-          p1[r] = fmaf(v[1][j], tv, p1[r]);
+          a0 = fmaf(v[0][j], tv, a0);
+          a1 = fmaf(v[1][j], tv, a1);
         }
+        p[r] = a0;
+        p[8 + r] = a1;
       }
-    }
-    const float s0 = f2_colsum32(p0, lane), s1 = f2_colsum32(p1, lane);
-    if (lane < R) {
-      T[r0 * R + lane] = s0;
-      if (r0 + 1 < rows) T[(r0 + 1) * R + lane] = s1;
+      const float sum = f2_colsum16(p, lane);          // lanes 0-7: row r0, table rows g..g+7; lanes 8-15: row r0 + 1
+      const int l = lane & 15, s = l >> 3, r = g + (l & 7);
+      if (lane < 16 && r < R && r0 + s < rows) T[(r0 + s) * R + r] = sum;
     }
   }
 }
 
 // H-axis contraction per plane:  out[p][a][ky] = sum_{h, r} tab[(h * 2 + r)][a] * T[(p * H + h)][2 ky + r]      a < A (= 2J)
-// CTA = one plane p; its half transform (H rows of 2 Ky floats, contiguous) is staged through shared memory; thread = (a, group
-// of KG ky values) with a fastest, so the table loads coalesce and the staged values are warp-wide broadcasts.
+// CTA = one plane p.  Both operands are staged through shared memory in chunks of F2_RC image rows (the plane's half
+// transform: F2_RC x 2 Ky contiguous floats; the table slice: 2 F2_RC x A contiguous floats), so the inner loop has no global
+// load: thread = (a, group of KG ky values) with a fastest reads its table value conflict-free and the staged values as broadcasts.
+constexpr int F2_RC = 64;
 template <int KG>
 __global__ void __launch_bounds__(256) fno2d_rows_kernel(const float* __restrict__ T, const float* __restrict__ tab,
                                                          float* __restrict__ out, int H, int Ky, int A) {
-  extern __shared__ float tile[];                      // [F2_HC][2 Ky]
+  extern __shared__ float sm[];                        // tile [F2_RC][2 Ky] | table slice [2 F2_RC][A]
   const long long p = blockIdx.x;
   const int R = 2 * Ky;
+  float* tile = sm;
+  float* tb = sm + F2_RC * R;
   const int ngroups = (Ky + KG - 1) / KG;
   const int a = threadIdx.x % A, g = threadIdx.x / A;   // A <= 256
   const bool active = g < ngroups;                      // requires A * ngroups <= 256 (checked on the host)
@@ -115,17 +122,18 @@ __global__ void __launch_bounds__(256) fno2d_rows_kernel(const float* __restrict
   float acc[KG];
 #pragma unroll
   for (int k = 0; k < KG; ++k) acc[k] = 0.f;
-  for (int h0 = 0; h0 < H; h0 += F2_HC) {
-    const int hc = min(F2_HC, H - h0);
+  for (int h0 = 0; h0 < H; h0 += F2_RC) {
+    const int hc = min(F2_RC, H - h0);
     __syncthreads();
     const float* src = T + (p * H + h0) * R;
     for (int e = threadIdx.x; e < hc * R; e += 256) tile[e] = __ldg(src + e);
+    const float* ts = tab + (long long)(h0 * 2) * A;
+    for (int e = threadIdx.x; e < 2 * hc * A; e += 256) tb[e] = __ldg(ts + e);
     __syncthreads();
     if (active) {
-      const float* t = tab + (long long)(h0 * 2) * A + a;
 #pragma unroll 4
       for (int h = 0; h < hc; ++h) {
-        const float u0 = __ldg(t + (long long)(2 * h) * A), u1 = __ldg(t + (long long)(2 * h + 1) * A);
+        const float u0 = tb[(2 * h) * A + a], u1 = tb[(2 * h + 1) * A + a];
         const float* s = tile + h * R + 2 * k0;
 #pragma unroll
         for (int k = 0; k < KG; ++k) {

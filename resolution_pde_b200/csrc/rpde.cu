@@ -405,7 +405,7 @@ size_t rpde_fno_block2d_workspace_bytes(int B, int I, int O, int H, int W, int m
 
 static int launch_fno2d_waxis(const float* x, const float* tab, float* T, long long rows, int N, int R, const float* z, int act,
                               float* xout, int kplanes, cudaStream_t s) {
-  const size_t smem = (size_t)R * N * sizeof(float);
+  const size_t smem = (size_t)((R + 7) & ~7) * N * sizeof(float);
   long long blocks = (rows + 15) / 16;
   if (blocks > 148 * 4) blocks = 148 * 4;
   const unsigned g = (unsigned)blocks;
@@ -425,7 +425,8 @@ static int launch_fno2d_waxis(const float* x, const float* tab, float* T, long l
   return RPDE_OK;
 }
 static int launch_fno2d_rows(const float* T, const float* tab, float* out, long long planes, int H, int Ky, int A, cudaStream_t s) {
-  const size_t smem = (size_t)F2_HC * 2 * Ky * sizeof(float);    // <= 32 KB
+  const size_t smem = (size_t)F2_RC * (2 * Ky + 2 * A) * sizeof(float);    // <= 64 * (32 + 512) * 4 = 136 KB, 30 KB at 12 x 12 modes
+  if (smem > 48 * 1024) RPDE_CUDA(cudaFuncSetAttribute(fno2d_rows_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   fno2d_rows_kernel<4><<<(unsigned)planes, 256, smem, s>>>(T, tab, out, H, Ky, A);
   RPDE_LAUNCH_CHECK();
   return RPDE_OK;
