@@ -254,49 +254,4 @@ __global__ void __launch_bounds__(256) fno1d_synth_bypass_kernel(const float* __
   }
 }
 
-// Mode-space kernels of the fused FNOBlock1d backward (spectra laid out [k][re|im][b][channel], weights in the parameter
-// layout (I, O, K) complex): they replace weight packing + two batched contractions + a memset + an unpack.
-//   dspec[k][.][b][i] = sum_o dom[k][.][b][o] * conj(w[i,o,k])          thread = (b, i, k), k fastest: the weight loads coalesce
-__global__ void __launch_bounds__(256) fno1d_mixadj_kernel(const float* __restrict__ dom, const float* __restrict__ w,
-                                                           float* __restrict__ dsp, int Bn, int I, int O, int K) {
-  const long long total = (long long)Bn * I * K;
-  for (long long t = (long long)blockIdx.x * 256 + threadIdx.x; t < total; t += (long long)gridDim.x * 256) {
-    const int k = (int)(t % K);
-    const long long r = t / K;
-    const int i = (int)(r % I), b = (int)(r / I);
-    const float* dr = dom + ((long long)(2 * k) * Bn + b) * O;
-    const float* di = dr + (long long)Bn * O;
-    const float* wp = w + ((long long)i * O * K + k) * 2;
-    float re = 0.f, im = 0.f;
-#pragma unroll 8
-    for (int o = 0; o < O; ++o) {
-      const float2 wv = __ldg(reinterpret_cast<const float2*>(wp + (long long)o * K * 2));
-      const float a = __ldg(dr + o), c = __ldg(di + o);
-      re = fmaf(a, wv.x, re); re = fmaf(c, wv.y, re);
-      im = fmaf(c, wv.x, im); im = fmaf(-a, wv.y, im);
-    }
-    dsp[((long long)(2 * k) * Bn + b) * I + i] = re;
-    dsp[((long long)(2 * k + 1) * Bn + b) * I + i] = im;
-  }
-}
-//   dw[i,o,k] = sum_b conj(spec[k][.][b][i]) * dom[k][.][b][o], written in the complex parameter layout (modes >= K: untouched)
-__global__ void __launch_bounds__(256) fno1d_wgrad_kernel(const float* __restrict__ spec, const float* __restrict__ dom,
-                                                          float* __restrict__ dw, int Bn, int I, int O, int K) {
-  const long long total = (long long)I * O * K;
-  for (long long t = (long long)blockIdx.x * 256 + threadIdx.x; t < total; t += (long long)gridDim.x * 256) {
-    const int k = (int)(t % K);
-    const long long r = t / K;
-    const int o = (int)(r % O), i = (int)(r / O);
-    float re = 0.f, im = 0.f;
-    for (int b = 0; b < Bn; ++b) {
-      const float sr = __ldg(spec + ((long long)(2 * k) * Bn + b) * I + i), si = __ldg(spec + ((long long)(2 * k + 1) * Bn + b) * I + i);
-      const float dr = __ldg(dom + ((long long)(2 * k) * Bn + b) * O + o), di = __ldg(dom + ((long long)(2 * k + 1) * Bn + b) * O + o);
-      re = fmaf(sr, dr, re); re = fmaf(si, di, re);
-      im = fmaf(sr, di, im); im = fmaf(-si, dr, im);
-    }
-    dw[t * 2] = re;
-    dw[t * 2 + 1] = im;
-  }
-}
-
 }  // namespace rpde

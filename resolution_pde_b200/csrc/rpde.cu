@@ -300,11 +300,8 @@ static int spectral1d_bwd_impl(const float* dy, const float* z, int act, const f
   float* dom = cv.take((size_t)K * B * 2 * O);
   float* dsp = cv.take((size_t)K * B * 2 * I);
   float* P = cv.take((size_t)K * 4 * I * O);
-  int rc = RPDE_OK;
-  if (!fs4) {
-    rc = pack_w(w, wp, I, O, modes, K, 1, 1, s);
-    if (rc) return rc;
-  }
+  int rc = pack_w(w, wp, I, O, modes, K, 1, 1, s);
+  if (rc) return rc;
   const long long BI = (long long)B * I, BO = (long long)B * O;
   // 3'. dom[(k,ro)][(b,o)] = sum_n dy[(b,o)][n] fs[n][(k,ro)]
   GemmP g = gemm_default();
@@ -321,28 +318,6 @@ static int spectral1d_bwd_impl(const float* dy, const float* z, int act, const f
     g.c = MatDesc{lin(0), lin(1), lin(BO)};
     g.splitk = 0;
     RPDE_CUDA(gemm(g, s));
-  }
-  if (fs4) {
-    // fused block: the mode-space products run on two small FMA kernels straight from / into the parameter layout
-    if (dw) {
-      fno1d_wgrad_kernel<<<grid_for((long long)I * O * K), 256, 0, s>>>(spec, dom, dw, B, I, O, K);
-      RPDE_LAUNCH_CHECK();
-    }
-    if (dx) {
-      fno1d_mixadj_kernel<<<grid_for((long long)B * I * K), 256, 0, s>>>(dom, w, dsp, B, I, O, K);
-      RPDE_LAUNCH_CHECK();
-      if (fuse_dx && !dx_accumulate)   // dx = analysis adjoint of dsp + the bypass conv's input gradient wb^T dpre, one kernel
-        return launch_fno1d_synth(dy, dsp, fa, wb, nullptr, dx, nullptr, B, /*reduction channels*/ O, /*outputs*/ I, N, K, ACT_NONE, 1, s);
-      GemmP g2 = gemm_default();
-      g2.A = dsp; g2.B = fa; g2.C = dx;
-      g2.M = B * I; g2.N = N; g2.K = 2 * K;
-      g2.a = MatDesc{lin(0), lin(1), lin(BI)};
-      g2.b = MatDesc{lin(0), lin(N), lin(1)};
-      g2.c = MatDesc{lin(0), lin(N), lin(1)};
-      g2.beta = dx_accumulate;
-      RPDE_CUDA(gemm(g2, s));
-    }
-    return RPDE_OK;
   }
   if (dw) {
     // dWp[k] = spec[k]^T dom[k]
@@ -368,6 +343,8 @@ static int spectral1d_bwd_impl(const float* dy, const float* z, int act, const f
     g.c = MatDesc{lin(2 * BI), lin(I), two(I, BI, 1)};
     RPDE_CUDA(gemm(g, s));
     // 1'. dx[(b,i)][n] (+)= sum_(k,ri) dsp[(k,ri)][(b,i)] fa[(k,ri)][n]
+    if (fuse_dx && !dx_accumulate)   // (+ the bypass conv's input gradient wb^T dpre in the same kernel; dy == dpre here)
+      return launch_fno1d_synth(dy, dsp, fa, wb, nullptr, dx, nullptr, B, /*reduction channels*/ O, /*outputs*/ I, N, K, ACT_NONE, 1, s);
     g = gemm_default();
     g.A = dsp; g.B = fa; g.C = dx;
     g.M = B * I; g.N = N; g.K = 2 * K;
