@@ -214,6 +214,18 @@ int rpde_rel_l2_fwd(const float* x, const float* y, float* acc, float* per_sampl
                     int reduce_mode, rpde_stream_t stream);
 int rpde_rel_l2_bwd(const float* x, const float* y, const float* acc, const float* gout, float* dx, int B,
                     long long S, int reduce_mode, rpde_stream_t stream);
+/* rpde_rel_l2_fwd_static: no counterpart in the reference; added for callers
+ * that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  Same kernels and results as rpde_rel_l2_fwd, but the 2*B-float accumulator lives in a file-scope
+ * __device__ array of the library (2 * RPDE_REL_L2_STATIC_MAX_B floats = 32 KB, held by every GPU that loads the
+ * library until exit) instead of a caller buffer; the call allocates nothing (no cudaMalloc / cudaFree / torch).
+ * B > RPDE_REL_L2_STATIC_MAX_B returns RPDE_E_WORKSPACE with a message in rpde_last_error().  The device that owns
+ * x / y / stream must be the current device.  All calls on one device share the array: it is cleared at the start of
+ * each call, and two calls that overlap on the GPU (different streams, no dependency) race -- serialise them.  The
+ * accumulator is not handed out, so there is no matching backward: use rpde_rel_l2_fwd when a gradient follows. */
+#define RPDE_REL_L2_STATIC_MAX_B 4096
+int rpde_rel_l2_fwd_static(const float* x, const float* y, float* per_sample, float* loss, int B, long long S,
+                           int reduce_mode, rpde_stream_t stream);
 
 /* ---- autoregressive rollout on the device (utils/autoregressive_step.py:284-309 perform_rollout_1d and the
  * per-step loss loop :170-196).  The state never leaves HBM between steps.

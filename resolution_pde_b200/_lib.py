@@ -64,6 +64,7 @@ SIGNATURES = {
     "rpde_concat_grid_bwd": (I, [P, P, I, I, I, I, I, I, S]),
     "rpde_rel_l2_fwd": (I, [P, P, P, P, P, I, L, I, S]),
     "rpde_rel_l2_bwd": (I, [P, P, P, P, P, I, L, I, S]),
+    "rpde_rel_l2_fwd_static": (I, [P, P, P, P, I, L, I, S]),
     "rpde_rollout_renorm": (I, [P, P, P, I, L, L, L, c_float, c_float, c_float, c_float, I, S]),
     "rpde_rollout_loss": (I, [P, P, P, P, P, I, I, L, L, L, L, L, c_float, c_float, I, S]),
     "rpde_moments_accumulate": (I, [P, L, P, S]),

@@ -1176,6 +1176,47 @@ int rpde_rel_l2_bwd(const float* x, const float* y, const float* acc, const floa
   return RPDE_OK;
 }
 
+// ---- rpde_rel_l2_fwd_static: the same two kernels as rpde_rel_l2_fwd with the 2*B-float accumulator in a
+// library-owned array instead of a caller buffer, for callers that may not allocate (CUDA graph capture, serving
+// loops).  Every device that loads the library holds the 32 KB until exit.  All calls on a device share the array:
+// it is cleared at the start of every call (it keeps the previous call's sums), and calls that overlap on the GPU race.
+static __device__ __align__(256) float g_rel_l2_static_acc[2 * RPDE_REL_L2_STATIC_MAX_B];
+
+// In host code g_rel_l2_static_acc is only the host-side stand-in of the symbol; the device address is looked up once
+// per device (with that device current) and cached.
+static int rel_l2_static_acc_ptr(float** out) {
+  constexpr int kMaxDev = 64;
+  static float* ptrs[kMaxDev] = {};
+  static std::mutex mu;
+  int dev = -1;
+  RPDE_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDev) return fail(RPDE_E_INVALID, "rpde_rel_l2_fwd_static: device index out of range%s");
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptrs[dev]) {
+    float* p = nullptr;
+    RPDE_CUDA(cudaGetSymbolAddress((void**)&p, g_rel_l2_static_acc));
+    if (!p) return fail(RPDE_E_CUDA, "rpde_rel_l2_fwd_static: cudaGetSymbolAddress returned a null address%s");
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return RPDE_OK;
+}
+
+int rpde_rel_l2_fwd_static(const float* x, const float* y, float* per_sample, float* loss, int B, long long S,
+                           int reduce_mode, rpde_stream_t stream) {
+  if (!x || !y || !per_sample || B <= 0 || S <= 0 || (reduce_mode && !loss))
+    return fail(RPDE_E_INVALID, "rpde_rel_l2_fwd_static: bad arguments%s");
+  if (B > RPDE_REL_L2_STATIC_MAX_B) {
+    snprintf(g_err, sizeof(g_err), "rpde_rel_l2_fwd_static: B = %d exceeds RPDE_REL_L2_STATIC_MAX_B = %d "
+             "(use rpde_rel_l2_fwd with a caller-owned accumulator)", B, RPDE_REL_L2_STATIC_MAX_B);
+    return RPDE_E_WORKSPACE;
+  }
+  float* acc = nullptr;
+  const int rc = rel_l2_static_acc_ptr(&acc);
+  if (rc != RPDE_OK) return rc;
+  return rpde_rel_l2_fwd(x, y, acc, per_sample, loss, B, S, reduce_mode, stream);
+}
+
 int rpde_rollout_renorm(const float* pred, float* preds_out, float* next_state, int B, long long S,
                         long long pred_batch_stride, long long preds_batch_stride, float y_scale, float y_mean,
                         float x_mean, float x_scale, int renorm, rpde_stream_t stream) {
