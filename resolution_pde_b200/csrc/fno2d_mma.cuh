@@ -1,0 +1,269 @@
+// FNOBlock2d W-axis kernels on the warp-level tensor path (mma.sync m16n8k8 TF32 with the 3xTF32 split: fp32 parity).
+//
+// These passes are HBM-bound (reduction lengths 24..64 per output), but as fp32-FMA register tiles they were instruction-
+// bound (fno1d_synth_bypass_kernel<128, 32>: 266 us against a 62 us HBM floor at 16 x 32 x 256^2).  One m16n8k8 MMA replaces
+// 32 FMAs per lane; with three MMAs per product the issue slots drop ~5x and the pass becomes a stream over x / y / z.
+//
+// fno2d_synth_mma_kernel (spectral_convolution.py:97 irfft2's last axis + fno_blocks.py:69-71):
+//   y[b,o,h,:] = act( sum_r Z[r][(b,h)][o] * tab[r][:]  +  sum_i wb[o,i] * x[b,i,h,:]  +  bb[o] ),   z = the pre-activation
+// as D[o][n] = A[o][k] * B[k][n] per image row (b, h): k runs over the 2*m2 spectral rows, then over the input channels.
+//   * persistent CTAs of eight warps; a warp owns 32 consecutive grid points of one image row (256 / W rows per iteration)
+//   * resident in shared memory, already split into TF32 hi / lo planes: the synthesis table (2 m2 x W) and the bypass weight
+//   * per image row: Z (2 m2 x O) staged hi / lo through a two-deep ring; x goes global -> registers as float4 (each element
+//     is used by exactly one warp), split in registers, prefetched one iteration ahead
+//   * the MMA column <-> grid point permutation (column c of n-tile j <-> point 4*pi(c) + j, pi(c) = (c >> 1) + 4 * (c & 1))
+//     makes every x load, table load and y / z store a float4 on 64..128 contiguous bytes per channel row
+// adjoint = 1 (backward): dx = analysis adjoint + wb^T dpre through the same code (table rows as stored, wb read transposed).
+#pragma once
+#include "common.cuh"
+
+namespace rpde {
+
+constexpr int F2M_LDA = 40;   // A-operand planes [k][o]: stride = 8 mod 32 -> the (t, g) fragment loads hit 32 distinct banks
+constexpr int F2M_MAXC = 32;  // channels (both sides) covered by the register tiles
+constexpr int F2M_MAXR = 32;  // spectral rows 2 * m2, rounded up to a multiple of 8
+
+__device__ __forceinline__ uint32_t tf32_hi(float v) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+  return r;
+}
+__device__ __forceinline__ void tf32_split(float v, uint32_t& hi, uint32_t& lo) {
+  hi = tf32_hi(v);
+  lo = __float_as_uint(v - __uint_as_float(hi));   // the tensor core reads the top 19 bits: residual 2^-11 * 2^-10 relative
+}
+__device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+// d += a * b to fp32 accuracy: the two cross terms first, the leading term last
+__device__ __forceinline__ void mma_3xtf32(float (&d)[4], const uint32_t (&ah)[4], const uint32_t (&al)[4], uint32_t bh0,
+                                           uint32_t bh1, uint32_t bl0, uint32_t bl1) {
+  mma_tf32(d, al, bh0, bh1);
+  mma_tf32(d, ah, bl0, bl1);
+  mma_tf32(d, ah, bh0, bh1);
+}
+
+__host__ __device__ constexpr size_t f2m_synth_smem(int W, int RP) {
+  return ((size_t)2 * RP * (W + 4)                      // table hi / lo
+          + (size_t)2 * F2M_MAXC * F2M_LDA              // bypass weight hi / lo
+          + (size_t)2 * 2 * (256 / W) * RP * F2M_LDA    // Z ring: 2 stages x hi / lo x rows per iteration
+          + F2M_MAXC) * sizeof(float);                  // bias
+}
+
+template <int W>
+__global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __restrict__ x, const float* __restrict__ Z,
+                                                                 const float* __restrict__ table, const float* __restrict__ wb,
+                                                                 const float* __restrict__ bb, float* __restrict__ y,
+                                                                 float* __restrict__ z, int Bn, int I, int O, int K, int act,
+                                                                 int adjoint, int Hd) {
+  static_assert(W == 64 || W == 128 || W == 256, "one warp per 32 grid points, eight warps");
+  constexpr int WPR = W / 32;        // warps per image row
+  constexpr int RPI = 8 / WPR;       // image rows per iteration
+  constexpr int LDT = W + 4;         // table planes [r][n]: stride = 4 mod 32 -> conflict-free float4 fragment loads
+  extern __shared__ __align__(16) float smem[];
+  const int R = 2 * K, RP = (R + 7) & ~7, KS_T = RP / 8, KS_X = wb ? (I + 7) / 8 : 0;
+  float* tabH = smem;
+  float* tabL = tabH + RP * LDT;
+  float* wbH = tabL + RP * LDT;
+  float* wbL = wbH + F2M_MAXC * F2M_LDA;
+  float* zring = wbL + F2M_MAXC * F2M_LDA;            // [stage][hi|lo][row][r][LDA]
+  float* biasS = zring + 2 * 2 * RPI * RP * F2M_LDA;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  const int pg = (g >> 1) + 4 * (g & 1);               // pi(g): this lane's float4 group inside the warp's 32 points
+  const int wrow = warp / WPR, n0 = (warp % WPR) * 32;
+
+  // ---- resident operands -------------------------------------------------------------------------------------------
+  for (int e = tid; e < RP * W; e += 256) {
+    const int r = e / W, n = e - r * W;
+    float v = 0.f;
+    if (r < R) v = __ldg(table + (adjoint ? (long long)r : (long long)(r & 1) * K + (r >> 1)) * W + n);
+    uint32_t hi, lo;
+    tf32_split(v, hi, lo);
+    tabH[r * LDT + n] = __uint_as_float(hi);
+    tabL[r * LDT + n] = __uint_as_float(tf32_hi(__uint_as_float(lo)));
+  }
+  for (int e = tid; e < F2M_MAXC * F2M_MAXC; e += 256) {
+    const int i = e / F2M_MAXC, o = e - i * F2M_MAXC;  // A[o][k = i]
+    float v = 0.f;
+    if (wb && i < I && o < O) v = __ldg(adjoint ? wb + (long long)i * O + o : wb + (long long)o * I + i);
+    uint32_t hi, lo;
+    tf32_split(v, hi, lo);
+    wbH[i * F2M_LDA + o] = __uint_as_float(hi);
+    wbL[i * F2M_LDA + o] = __uint_as_float(tf32_hi(__uint_as_float(lo)));
+  }
+  if (tid < F2M_MAXC) biasS[tid] = (bb && tid < O) ? __ldg(bb + tid) : 0.f;
+
+  const int ntiles = (Bn + RPI - 1) / RPI;
+  constexpr int ZPT = (RPI * F2M_MAXR * F2M_MAXC + 255) / 256;   // Z elements per thread and iteration (upper bound)
+  const int zcount = RPI * RP * F2M_MAXC;
+
+  // loads of one iteration: this warp's x rows (two float4 per k-step) and the thread's share of the Z rows
+  auto load_x = [&](int tile, float4 (&xb)[8]) {
+    const int row = tile * RPI + wrow;
+    const bool ok = row < Bn;
+    const int bh = row / Hd, hh = row - bh * Hd;
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int i = 8 * ks + t + 4 * h;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (ok && ks < KS_X && i < I)
+          v = __ldg(reinterpret_cast<const float4*>(x + (((long long)bh * I + i) * Hd + hh) * W + n0 + 4 * pg));
+        xb[2 * ks + h] = v;
+      }
+    }
+  };
+  auto load_z = [&](int tile, float (&zb)[ZPT]) {
+#pragma unroll
+    for (int q = 0; q < ZPT; ++q) {
+      const int e = tid + 256 * q;
+      const int o = e % F2M_MAXC, rr = e / F2M_MAXC;       // rr = rowslot * RP + r
+      const int slot = rr / RP, r = rr - slot * RP;
+      const int row = tile * RPI + slot;
+      float v = 0.f;
+      if (e < zcount && row < Bn && r < R && o < O) v = __ldg(Z + ((long long)r * Bn + row) * O + o);
+      zb[q] = v;
+    }
+  };
+  auto store_z = [&](int stage, const float (&zb)[ZPT]) {
+    float* zh = zring + (size_t)stage * 2 * RPI * RP * F2M_LDA;
+    float* zl = zh + RPI * RP * F2M_LDA;
+#pragma unroll
+    for (int q = 0; q < ZPT; ++q) {
+      const int e = tid + 256 * q;
+      if (e >= zcount) continue;
+      const int o = e % F2M_MAXC, rr = e / F2M_MAXC;
+      uint32_t hi, lo;
+      tf32_split(zb[q], hi, lo);
+      zh[rr * F2M_LDA + o] = __uint_as_float(hi);
+      zl[rr * F2M_LDA + o] = __uint_as_float(lo);
+    }
+  };
+
+  float4 xb[8];
+  float zb[ZPT];
+  int tile = blockIdx.x;
+  if (tile < ntiles) {
+    load_x(tile, xb);
+    load_z(tile, zb);
+    store_z(0, zb);
+  }
+  __syncthreads();
+
+  int stage = 0;
+  for (; tile < ntiles; tile += gridDim.x) {
+    const int next = tile + gridDim.x;
+    float4 xn[8];
+    if (next < ntiles) {
+      load_x(next, xn);
+      load_z(next, zb);
+    }
+    const int row = tile * RPI + wrow;
+    if (row < Bn) {
+      float acc[2][4][4];
+#pragma unroll
+      for (int m = 0; m < 2; ++m)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+          for (int c = 0; c < 4; ++c) acc[m][j][c] = 0.f;
+      const float* zh = zring + (size_t)stage * 2 * RPI * RP * F2M_LDA + (size_t)wrow * RP * F2M_LDA;
+      const float* zl = zh + RPI * RP * F2M_LDA;
+      // spectral rows
+      for (int ks = 0; ks < KS_T; ++ks) {
+        const int r0 = 8 * ks + t;
+        const float4 h0 = *reinterpret_cast<const float4*>(tabH + r0 * LDT + n0 + 4 * pg);
+        const float4 h1 = *reinterpret_cast<const float4*>(tabH + (r0 + 4) * LDT + n0 + 4 * pg);
+        const float4 l0 = *reinterpret_cast<const float4*>(tabL + r0 * LDT + n0 + 4 * pg);
+        const float4 l1 = *reinterpret_cast<const float4*>(tabL + (r0 + 4) * LDT + n0 + 4 * pg);
+        const float bh0[4] = {h0.x, h0.y, h0.z, h0.w}, bh1[4] = {h1.x, h1.y, h1.z, h1.w};
+        const float bl0[4] = {l0.x, l0.y, l0.z, l0.w}, bl1[4] = {l1.x, l1.y, l1.z, l1.w};
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+          uint32_t ah[4], al[4];
+          const int o = 16 * m + g;
+          ah[0] = __float_as_uint(zh[r0 * F2M_LDA + o]);
+          ah[1] = __float_as_uint(zh[r0 * F2M_LDA + o + 8]);
+          ah[2] = __float_as_uint(zh[(r0 + 4) * F2M_LDA + o]);
+          ah[3] = __float_as_uint(zh[(r0 + 4) * F2M_LDA + o + 8]);
+          al[0] = __float_as_uint(zl[r0 * F2M_LDA + o]);
+          al[1] = __float_as_uint(zl[r0 * F2M_LDA + o + 8]);
+          al[2] = __float_as_uint(zl[(r0 + 4) * F2M_LDA + o]);
+          al[3] = __float_as_uint(zl[(r0 + 4) * F2M_LDA + o + 8]);
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            mma_3xtf32(acc[m][j], ah, al, __float_as_uint(bh0[j]), __float_as_uint(bh1[j]), __float_as_uint(bl0[j]),
+                       __float_as_uint(bl1[j]));
+        }
+      }
+      // bypass conv: input channels
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks) {
+        if (ks < KS_X) {
+          const int i0 = 8 * ks + t;
+          const float v0[4] = {xb[2 * ks].x, xb[2 * ks].y, xb[2 * ks].z, xb[2 * ks].w};
+          const float v1[4] = {xb[2 * ks + 1].x, xb[2 * ks + 1].y, xb[2 * ks + 1].z, xb[2 * ks + 1].w};
+          uint32_t bh0[4], bh1[4], bl0[4], bl1[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            tf32_split(v0[j], bh0[j], bl0[j]);
+            tf32_split(v1[j], bh1[j], bl1[j]);
+          }
+#pragma unroll
+          for (int m = 0; m < 2; ++m) {
+            uint32_t ah[4], al[4];
+            const int o = 16 * m + g;
+            ah[0] = __float_as_uint(wbH[i0 * F2M_LDA + o]);
+            ah[1] = __float_as_uint(wbH[i0 * F2M_LDA + o + 8]);
+            ah[2] = __float_as_uint(wbH[(i0 + 4) * F2M_LDA + o]);
+            ah[3] = __float_as_uint(wbH[(i0 + 4) * F2M_LDA + o + 8]);
+            al[0] = __float_as_uint(wbL[i0 * F2M_LDA + o]);
+            al[1] = __float_as_uint(wbL[i0 * F2M_LDA + o + 8]);
+            al[2] = __float_as_uint(wbL[(i0 + 4) * F2M_LDA + o]);
+            al[3] = __float_as_uint(wbL[(i0 + 4) * F2M_LDA + o + 8]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) mma_3xtf32(acc[m][j], ah, al, bh0[j], bh1[j], bl0[j], bl1[j]);
+          }
+        }
+      }
+      // epilogue: lane holds, for channels o = 16 m + g (+ 8), the points n0 + 4 t + {0..3} (accumulator columns 2 t of the
+      // four n-tiles) and n0 + 16 + 4 t + {0..3} (columns 2 t + 1)
+      const int bh = row / Hd, hh = row - bh * Hd;
+#pragma unroll
+      for (int m = 0; m < 2; ++m) {
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          const int o = 16 * m + g + 8 * half;
+          if (o < O) {
+            const float bias = biasS[o];
+            const long long base = (((long long)bh * O + o) * Hd + hh) * W + n0 + 4 * t;
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+              float pre[4], out[4];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                pre[j] = acc[m][j][2 * half + c] + bias;
+                out[j] = act_f(act, pre[j]);
+              }
+              *reinterpret_cast<float4*>(y + base + 16 * c) = make_float4(out[0], out[1], out[2], out[3]);
+              if (z) *reinterpret_cast<float4*>(z + base + 16 * c) = make_float4(pre[0], pre[1], pre[2], pre[3]);
+            }
+          }
+        }
+      }
+    }
+    if (next < ntiles) {
+      store_z(stage ^ 1, zb);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) xb[q] = xn[q];
+    }
+    __syncthreads();
+    stage ^= 1;
+  }
+}
+
+}  // namespace rpde

@@ -17,6 +17,7 @@
 #include "pointwise.cuh"
 #include "fno_fused.cuh"
 #include "fno2d_fused.cuh"
+#include "fno2d_mma.cuh"
 #ifdef RPDE_WITH_TC
 #include "gemm_tc.cuh"
 #endif
@@ -226,6 +227,26 @@ int rpde_spectral1d_fwd(const float* x, const float* w, const float* fa, const f
 static int launch_fno1d_synth(const float* x, const float* om, const float* table, const float* wb, const float* bb, float* y,
                               float* z, int B, int I, int O, int N, int modes, int act, int adjoint, cudaStream_t s, int Hd = 1) {
   static const int tn_sel = getenv("RPDE_FNO_TN") ? atoi(getenv("RPDE_FNO_TN")) : 0;   // bring-up switch: 64 or 128
+  static const bool use_mma = !(getenv("RPDE_FNO2D_MMA") && atoi(getenv("RPDE_FNO2D_MMA")) == 0);
+  // FNOBlock2d image rows of 64 / 128 / 256 points, at most 32 channels: the tensor-path kernel (fno2d_mma.cuh)
+  if (use_mma && Hd > 1 && (N == 64 || N == 128 || N == 256) && I <= F2M_MAXC && O <= F2M_MAXC && 2 * modes <= F2M_MAXR) {
+    const int RP = (2 * modes + 7) & ~7;
+    const size_t smem = f2m_synth_smem(N, RP);
+    const int rpi = 256 / N;
+    long long tiles = ((long long)B + rpi - 1) / rpi;
+    const unsigned grid = (unsigned)(tiles < 2 * 148 ? tiles : 2 * 148);
+#define RPDE_SYNTH_MMA(WW)                                                                                                   \
+  do {                                                                                                                       \
+    RPDE_CUDA(cudaFuncSetAttribute(fno2d_synth_mma_kernel<WW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));     \
+    fno2d_synth_mma_kernel<WW><<<grid, 256, smem, s>>>(x, om, table, wb, bb, y, z, B, I, O, modes, act, adjoint, Hd);        \
+  } while (0)
+    if (N == 64) RPDE_SYNTH_MMA(64);
+    else if (N == 128) RPDE_SYNTH_MMA(128);
+    else RPDE_SYNTH_MMA(256);
+#undef RPDE_SYNTH_MMA
+    RPDE_LAUNCH_CHECK();
+    return RPDE_OK;
+  }
   const bool wide = tn_sel ? tn_sel == 128 : (long long)((N + 127) / 128) * B >= 2 * 148;   // enough 128-point tiles to fill the SMs twice
   if (O <= 32 && (wide || Hd > 1)) {     // narrow layers (FNO2d width 32): a 32-channel register tile, no padded FMAs
     dim3 g2((unsigned)((N + 127) / 128), (unsigned)B);
