@@ -1050,6 +1050,19 @@ int rpde_conv1x1_bwd_params(const float* dy, const float* x, float* dw, float* d
     return fail(RPDE_E_INVALID, "rpde_conv1x1_bwd_params: bad arguments%s");
   cudaStream_t s = (cudaStream_t)stream;
   RPDE_CUDA(cudaMemsetAsync(dw, 0, (size_t)O * I * sizeof(float), s));
+  static const bool use_mma = !(getenv("RPDE_FNO2D_MMA") && atoi(getenv("RPDE_FNO2D_MMA")) == 0);
+  auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+  if (use_mma && S % 32 == 0 && I <= 64 && O <= 64 && al16(dy) && al16(x)) {
+    // weight and bias gradient in one streaming pass on the warp-level tensor path (fno2d_mma.cuh)
+    if (db) RPDE_CUDA(cudaMemsetAsync(db, 0, (size_t)O * sizeof(float), s));
+    const int nb = ((I + 31) / 32) * ((O + 31) / 32), nstreams = 8 / nb;
+    const long long tiles = (long long)B * (S / 32);
+    long long ctas = (tiles + nstreams - 1) / nstreams;
+    if (ctas > 2 * 148) ctas = 2 * 148;
+    conv1x1_wgrad_mma_kernel<<<(unsigned)ctas, 256, 0, s>>>(dy, x, dw, db, B, I, O, (int)S);
+    RPDE_LAUNCH_CHECK();
+    return RPDE_OK;
+  }
   GemmP g = gemm_default();
   g.A = dy; g.B = x; g.C = dw;
   g.M = O; g.N = I; g.K = (int)(B * S);
