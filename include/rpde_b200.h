@@ -182,6 +182,18 @@ int rpde_conv1x1_bwd_input(const float* dy, const float* w, const float* zprev, 
 int rpde_conv1x1_bwd_params(const float* dy, const float* x, float* dw, float* db, int B, int I, int O,
                             long long S, rpde_stream_t stream);
 
+/* ---- projection MLP of FNO1d / FNO2d as one kernel per direction (models/fno_blocks.py:35-45 MLP1d, :73-83 MLP2d;
+ * fno.py:20,45: mid_channels = 4 * width): y = W2 gelu(W1 x + b1) + b2 on channels-first x (B, I, S), w1 (Hd, I), w2 (O, Hd).
+ * The hidden activations stay in registers (forward) and are recomputed from x (backward): nothing but x, dy, y, dx and the
+ * parameter gradients crosses HBM.  rpde_mlp_supported: I <= 64, Hd rounded up to 32 in {32, 64, 128, 256}, O <= 4,
+ * S % 32 == 0; other shapes use rpde_conv1x1_fwd / _bwd_input / _bwd_params.  dx may be NULL; db1 / db2 may be NULL.
+ * The parameter gradients are overwritten (zero-filled inside, accumulated with atomics). */
+int rpde_mlp_supported(int I, int Hd, int O, long long S);
+int rpde_mlp_fwd(const float* x, const float* w1, const float* b1, const float* w2, const float* b2, float* y, int B, int I,
+                 int Hd, int O, long long S, rpde_stream_t stream);
+int rpde_mlp_bwd(const float* x, const float* dy, const float* w1, const float* b1, const float* w2, float* dx, float* dw1,
+                 float* db1, float* dw2, float* db2, int B, int I, int Hd, int O, long long S, rpde_stream_t stream);
+
 /* out = dy * act'(z)   (backward of the FNO block activation, fno_blocks.py:33,71) */
 int rpde_act_bwd(const float* dy, const float* z, float* out, long long n, int act, rpde_stream_t stream);
 /* out = (res ? res : 0) + act(x)   (FSpectralConv1d activation + FFNO1D residual, spectral_convolution.py:155; ffno.py:118) */

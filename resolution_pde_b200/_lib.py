@@ -54,6 +54,9 @@ SIGNATURES = {
     "rpde_conv1x1_fwd": (I, [P, P, P, P, P, I, I, I, L, I, I, S]),
     "rpde_conv1x1_bwd_input": (I, [P, P, P, I, P, I, I, I, I, L, S]),
     "rpde_conv1x1_bwd_params": (I, [P, P, P, P, I, I, I, L, S]),
+    "rpde_mlp_supported": (I, [I, I, I, L]),
+    "rpde_mlp_fwd": (I, [P, P, P, P, P, P, I, I, I, I, L, S]),
+    "rpde_mlp_bwd": (I, [P, P, P, P, P, P, P, P, P, P, I, I, I, I, L, S]),
     "rpde_act_bwd": (I, [P, P, P, L, I, S]),
     "rpde_act_fwd": (I, [P, P, P, L, I, S]),
     "rpde_layernorm_fwd": (I, [P, P, P, P, P, P, P, L, I, c_float, S]),

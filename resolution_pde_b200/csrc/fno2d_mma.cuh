@@ -32,6 +32,12 @@ __device__ __forceinline__ void tf32_split(float v, uint32_t& hi, uint32_t& lo) 
   hi = tf32_hi(v);
   lo = __float_as_uint(v - __uint_as_float(hi));   // the tensor core reads the top 19 bits: residual 2^-11 * 2^-10 relative
 }
+// the same, pinned where it is written: inside a loop over output chunks the compiler would otherwise hoist the split of
+// loop-invariant operands and keep hi and lo planes live (2x the registers of the raw operand)
+__device__ __forceinline__ void tf32_split_here(float v, uint32_t& hi, uint32_t& lo) {
+  asm volatile("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(v));
+  lo = __float_as_uint(v - __uint_as_float(hi));
+}
 __device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
   asm volatile(
       "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
@@ -380,6 +386,456 @@ __global__ void __launch_bounds__(256, 2) conv1x1_wgrad_mma_kernel(const float* 
       const int i = (bk % nbi) * 32 + col;
       if (i < I) atomicAdd(dw + (long long)o * I + i, v);
     }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Projection MLP of FNO1d / FNO2d (fno_blocks.py:35-45, 73-83; fno.py:20,45): y = W2 gelu(W1 x + b1) + b2, channels first,
+// x (B, I, S) -> hidden (Hd = 4 * width) -> y (B, O, S) with O = out_channels (1 for every configured dataset).
+// Composed, the hidden tensor and gelu'(z) are 2 x 537 MB at C4-256 (0.63 ms forward, 1.05 ms backward).  Fused, the hidden
+// activations live in MMA accumulators: forward reads x and writes y; backward recomputes them from x.
+//
+// mlp_fwd_mma_kernel: a warp owns 32 consecutive points; per 32-row chunk of the hidden layer it forms z = W1 x (3xTF32,
+// D[h][n] = A[h][i] B[i][n]; W1 resident in shared memory as interleaved (hi, lo) pairs, x in registers as float4 B
+// fragments with the same column <-> point permutation as fno2d_synth_mma_kernel), applies bias + GELU and folds the rows
+// into y[o][n] += w2[o][h] gelu(z) on the CUDA cores; one 8-lane shuffle reduction per tile, float4 stores.
+constexpr int MLP_MAXO = 4;
+__host__ __device__ constexpr int mlp_ip(int I) { return I <= 32 ? 32 : 64; }          // input channels as the register tiles see them
+__host__ __device__ constexpr int mlp_ldw(int I) { return 2 * mlp_ip(I) + 8; }         // floats per W1 row (hi, lo pairs), = 8 mod 32
+__host__ __device__ constexpr size_t mlp_fwd_smem(int I, int Hd) {
+  return ((size_t)((Hd + 31) & ~31) * mlp_ldw(I) + (size_t)(MLP_MAXO + 1) * ((Hd + 31) & ~31)) * sizeof(float);
+}
+
+// W1 (Hd, I) -> shared (hi, lo) pairs, rows and columns zero-padded to multiples of 32 / 8
+__device__ __forceinline__ void mlp_stage_w1(const float* __restrict__ w1, float* w1s, int I, int Hd, int HP, int LDW) {
+  const int IP = mlp_ip(I);
+  for (int e = threadIdx.x; e < HP * IP; e += blockDim.x) {
+    const int h = e / IP, i = e - h * IP;
+    const float v = (h < Hd && i < I) ? __ldg(w1 + (long long)h * I + i) : 0.f;
+    uint32_t hi, lo;
+    tf32_split(v, hi, lo);
+    *reinterpret_cast<float2*>(w1s + h * LDW + 2 * i) = make_float2(__uint_as_float(hi), __uint_as_float(tf32_hi(__uint_as_float(lo))));
+  }
+}
+
+template <int KS, int NO>   // k-steps of eight input channels: 4 (I <= 32) or 8 (I <= 64); NO: outputs held (1 or MLP_MAXO)
+__global__ void __launch_bounds__(256, KS == 4 ? 2 : 1) mlp_fwd_mma_kernel(const float* __restrict__ x, const float* __restrict__ w1,
+                                                                          const float* __restrict__ b1, const float* __restrict__ w2,
+                                                                          const float* __restrict__ b2, float* __restrict__ y, int Bn,
+                                                                          int I, int Hd, int O, int S) {
+  extern __shared__ __align__(16) float smem[];
+  const int HP = (Hd + 31) & ~31, LDW = mlp_ldw(I);
+  float* w1s = smem;                  // [HP][LDW]  (hi, lo) pairs
+  float* b1s = w1s + HP * LDW;        // [HP]
+  float* w2s = b1s + HP;              // [MLP_MAXO][HP]
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  const int pg = (g >> 1) + 4 * (g & 1);
+  mlp_stage_w1(w1, w1s, I, Hd, HP, LDW);
+  for (int e = tid; e < HP; e += 256) {
+    b1s[e] = (b1 && e < Hd) ? __ldg(b1 + e) : 0.f;
+#pragma unroll
+    for (int o = 0; o < MLP_MAXO; ++o) w2s[o * HP + e] = (o < O && e < Hd) ? __ldg(w2 + (long long)o * Hd + e) : 0.f;
+  }
+  __syncthreads();
+  const int segs = S / 32;
+  const long long ntiles = (long long)Bn * segs;
+  for (long long tile = (long long)blockIdx.x * 8 + warp; tile < ntiles; tile += (long long)gridDim.x * 8) {
+    const int b = (int)(tile / segs), n0 = (int)(tile - (long long)b * segs) * 32;
+    float4 xb[2 * KS];
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int i = 8 * ks + t + 4 * h;
+        xb[2 * ks + h] = i < I ? __ldg(reinterpret_cast<const float4*>(x + ((long long)b * I + i) * S + n0 + 4 * pg))
+                               : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    float ysum[NO][4][2];
+#pragma unroll
+    for (int o = 0; o < NO; ++o)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) ysum[o][j][0] = ysum[o][j][1] = 0.f;
+    for (int hc = 0; hc < HP; hc += 32) {
+      float acc[2][4][4];
+#pragma unroll
+      for (int m = 0; m < 2; ++m)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+          for (int c = 0; c < 4; ++c) acc[m][j][c] = 0.f;
+#pragma unroll
+      for (int ks = 0; ks < KS; ++ks) {
+        const float v0[4] = {xb[2 * ks].x, xb[2 * ks].y, xb[2 * ks].z, xb[2 * ks].w};
+        const float v1[4] = {xb[2 * ks + 1].x, xb[2 * ks + 1].y, xb[2 * ks + 1].z, xb[2 * ks + 1].w};
+        uint32_t bh0[4], bh1[4], bl0[4], bl1[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          tf32_split_here(v0[j], bh0[j], bl0[j]);
+          tf32_split_here(v1[j], bh1[j], bl1[j]);
+        }
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+          const float* wr = w1s + (hc + 16 * m + g) * LDW + 2 * (8 * ks + t);
+          const float2 a0 = *reinterpret_cast<const float2*>(wr);
+          const float2 a1 = *reinterpret_cast<const float2*>(wr + 8 * LDW);
+          const float2 a2 = *reinterpret_cast<const float2*>(wr + 8);
+          const float2 a3 = *reinterpret_cast<const float2*>(wr + 8 * LDW + 8);
+          const uint32_t ah[4] = {__float_as_uint(a0.x), __float_as_uint(a1.x), __float_as_uint(a2.x), __float_as_uint(a3.x)};
+          const uint32_t al[4] = {__float_as_uint(a0.y), __float_as_uint(a1.y), __float_as_uint(a2.y), __float_as_uint(a3.y)};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) mma_3xtf32(acc[m][j], ah, al, bh0[j], bh1[j], bl0[j], bl1[j]);
+        }
+      }
+      // bias + GELU, rows folded into the outputs
+#pragma unroll
+      for (int m = 0; m < 2; ++m)
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          const int h = hc + 16 * m + g + 8 * hh;
+          const float bias = b1s[h];
+          float hv[4][2];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            float d0, d1;
+            gelu_both2(acc[m][j][2 * hh] + bias, acc[m][j][2 * hh + 1] + bias, hv[j][0], hv[j][1], d0, d1);
+          }
+#pragma unroll
+          for (int o = 0; o < NO; ++o) {
+            if (o < O) {
+              const float w = w2s[o * HP + h];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                ysum[o][j][0] = fmaf(w, hv[j][0], ysum[o][j][0]);
+                ysum[o][j][1] = fmaf(w, hv[j][1], ysum[o][j][1]);
+              }
+            }
+          }
+        }
+    }
+    // the eight lanes of equal t hold the partial sums of the same 8 points: butterfly over g, lane g == o stores output o
+#pragma unroll
+    for (int o = 0; o < NO; ++o) {
+      if (o < O) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            float v = ysum[o][j][c];
+            v += __shfl_xor_sync(0xffffffffu, v, 4);
+            v += __shfl_xor_sync(0xffffffffu, v, 8);
+            v += __shfl_xor_sync(0xffffffffu, v, 16);
+            ysum[o][j][c] = v;
+          }
+        if (g == o) {
+          const float bo = b2 ? __ldg(b2 + o) : 0.f;
+          float* yp = y + ((long long)b * O + o) * S + n0 + 4 * t;
+          *reinterpret_cast<float4*>(yp) = make_float4(ysum[o][0][0] + bo, ysum[o][1][0] + bo, ysum[o][2][0] + bo, ysum[o][3][0] + bo);
+          *reinterpret_cast<float4*>(yp + 16) = make_float4(ysum[o][0][1] + bo, ysum[o][1][1] + bo, ysum[o][2][1] + bo, ysum[o][3][1] + bo);
+        }
+      }
+    }
+  }
+}
+
+// mlp_bwd_mma_kernel: every gradient of the projection MLP in one pass over x and dy.  A warp owns (32 points, one 32-row
+// chunk of the hidden layer); the NCH = Hd / 32 chunks of a point tile sit in NCH warps of the CTA (8 / NCH point tiles per
+// iteration).  Per iteration and warp:
+//   1. z = W1[chunk] x  (3xTF32; the x tile arrives through a cp.async double buffer shared by the chunk warps)
+//   2. h = gelu(z + b1), dz = (sum_o w2[o] dy[o]) * gelu'(z + b1) in the accumulator registers; dw2 / db1 partial sums
+//   3. dw1[chunk] += dz x^T: dz is the A operand straight from the accumulator layout (k <-> the accumulator's columns)
+//   4. dx partial = W1[chunk]^T dz: dz goes through the warp's shared-memory tile to reach the B-operand layout
+//   5. the chunk warps add their dx partials through shared memory, 16 input channels at a time; float4 stores
+// dw1 / db1 / dw2 / db2 leave the CTA as atomics at the end of the persistent loop (zero-filled by the caller).
+constexpr int MLP_LDX = 36;   // x / dz tiles [row][32 points]: stride = 4 mod 32
+__host__ __device__ constexpr size_t mlp_bwd_smem(int I, int Hd) {
+  const int HP = (Hd + 31) & ~31, IP = mlp_ip(I);
+  return ((size_t)HP * mlp_ldw(I) + (size_t)(MLP_MAXO + 1) * HP + (size_t)2 * (256 / HP) * IP * MLP_LDX + (size_t)8 * 32 * MLP_LDX) *
+         sizeof(float);
+}
+
+template <int KS, int NO>
+__global__ void __launch_bounds__(256, 1) mlp_bwd_mma_kernel(const float* __restrict__ x, const float* __restrict__ dy,
+                                                             const float* __restrict__ w1, const float* __restrict__ b1,
+                                                             const float* __restrict__ w2, float* __restrict__ dx,
+                                                             float* __restrict__ dw1, float* __restrict__ db1,
+                                                             float* __restrict__ dw2, float* __restrict__ db2, int Bn, int I, int Hd,
+                                                             int O, int S) {
+  constexpr int IP = 8 * KS, IT = KS / 2;
+  extern __shared__ __align__(16) float smem[];
+  const int HP = (Hd + 31) & ~31, LDW = mlp_ldw(I), NCH = HP / 32, PT = 8 / NCH;
+  float* w1s = smem;
+  float* b1s = w1s + HP * LDW;
+  float* w2s = b1s + HP;
+  float* xs = w2s + MLP_MAXO * HP;                     // [2][PT][IP][MLP_LDX]
+  float* bufs = xs + 2 * PT * IP * MLP_LDX;            // [8 warps][32][MLP_LDX]: dz tile, then dx partials
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  const int pg = (g >> 1) + 4 * (g & 1);
+  const int ptid = warp / NCH, hc = (warp % NCH) * 32;
+  float* mybuf = bufs + warp * 32 * MLP_LDX;
+  mlp_stage_w1(w1, w1s, I, Hd, HP, LDW);
+  for (int e = tid; e < HP; e += 256) {
+    b1s[e] = (b1 && e < Hd) ? __ldg(b1 + e) : 0.f;
+#pragma unroll
+    for (int o = 0; o < MLP_MAXO; ++o) w2s[o * HP + e] = (o < O && e < Hd) ? __ldg(w2 + (long long)o * Hd + e) : 0.f;
+  }
+  for (int e = tid; e < 2 * PT * IP * MLP_LDX; e += 256) xs[e] = 0.f;   // rows i >= I stay zero
+  __syncthreads();
+
+  const int segs = S / 32;
+  const long long ntiles = (long long)Bn * segs, ngroups = (ntiles + PT - 1) / PT;
+  auto stage_x = [&](long long group, int bufi) {
+    // PT tiles x I rows x eight 16-byte pieces
+    for (int e = tid; e < PT * I * 8; e += 256) {
+      const int piece = e & 7, r = e >> 3, p = r / I, i = r - p * I;
+      const long long tile = group * PT + p;
+      if (tile < ntiles) {
+        const int b = (int)(tile / segs), n0 = (int)(tile - (long long)b * segs) * 32;
+        const float* src = x + ((long long)b * I + i) * S + n0 + 4 * piece;
+        const uint32_t dst = (uint32_t)__cvta_generic_to_shared(xs + ((bufi * PT + p) * IP + i) * MLP_LDX + 4 * piece);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src));
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+
+  float dw1acc[2][KS][4];
+  float db1p[2][2], dw2p[NO][2][2], db2p[NO];
+#pragma unroll
+  for (int m = 0; m < 2; ++m) {
+    db1p[m][0] = db1p[m][1] = 0.f;
+#pragma unroll
+    for (int o = 0; o < NO; ++o) dw2p[o][m][0] = dw2p[o][m][1] = 0.f;
+#pragma unroll
+    for (int q = 0; q < KS; ++q)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) dw1acc[m][q][c] = 0.f;
+  }
+#pragma unroll
+  for (int o = 0; o < NO; ++o) db2p[o] = 0.f;
+
+  long long group = blockIdx.x;
+  int bufi = 0;
+  if (group < ngroups) stage_x(group, 0);
+  for (; group < ngroups; group += gridDim.x) {
+    const long long nextg = group + gridDim.x;
+    if (nextg < ngroups) {
+      stage_x(nextg, bufi ^ 1);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();
+    const long long tile = group * PT + ptid;
+    const bool live = tile < ntiles;
+    const int b = live ? (int)(tile / segs) : 0, n0 = live ? (int)(tile - (long long)b * segs) * 32 : 0;
+    const float* xt = xs + (bufi * PT + ptid) * IP * MLP_LDX;
+    float dxacc[IT][4][4];
+#pragma unroll
+    for (int mt = 0; mt < IT; ++mt)
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) dxacc[mt][j][c] = 0.f;
+    if (live) {
+      // ---- 1. z chunk ------------------------------------------------------------------------------------------
+      float acc[2][4][4];
+#pragma unroll
+      for (int m = 0; m < 2; ++m)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+          for (int c = 0; c < 4; ++c) acc[m][j][c] = 0.f;
+#pragma unroll
+      for (int ks = 0; ks < KS; ++ks) {
+        const float4 x0 = *reinterpret_cast<const float4*>(xt + (8 * ks + t) * MLP_LDX + 4 * pg);
+        const float4 x1 = *reinterpret_cast<const float4*>(xt + (8 * ks + t + 4) * MLP_LDX + 4 * pg);
+        const float v0[4] = {x0.x, x0.y, x0.z, x0.w}, v1[4] = {x1.x, x1.y, x1.z, x1.w};
+        uint32_t bh0[4], bh1[4], bl0[4], bl1[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          tf32_split(v0[j], bh0[j], bl0[j]);
+          tf32_split(v1[j], bh1[j], bl1[j]);
+        }
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+          const float* wr = w1s + (hc + 16 * m + g) * LDW + 2 * (8 * ks + t);
+          const float2 a0 = *reinterpret_cast<const float2*>(wr);
+          const float2 a1 = *reinterpret_cast<const float2*>(wr + 8 * LDW);
+          const float2 a2 = *reinterpret_cast<const float2*>(wr + 8);
+          const float2 a3 = *reinterpret_cast<const float2*>(wr + 8 * LDW + 8);
+          const uint32_t ah[4] = {__float_as_uint(a0.x), __float_as_uint(a1.x), __float_as_uint(a2.x), __float_as_uint(a3.x)};
+          const uint32_t al[4] = {__float_as_uint(a0.y), __float_as_uint(a1.y), __float_as_uint(a2.y), __float_as_uint(a3.y)};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) mma_3xtf32(acc[m][j], ah, al, bh0[j], bh1[j], bl0[j], bl1[j]);
+        }
+      }
+      // ---- 2. dz in place; column (j, c) of the accumulators <-> point n0 + 16 c + 4 t + j ----------------------------
+      float dyv[NO][4][2];
+#pragma unroll
+      for (int o = 0; o < NO; ++o) {
+        if (o < O) {
+          const float* dp = dy + ((long long)b * O + o) * S + n0 + 4 * t;
+          const float4 d0 = __ldg(reinterpret_cast<const float4*>(dp)), d1 = __ldg(reinterpret_cast<const float4*>(dp + 16));
+          dyv[o][0][0] = d0.x; dyv[o][1][0] = d0.y; dyv[o][2][0] = d0.z; dyv[o][3][0] = d0.w;
+          dyv[o][0][1] = d1.x; dyv[o][1][1] = d1.y; dyv[o][2][1] = d1.z; dyv[o][3][1] = d1.w;
+          if (hc == 0 && g == 0) db2p[o] += ((d0.x + d0.y) + (d0.z + d0.w)) + ((d1.x + d1.y) + (d1.z + d1.w));
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) dyv[o][j][0] = dyv[o][j][1] = 0.f;
+        }
+      }
+#pragma unroll
+      for (int m = 0; m < 2; ++m)
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          const int hl = 16 * m + g + 8 * hh, h = hc + hl;
+          const float bias = b1s[h];
+          float w2v[NO];
+#pragma unroll
+          for (int o = 0; o < NO; ++o) w2v[o] = w2s[o * HP + h];
+          float dzr[4][2];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            float h0, h1, g0, g1;
+            gelu_both2(acc[m][j][2 * hh] + bias, acc[m][j][2 * hh + 1] + bias, h0, h1, g0, g1);
+            float dh0 = 0.f, dh1 = 0.f;
+#pragma unroll
+            for (int o = 0; o < NO; ++o) {
+              dh0 = fmaf(w2v[o], dyv[o][j][0], dh0);
+              dh1 = fmaf(w2v[o], dyv[o][j][1], dh1);
+              dw2p[o][m][hh] = fmaf(dyv[o][j][0], h0, fmaf(dyv[o][j][1], h1, dw2p[o][m][hh]));
+            }
+            dzr[j][0] = dh0 * g0;
+            dzr[j][1] = dh1 * g1;
+            db1p[m][hh] += dzr[j][0] + dzr[j][1];
+            acc[m][j][2 * hh] = dzr[j][0];
+            acc[m][j][2 * hh + 1] = dzr[j][1];
+          }
+          *reinterpret_cast<float4*>(mybuf + hl * MLP_LDX + 4 * t) = make_float4(dzr[0][0], dzr[1][0], dzr[2][0], dzr[3][0]);
+          *reinterpret_cast<float4*>(mybuf + hl * MLP_LDX + 16 + 4 * t) = make_float4(dzr[0][1], dzr[1][1], dzr[2][1], dzr[3][1]);
+        }
+      __syncwarp();
+      // ---- 3. dw1[chunk] += dz x^T: k-step j, k = t <-> point 4 t + j, k = t + 4 <-> point 16 + 4 t + j -----------------
+      {
+        float4 xa[KS], xc[KS];
+#pragma unroll
+        for (int q = 0; q < KS; ++q) {
+          xa[q] = *reinterpret_cast<const float4*>(xt + (8 * q + g) * MLP_LDX + 4 * t);
+          xc[q] = *reinterpret_cast<const float4*>(xt + (8 * q + g) * MLP_LDX + 16 + 4 * t);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint32_t ah[2][4], al[2][4];
+#pragma unroll
+          for (int m = 0; m < 2; ++m) {
+            tf32_split(acc[m][j][0], ah[m][0], al[m][0]);
+            tf32_split(acc[m][j][2], ah[m][1], al[m][1]);
+            tf32_split(acc[m][j][1], ah[m][2], al[m][2]);
+            tf32_split(acc[m][j][3], ah[m][3], al[m][3]);
+          }
+#pragma unroll
+          for (int q = 0; q < KS; ++q) {
+            const float va = j == 0 ? xa[q].x : j == 1 ? xa[q].y : j == 2 ? xa[q].z : xa[q].w;
+            const float vc = j == 0 ? xc[q].x : j == 1 ? xc[q].y : j == 2 ? xc[q].z : xc[q].w;
+            uint32_t bh0, bl0, bh1, bl1;
+            tf32_split(va, bh0, bl0);
+            tf32_split(vc, bh1, bl1);
+            mma_3xtf32(dw1acc[0][q], ah[0], al[0], bh0, bh1, bl0, bl1);
+            mma_3xtf32(dw1acc[1][q], ah[1], al[1], bh0, bh1, bl0, bl1);
+          }
+        }
+      }
+      // ---- 4. dx partial = W1[chunk]^T dz --------------------------------------------------------------------------
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks) {
+        const float4 z0 = *reinterpret_cast<const float4*>(mybuf + (8 * ks + t) * MLP_LDX + 4 * pg);
+        const float4 z1 = *reinterpret_cast<const float4*>(mybuf + (8 * ks + t + 4) * MLP_LDX + 4 * pg);
+        const float v0[4] = {z0.x, z0.y, z0.z, z0.w}, v1[4] = {z1.x, z1.y, z1.z, z1.w};
+        uint32_t bh0[4], bh1[4], bl0[4], bl1[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          tf32_split(v0[j], bh0[j], bl0[j]);
+          tf32_split(v1[j], bh1[j], bl1[j]);
+        }
+#pragma unroll
+        for (int mt = 0; mt < IT; ++mt) {
+          const float* wr = w1s + (hc + 8 * ks + t) * LDW + 2 * (16 * mt + g);
+          const float2 a0 = *reinterpret_cast<const float2*>(wr);
+          const float2 a1 = *reinterpret_cast<const float2*>(wr + 16);
+          const float2 a2 = *reinterpret_cast<const float2*>(wr + 4 * LDW);
+          const float2 a3 = *reinterpret_cast<const float2*>(wr + 4 * LDW + 16);
+          const uint32_t ah[4] = {__float_as_uint(a0.x), __float_as_uint(a1.x), __float_as_uint(a2.x), __float_as_uint(a3.x)};
+          const uint32_t al[4] = {__float_as_uint(a0.y), __float_as_uint(a1.y), __float_as_uint(a2.y), __float_as_uint(a3.y)};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) mma_3xtf32(dxacc[mt][j], ah, al, bh0[j], bh1[j], bl0[j], bl1[j]);
+        }
+      }
+      __syncwarp();
+    }
+    // ---- 5. dx = sum over the chunk warps, 16 input channels per round --------------------------------------------
+#pragma unroll
+    for (int mt = 0; mt < IT; ++mt) {
+      if (live) {
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          float* row = mybuf + (g + 8 * hh) * MLP_LDX;
+          *reinterpret_cast<float4*>(row + 4 * t) =
+              make_float4(dxacc[mt][0][2 * hh], dxacc[mt][1][2 * hh], dxacc[mt][2][2 * hh], dxacc[mt][3][2 * hh]);
+          *reinterpret_cast<float4*>(row + 16 + 4 * t) =
+              make_float4(dxacc[mt][0][2 * hh + 1], dxacc[mt][1][2 * hh + 1], dxacc[mt][2][2 * hh + 1], dxacc[mt][3][2 * hh + 1]);
+        }
+      }
+      __syncthreads();
+      if (dx) {
+        // the point tile's NCH warps share its 16 rows x 8 float4
+        for (int e = tid - ptid * NCH * 32; live && e < 128; e += NCH * 32) {
+          const int r = e >> 3, p4 = e & 7, i = 16 * mt + r;
+          if (i < I) {
+            float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int w = 0; w < NCH; ++w) {
+              const float4 v = *reinterpret_cast<const float4*>(bufs + ((ptid * NCH + w) * 32 + r) * MLP_LDX + 4 * p4);
+              sum.x += v.x; sum.y += v.y; sum.z += v.z; sum.w += v.w;
+            }
+            *reinterpret_cast<float4*>(dx + ((long long)b * I + i) * S + n0 + 4 * p4) = sum;
+          }
+        }
+      }
+      __syncthreads();
+    }
+    bufi ^= 1;
+  }
+  // ---- parameter gradients ---------------------------------------------------------------------------------------
+#pragma unroll
+  for (int m = 0; m < 2; ++m) {
+#pragma unroll
+    for (int q = 0; q < KS; ++q)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const int h = hc + 16 * m + g + 8 * (c >> 1), i = 8 * q + 2 * t + (c & 1);
+        if (h < Hd && i < I) atomicAdd(dw1 + (long long)h * I + i, dw1acc[m][q][c]);
+      }
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      const int h = hc + 16 * m + g + 8 * hh;
+      float v = db1p[m][hh];
+      v += __shfl_xor_sync(0xffffffffu, v, 1);
+      v += __shfl_xor_sync(0xffffffffu, v, 2);
+      if (t == 0 && h < Hd && db1) atomicAdd(db1 + h, v);
+#pragma unroll
+      for (int o = 0; o < NO; ++o) {
+        float u = dw2p[o][m][hh];
+        u += __shfl_xor_sync(0xffffffffu, u, 1);
+        u += __shfl_xor_sync(0xffffffffu, u, 2);
+        if (t == 0 && h < Hd && o < O) atomicAdd(dw2 + (long long)o * Hd + h, u);
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 0; o < NO; ++o) {
+    float v = db2p[o];   // non-zero only in lanes g == 0 of the chunk-0 warps: the four t lanes hold disjoint points
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    if (lane == 0 && hc == 0 && o < O && db2) atomicAdd(db2 + o, v);
   }
 }
 

@@ -1075,6 +1075,66 @@ int rpde_conv1x1_bwd_params(const float* dy, const float* x, float* dw, float* d
   return RPDE_OK;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Fused projection MLP (fno2d_mma.cuh): the hidden layer never reaches HBM
+// ------------------------------------------------------------------------------------------------
+int rpde_mlp_supported(int I, int Hd, int O, long long S) {
+  static const bool use_mma = !(getenv("RPDE_FNO2D_MMA") && atoi(getenv("RPDE_FNO2D_MMA")) == 0);
+  const int HP = (Hd + 31) & ~31;
+  return use_mma && I >= 1 && I <= 64 && Hd >= 1 && (HP == 32 || HP == 64 || HP == 128 || HP == 256) && O >= 1 && O <= MLP_MAXO &&
+                 S > 0 && S % 32 == 0 && S <= INT_MAX
+             ? 1 : 0;
+}
+
+int rpde_mlp_fwd(const float* x, const float* w1, const float* b1, const float* w2, const float* b2, float* y, int B, int I, int Hd,
+                 int O, long long S, rpde_stream_t stream) {
+  if (!x || !w1 || !w2 || !y || B <= 0) return fail(RPDE_E_INVALID, "rpde_mlp_fwd: bad arguments%s");
+  if (!rpde_mlp_supported(I, Hd, O, S))
+    return fail(RPDE_E_INVALID, "rpde_mlp_fwd: shape outside the fused kernel (I <= 64, hidden 32/64/128/256, O <= 4, S % 32 == 0)%s");
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t smem = mlp_fwd_smem(I, Hd);
+  const long long tiles = (long long)B * (S / 32);
+  const int per_sm = I <= 32 ? 2 : 1;
+  long long ctas = (tiles + 7) / 8;
+  if (ctas > 148LL * per_sm) ctas = 148LL * per_sm;
+#define RPDE_MLP_FWD(KS, NO)                                                                                                    \
+  do {                                                                                                                          \
+    RPDE_CUDA(cudaFuncSetAttribute(mlp_fwd_mma_kernel<KS, NO>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));        \
+    mlp_fwd_mma_kernel<KS, NO><<<(unsigned)ctas, 256, smem, s>>>(x, w1, b1, w2, b2, y, B, I, Hd, O, (int)S);                    \
+  } while (0)
+  if (I <= 32) { if (O == 1) RPDE_MLP_FWD(4, 1); else RPDE_MLP_FWD(4, MLP_MAXO); }
+  else { if (O == 1) RPDE_MLP_FWD(8, 1); else RPDE_MLP_FWD(8, MLP_MAXO); }
+#undef RPDE_MLP_FWD
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+
+int rpde_mlp_bwd(const float* x, const float* dy, const float* w1, const float* b1, const float* w2, float* dx, float* dw1,
+                 float* db1, float* dw2, float* db2, int B, int I, int Hd, int O, long long S, rpde_stream_t stream) {
+  if (!x || !dy || !w1 || !w2 || !dw1 || !dw2 || B <= 0) return fail(RPDE_E_INVALID, "rpde_mlp_bwd: bad arguments%s");
+  if (!rpde_mlp_supported(I, Hd, O, S)) return fail(RPDE_E_INVALID, "rpde_mlp_bwd: shape outside the fused kernel%s");
+  cudaStream_t s = (cudaStream_t)stream;
+  RPDE_CUDA(cudaMemsetAsync(dw1, 0, (size_t)Hd * I * sizeof(float), s));
+  RPDE_CUDA(cudaMemsetAsync(dw2, 0, (size_t)O * Hd * sizeof(float), s));
+  if (db1) RPDE_CUDA(cudaMemsetAsync(db1, 0, (size_t)Hd * sizeof(float), s));
+  if (db2) RPDE_CUDA(cudaMemsetAsync(db2, 0, (size_t)O * sizeof(float), s));
+  const size_t smem = mlp_bwd_smem(I, Hd);
+  const int HP = (Hd + 31) & ~31, PT = 256 / HP;
+  const long long tiles = (long long)B * (S / 32);
+  long long ctas = (tiles + PT - 1) / PT;
+  if (ctas > 148) ctas = 148;
+#define RPDE_MLP_BWD(KS, NO)                                                                                                    \
+  do {                                                                                                                          \
+    RPDE_CUDA(cudaFuncSetAttribute(mlp_bwd_mma_kernel<KS, NO>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));        \
+    mlp_bwd_mma_kernel<KS, NO><<<(unsigned)ctas, 256, smem, s>>>(x, dy, w1, b1, w2, dx, dw1, db1, dw2, db2, B, I, Hd, O, (int)S); \
+  } while (0)
+  if (I <= 32) { if (O == 1) RPDE_MLP_BWD(4, 1); else RPDE_MLP_BWD(4, MLP_MAXO); }
+  else { if (O == 1) RPDE_MLP_BWD(8, 1); else RPDE_MLP_BWD(8, MLP_MAXO); }
+#undef RPDE_MLP_BWD
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+
 int rpde_act_bwd(const float* dy, const float* z, float* out, long long n, int act, rpde_stream_t stream) {
   if (!dy || !z || !out || n <= 0) return fail(RPDE_E_INVALID, "rpde_act_bwd: bad arguments%s");
   dact_mul_kernel<<<grid_for(n), 256, 0, (cudaStream_t)stream>>>(dy, z, out, n, act);

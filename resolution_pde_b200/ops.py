@@ -721,6 +721,9 @@ def conv1x1(x, w, b=None):
     return _Conv1x1Fn.apply(x, w, b)
 
 
+_mlp_fused = True   # tests flip it to run the composed projection MLP (two 1x1 convs through the contraction engine)
+
+
 class _MLPFn(torch.autograd.Function):
     """projection MLP (fno_blocks.py:35-45, 73-83): conv1x1 -> GELU -> conv1x1, GELU fused in both directions."""
 
@@ -735,26 +738,46 @@ class _MLPFn(torch.autograd.Function):
         w1c = w1.detach().reshape(H, I).contiguous()
         w2c = w2.detach().reshape(O, H).contiguous()
         need_grad = grad_on and any(ctx.needs_input_grad)
+        y = torch.empty((B, O) + spatial, dtype=torch.float32, device=x.device)
+        with _Ctx(x) as c:
+            if _mlp_fused and c.lib.rpde_mlp_supported(I, H, O, S):
+                # one kernel, hidden layer in registers (csrc/fno2d_mma.cuh); backward recomputes it from x
+                _lib.check(c.lib.rpde_mlp_fwd(_p(x), _p(w1c), _p(b1), _p(w2c), _p(b2), _p(y), B, I, H, O, S, c.stream),
+                           "rpde_mlp_fwd")
+                ctx.save_for_backward(x, w1, w2, b1)
+                ctx.cfg = (B, I, H, O, S, b1 is not None, b2 is not None, True)
+                return y
         h = torch.empty((B, H) + spatial, dtype=torch.float32, device=x.device)
         z = torch.empty_like(h) if need_grad else None
-        y = torch.empty((B, O) + spatial, dtype=torch.float32, device=x.device)
         with _Ctx(x) as c:
             _lib.check(c.lib.rpde_conv1x1_fwd(_p(x), _p(w1c), _p(b1), _p(h), _p(z), B, I, H, S, ACT_GELU, 0, c.stream),
                        "rpde_conv1x1_fwd")
             _lib.check(c.lib.rpde_conv1x1_fwd(_p(h), _p(w2c), _p(b2), _p(y), None, B, H, O, S, ACT_NONE, 0, c.stream),
                        "rpde_conv1x1_fwd")
         ctx.save_for_backward(x, w1, w2, h, z)
-        ctx.cfg = (B, I, H, O, S, b1 is not None, b2 is not None)
+        ctx.cfg = (B, I, H, O, S, b1 is not None, b2 is not None, False)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        x, w1, w2, h, z = ctx.saved_tensors
-        B, I, H, O, S, hb1, hb2 = ctx.cfg
+        B, I, H, O, S, hb1, hb2, fused = ctx.cfg
         dy = dy.contiguous()
+        dev = dy.device
+        if fused:
+            x, w1, w2, b1 = ctx.saved_tensors
+            w1c = w1.detach().reshape(H, I).contiguous()
+            w2c = w2.detach().reshape(O, H).contiguous()
+            dx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
+            dw1, dw2 = torch.empty_like(w1), torch.empty_like(w2)
+            db1 = torch.empty(H, dtype=torch.float32, device=dev) if hb1 else None
+            db2 = torch.empty(O, dtype=torch.float32, device=dev) if hb2 else None
+            with _Ctx(x) as c:
+                _lib.check(c.lib.rpde_mlp_bwd(_p(x), _p(dy), _p(w1c), _p(b1), _p(w2c), _p(dx), _p(dw1), _p(db1), _p(dw2), _p(db2),
+                                              B, I, H, O, S, c.stream), "rpde_mlp_bwd")
+            return dx, dw1, db1, dw2, db2, None
+        x, w1, w2, h, z = ctx.saved_tensors
         w1c = w1.detach().reshape(H, I).contiguous()
         w2c = w2.detach().reshape(O, H).contiguous()
-        dev = x.device
         dx = None
         with _Ctx(x) as c:
             dw2 = torch.empty_like(w2)
