@@ -28,14 +28,23 @@ __device__ __forceinline__ uint32_t tf32_hi(float v) {
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
   return r;
 }
-__device__ __forceinline__ void tf32_split(float v, uint32_t& hi, uint32_t& lo) {
+// resident operands (split once): round to nearest
+__device__ __forceinline__ void tf32_split_rn(float v, uint32_t& hi, uint32_t& lo) {
   hi = tf32_hi(v);
-  lo = __float_as_uint(v - __uint_as_float(hi));   // the tensor core reads the top 19 bits: residual 2^-11 * 2^-10 relative
+  lo = __float_as_uint(v - __uint_as_float(hi));
+}
+// streamed operands: hi = v rounded to 10 mantissa bits, half away from zero, by an integer add and a mask (cvt.rna.tf32
+// costs four instructions on sm_100: compare against inf, add, mask, select), lo = v - hi exactly.  Rounding, not truncating:
+// a truncated hi leaves lo with the sign of v, and the tensor core's own truncation of lo then biases every product the same
+// way -- measured 2.4e-5 on a cancelling 262144-term weight-gradient sum; with a rounded hi the residual errors have random sign.
+__device__ __forceinline__ void tf32_split(float v, uint32_t& hi, uint32_t& lo) {
+  hi = (__float_as_uint(v) + 0x1000u) & 0xffffe000u;
+  lo = __float_as_uint(v - __uint_as_float(hi));
 }
 // the same, pinned where it is written: inside a loop over output chunks the compiler would otherwise hoist the split of
 // loop-invariant operands and keep hi and lo planes live (2x the registers of the raw operand)
 __device__ __forceinline__ void tf32_split_here(float v, uint32_t& hi, uint32_t& lo) {
-  asm volatile("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(v));
+  asm volatile("and.b32 %0, %1, 0xffffe000;" : "=r"(hi) : "r"(__float_as_uint(v) + 0x1000u));
   lo = __float_as_uint(v - __uint_as_float(hi));
 }
 __device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
@@ -87,7 +96,7 @@ __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __
     float v = 0.f;
     if (r < R) v = __ldg(table + (adjoint ? (long long)r : (long long)(r & 1) * K + (r >> 1)) * W + n);
     uint32_t hi, lo;
-    tf32_split(v, hi, lo);
+    tf32_split_rn(v, hi, lo);
     tabH[r * LDT + n] = __uint_as_float(hi);
     tabL[r * LDT + n] = __uint_as_float(tf32_hi(__uint_as_float(lo)));
   }
@@ -96,7 +105,7 @@ __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __
     float v = 0.f;
     if (wb && i < I && o < O) v = __ldg(adjoint ? wb + (long long)i * O + o : wb + (long long)o * I + i);
     uint32_t hi, lo;
-    tf32_split(v, hi, lo);
+    tf32_split_rn(v, hi, lo);
     wbH[i * F2M_LDA + o] = __uint_as_float(hi);
     wbL[i * F2M_LDA + o] = __uint_as_float(tf32_hi(__uint_as_float(lo)));
   }
@@ -150,11 +159,24 @@ __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __
     }
   };
 
-  float4 xb[8];
+  // the next iteration's x rows are only pulled into L2 (no registers held across the MMA loop; the eight lanes g = 0..7
+  // of equal t share a 128-byte line, lane g = 0 asks for it)
+  auto prefetch_x = [&](int tile) {
+    const int row = tile * RPI + wrow;
+    if (row >= Bn || g != 0) return;
+    const int bh = row / Hd, hh = row - bh * Hd;
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int i = 8 * ks + t + 4 * h;
+        if (ks < KS_X && i < I)
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(x + (((long long)bh * I + i) * Hd + hh) * W + n0));
+      }
+  };
   float zb[ZPT];
   int tile = blockIdx.x;
   if (tile < ntiles) {
-    load_x(tile, xb);
     load_z(tile, zb);
     store_z(0, zb);
   }
@@ -163,9 +185,10 @@ __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __
   int stage = 0;
   for (; tile < ntiles; tile += gridDim.x) {
     const int next = tile + gridDim.x;
-    float4 xn[8];
+    float4 xb[8];
+    load_x(tile, xb);
     if (next < ntiles) {
-      load_x(next, xn);
+      prefetch_x(next);
       load_z(next, zb);
     }
     const int row = tile * RPI + wrow;
@@ -251,9 +274,14 @@ __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __
             for (int c = 0; c < 2; ++c) {
               float pre[4], out[4];
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                pre[j] = acc[m][j][2 * half + c] + bias;
-                out[j] = act_f(act, pre[j]);
+              for (int j = 0; j < 4; ++j) pre[j] = acc[m][j][2 * half + c] + bias;
+              if (act == ACT_GELU) {   // two elements per instruction on the packed fp32x2 pipe
+                float d0, d1;
+                gelu_both2(pre[0], pre[1], out[0], out[1], d0, d1);
+                gelu_both2(pre[2], pre[3], out[2], out[3], d0, d1);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) out[j] = act_f(act, pre[j]);
               }
               *reinterpret_cast<float4*>(y + base + 16 * c) = make_float4(out[0], out[1], out[2], out[3]);
               if (z) *reinterpret_cast<float4*>(z + base + 16 * c) = make_float4(pre[0], pre[1], pre[2], pre[3]);
@@ -262,11 +290,7 @@ __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __
         }
       }
     }
-    if (next < ntiles) {
-      store_z(stage ^ 1, zb);
-#pragma unroll
-      for (int q = 0; q < 8; ++q) xb[q] = xn[q];
-    }
+    if (next < ntiles) store_z(stage ^ 1, zb);
     __syncthreads();
     stage ^= 1;
   }
@@ -287,23 +311,20 @@ __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __
 __global__ void __launch_bounds__(256, 2) conv1x1_wgrad_mma_kernel(const float* __restrict__ dy, const float* __restrict__ x,
                                                                    float* __restrict__ dw, float* __restrict__ db, int Bn, int I,
                                                                    int O, int S) {
-  __shared__ float red[8][32 * 33];
+  // per-warp sums [32 o][40]: columns 0..31 the weight block, 32 the bias; stride 40 keeps the float2 updates conflict-free
+  __shared__ __align__(16) float red[8][32 * 40];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
   const int nbi = (I + 31) / 32, nbo = (O + 31) / 32, NB = nbi * nbo;      // 1, 2 or 4 blocks
   const int blk = warp % NB, stream = warp / NB, nstreams = 8 / NB;
   const int o0 = (blk / nbi) * 32, i0 = (blk % nbi) * 32;
   const int segs = S / 32;
   const long long ntiles = (long long)Bn * segs;
-  float acc[2][4][4];
   float bsum[2][2];
 #pragma unroll
-  for (int m = 0; m < 2; ++m) {
-    bsum[m][0] = bsum[m][1] = 0.f;
-#pragma unroll
-    for (int q = 0; q < 4; ++q)
-#pragma unroll
-      for (int c = 0; c < 4; ++c) acc[m][q][c] = 0.f;
-  }
+  for (int m = 0; m < 2; ++m) bsum[m][0] = bsum[m][1] = 0.f;
+  float* mine = red[warp];
+  for (int e = lane; e < 32 * 40; e += 32) mine[e] = 0.f;
+  __syncwarp();
   for (long long tile = (long long)blockIdx.x * nstreams + stream; tile < ntiles; tile += (long long)gridDim.x * nstreams) {
     const int b = (int)(tile / segs), n0 = (int)(tile - (long long)b * segs) * 32;
     float4 dv[2][2][2], xv[4][2];
@@ -331,6 +352,15 @@ __global__ void __launch_bounds__(256, 2) conv1x1_wgrad_mma_kernel(const float* 
       for (int hh = 0; hh < 2; ++hh)
 #pragma unroll
         for (int c = 0; c < 2; ++c) bsum[m][hh] += (dv[m][hh][c].x + dv[m][hh][c].y) + (dv[m][hh][c].z + dv[m][hh][c].w);
+    // the tile's MMA chain starts from zero and is added to the warp's sums with round-to-nearest adds: the tensor core
+    // truncates when it adds into its accumulator, and a chain over all tiles would bias cancelling sums by ~1e-5
+    float acc[2][4][4];
+#pragma unroll
+    for (int m = 0; m < 2; ++m)
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) acc[m][q][c] = 0.f;
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       auto comp = [&](const float4& v) { return j == 0 ? v.x : j == 1 ? v.y : j == 2 ? v.z : v.w; };
@@ -350,18 +380,20 @@ __global__ void __launch_bounds__(256, 2) conv1x1_wgrad_mma_kernel(const float* 
         for (int q = 0; q < 4; ++q) mma_3xtf32(acc[m][q], ah, al, bh[q][0], bh[q][1], bl[q][0], bl[q][1]);
       }
     }
+#pragma unroll
+    for (int m = 0; m < 2; ++m)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        float2* p0 = reinterpret_cast<float2*>(mine + (16 * m + g) * 40 + 8 * q + 2 * t);
+        float2* p1 = reinterpret_cast<float2*>(mine + (16 * m + g + 8) * 40 + 8 * q + 2 * t);
+        float2 a = *p0, b = *p1;
+        a.x += acc[m][q][0]; a.y += acc[m][q][1];
+        b.x += acc[m][q][2]; b.y += acc[m][q][3];
+        *p0 = a;
+        *p1 = b;
+      }
   }
   // CTA reduction: the streams of one block add up in shared memory, then one atomic per element
-  float* mine = red[warp];
-#pragma unroll
-  for (int m = 0; m < 2; ++m)
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      mine[(16 * m + g) * 33 + 8 * q + 2 * t] = acc[m][q][0];
-      mine[(16 * m + g) * 33 + 8 * q + 2 * t + 1] = acc[m][q][1];
-      mine[(16 * m + g + 8) * 33 + 8 * q + 2 * t] = acc[m][q][2];
-      mine[(16 * m + g + 8) * 33 + 8 * q + 2 * t + 1] = acc[m][q][3];
-    }
   // bias partial sums: the four lanes of a group hold the same rows; column 32 of the staging tile carries them
 #pragma unroll
   for (int m = 0; m < 2; ++m)
@@ -370,14 +402,14 @@ __global__ void __launch_bounds__(256, 2) conv1x1_wgrad_mma_kernel(const float* 
       float v = bsum[m][hh];
       v += __shfl_xor_sync(0xffffffffu, v, 1);
       v += __shfl_xor_sync(0xffffffffu, v, 2);
-      if (t == 0) mine[(16 * m + g + 8 * hh) * 33 + 32] = v;
+      if (t == 0) mine[(16 * m + g + 8 * hh) * 40 + 32] = v;
     }
   __syncthreads();
   for (int e = tid; e < NB * 32 * 33; e += 256) {
     const int bk = e / (32 * 33), r = e - bk * 32 * 33;
     const int row = r / 33, col = r - row * 33;
     float v = 0.f;
-    for (int st = 0; st < nstreams; ++st) v += red[st * NB + bk][r];
+    for (int st = 0; st < nstreams; ++st) v += red[st * NB + bk][row * 40 + col];
     const int o = (bk / nbi) * 32 + row;
     if (o >= O) continue;
     if (col == 32) {
@@ -401,21 +433,42 @@ __global__ void __launch_bounds__(256, 2) conv1x1_wgrad_mma_kernel(const float* 
 // into y[o][n] += w2[o][h] gelu(z) on the CUDA cores; one 8-lane shuffle reduction per tile, float4 stores.
 constexpr int MLP_MAXO = 4;
 __host__ __device__ constexpr int mlp_ip(int I) { return I <= 32 ? 32 : 64; }          // input channels as the register tiles see them
-__host__ __device__ constexpr int mlp_ldw(int I) { return 2 * mlp_ip(I) + 8; }         // floats per W1 row (hi, lo pairs), = 8 mod 32
+__host__ __device__ constexpr int mlp_ldw(int I) { return mlp_ip(I) + 4; }             // W1 plane row stride, = 4 mod 32
 __host__ __device__ constexpr size_t mlp_fwd_smem(int I, int Hd) {
-  return ((size_t)((Hd + 31) & ~31) * mlp_ldw(I) + (size_t)(MLP_MAXO + 1) * ((Hd + 31) & ~31)) * sizeof(float);
+  return ((size_t)2 * ((Hd + 31) & ~31) * mlp_ldw(I) + (size_t)(MLP_MAXO + 1) * ((Hd + 31) & ~31)) * sizeof(float);
 }
-
-// W1 (Hd, I) -> shared (hi, lo) pairs, rows and columns zero-padded to multiples of 32 / 8
-__device__ __forceinline__ void mlp_stage_w1(const float* __restrict__ w1, float* w1s, int I, int Hd, int HP, int LDW) {
-  const int IP = mlp_ip(I);
+// W1 lives in shared memory as two planes (TF32 hi, lo) [h][LDW], read with scalar loads at compile-time offsets from one
+// per-lane base (no address arithmetic and no register shuffling in front of the MMA).  LDW = 4 mod 32: the fragments of
+// z = W1 x (A[m = h][k = i]: lanes (g, t) -> row h0 + g, column i0 + t) hit 32 distinct banks, those of dx = W1^T dz
+// (A[m = i][k = h]: lanes (g, t) -> row h0 + t, column i0 + g) take a 2-way conflict (cheaper than a second copy).
+__device__ __forceinline__ void mlp_stage_w1(const float* __restrict__ w1, float* w1h, float* w1l, int I, int Hd, int HP, int IP) {
+  const int LDW = IP + 4;
   for (int e = threadIdx.x; e < HP * IP; e += blockDim.x) {
     const int h = e / IP, i = e - h * IP;
     const float v = (h < Hd && i < I) ? __ldg(w1 + (long long)h * I + i) : 0.f;
     uint32_t hi, lo;
-    tf32_split(v, hi, lo);
-    *reinterpret_cast<float2*>(w1s + h * LDW + 2 * i) = make_float2(__uint_as_float(hi), __uint_as_float(tf32_hi(__uint_as_float(lo))));
+    tf32_split_rn(v, hi, lo);
+    w1h[h * LDW + i] = __uint_as_float(hi);
+    w1l[h * LDW + i] = __uint_as_float(tf32_hi(__uint_as_float(lo)));
   }
+}
+// A fragment of the z orientation at (h0, i0): bz = plane + g * LDW + t
+template <int LDW>
+__device__ __forceinline__ void mlp_afrag_z(const float* bzh, const float* bzl, int h0, int i0, uint32_t (&ah)[4], uint32_t (&al)[4]) {
+  const int o = h0 * LDW + i0;
+  ah[0] = __float_as_uint(bzh[o]); ah[1] = __float_as_uint(bzh[o + 8 * LDW]);
+  ah[2] = __float_as_uint(bzh[o + 4]); ah[3] = __float_as_uint(bzh[o + 8 * LDW + 4]);
+  al[0] = __float_as_uint(bzl[o]); al[1] = __float_as_uint(bzl[o + 8 * LDW]);
+  al[2] = __float_as_uint(bzl[o + 4]); al[3] = __float_as_uint(bzl[o + 8 * LDW + 4]);
+}
+// A fragment of the transposed orientation at (h0, i0): rows (m) are input channels, columns (k) hidden rows; bx = plane + t * LDW + g
+template <int LDW>
+__device__ __forceinline__ void mlp_afrag_x(const float* bxh, const float* bxl, int h0, int i0, uint32_t (&ah)[4], uint32_t (&al)[4]) {
+  const int o = h0 * LDW + i0;
+  ah[0] = __float_as_uint(bxh[o]); ah[1] = __float_as_uint(bxh[o + 8]);
+  ah[2] = __float_as_uint(bxh[o + 4 * LDW]); ah[3] = __float_as_uint(bxh[o + 4 * LDW + 8]);
+  al[0] = __float_as_uint(bxl[o]); al[1] = __float_as_uint(bxl[o + 8]);
+  al[2] = __float_as_uint(bxl[o + 4 * LDW]); al[3] = __float_as_uint(bxl[o + 4 * LDW + 8]);
 }
 
 template <int KS, int NO>   // k-steps of eight input channels: 4 (I <= 32) or 8 (I <= 64); NO: outputs held (1 or MLP_MAXO)
@@ -424,13 +477,15 @@ __global__ void __launch_bounds__(256, KS == 4 ? 2 : 1) mlp_fwd_mma_kernel(const
                                                                           const float* __restrict__ b2, float* __restrict__ y, int Bn,
                                                                           int I, int Hd, int O, int S) {
   extern __shared__ __align__(16) float smem[];
-  const int HP = (Hd + 31) & ~31, LDW = mlp_ldw(I);
-  float* w1s = smem;                  // [HP][LDW]  (hi, lo) pairs
-  float* b1s = w1s + HP * LDW;        // [HP]
+  constexpr int IP = 8 * KS, LDW = IP + 4;
+  const int HP = (Hd + 31) & ~31;
+  float* w1h = smem;                  // [HP][LDW]
+  float* w1l = w1h + HP * LDW;
+  float* b1s = w1l + HP * LDW;        // [HP]
   float* w2s = b1s + HP;              // [MLP_MAXO][HP]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
   const int pg = (g >> 1) + 4 * (g & 1);
-  mlp_stage_w1(w1, w1s, I, Hd, HP, LDW);
+  mlp_stage_w1(w1, w1h, w1l, I, Hd, HP, IP);
   for (int e = tid; e < HP; e += 256) {
     b1s[e] = (b1 && e < Hd) ? __ldg(b1 + e) : 0.f;
 #pragma unroll
@@ -456,6 +511,8 @@ __global__ void __launch_bounds__(256, KS == 4 ? 2 : 1) mlp_fwd_mma_kernel(const
 #pragma unroll
       for (int j = 0; j < 4; ++j) ysum[o][j][0] = ysum[o][j][1] = 0.f;
     for (int hc = 0; hc < HP; hc += 32) {
+      const float* bzh = w1h + (hc + g) * LDW + t;
+      const float* bzl = w1l + (hc + g) * LDW + t;
       float acc[2][4][4];
 #pragma unroll
       for (int m = 0; m < 2; ++m)
@@ -475,13 +532,8 @@ __global__ void __launch_bounds__(256, KS == 4 ? 2 : 1) mlp_fwd_mma_kernel(const
         }
 #pragma unroll
         for (int m = 0; m < 2; ++m) {
-          const float* wr = w1s + (hc + 16 * m + g) * LDW + 2 * (8 * ks + t);
-          const float2 a0 = *reinterpret_cast<const float2*>(wr);
-          const float2 a1 = *reinterpret_cast<const float2*>(wr + 8 * LDW);
-          const float2 a2 = *reinterpret_cast<const float2*>(wr + 8);
-          const float2 a3 = *reinterpret_cast<const float2*>(wr + 8 * LDW + 8);
-          const uint32_t ah[4] = {__float_as_uint(a0.x), __float_as_uint(a1.x), __float_as_uint(a2.x), __float_as_uint(a3.x)};
-          const uint32_t al[4] = {__float_as_uint(a0.y), __float_as_uint(a1.y), __float_as_uint(a2.y), __float_as_uint(a3.y)};
+          uint32_t ah[4], al[4];
+          mlp_afrag_z<LDW>(bzh, bzl, 16 * m, 8 * ks, ah, al);
 #pragma unroll
           for (int j = 0; j < 4; ++j) mma_3xtf32(acc[m][j], ah, al, bh0[j], bh1[j], bl0[j], bl1[j]);
         }
@@ -549,22 +601,23 @@ __global__ void __launch_bounds__(256, KS == 4 ? 2 : 1) mlp_fwd_mma_kernel(const
 constexpr int MLP_LDX = 36;   // x / dz tiles [row][32 points]: stride = 4 mod 32
 __host__ __device__ constexpr size_t mlp_bwd_smem(int I, int Hd) {
   const int HP = (Hd + 31) & ~31, IP = mlp_ip(I);
-  return ((size_t)HP * mlp_ldw(I) + (size_t)(MLP_MAXO + 1) * HP + (size_t)2 * (256 / HP) * IP * MLP_LDX + (size_t)8 * 32 * MLP_LDX) *
+  return ((size_t)2 * HP * (IP + 4) + (size_t)(MLP_MAXO + 1) * HP + (size_t)2 * (256 / HP) * IP * MLP_LDX + (size_t)8 * 32 * MLP_LDX) *
          sizeof(float);
 }
 
 template <int KS, int NO>
-__global__ void __launch_bounds__(256, 1) mlp_bwd_mma_kernel(const float* __restrict__ x, const float* __restrict__ dy,
+__global__ void __launch_bounds__(256, KS == 4 ? 2 : 1) mlp_bwd_mma_kernel(const float* __restrict__ x, const float* __restrict__ dy,
                                                              const float* __restrict__ w1, const float* __restrict__ b1,
                                                              const float* __restrict__ w2, float* __restrict__ dx,
                                                              float* __restrict__ dw1, float* __restrict__ db1,
                                                              float* __restrict__ dw2, float* __restrict__ db2, int Bn, int I, int Hd,
                                                              int O, int S) {
-  constexpr int IP = 8 * KS, IT = KS / 2;
+  constexpr int IP = 8 * KS, IT = KS / 2, LDW = IP + 4;
   extern __shared__ __align__(16) float smem[];
-  const int HP = (Hd + 31) & ~31, LDW = mlp_ldw(I), NCH = HP / 32, PT = 8 / NCH;
-  float* w1s = smem;
-  float* b1s = w1s + HP * LDW;
+  const int HP = (Hd + 31) & ~31, NCH = HP / 32, PT = 8 / NCH;
+  float* w1h = smem;
+  float* w1l = w1h + HP * LDW;
+  float* b1s = w1l + HP * LDW;
   float* w2s = b1s + HP;
   float* xs = w2s + MLP_MAXO * HP;                     // [2][PT][IP][MLP_LDX]
   float* bufs = xs + 2 * PT * IP * MLP_LDX;            // [8 warps][32][MLP_LDX]: dz tile, then dx partials
@@ -572,7 +625,11 @@ __global__ void __launch_bounds__(256, 1) mlp_bwd_mma_kernel(const float* __rest
   const int pg = (g >> 1) + 4 * (g & 1);
   const int ptid = warp / NCH, hc = (warp % NCH) * 32;
   float* mybuf = bufs + warp * 32 * MLP_LDX;
-  mlp_stage_w1(w1, w1s, I, Hd, HP, LDW);
+  const float* bzh = w1h + (hc + g) * LDW + t;       // fragment bases of this warp's chunk, both orientations
+  const float* bzl = w1l + (hc + g) * LDW + t;
+  const float* bxh = w1h + (hc + t) * LDW + g;
+  const float* bxl = w1l + (hc + t) * LDW + g;
+  mlp_stage_w1(w1, w1h, w1l, I, Hd, HP, IP);
   for (int e = tid; e < HP; e += 256) {
     b1s[e] = (b1 && e < Hd) ? __ldg(b1 + e) : 0.f;
 #pragma unroll
@@ -658,13 +715,8 @@ __global__ void __launch_bounds__(256, 1) mlp_bwd_mma_kernel(const float* __rest
         }
 #pragma unroll
         for (int m = 0; m < 2; ++m) {
-          const float* wr = w1s + (hc + 16 * m + g) * LDW + 2 * (8 * ks + t);
-          const float2 a0 = *reinterpret_cast<const float2*>(wr);
-          const float2 a1 = *reinterpret_cast<const float2*>(wr + 8 * LDW);
-          const float2 a2 = *reinterpret_cast<const float2*>(wr + 8);
-          const float2 a3 = *reinterpret_cast<const float2*>(wr + 8 * LDW + 8);
-          const uint32_t ah[4] = {__float_as_uint(a0.x), __float_as_uint(a1.x), __float_as_uint(a2.x), __float_as_uint(a3.x)};
-          const uint32_t al[4] = {__float_as_uint(a0.y), __float_as_uint(a1.y), __float_as_uint(a2.y), __float_as_uint(a3.y)};
+          uint32_t ah[4], al[4];
+          mlp_afrag_z<LDW>(bzh, bzl, 16 * m, 8 * ks, ah, al);
 #pragma unroll
           for (int j = 0; j < 4; ++j) mma_3xtf32(acc[m][j], ah, al, bh0[j], bh1[j], bl0[j], bl1[j]);
         }
@@ -716,34 +768,47 @@ __global__ void __launch_bounds__(256, 1) mlp_bwd_mma_kernel(const float* __rest
         }
       __syncwarp();
       // ---- 3. dw1[chunk] += dz x^T: k-step j, k = t <-> point 4 t + j, k = t + 4 <-> point 16 + 4 t + j -----------------
-      {
-        float4 xa[KS], xc[KS];
+      // The tensor core adds into its accumulator with truncation: a chain over all of a warp's tiles (~170 MMAs) leaves
+      // a systematic 1e-5 error on cancelling sums.  Each tile's 12-MMA chain therefore starts from zero and is added to the
+      // persistent sums on the CUDA cores (round to nearest).  Half of the input channels at a time (register budget); the
+      // x values are re-read per (j, q) as scalars (4-way bank conflicts on 32 loads cost less than holding 2 KS float4).
 #pragma unroll
-        for (int q = 0; q < KS; ++q) {
-          xa[q] = *reinterpret_cast<const float4*>(xt + (8 * q + g) * MLP_LDX + 4 * t);
-          xc[q] = *reinterpret_cast<const float4*>(xt + (8 * q + g) * MLP_LDX + 16 + 4 * t);
-        }
+      for (int qh = 0; qh < 2; ++qh) {
+        float tmp[2][KS / 2][4];
+#pragma unroll
+        for (int m = 0; m < 2; ++m)
+#pragma unroll
+          for (int q = 0; q < KS / 2; ++q)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) tmp[m][q][c] = 0.f;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           uint32_t ah[2][4], al[2][4];
 #pragma unroll
           for (int m = 0; m < 2; ++m) {
-            tf32_split(acc[m][j][0], ah[m][0], al[m][0]);
-            tf32_split(acc[m][j][2], ah[m][1], al[m][1]);
-            tf32_split(acc[m][j][1], ah[m][2], al[m][2]);
-            tf32_split(acc[m][j][3], ah[m][3], al[m][3]);
+            tf32_split_here(acc[m][j][0], ah[m][0], al[m][0]);   // pinned: not merged across the two halves
+            tf32_split_here(acc[m][j][2], ah[m][1], al[m][1]);
+            tf32_split_here(acc[m][j][1], ah[m][2], al[m][2]);
+            tf32_split_here(acc[m][j][3], ah[m][3], al[m][3]);
           }
 #pragma unroll
-          for (int q = 0; q < KS; ++q) {
-            const float va = j == 0 ? xa[q].x : j == 1 ? xa[q].y : j == 2 ? xa[q].z : xa[q].w;
-            const float vc = j == 0 ? xc[q].x : j == 1 ? xc[q].y : j == 2 ? xc[q].z : xc[q].w;
+          for (int q = 0; q < KS / 2; ++q) {
+            const int qq = qh * (KS / 2) + q;
+            const float va = xt[(8 * qq + g) * MLP_LDX + 4 * t + j];
+            const float vc = xt[(8 * qq + g) * MLP_LDX + 16 + 4 * t + j];
             uint32_t bh0, bl0, bh1, bl1;
             tf32_split(va, bh0, bl0);
             tf32_split(vc, bh1, bl1);
-            mma_3xtf32(dw1acc[0][q], ah[0], al[0], bh0, bh1, bl0, bl1);
-            mma_3xtf32(dw1acc[1][q], ah[1], al[1], bh0, bh1, bl0, bl1);
+            mma_3xtf32(tmp[0][q], ah[0], al[0], bh0, bh1, bl0, bl1);
+            mma_3xtf32(tmp[1][q], ah[1], al[1], bh0, bh1, bl0, bl1);
           }
         }
+#pragma unroll
+        for (int m = 0; m < 2; ++m)
+#pragma unroll
+          for (int q = 0; q < KS / 2; ++q)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) dw1acc[m][qh * (KS / 2) + q][c] += tmp[m][q][c];
       }
       // ---- 4. dx partial = W1[chunk]^T dz --------------------------------------------------------------------------
 #pragma unroll
@@ -759,13 +824,8 @@ __global__ void __launch_bounds__(256, 1) mlp_bwd_mma_kernel(const float* __rest
         }
 #pragma unroll
         for (int mt = 0; mt < IT; ++mt) {
-          const float* wr = w1s + (hc + 8 * ks + t) * LDW + 2 * (16 * mt + g);
-          const float2 a0 = *reinterpret_cast<const float2*>(wr);
-          const float2 a1 = *reinterpret_cast<const float2*>(wr + 16);
-          const float2 a2 = *reinterpret_cast<const float2*>(wr + 4 * LDW);
-          const float2 a3 = *reinterpret_cast<const float2*>(wr + 4 * LDW + 16);
-          const uint32_t ah[4] = {__float_as_uint(a0.x), __float_as_uint(a1.x), __float_as_uint(a2.x), __float_as_uint(a3.x)};
-          const uint32_t al[4] = {__float_as_uint(a0.y), __float_as_uint(a1.y), __float_as_uint(a2.y), __float_as_uint(a3.y)};
+          uint32_t ah[4], al[4];
+          mlp_afrag_x<LDW>(bxh, bxl, 8 * ks, 16 * mt, ah, al);
 #pragma unroll
           for (int j = 0; j < 4; ++j) mma_3xtf32(dxacc[mt][j], ah, al, bh0[j], bh1[j], bl0[j], bl1[j]);
         }

@@ -1122,7 +1122,8 @@ int rpde_mlp_bwd(const float* x, const float* dy, const float* w1, const float* 
   const int HP = (Hd + 31) & ~31, PT = 256 / HP;
   const long long tiles = (long long)B * (S / 32);
   long long ctas = (tiles + PT - 1) / PT;
-  if (ctas > 148) ctas = 148;
+  const long long resident = 148LL * (I <= 32 ? 2 : 1);
+  if (ctas > resident) ctas = resident;
 #define RPDE_MLP_BWD(KS, NO)                                                                                                    \
   do {                                                                                                                          \
     RPDE_CUDA(cudaFuncSetAttribute(mlp_bwd_mma_kernel<KS, NO>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));        \
