@@ -899,4 +899,144 @@ __global__ void __launch_bounds__(256, KS == 4 ? 2 : 1) mlp_bwd_mma_kernel(const
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// fno2d_waxis_mma_kernel: the W-axis truncated DFT of the image rows (spectral_convolution.py:82 rfft2's last axis) and, in
+// the backward pass, the adjoint of the W-axis synthesis with act'(z) applied on load and dpre written once:
+//   T[row][r] = sum_w x[row][w] * tab[r][w],   row = (b, c, h),  r < R = 2 m2 <= 32
+// as D[row][r] = A[row][k = w] B[k = w][r]: a warp owns 16 image rows, walks the row in groups of 32 points (four k-steps;
+// k-step j <-> points 4 t' + j, so the lane's two float4 per row feed all four), the table is resident in shared memory as
+// TF32 hi / lo planes.  Each group's 12-MMA chain starts from zero and is added to the row sums on the CUDA cores (the tensor
+// core's truncating accumulation would bias the cancelling spectral sums).  The next group's loads are issued before the
+// current group's MMAs.  Same arguments as fno2d_waxis_kernel; W % 32 == 0.
+__host__ __device__ constexpr size_t f2m_waxis_smem(int W, int RP) { return (size_t)2 * RP * (W + 16) * sizeof(float); }
+
+__global__ void __launch_bounds__(256, 2) fno2d_waxis_mma_kernel(const float* __restrict__ x, const float* __restrict__ tab,
+                                                                 float* __restrict__ T, long long rows, int W, int R,
+                                                                 const float* __restrict__ z, int act, float* __restrict__ xout,
+                                                                 int kplanes) {
+  extern __shared__ __align__(16) float smem[];
+  const int RP = (R + 7) & ~7, NT = RP / 8, LDT = W + 16;     // stride = 16 mod 32: conflict-free float4 B fragments
+  float* tabH = smem;
+  float* tabL = tabH + RP * LDT;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  for (int e = tid; e < RP * W; e += 256) {
+    const int r = e / W, n = e - r * W;
+    const int tr = kplanes ? (r & 1) * kplanes + (r >> 1) : r;
+    const float v = r < R ? __ldg(tab + (long long)tr * W + n) : 0.f;
+    uint32_t hi, lo;
+    tf32_split_rn(v, hi, lo);
+    tabH[r * LDT + n] = __uint_as_float(hi);
+    tabL[r * LDT + n] = __uint_as_float(tf32_hi(__uint_as_float(lo)));
+  }
+  __syncthreads();
+  const int groups = W / 32;
+  const long long mtiles = (rows + 15) / 16;
+  for (long long mt = (long long)blockIdx.x * 8 + warp; mt < mtiles; mt += (long long)gridDim.x * 8) {
+    const long long row0 = mt * 16 + g, row1 = row0 + 8;
+    const bool ok0 = row0 < rows, ok1 = row1 < rows;
+    const float* x0 = x + row0 * W + 4 * t;
+    const float* x1 = x + row1 * W + 4 * t;
+    float sum[4][4];
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) sum[nt][c] = 0.f;
+    // v[0..1]: row g at points 4 t and 16 + 4 t of the group, v[2..3]: row g + 8
+    auto load = [&](int gi, float4 (&v)[4]) {
+      const int p = 32 * gi;
+      const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+      v[0] = ok0 ? __ldg(reinterpret_cast<const float4*>(x0 + p)) : zero;
+      v[1] = ok0 ? __ldg(reinterpret_cast<const float4*>(x0 + p + 16)) : zero;
+      v[2] = ok1 ? __ldg(reinterpret_cast<const float4*>(x1 + p)) : zero;
+      v[3] = ok1 ? __ldg(reinterpret_cast<const float4*>(x1 + p + 16)) : zero;
+      if (z) {
+        const float* z0 = z + row0 * W + 4 * t + p;
+        const float* z1 = z + row1 * W + 4 * t + p;
+        float4 zz[4];
+        zz[0] = ok0 ? __ldg(reinterpret_cast<const float4*>(z0)) : zero;
+        zz[1] = ok0 ? __ldg(reinterpret_cast<const float4*>(z0 + 16)) : zero;
+        zz[2] = ok1 ? __ldg(reinterpret_cast<const float4*>(z1)) : zero;
+        zz[3] = ok1 ? __ldg(reinterpret_cast<const float4*>(z1 + 16)) : zero;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          float d0, d1, d2, d3;
+          if (act == ACT_GELU) {   // two derivatives per instruction on the packed fp32x2 pipe
+            float h0, h1;
+            gelu_both2(zz[q].x, zz[q].y, h0, h1, d0, d1);
+            gelu_both2(zz[q].z, zz[q].w, h0, h1, d2, d3);
+          } else {
+            d0 = dact_f(act, zz[q].x); d1 = dact_f(act, zz[q].y); d2 = dact_f(act, zz[q].z); d3 = dact_f(act, zz[q].w);
+          }
+          v[q].x *= d0; v[q].y *= d1; v[q].z *= d2; v[q].w *= d3;
+        }
+        if (xout) {
+          float* o0 = xout + row0 * W + 4 * t + p;
+          float* o1 = xout + row1 * W + 4 * t + p;
+          if (ok0) {
+            *reinterpret_cast<float4*>(o0) = v[0];
+            *reinterpret_cast<float4*>(o0 + 16) = v[1];
+          }
+          if (ok1) {
+            *reinterpret_cast<float4*>(o1) = v[2];
+            *reinterpret_cast<float4*>(o1 + 16) = v[3];
+          }
+        }
+      }
+    };
+    float4 cur[4], nxt[4];
+    load(0, cur);
+    for (int gi = 0; gi < groups; ++gi) {
+      if (gi + 1 < groups) load(gi + 1, nxt);
+      float acc[4][4];
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) acc[nt][c] = 0.f;
+      const float a0[4] = {cur[0].x, cur[0].y, cur[0].z, cur[0].w}, a2[4] = {cur[1].x, cur[1].y, cur[1].z, cur[1].w};
+      const float a1[4] = {cur[2].x, cur[2].y, cur[2].z, cur[2].w}, a3[4] = {cur[3].x, cur[3].y, cur[3].z, cur[3].w};
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) {
+        if (nt < NT) {
+          const float* th = tabH + (8 * nt + g) * LDT + 32 * gi + 4 * t;
+          const float* tl = tabL + (8 * nt + g) * LDT + 32 * gi + 4 * t;
+          const float4 h0 = *reinterpret_cast<const float4*>(th), h1 = *reinterpret_cast<const float4*>(th + 16);
+          const float4 l0 = *reinterpret_cast<const float4*>(tl), l1 = *reinterpret_cast<const float4*>(tl + 16);
+          const float bh0[4] = {h0.x, h0.y, h0.z, h0.w}, bh1[4] = {h1.x, h1.y, h1.z, h1.w};
+          const float bl0[4] = {l0.x, l0.y, l0.z, l0.w}, bl1[4] = {l1.x, l1.y, l1.z, l1.w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint32_t ah[4], al[4];
+            tf32_split(a0[j], ah[0], al[0]);
+            tf32_split(a1[j], ah[1], al[1]);
+            tf32_split(a2[j], ah[2], al[2]);
+            tf32_split(a3[j], ah[3], al[3]);
+            mma_3xtf32(acc[nt], ah, al, __float_as_uint(bh0[j]), __float_as_uint(bh1[j]), __float_as_uint(bl0[j]),
+                       __float_as_uint(bl1[j]));
+          }
+        }
+      }
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) sum[nt][c] += acc[nt][c];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) cur[q] = nxt[q];
+    }
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) {
+      const int r = 8 * nt + 2 * t;
+      if (nt < NT) {
+        if (ok0) {
+          if (r < R) T[row0 * R + r] = sum[nt][0];
+          if (r + 1 < R) T[row0 * R + r + 1] = sum[nt][1];
+        }
+        if (ok1) {
+          if (r < R) T[row1 * R + r] = sum[nt][2];
+          if (r + 1 < R) T[row1 * R + r + 1] = sum[nt][3];
+        }
+      }
+    }
+  }
+}
+
 }  // namespace rpde

@@ -426,6 +426,18 @@ size_t rpde_fno_block2d_workspace_bytes(int B, int I, int O, int H, int W, int m
 
 static int launch_fno2d_waxis(const float* x, const float* tab, float* T, long long rows, int N, int R, const float* z, int act,
                               float* xout, int kplanes, cudaStream_t s) {
+  static const bool use_mma = !(getenv("RPDE_FNO2D_MMA") && atoi(getenv("RPDE_FNO2D_MMA")) == 0);
+  auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+  if (use_mma && N % 32 == 0 && R <= F2M_MAXR && f2m_waxis_smem(N, (R + 7) & ~7) <= 100 * 1024 && al16(x) && al16(z) && al16(xout)) {
+    // image rows on the warp-level tensor path (fno2d_mma.cuh): 16 rows per warp, table resident as TF32 hi / lo planes
+    const size_t sm = f2m_waxis_smem(N, (R + 7) & ~7);
+    long long ctas = ((rows + 15) / 16 + 7) / 8;
+    if (ctas > 2 * 148) ctas = 2 * 148;
+    RPDE_CUDA(cudaFuncSetAttribute(fno2d_waxis_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    fno2d_waxis_mma_kernel<<<(unsigned)ctas, 256, sm, s>>>(x, tab, T, rows, N, R, z, act, xout, kplanes);
+    RPDE_LAUNCH_CHECK();
+    return RPDE_OK;
+  }
   const size_t smem = (size_t)((R + 7) & ~7) * N * sizeof(float);
   long long blocks = (rows + 15) / 16;
   if (blocks > 148 * 4) blocks = 148 * 4;
