@@ -218,23 +218,30 @@ __global__ void __launch_bounds__(256) fno2d_wgrad_kernel(const float* __restric
 }
 
 // Z[(2 ky + r)][b * H + h][c] = sum_{a} tab[(h * 2 + r)][a] * in[(b, c)][a][ky]         a < A (= 2J), r in {0, 1}
-// grid (ceil(H / 32), B), 256 threads = 8 image rows x 32 channels, four row groups per CTA; the plane tiles in[(b, c)] are
-// staged through shared memory transposed to [a][ky][c] in chunks of F2_AC values of a, so the inner loop reads
-// conflict-free shared memory (channel = lane) and the results leave as coalesced 128-byte stores.
+// grid (ceil(H / 16), B), 256 threads = 8 image rows x 32 channels, two row groups per CTA.  The CTA's 32 table rows sit in
+// shared memory (broadcast reads in the inner loop, no global load there); the plane tiles in[(b, c)] are staged transposed
+// to [a][ky][c] (row stride 33: the transposing stores are conflict-free) in chunks of F2_AC values of a, so the inner loop
+// reads conflict-free shared memory (channel = lane) and the results leave as coalesced 128-byte stores.
 constexpr int F2_AC = 16;
+constexpr int F2_EH = 16;   // image rows per CTA
 template <int KYT>
 __global__ void __launch_bounds__(256) fno2d_expand_kernel(const float* __restrict__ in, const float* __restrict__ tab,
                                                            float* __restrict__ Z, int Bn, int C, int H, int Ky, int A) {
-  __shared__ float sm[F2_AC * KYT * 32];               // [a][ky][c]
-  const int b = blockIdx.y;
+  extern __shared__ float sm[];                        // [F2_AC * KYT][33] | table rows [2 F2_EH][A]
+  float* ts = sm + F2_AC * KYT * 33;
+  const int b = blockIdx.y, h0 = blockIdx.x * F2_EH;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const long long BH = (long long)Bn * H;
+  for (int e = threadIdx.x; e < 2 * F2_EH * A; e += 256) {
+    const int r = e / A;
+    ts[e] = (h0 + r / 2 < H) ? __ldg(tab + (long long)h0 * 2 * A + e) : 0.f;
+  }
   for (int c0 = 0; c0 < C; c0 += 32) {
     const int c = c0 + lane;
     for (int k0 = 0; k0 < Ky; k0 += KYT) {
-      float a0[4][KYT], a1[4][KYT];
+      float a0[2][KYT], a1[2][KYT];
 #pragma unroll
-      for (int q = 0; q < 4; ++q)
+      for (int q = 0; q < 2; ++q)
 #pragma unroll
         for (int k = 0; k < KYT; ++k) a0[q][k] = a1[q][k] = 0.f;
       for (int ac = 0; ac < A; ac += F2_AC) {
@@ -246,21 +253,20 @@ __global__ void __launch_bounds__(256) fno2d_expand_kernel(const float* __restri
           const int aa = rem / KYT, k = rem - aa * KYT;
           float v = 0.f;
           if (c0 + cc < C && k0 + k < Ky) v = __ldg(in + (((long long)b * C + c0 + cc) * A + ac + aa) * Ky + k0 + k);
-          sm[(aa * KYT + k) * 32 + cc] = v;
+          sm[(aa * KYT + k) * 33 + cc] = v;
         }
         __syncthreads();
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int h = blockIdx.x * 32 + q * 8 + warp;
-          if (h >= H) continue;
-          const float* t0 = tab + (long long)(h * 2) * A + ac;
+        for (int q = 0; q < 2; ++q) {
+          const float* t0 = ts + (2 * (q * 8 + warp)) * A + ac;
           const float* t1 = t0 + A;
+#pragma unroll 4
           for (int aa = 0; aa < na; ++aa) {
-            const float u0 = __ldg(t0 + aa), u1 = __ldg(t1 + aa);
-            const float* s = sm + aa * KYT * 32 + lane;
+            const float u0 = t0[aa], u1 = t1[aa];
+            const float* s = sm + aa * KYT * 33 + lane;
 #pragma unroll
             for (int k = 0; k < KYT; ++k) {
-              const float v = s[k * 32];
+              const float v = s[k * 33];
               a0[q][k] = fmaf(u0, v, a0[q][k]);
               a1[q][k] = fmaf(u1, v, a1[q][k]);
             }
@@ -269,8 +275,8 @@ __global__ void __launch_bounds__(256) fno2d_expand_kernel(const float* __restri
       }
       if (c < C) {
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int h = blockIdx.x * 32 + q * 8 + warp;
+        for (int q = 0; q < 2; ++q) {
+          const int h = h0 + q * 8 + warp;
           if (h >= H) continue;
 #pragma unroll
           for (int k = 0; k < KYT; ++k) {

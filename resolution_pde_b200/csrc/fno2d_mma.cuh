@@ -941,8 +941,9 @@ __global__ void __launch_bounds__(256, 2) fno2d_waxis_mma_kernel(const float* __
     for (int nt = 0; nt < 4; ++nt)
 #pragma unroll
       for (int c = 0; c < 4; ++c) sum[nt][c] = 0.f;
-    // v[0..1]: row g at points 4 t and 16 + 4 t of the group, v[2..3]: row g + 8
-    auto load = [&](int gi, float4 (&v)[4]) {
+    // raw loads of one group: v[0..1] row g at points 4 t and 16 + 4 t, v[2..3] row g + 8 (zz: the pre-activations).  They are
+    // issued one group ahead; act'(z), the dpre store and the TF32 split happen when the group is consumed.
+    auto load = [&](int gi, float4 (&v)[4], float4 (&zz)[4]) {
       const int p = 32 * gi;
       const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
       v[0] = ok0 ? __ldg(reinterpret_cast<const float4*>(x0 + p)) : zero;
@@ -952,48 +953,58 @@ __global__ void __launch_bounds__(256, 2) fno2d_waxis_mma_kernel(const float* __
       if (z) {
         const float* z0 = z + row0 * W + 4 * t + p;
         const float* z1 = z + row1 * W + 4 * t + p;
-        float4 zz[4];
         zz[0] = ok0 ? __ldg(reinterpret_cast<const float4*>(z0)) : zero;
         zz[1] = ok0 ? __ldg(reinterpret_cast<const float4*>(z0 + 16)) : zero;
         zz[2] = ok1 ? __ldg(reinterpret_cast<const float4*>(z1)) : zero;
         zz[3] = ok1 ? __ldg(reinterpret_cast<const float4*>(z1 + 16)) : zero;
+      }
+    };
+    float4 nv[4], nz[4];
+    load(0, nv, nz);
+    for (int gi = 0; gi < groups; ++gi) {
+      float4 cur[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) cur[q] = nv[q];
+      if (z) {
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           float d0, d1, d2, d3;
           if (act == ACT_GELU) {   // two derivatives per instruction on the packed fp32x2 pipe
             float h0, h1;
-            gelu_both2(zz[q].x, zz[q].y, h0, h1, d0, d1);
-            gelu_both2(zz[q].z, zz[q].w, h0, h1, d2, d3);
+            gelu_both2(nz[q].x, nz[q].y, h0, h1, d0, d1);
+            gelu_both2(nz[q].z, nz[q].w, h0, h1, d2, d3);
           } else {
-            d0 = dact_f(act, zz[q].x); d1 = dact_f(act, zz[q].y); d2 = dact_f(act, zz[q].z); d3 = dact_f(act, zz[q].w);
+            d0 = dact_f(act, nz[q].x); d1 = dact_f(act, nz[q].y); d2 = dact_f(act, nz[q].z); d3 = dact_f(act, nz[q].w);
           }
-          v[q].x *= d0; v[q].y *= d1; v[q].z *= d2; v[q].w *= d3;
+          cur[q].x *= d0; cur[q].y *= d1; cur[q].z *= d2; cur[q].w *= d3;
         }
         if (xout) {
-          float* o0 = xout + row0 * W + 4 * t + p;
-          float* o1 = xout + row1 * W + 4 * t + p;
+          float* o0 = xout + row0 * W + 4 * t + 32 * gi;
+          float* o1 = xout + row1 * W + 4 * t + 32 * gi;
           if (ok0) {
-            *reinterpret_cast<float4*>(o0) = v[0];
-            *reinterpret_cast<float4*>(o0 + 16) = v[1];
+            *reinterpret_cast<float4*>(o0) = cur[0];
+            *reinterpret_cast<float4*>(o0 + 16) = cur[1];
           }
           if (ok1) {
-            *reinterpret_cast<float4*>(o1) = v[2];
-            *reinterpret_cast<float4*>(o1 + 16) = v[3];
+            *reinterpret_cast<float4*>(o1) = cur[2];
+            *reinterpret_cast<float4*>(o1 + 16) = cur[3];
           }
         }
       }
-    };
-    float4 cur[4], nxt[4];
-    load(0, cur);
-    for (int gi = 0; gi < groups; ++gi) {
-      if (gi + 1 < groups) load(gi + 1, nxt);
-      float acc[4][4];
+      if (gi + 1 < groups) load(gi + 1, nv, nz);
+      // A fragments of the four k-steps: a0 = (row g, k = t), a1 = (row g + 8, t), a2 = (row g, t + 4), a3 = (row g + 8, t + 4)
+      uint32_t ah[4][4], al[4][4];
+      {
+        const float a0[4] = {cur[0].x, cur[0].y, cur[0].z, cur[0].w}, a2[4] = {cur[1].x, cur[1].y, cur[1].z, cur[1].w};
+        const float a1[4] = {cur[2].x, cur[2].y, cur[2].z, cur[2].w}, a3[4] = {cur[3].x, cur[3].y, cur[3].z, cur[3].w};
 #pragma unroll
-      for (int nt = 0; nt < 4; ++nt)
-#pragma unroll
-        for (int c = 0; c < 4; ++c) acc[nt][c] = 0.f;
-      const float a0[4] = {cur[0].x, cur[0].y, cur[0].z, cur[0].w}, a2[4] = {cur[1].x, cur[1].y, cur[1].z, cur[1].w};
-      const float a1[4] = {cur[2].x, cur[2].y, cur[2].z, cur[2].w}, a3[4] = {cur[3].x, cur[3].y, cur[3].z, cur[3].w};
+        for (int j = 0; j < 4; ++j) {
+          tf32_split(a0[j], ah[j][0], al[j][0]);
+          tf32_split(a1[j], ah[j][1], al[j][1]);
+          tf32_split(a2[j], ah[j][2], al[j][2]);
+          tf32_split(a3[j], ah[j][3], al[j][3]);
+        }
+      }
 #pragma unroll
       for (int nt = 0; nt < 4; ++nt) {
         if (nt < NT) {
@@ -1003,24 +1014,15 @@ __global__ void __launch_bounds__(256, 2) fno2d_waxis_mma_kernel(const float* __
           const float4 l0 = *reinterpret_cast<const float4*>(tl), l1 = *reinterpret_cast<const float4*>(tl + 16);
           const float bh0[4] = {h0.x, h0.y, h0.z, h0.w}, bh1[4] = {h1.x, h1.y, h1.z, h1.w};
           const float bl0[4] = {l0.x, l0.y, l0.z, l0.w}, bl1[4] = {l1.x, l1.y, l1.z, l1.w};
+          float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            uint32_t ah[4], al[4];
-            tf32_split(a0[j], ah[0], al[0]);
-            tf32_split(a1[j], ah[1], al[1]);
-            tf32_split(a2[j], ah[2], al[2]);
-            tf32_split(a3[j], ah[3], al[3]);
-            mma_3xtf32(acc[nt], ah, al, __float_as_uint(bh0[j]), __float_as_uint(bh1[j]), __float_as_uint(bl0[j]),
+          for (int j = 0; j < 4; ++j)
+            mma_3xtf32(acc, ah[j], al[j], __float_as_uint(bh0[j]), __float_as_uint(bh1[j]), __float_as_uint(bl0[j]),
                        __float_as_uint(bl1[j]));
-          }
+#pragma unroll
+          for (int c = 0; c < 4; ++c) sum[nt][c] += acc[c];
         }
       }
-#pragma unroll
-      for (int nt = 0; nt < 4; ++nt)
-#pragma unroll
-        for (int c = 0; c < 4; ++c) sum[nt][c] += acc[nt][c];
-#pragma unroll
-      for (int q = 0; q < 4; ++q) cur[q] = nxt[q];
     }
 #pragma unroll
     for (int nt = 0; nt < 4; ++nt) {

@@ -465,10 +465,19 @@ static int launch_fno2d_rows(const float* T, const float* tab, float* out, long 
   return RPDE_OK;
 }
 static int launch_fno2d_expand(const float* in, const float* tab, float* Z, int B, int C, int H, int Ky, int A, cudaStream_t s) {
-  dim3 g((unsigned)((H + 31) / 32), (unsigned)B);
-  if (Ky <= 4) fno2d_expand_kernel<4><<<g, 256, 0, s>>>(in, tab, Z, B, C, H, Ky, A);
-  else if (Ky <= 8) fno2d_expand_kernel<8><<<g, 256, 0, s>>>(in, tab, Z, B, C, H, Ky, A);
-  else fno2d_expand_kernel<12><<<g, 256, 0, s>>>(in, tab, Z, B, C, H, Ky, A);
+  dim3 g((unsigned)((H + F2_EH - 1) / F2_EH), (unsigned)B);
+  // A <= 256 (fno2d_fused_ok): at most 16 * 12 * 33 + 32 * 256 floats = 57 KB
+#define RPDE_EXPAND(KYT)                                                                                                     \
+  do {                                                                                                                       \
+    const size_t smem = ((size_t)F2_AC * KYT * 33 + (size_t)2 * F2_EH * A) * sizeof(float);                                  \
+    if (smem > 48 * 1024)                                                                                                    \
+      RPDE_CUDA(cudaFuncSetAttribute(fno2d_expand_kernel<KYT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));     \
+    fno2d_expand_kernel<KYT><<<g, 256, smem, s>>>(in, tab, Z, B, C, H, Ky, A);                                             \
+  } while (0)
+  if (Ky <= 4) RPDE_EXPAND(4);
+  else if (Ky <= 8) RPDE_EXPAND(8);
+  else RPDE_EXPAND(12);
+#undef RPDE_EXPAND
   RPDE_LAUNCH_CHECK();
   return RPDE_OK;
 }
