@@ -1041,4 +1041,147 @@ __global__ void __launch_bounds__(256, 2) fno2d_waxis_mma_kernel(const float* __
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// H-axis kernels of FNOBlock2d on the warp-level tensor path.  Both read their table as [(h, r)][a], a < A = 4 m1 (the C2C
+// analysis / synthesis of the kept rows [0, m1) U [H - m1, H), spectral_convolution.py:82,97); the fp32-FMA versions
+// (fno2d_rows_kernel / fno2d_expand_kernel) were latency-bound at 31 / 42 us for 150 MFLOP and 12.6 MB.
+//
+// fno2d_expand_mma_kernel:  Z[(2 ky + r)][b * H + h][c] = sum_a tab[(h * 2 + r)][a] * in[(b, c)][a][ky]
+// as D[(h, r)][c] = A[(h, r)][a] B[a][c] per (b, ky).  A warp owns 16 table rows (8 image rows x {re, im}) with its A
+// fragments resident in registers as TF32 hi / lo; it loops over channel tiles and ky quads, reading B straight from global
+// memory: for a fixed (c, a) the ky values are contiguous, so three float4 per lane carry all twelve ky of a fragment element.
+// CTA = four warps = 32 image rows of one batch element.  KS = k-steps of eight a (A <= 8 KS).  Ky % 4 == 0, C % 8 == 0.
+template <int KS>
+__global__ void __launch_bounds__(128) fno2d_expand_mma_kernel(const float* __restrict__ in, const float* __restrict__ tab,
+                                                               float* __restrict__ Z, int Bn, int C, int H, int Ky, int A) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int b = blockIdx.y;
+  const int row_base = (blockIdx.x * 4 + warp) * 16;          // first table row (h * 2 + r) of this warp
+  if (row_base >= 2 * H) return;
+  const long long BH = (long long)Bn * H;
+  uint32_t ah[KS][4], al[KS][4];
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int row = row_base + g + 8 * (q & 1), a = 8 * ks + t + 4 * (q >> 1);
+      const float v = (row < 2 * H && a < A) ? __ldg(tab + (long long)row * A + a) : 0.f;
+      tf32_split_rn(v, ah[ks][q], al[ks][q]);
+    }
+  }
+  // rows of the accumulator fragment: g -> table row row_base + g, g + 8 -> row_base + g + 8
+  const int tr0 = row_base + g, tr1 = tr0 + 8;
+  const int h0 = tr0 >> 1, r0 = tr0 & 1, h1 = tr1 >> 1, r1 = tr1 & 1;
+  for (int c0 = 0; c0 < C; c0 += 8) {
+    const int c = c0 + g;                                      // B fragment column (n = g)
+    const float* src = in + ((long long)b * C + c) * A * Ky;
+    for (int kq = 0; kq < Ky; kq += 4) {
+      float acc[4][4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) acc[k][q] = 0.f;
+      float4 b0[KS], b1[KS];
+#pragma unroll
+      for (int ks = 0; ks < KS; ++ks) {
+        const int a0 = 8 * ks + t, a1 = a0 + 4;
+        b0[ks] = a0 < A ? __ldg(reinterpret_cast<const float4*>(src + (long long)a0 * Ky + kq)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        b1[ks] = a1 < A ? __ldg(reinterpret_cast<const float4*>(src + (long long)a1 * Ky + kq)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int ks = 0; ks < KS; ++ks) {
+        const float v0[4] = {b0[ks].x, b0[ks].y, b0[ks].z, b0[ks].w}, v1[4] = {b1[ks].x, b1[ks].y, b1[ks].z, b1[ks].w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          uint32_t bh0, bl0, bh1, bl1;
+          tf32_split(v0[k], bh0, bl0);
+          tf32_split(v1[k], bh1, bl1);
+          mma_3xtf32(acc[k], ah[ks], al[ks], bh0, bh1, bl0, bl1);
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int ky = kq + k;
+        if (ky < Ky) {
+          if (h0 < H)
+            *reinterpret_cast<float2*>(Z + ((long long)(2 * ky + r0) * BH + (long long)b * H + h0) * C + c0 + 2 * t) =
+                make_float2(acc[k][0], acc[k][1]);
+          if (h1 < H)
+            *reinterpret_cast<float2*>(Z + ((long long)(2 * ky + r1) * BH + (long long)b * H + h1) * C + c0 + 2 * t) =
+                make_float2(acc[k][2], acc[k][3]);
+        }
+      }
+    }
+  }
+}
+
+// fno2d_rows_mma_kernel:  out[p][a][ky] = sum_(h, r) tab[(h * 2 + r)][a] * T[(p * H + h)][2 ky + r]     p = (b, c) plane
+// as D[a][(p, ky)] = A[a][k] B[k][(p, ky)] with k = (h, r).  CTA = two planes; its eight warps split the 2 H reduction
+// (every warp: all three 16-row tiles of a x both planes x its k range), add their partial tiles in shared memory with
+// round-to-nearest adds and write the two planes' (a, ky) tiles as contiguous rows.  A <= 48 + ... : MT = ceil(A / 16) <= 4
+// row tiles; Ky <= 12 (n-tile pairs per plane: 16 columns, ky >= Ky padded with zero).
+template <int MT>
+__global__ void __launch_bounds__(256) fno2d_rows_mma_kernel(const float* __restrict__ T, const float* __restrict__ tab,
+                                                             float* __restrict__ out, long long planes, int H, int Ky, int A) {
+  extern __shared__ float red_raw[];                    // per warp: [a][(plane, ky16)], row stride 33
+  float (*red)[MT * 16][33] = reinterpret_cast<float (*)[MT * 16][33]>(red_raw);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const long long p0 = (long long)blockIdx.x * 2;
+  const int R = 2 * Ky, K = 2 * H, ksteps = (K + 7) / 8;
+  const int per = (ksteps + 7) / 8;                      // k-steps per warp
+  float acc[MT][4][4];
+#pragma unroll
+  for (int m = 0; m < MT; ++m)
+#pragma unroll
+    for (int n = 0; n < 4; ++n)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) acc[m][n][q] = 0.f;
+  for (int ks = warp * per; ks < min(ksteps, (warp + 1) * per); ++ks) {
+    // B fragments: k = 8 ks + t (+ 4) -> (h, r) = (k >> 1, k & 1); column n = g of tile nt -> plane nt >> 1, ky = 8 (nt & 1) + g
+    uint32_t bh[4][2], bl[4][2];
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) {
+      const long long p = p0 + (nt >> 1);
+      const int ky = 8 * (nt & 1) + g;
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const int k = 8 * ks + t + 4 * q;
+        const float v = (p < planes && ky < Ky && k < K) ? __ldg(T + (p * H + (k >> 1)) * R + 2 * ky + (k & 1)) : 0.f;
+        tf32_split(v, bh[nt][q], bl[nt][q]);
+      }
+    }
+#pragma unroll
+    for (int m = 0; m < MT; ++m) {
+      uint32_t ah[4], al[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int a = 16 * m + g + 8 * (q & 1), k = 8 * ks + t + 4 * (q >> 1);
+        const float v = (a < A && k < K) ? __ldg(tab + (long long)k * A + a) : 0.f;
+        tf32_split(v, ah[q], al[q]);
+      }
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) mma_3xtf32(acc[m][nt], ah, al, bh[nt][0], bh[nt][1], bl[nt][0], bl[nt][1]);
+    }
+  }
+#pragma unroll
+  for (int m = 0; m < MT; ++m)
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) {
+      red[warp][16 * m + g][8 * nt + 2 * t] = acc[m][nt][0];
+      red[warp][16 * m + g][8 * nt + 2 * t + 1] = acc[m][nt][1];
+      red[warp][16 * m + g + 8][8 * nt + 2 * t] = acc[m][nt][2];
+      red[warp][16 * m + g + 8][8 * nt + 2 * t + 1] = acc[m][nt][3];
+    }
+  __syncthreads();
+  for (int e = threadIdx.x; e < 2 * A * Ky; e += 256) {
+    const int pl = e / (A * Ky), rem = e - pl * (A * Ky);
+    const int a = rem / Ky, ky = rem - a * Ky;
+    if (p0 + pl >= planes) continue;
+    float v = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) v += red[w][a][16 * pl + ky];
+    out[(p0 + pl) * A * Ky + rem] = v;
+  }
+}
+
 }  // namespace rpde

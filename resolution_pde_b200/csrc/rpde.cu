@@ -458,6 +458,23 @@ static int launch_fno2d_waxis(const float* x, const float* tab, float* T, long l
   return RPDE_OK;
 }
 static int launch_fno2d_rows(const float* T, const float* tab, float* out, long long planes, int H, int Ky, int A, cudaStream_t s) {
+  static const bool use_mma = !(getenv("RPDE_FNO2D_MMA") && atoi(getenv("RPDE_FNO2D_MMA")) == 0);
+  if (use_mma && A <= 48 && Ky <= 12) {   // two planes per CTA on the warp-level tensor path (fno2d_mma.cuh)
+    const unsigned grid = (unsigned)((planes + 1) / 2);
+#define RPDE_ROWS_MMA(MT)                                                                                                   \
+  do {                                                                                                                       \
+    const size_t sm = (size_t)8 * MT * 16 * 33 * sizeof(float);                                                             \
+    if (sm > 48 * 1024)                                                                                                      \
+      RPDE_CUDA(cudaFuncSetAttribute(fno2d_rows_mma_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));      \
+    fno2d_rows_mma_kernel<MT><<<grid, 256, sm, s>>>(T, tab, out, planes, H, Ky, A);                                         \
+  } while (0)
+    if (A <= 16) RPDE_ROWS_MMA(1);
+    else if (A <= 32) RPDE_ROWS_MMA(2);
+    else RPDE_ROWS_MMA(3);
+#undef RPDE_ROWS_MMA
+    RPDE_LAUNCH_CHECK();
+    return RPDE_OK;
+  }
   const size_t smem = (size_t)F2_RC * (2 * Ky + 2 * A) * sizeof(float);    // <= 64 * (32 + 512) * 4 = 136 KB, 30 KB at 12 x 12 modes
   if (smem > 48 * 1024) RPDE_CUDA(cudaFuncSetAttribute(fno2d_rows_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   fno2d_rows_kernel<4><<<(unsigned)planes, 256, smem, s>>>(T, tab, out, H, Ky, A);
@@ -465,6 +482,17 @@ static int launch_fno2d_rows(const float* T, const float* tab, float* out, long 
   return RPDE_OK;
 }
 static int launch_fno2d_expand(const float* in, const float* tab, float* Z, int B, int C, int H, int Ky, int A, cudaStream_t s) {
+  static const bool use_mma = !(getenv("RPDE_FNO2D_MMA") && atoi(getenv("RPDE_FNO2D_MMA")) == 0);
+  if (use_mma && A <= 64 && Ky % 4 == 0 && C % 8 == 0 && (reinterpret_cast<uintptr_t>(in) & 15) == 0 &&
+      (reinterpret_cast<uintptr_t>(Z) & 7) == 0) {
+    // 32 image rows per CTA (four warps x 16 table rows) on the warp-level tensor path (fno2d_mma.cuh)
+    dim3 gm((unsigned)((2 * H + 63) / 64), (unsigned)B);
+    if (A <= 32) fno2d_expand_mma_kernel<4><<<gm, 128, 0, s>>>(in, tab, Z, B, C, H, Ky, A);
+    else if (A <= 48) fno2d_expand_mma_kernel<6><<<gm, 128, 0, s>>>(in, tab, Z, B, C, H, Ky, A);
+    else fno2d_expand_mma_kernel<8><<<gm, 128, 0, s>>>(in, tab, Z, B, C, H, Ky, A);
+    RPDE_LAUNCH_CHECK();
+    return RPDE_OK;
+  }
   dim3 g((unsigned)((H + F2_EH - 1) / F2_EH), (unsigned)B);
   // A <= 256 (fno2d_fused_ok): at most 16 * 12 * 33 + 32 * 256 floats = 57 KB
 #define RPDE_EXPAND(KYT)                                                                                                     \
