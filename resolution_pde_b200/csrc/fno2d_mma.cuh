@@ -908,25 +908,35 @@ __global__ void __launch_bounds__(256, KS == 4 ? 2 : 1) mlp_bwd_mma_kernel(const
 // TF32 hi / lo planes.  Each group's 12-MMA chain starts from zero and is added to the row sums on the CUDA cores (the tensor
 // core's truncating accumulation would bias the cancelling spectral sums).  The next group's loads are issued before the
 // current group's MMAs.  Same arguments as fno2d_waxis_kernel; W % 32 == 0.
-__host__ __device__ constexpr size_t f2m_waxis_smem(int W, int RP) { return (size_t)2 * RP * (W + 16) * sizeof(float); }
+// PRESPLIT = false (long rows: FNO1d at N = 1024 would need 266 KB for two planes): the table stays in shared memory as one
+// fp32 plane and its fragments are split when they are read.  The output element (row, r) goes to T[row * s_row + r * s_r]:
+// (R, 1) for the 2-D half transform, (1, rows) for the FNO1d spectrum layout [mode][re|im][b][i] (fno_fused.cuh).
+__host__ __device__ constexpr size_t f2m_waxis_smem(int W, int RP, bool presplit) {
+  return (size_t)(presplit ? 2 : 1) * RP * (W + 16) * sizeof(float);
+}
 
-__global__ void __launch_bounds__(256, 2) fno2d_waxis_mma_kernel(const float* __restrict__ x, const float* __restrict__ tab,
+template <bool PRESPLIT>
+__global__ void __launch_bounds__(256, PRESPLIT ? 2 : 1) fno2d_waxis_mma_kernel(const float* __restrict__ x, const float* __restrict__ tab,
                                                                  float* __restrict__ T, long long rows, int W, int R,
                                                                  const float* __restrict__ z, int act, float* __restrict__ xout,
-                                                                 int kplanes) {
+                                                                 int kplanes, long long s_row, long long s_r) {
   extern __shared__ __align__(16) float smem[];
   const int RP = (R + 7) & ~7, NT = RP / 8, LDT = W + 16;     // stride = 16 mod 32: conflict-free float4 B fragments
   float* tabH = smem;
-  float* tabL = tabH + RP * LDT;
+  float* tabL = tabH + (PRESPLIT ? RP * LDT : 0);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
   for (int e = tid; e < RP * W; e += 256) {
     const int r = e / W, n = e - r * W;
     const int tr = kplanes ? (r & 1) * kplanes + (r >> 1) : r;
     const float v = r < R ? __ldg(tab + (long long)tr * W + n) : 0.f;
-    uint32_t hi, lo;
-    tf32_split_rn(v, hi, lo);
-    tabH[r * LDT + n] = __uint_as_float(hi);
-    tabL[r * LDT + n] = __uint_as_float(tf32_hi(__uint_as_float(lo)));
+    if (PRESPLIT) {
+      uint32_t hi, lo;
+      tf32_split_rn(v, hi, lo);
+      tabH[r * LDT + n] = __uint_as_float(hi);
+      tabL[r * LDT + n] = __uint_as_float(tf32_hi(__uint_as_float(lo)));
+    } else {
+      tabH[r * LDT + n] = v;
+    }
   }
   __syncthreads();
   const int groups = W / 32;
@@ -1011,14 +1021,26 @@ __global__ void __launch_bounds__(256, 2) fno2d_waxis_mma_kernel(const float* __
           const float* th = tabH + (8 * nt + g) * LDT + 32 * gi + 4 * t;
           const float* tl = tabL + (8 * nt + g) * LDT + 32 * gi + 4 * t;
           const float4 h0 = *reinterpret_cast<const float4*>(th), h1 = *reinterpret_cast<const float4*>(th + 16);
-          const float4 l0 = *reinterpret_cast<const float4*>(tl), l1 = *reinterpret_cast<const float4*>(tl + 16);
-          const float bh0[4] = {h0.x, h0.y, h0.z, h0.w}, bh1[4] = {h1.x, h1.y, h1.z, h1.w};
-          const float bl0[4] = {l0.x, l0.y, l0.z, l0.w}, bl1[4] = {l1.x, l1.y, l1.z, l1.w};
+          const float bv0[4] = {h0.x, h0.y, h0.z, h0.w}, bv1[4] = {h1.x, h1.y, h1.z, h1.w};
+          uint32_t bh0[4], bh1[4], bl0[4], bl1[4];
+          if (PRESPLIT) {
+            const float4 l0 = *reinterpret_cast<const float4*>(tl), l1 = *reinterpret_cast<const float4*>(tl + 16);
+            const float lv0[4] = {l0.x, l0.y, l0.z, l0.w}, lv1[4] = {l1.x, l1.y, l1.z, l1.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              bh0[j] = __float_as_uint(bv0[j]); bh1[j] = __float_as_uint(bv1[j]);
+              bl0[j] = __float_as_uint(lv0[j]); bl1[j] = __float_as_uint(lv1[j]);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              tf32_split(bv0[j], bh0[j], bl0[j]);
+              tf32_split(bv1[j], bh1[j], bl1[j]);
+            }
+          }
           float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-          for (int j = 0; j < 4; ++j)
-            mma_3xtf32(acc, ah[j], al[j], __float_as_uint(bh0[j]), __float_as_uint(bh1[j]), __float_as_uint(bl0[j]),
-                       __float_as_uint(bl1[j]));
+          for (int j = 0; j < 4; ++j) mma_3xtf32(acc, ah[j], al[j], bh0[j], bh1[j], bl0[j], bl1[j]);
 #pragma unroll
           for (int c = 0; c < 4; ++c) sum[nt][c] += acc[c];
         }
@@ -1029,12 +1051,12 @@ __global__ void __launch_bounds__(256, 2) fno2d_waxis_mma_kernel(const float* __
       const int r = 8 * nt + 2 * t;
       if (nt < NT) {
         if (ok0) {
-          if (r < R) T[row0 * R + r] = sum[nt][0];
-          if (r + 1 < R) T[row0 * R + r + 1] = sum[nt][1];
+          if (r < R) T[row0 * s_row + r * s_r] = sum[nt][0];
+          if (r + 1 < R) T[row0 * s_row + (r + 1) * s_r] = sum[nt][1];
         }
         if (ok1) {
-          if (r < R) T[row1 * R + r] = sum[nt][2];
-          if (r + 1 < R) T[row1 * R + r + 1] = sum[nt][3];
+          if (r < R) T[row1 * s_row + r * s_r] = sum[nt][2];
+          if (r + 1 < R) T[row1 * s_row + (r + 1) * s_r] = sum[nt][3];
         }
       }
     }

@@ -262,9 +262,23 @@ static int launch_fno1d_synth(const float* x, const float* om, const float* tabl
   return RPDE_OK;
 }
 
+static int launch_waxis_mma(const float* x, const float* tab, float* T, long long rows, int N, int R, const float* z, int act,
+                            float* xout, int kplanes, long long s_row, long long s_r, cudaStream_t s);
+
 // analysis launch shared by the fused forward (x -> spec) and the fused backward prologue (dy, z -> dpre, dom)
 static int launch_fno1d_analysis(const float* x, const float* table, float* out, int B, int rows_per_b, int N, int modes,
                                  const float* z, int act, float* xout, int rowmap, cudaStream_t s) {
+  {
+    // enough rows to give every SM two 16-row tiles: the tensor-path kernel (the FMA kernel is faster on small batches,
+    // where eight CTAs would each stage the whole table)
+    static const bool use_mma = !(getenv("RPDE_FNO2D_MMA") && atoi(getenv("RPDE_FNO2D_MMA")) == 0);
+    auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+    const long long rows = (long long)B * rows_per_b;
+    const int R = 2 * modes;
+    if (use_mma && rows >= 16LL * 2 * 148 && N % 32 == 0 && R <= F2M_MAXR && f2m_waxis_smem(N, (R + 7) & ~7, false) <= 200 * 1024 &&
+        al16(x) && al16(z) && al16(xout))
+      return launch_waxis_mma(x, table, out, rows, N, R, z, act, xout, rowmap ? modes : 0, 1, rows, s);
+  }
   dim3 g1((unsigned)(((long long)B * rows_per_b + 7) / 8), (unsigned)((2 * modes + FNO_RC - 1) / FNO_RC));
   const size_t smem1 = (size_t)FNO_RC * N * sizeof(float);
   if (smem1 > 48 * 1024)      // N in (1536, 2048]: 64 KB table chunk (the attribute is per device: set it on every call)
@@ -424,20 +438,33 @@ size_t rpde_fno_block2d_workspace_bytes(int B, int I, int O, int H, int W, int m
   return f;
 }
 
+// W-axis / 1-D analysis on the warp-level tensor path (fno2d_mma.cuh): 16 rows per warp, the table resident in shared memory
+// as TF32 hi / lo planes when both fit in 100 KB (two CTAs per SM), as one fp32 plane split on the fly otherwise
+static int launch_waxis_mma(const float* x, const float* tab, float* T, long long rows, int N, int R, const float* z, int act,
+                            float* xout, int kplanes, long long s_row, long long s_r, cudaStream_t s) {
+  const int RP = (R + 7) & ~7;
+  const bool presplit = f2m_waxis_smem(N, RP, true) <= 100 * 1024;
+  const size_t sm = f2m_waxis_smem(N, RP, presplit);
+  long long ctas = ((rows + 15) / 16 + 7) / 8;
+  const long long resident = presplit ? 2 * 148 : 148;
+  if (ctas > resident) ctas = resident;
+  if (presplit) {
+    RPDE_CUDA(cudaFuncSetAttribute(fno2d_waxis_mma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    fno2d_waxis_mma_kernel<true><<<(unsigned)ctas, 256, sm, s>>>(x, tab, T, rows, N, R, z, act, xout, kplanes, s_row, s_r);
+  } else {
+    RPDE_CUDA(cudaFuncSetAttribute(fno2d_waxis_mma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    fno2d_waxis_mma_kernel<false><<<(unsigned)ctas, 256, sm, s>>>(x, tab, T, rows, N, R, z, act, xout, kplanes, s_row, s_r);
+  }
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+
 static int launch_fno2d_waxis(const float* x, const float* tab, float* T, long long rows, int N, int R, const float* z, int act,
                               float* xout, int kplanes, cudaStream_t s) {
   static const bool use_mma = !(getenv("RPDE_FNO2D_MMA") && atoi(getenv("RPDE_FNO2D_MMA")) == 0);
   auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
-  if (use_mma && N % 32 == 0 && R <= F2M_MAXR && f2m_waxis_smem(N, (R + 7) & ~7) <= 100 * 1024 && al16(x) && al16(z) && al16(xout)) {
-    // image rows on the warp-level tensor path (fno2d_mma.cuh): 16 rows per warp, table resident as TF32 hi / lo planes
-    const size_t sm = f2m_waxis_smem(N, (R + 7) & ~7);
-    long long ctas = ((rows + 15) / 16 + 7) / 8;
-    if (ctas > 2 * 148) ctas = 2 * 148;
-    RPDE_CUDA(cudaFuncSetAttribute(fno2d_waxis_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    fno2d_waxis_mma_kernel<<<(unsigned)ctas, 256, sm, s>>>(x, tab, T, rows, N, R, z, act, xout, kplanes);
-    RPDE_LAUNCH_CHECK();
-    return RPDE_OK;
-  }
+  if (use_mma && N % 32 == 0 && R <= F2M_MAXR && f2m_waxis_smem(N, (R + 7) & ~7, true) <= 100 * 1024 && al16(x) && al16(z) && al16(xout))
+    return launch_waxis_mma(x, tab, T, rows, N, R, z, act, xout, kplanes, R, 1, s);
   const size_t smem = (size_t)((R + 7) & ~7) * N * sizeof(float);
   long long blocks = (rows + 15) / 16;
   if (blocks > 148 * 4) blocks = 148 * 4;

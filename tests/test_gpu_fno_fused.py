@@ -59,6 +59,10 @@ SHAPES = [  # B, I, O, N, K, bypass, bias, act
     (1, 70, 33, 47, 24, True, True, "relu"),
     (2, 4, 4, 16, 9, True, True, "none"),          # Nyquist bin kept
     (2, 32, 32, 2048, 1, True, True, "gelu"),
+    # >= 4736 rows (b, i): the analysis runs on the warp-level tensor path (csrc/fno2d_mma.cuh), table as one fp32 plane
+    # split on the fly at N = 1024, as resident TF32 hi / lo planes at N = 256
+    (80, 64, 64, 1024, 16, True, True, "gelu"),
+    (160, 32, 32, 256, 12, True, True, "relu"),
 ]
 
 

@@ -113,6 +113,29 @@ def test_fno1d_resolutions(n):
     _compare_model("FNO1d", m, x, y, hyper)
 
 
+def test_fno1d_relu_kink_seed_stays_on_record():
+    """The draw test_fno1d_resolutions[512] skips (seed 512) kept visible: the fp64 oracle has a ReLU input at ~1e-8 of the
+    rms there, so the mask of that one element is a coin toss in fp32.  The forward pass is continuous at the kink and is held
+    to 1e-5; the gradients are compared too, and a miss is reported as an expected failure with the measured numbers."""
+    import resolution_pde_b200 as R
+    hyper = dict(activation="relu", n_blocks=4)
+    torch.manual_seed(512)
+    m = R.FNO1d(1, 1, modes=16, width=32)
+    with torch.no_grad():
+        for b in m.fno_blocks:
+            b.spectral_conv.weights1.mul_(20.0)
+    x, y = torch.randn(3, 1, 512), torch.randn(3, 1, 512)
+    margin = _relu_margin("FNO1d", m, x, y, hyper)
+    assert margin < 1e-6, margin      # if this draw ever stops being a kink case it belongs back in the sweep
+    sd = {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+    pred_o, loss_o, g_o = _oracle_step("FNO1d", sd, x, y, **hyper)
+    out, loss, gx, g = _step(m.to(DEV), x.to(DEV), y.to(DEV))
+    assert rel(out, pred_o) < TOL, rel(out, pred_o)
+    worst = max((rel(g[k], v), k) for k, v in g_o.items() if v.abs().max() > 1e-8)
+    if worst[0] >= TOL:
+        pytest.xfail(f"ReLU mask flip at margin {margin:.2e} of the rms: worst gradient {worst[1]} differs by {worst[0]:.2e}")
+
+
 @pytest.mark.parametrize("hw", [(32, 32), (64, 64), (64, 128), (128, 128), (33, 47)])
 def test_fno2d_resolutions(hw):
     import resolution_pde_b200 as R
