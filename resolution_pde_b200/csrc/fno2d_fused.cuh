@@ -169,6 +169,7 @@ __global__ void __launch_bounds__(256) fno2d_mix_kernel(const float* __restrict_
     const float* w = j < m1 ? w1 : w2;
     const int jj = j < m1 ? j : j - m1;
     float re = 0.f, im = 0.f;
+#pragma unroll 8   // eight channels' loads in flight per round trip (the loop is a pure L2-latency chain otherwise)
     for (int cl = 0; cl < Cl; ++cl) {
       const int i = mode ? co : cl, o = mode ? cl : co;
       const float* sp = in + (((long long)b * Cl + cl) * (2 * J) + 2 * j) * Ky + ky;
@@ -202,6 +203,7 @@ __global__ void __launch_bounds__(256) fno2d_wgrad_kernel(const float* __restric
     const int o = (int)(r % O);
     const int i = (int)(r / O);
     float re = 0.f, im = 0.f;
+#pragma unroll 8
     for (int b = 0; b < Bn; ++b) {
       const float* sp = spec + (((long long)b * I + i) * (2 * J) + 2 * j) * Ky + ky;
       const float* dp = dom + (((long long)b * O + o) * (2 * J) + 2 * j) * Ky + ky;

@@ -1158,9 +1158,11 @@ __global__ void __launch_bounds__(256) fno2d_rows_mma_kernel(const float* __rest
     for (int n = 0; n < 4; ++n)
 #pragma unroll
       for (int q = 0; q < 4; ++q) acc[m][n][q] = 0.f;
-  for (int ks = warp * per; ks < min(ksteps, (warp + 1) * per); ++ks) {
-    // B fragments: k = 8 ks + t (+ 4) -> (h, r) = (k >> 1, k & 1); column n = g of tile nt -> plane nt >> 1, ky = 8 (nt & 1) + g
-    uint32_t bh[4][2], bl[4][2];
+  // raw operands of one k-step: every global load is issued before the first value is used, and the next k-step's loads go
+  // out before the current k-step's MMAs (the loop is a chain of L2 round trips otherwise)
+  const int ks_end = min(ksteps, (warp + 1) * per);
+  auto load = [&](int ks, float (&braw)[4][2], float (&araw)[MT][4]) {
+    // B: k = 8 ks + t (+ 4) -> (h, r) = (k >> 1, k & 1); column n = g of tile nt -> plane nt >> 1, ky = 8 (nt & 1) + g
 #pragma unroll
     for (int nt = 0; nt < 4; ++nt) {
       const long long p = p0 + (nt >> 1);
@@ -1168,19 +1170,42 @@ __global__ void __launch_bounds__(256) fno2d_rows_mma_kernel(const float* __rest
 #pragma unroll
       for (int q = 0; q < 2; ++q) {
         const int k = 8 * ks + t + 4 * q;
-        const float v = (p < planes && ky < Ky && k < K) ? __ldg(T + (p * H + (k >> 1)) * R + 2 * ky + (k & 1)) : 0.f;
-        tf32_split(v, bh[nt][q], bl[nt][q]);
+        braw[nt][q] = (p < planes && ky < Ky && k < K) ? __ldg(T + (p * H + (k >> 1)) * R + 2 * ky + (k & 1)) : 0.f;
       }
+    }
+#pragma unroll
+    for (int m = 0; m < MT; ++m)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int a = 16 * m + g + 8 * (q & 1), k = 8 * ks + t + 4 * (q >> 1);
+        araw[m][q] = (a < A && k < K) ? __ldg(tab + (long long)k * A + a) : 0.f;
+      }
+  };
+  float bnext[4][2], anext[MT][4];
+  if (warp * per < ks_end) load(warp * per, bnext, anext);
+  for (int ks = warp * per; ks < ks_end; ++ks) {
+    float braw[4][2], araw[MT][4];
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) {
+      braw[nt][0] = bnext[nt][0];
+      braw[nt][1] = bnext[nt][1];
+    }
+#pragma unroll
+    for (int m = 0; m < MT; ++m)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) araw[m][q] = anext[m][q];
+    if (ks + 1 < ks_end) load(ks + 1, bnext, anext);
+    uint32_t bh[4][2], bl[4][2];
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) {
+      tf32_split(braw[nt][0], bh[nt][0], bl[nt][0]);
+      tf32_split(braw[nt][1], bh[nt][1], bl[nt][1]);
     }
 #pragma unroll
     for (int m = 0; m < MT; ++m) {
       uint32_t ah[4], al[4];
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const int a = 16 * m + g + 8 * (q & 1), k = 8 * ks + t + 4 * (q >> 1);
-        const float v = (a < A && k < K) ? __ldg(tab + (long long)k * A + a) : 0.f;
-        tf32_split(v, ah[q], al[q]);
-      }
+      for (int q = 0; q < 4; ++q) tf32_split(araw[m][q], ah[q], al[q]);
 #pragma unroll
       for (int nt = 0; nt < 4; ++nt) mma_3xtf32(acc[m][nt], ah, al, bh[nt][0], bh[nt][1], bl[nt][0], bl[nt][1]);
     }
