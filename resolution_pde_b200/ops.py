@@ -354,8 +354,12 @@ class _FFNOFourierFn(torch.autograd.Function):
     """1-D: x (B,N,C), weights (w,).  2-D: x (B,M,N,C), weights (w_y, w_x); result = x-pass + y-pass."""
 
     @staticmethod
-    def forward(ctx, x, n_modes, mix, norm, grad_on, *weights):
+    def forward(ctx, x, n_modes, mix, norm, grad_on, with_skip, *weights):
+        # with_skip: x is returned as a second output (the layer's skip connection, F-FNO `x + layer(x)`).  Its gradient then
+        # arrives HERE together with the gradient of the spectral result, and the first backward pass accumulates onto it
+        # in place: no separate add kernel for the two uses of x (autograd would insert one).
         _need_cuda(x, *weights)
+        x_in = x
         x = x.contiguous()
         C = x.shape[-1]
         B = x.shape[0]
@@ -381,19 +385,30 @@ class _FFNOFourierFn(torch.autograd.Function):
                                                     rest, C, k, w.shape[2], mix, _p(ws), nb, c.stream),
                            "rpde_ffno_axis_fwd")
                 specs.append(spec)
-        keep_spec = grad_on and mix == MIX_FULL and any(ctx.needs_input_grad[5:])
+        keep_spec = grad_on and mix == MIX_FULL and any(ctx.needs_input_grad[6:])
         ctx.save_for_backward(*weights, *(specs if keep_spec else []))
         ctx.cfg = (n_modes, mix, norm, passes, C, len(weights), keep_spec, tuple(x.shape))
+        if with_skip:
+            return y, x_in
         return y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, dskip=None):
         n_modes, mix, norm, passes, C, nw, keep_spec, xshape = ctx.cfg
         saved = ctx.saved_tensors
         weights, specs = saved[:nw], saved[nw:]
         dy = dy.contiguous()
         need_x = ctx.needs_input_grad[0]
-        dx = torch.empty(xshape, dtype=torch.float32, device=dy.device) if need_x else None
+        acc0 = 0
+        dx = None
+        if need_x:
+            if dskip is not None and dskip.is_contiguous() and dskip.dtype == torch.float32 and tuple(dskip.shape) == xshape:
+                dx, acc0 = dskip, 1        # the skip connection's gradient: the passes add onto it in place
+            else:
+                dx = torch.empty(xshape, dtype=torch.float32, device=dy.device)
+                if dskip is not None:
+                    dx.copy_(dskip)
+                    acc0 = 1
         dws = [None] * nw
         with _Ctx(dy) as c:
             for pi, (outer, n, rest, wi) in enumerate(passes):
@@ -402,7 +417,7 @@ class _FFNOFourierFn(torch.autograd.Function):
                 fa = dft_table(0, n, k, 0, sf, dy.device)
                 fs = dft_table(1, n, k, 0, si, dy.device)
                 w = weights[wi].detach().contiguous()
-                want_w = keep_spec and ctx.needs_input_grad[5 + wi]
+                want_w = keep_spec and ctx.needs_input_grad[6 + wi]
                 dw = None
                 if want_w:
                     dw = torch.empty_like(w)
@@ -410,16 +425,17 @@ class _FFNOFourierFn(torch.autograd.Function):
                 spec = specs[pi] if keep_spec else None
                 nb = c.lib.rpde_ffno_axis_workspace_bytes(outer, n, rest, C, k)
                 ws = _ws(nb, dy.device)
-                _lib.check(c.lib.rpde_ffno_axis_bwd(_p(dy), _p(w), _p(fa), _p(fs), _p(spec), _p(dx), 1 if pi else 0, _p(dw), 0,
+                _lib.check(c.lib.rpde_ffno_axis_bwd(_p(dy), _p(w), _p(fa), _p(fs), _p(spec), _p(dx), 1 if pi else acc0, _p(dw), 0,
                                                     outer, n, rest, C, k, w.shape[2], mix, _p(ws), nb, c.stream),
                            "rpde_ffno_axis_bwd")
         if mix != MIX_FULL:
-            dws = [torch.zeros_like(w) if ctx.needs_input_grad[5 + i] else None for i, w in enumerate(weights)]
-        return (dx, None, None, None, None, *dws)
+            dws = [torch.zeros_like(w) if ctx.needs_input_grad[6 + i] else None for i, w in enumerate(weights)]
+        return (dx, None, None, None, None, None, *dws)
 
 
-def ffno_fourier(x, weights: Sequence[torch.Tensor], n_modes: int, mix: int = MIX_FULL, norm: str = "ortho"):
-    return _FFNOFourierFn.apply(x, n_modes, mix, norm, torch.is_grad_enabled(), *weights)
+def ffno_fourier(x, weights: Sequence[torch.Tensor], n_modes: int, mix: int = MIX_FULL, norm: str = "ortho", with_skip: bool = False):
+    """with_skip=True returns (fourier(x), x): route the layer's skip connection through the second output (see forward)."""
+    return _FFNOFourierFn.apply(x, n_modes, mix, norm, torch.is_grad_enabled(), bool(with_skip), *weights)
 
 
 # ---------------------------------------------------------------------------------------------

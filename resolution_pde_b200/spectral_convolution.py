@@ -65,6 +65,12 @@ def _init_fourier_weights(d_model, modes, n):
     return ws
 
 
+def _route_skip(x):
+    """True when the layer's skip connection should travel through the Fourier function's second output, so that its gradient
+    is accumulated inside the spectral backward pass instead of by a separate add (only matters when a backward pass follows)."""
+    return torch.is_grad_enabled() and x.requires_grad and x.is_cuda
+
+
 class FSpectralConv1d(nn.Module):
     """spectral_convolution.py:108-204.  forward(x (B,N,C), batch_dt=None) -> (act(backcast_ff(fourier(x))), None)."""
 
@@ -91,20 +97,23 @@ class FSpectralConv1d(nn.Module):
     def forward(self, x, batch_dt=None, residual=None):
         """`residual` (not in the reference signature, default None) lets FFNO1D fuse its skip connection."""
         if self.mode != 'no-fourier':
-            x = self.forward_fourier(x)
+            if residual is x and _route_skip(x):
+                x, residual = self.forward_fourier(x, with_skip=True)
+            else:
+                x = self.forward_fourier(x)
         if isinstance(self.backcast_ff, FeedForward):
             return self.backcast_ff(x, residual=residual, final_act=self._act_id), None
         b = self.act(self.backcast_ff(x))  # injected foreign feed-forward module
         return (b if residual is None else residual + b), None
 
-    def forward_fourier(self, x):
+    def forward_fourier(self, x, with_skip=False):
         if self.mode == 'full':
             mix = ops.MIX_FULL
         elif self.mode == 'low-pass':
             mix = ops.MIX_LOWPASS
         else:
             raise ValueError(f"Mode {self.mode} not recognized")
-        return ops.ffno_fourier(x, [self.fourier_weight[0]], self.n_modes, mix, self.fft_norm)
+        return ops.ffno_fourier(x, [self.fourier_weight[0]], self.n_modes, mix, self.fft_norm, with_skip=with_skip)
 
 
 class FSpectralConv2d(nn.Module):
@@ -134,7 +143,10 @@ class FSpectralConv2d(nn.Module):
 
     def forward(self, x, batch_dt=None, residual=None):
         if self.mode != 'no-fourier':
-            x = self.forward_fourier(x)
+            if residual is x and self.mode in ('full', 'low-pass') and _route_skip(x):
+                x, residual = self.forward_fourier(x, with_skip=True)
+            else:
+                x = self.forward_fourier(x)
         if isinstance(self.backcast_ff, FeedForward):
             b = self.backcast_ff(x, residual=residual)
         else:
@@ -143,7 +155,7 @@ class FSpectralConv2d(nn.Module):
         f = self.forecast_ff(x) if self.use_fork else None
         return b, f
 
-    def forward_fourier(self, x):
+    def forward_fourier(self, x, with_skip=False):
         if self.mode == 'full':
             mix = ops.MIX_FULL
         elif self.mode == 'low-pass':
@@ -151,4 +163,5 @@ class FSpectralConv2d(nn.Module):
         else:
             # the reference has no `else` branch: both spectra stay zero (spectral_convolution.py:273-281)
             return torch.zeros_like(x)
-        return ops.ffno_fourier(x, [self.fourier_weight[0], self.fourier_weight[1]], self.n_modes, mix, "ortho")
+        return ops.ffno_fourier(x, [self.fourier_weight[0], self.fourier_weight[1]], self.n_modes, mix, "ortho",
+                                with_skip=with_skip)
