@@ -62,11 +62,19 @@ __device__ __forceinline__ void mma_3xtf32(float (&d)[4], const uint32_t (&ah)[4
 }
 
 __host__ __device__ constexpr size_t f2m_synth_smem(int W, int RP) {
-  return ((size_t)2 * RP * (W + 4)                      // table hi / lo
+  return ((size_t)2 * (RP / 2) * (2 * W + 4)            // table hi / lo, rows t and t + 4 of a k-step interleaved per point
           + (size_t)2 * F2M_MAXC * F2M_LDA              // bypass weight hi / lo
           + (size_t)2 * 2 * (256 / W) * RP * F2M_LDA    // Z ring: 2 stages x hi / lo x rows per iteration
           + F2M_MAXC) * sizeof(float);                  // bias
 }
+
+// Table layout in shared memory.  An HMMA takes its B operand from a register PAIR (k = t, k = t + 4) and a lane needs that
+// pair for four points, so rows t and t + 4 of each k-step are interleaved per point: one float4 = the pairs of two points,
+// loaded straight into the registers the MMA reads (assembling the pairs from two row-major float4 cost two MOVs per HMMA).
+// Row (ks, t) holds, per 32-point warp segment, eight 8-float groups (four points x two rows); group pg sits at slot
+// sigma(pg) so that the two point groups read in one shared-memory phase (lanes g = 2 q, 2 q + 1 -> groups q, 4 + q) are 16
+// floats apart, and with a row stride of 4 mod 32 the eight lanes of a phase cover all 32 banks.
+__device__ __forceinline__ int f2m_slot(int pg) { return pg < 4 ? (pg & 1) + 4 * (pg >> 1) : ((pg - 4) & 1) + 4 * ((pg - 4) >> 1) + 2; }
 
 template <int W>
 __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __restrict__ x, const float* __restrict__ Z,
@@ -77,12 +85,12 @@ __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __
   static_assert(W == 64 || W == 128 || W == 256, "one warp per 32 grid points, eight warps");
   constexpr int WPR = W / 32;        // warps per image row
   constexpr int RPI = 8 / WPR;       // image rows per iteration
-  constexpr int LDT = W + 4;         // table planes [r][n]: stride = 4 mod 32 -> conflict-free float4 fragment loads
+  constexpr int LDP = 2 * W + 4;     // paired table rows: stride = 4 mod 32
   extern __shared__ __align__(16) float smem[];
   const int R = 2 * K, RP = (R + 7) & ~7, KS_T = RP / 8, KS_X = wb ? (I + 7) / 8 : 0;
-  float* tabH = smem;
-  float* tabL = tabH + RP * LDT;
-  float* wbH = tabL + RP * LDT;
+  float* tabH = smem;                                   // [ks * 4 + t][LDP]
+  float* tabL = tabH + (RP / 2) * LDP;
+  float* wbH = tabL + (RP / 2) * LDP;
   float* wbL = wbH + F2M_MAXC * F2M_LDA;
   float* zring = wbL + F2M_MAXC * F2M_LDA;            // [stage][hi|lo][row][r][LDA]
   float* biasS = zring + 2 * 2 * RPI * RP * F2M_LDA;
@@ -97,8 +105,10 @@ __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __
     if (r < R) v = __ldg(table + (adjoint ? (long long)r : (long long)(r & 1) * K + (r >> 1)) * W + n);
     uint32_t hi, lo;
     tf32_split_rn(v, hi, lo);
-    tabH[r * LDT + n] = __uint_as_float(hi);
-    tabL[r * LDT + n] = __uint_as_float(tf32_hi(__uint_as_float(lo)));
+    const int ks = r >> 3, tt = r & 3, half = (r >> 2) & 1;
+    const int off = (ks * 4 + tt) * LDP + (n >> 5) * 64 + f2m_slot((n >> 2) & 7) * 8 + (n & 3) * 2 + half;
+    tabH[off] = __uint_as_float(hi);
+    tabL[off] = __uint_as_float(tf32_hi(__uint_as_float(lo)));
   }
   for (int e = tid; e < F2M_MAXC * F2M_MAXC; e += 256) {
     const int i = e / F2M_MAXC, o = e - i * F2M_MAXC;  // A[o][k = i]
@@ -114,30 +124,41 @@ __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __
   const int ntiles = (Bn + RPI - 1) / RPI;
   constexpr int ZPT = (RPI * F2M_MAXR * F2M_MAXC + 255) / 256;   // Z elements per thread and iteration (upper bound)
   const int zcount = RPI * RP * F2M_MAXC;
+  const long long chan = (long long)Hd * W;                      // elements between two channels of one image
+  // per-lane table fragment base (row t of k-step 0, this lane's point group) and A fragment bases
+  const int tab_off = t * LDP + (n0 >> 5) * 64 + f2m_slot(pg) * 8;
+  const int a_off = t * F2M_LDA + g;
 
-  // loads of one iteration: this warp's x rows (two float4 per k-step) and the thread's share of the Z rows
-  auto load_x = [&](int tile, float4 (&xb)[8]) {
-    const int row = tile * RPI + wrow;
-    const bool ok = row < Bn;
+  // this warp's x rows (two float4 per k-step): the address of channel t, point group pg of image row `row`
+  auto x_ptr = [&](int row) {
     const int bh = row / Hd, hh = row - bh * Hd;
+    return x + ((long long)bh * I * Hd + hh) * W + n0 + 4 * pg + (long long)t * chan;
+  };
+  auto load_x = [&](int row, float4 (&xb)[8]) {
+    const float* p = x_ptr(row);
+    const bool ok = row < Bn;
 #pragma unroll
-    for (int ks = 0; ks < 4; ++ks) {
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int i = 8 * ks + t + 4 * h;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (ok && ks < KS_X && i < I)
-          v = __ldg(reinterpret_cast<const float4*>(x + (((long long)bh * I + i) * Hd + hh) * W + n0 + 4 * pg));
-        xb[2 * ks + h] = v;
-      }
+    for (int q = 0; q < 8; ++q) {    // channel t + 4 q: k-step q >> 1, fragment row t (+ 4)
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (ok && (q >> 1) < KS_X && t + 4 * q < I) v = __ldg(reinterpret_cast<const float4*>(p + 4 * q * chan));
+      xb[q] = v;
     }
+  };
+  // the next iteration's x rows are only pulled into L2 (no registers held across the MMA loop; the eight lanes g = 0..7
+  // of equal t share a 128-byte line, lane g = 0 asks for it)
+  auto prefetch_x = [&](int row) {
+    if (row >= Bn || g != 0) return;
+    const float* p = x_ptr(row);
+#pragma unroll
+    for (int q = 0; q < 8; ++q)
+      if ((q >> 1) < KS_X && t + 4 * q < I) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + 4 * q * chan));
   };
   auto load_z = [&](int tile, float (&zb)[ZPT]) {
 #pragma unroll
     for (int q = 0; q < ZPT; ++q) {
       const int e = tid + 256 * q;
       const int o = e % F2M_MAXC, rr = e / F2M_MAXC;       // rr = rowslot * RP + r
-      const int slot = rr / RP, r = rr - slot * RP;
+      const int slot = RPI == 1 ? 0 : rr / RP, r = rr - slot * RP;
       const int row = tile * RPI + slot;
       float v = 0.f;
       if (e < zcount && row < Bn && r < R && o < O) v = __ldg(Z + ((long long)r * Bn + row) * O + o);
@@ -158,22 +179,6 @@ __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __
       zl[rr * F2M_LDA + o] = __uint_as_float(lo);
     }
   };
-
-  // the next iteration's x rows are only pulled into L2 (no registers held across the MMA loop; the eight lanes g = 0..7
-  // of equal t share a 128-byte line, lane g = 0 asks for it)
-  auto prefetch_x = [&](int tile) {
-    const int row = tile * RPI + wrow;
-    if (row >= Bn || g != 0) return;
-    const int bh = row / Hd, hh = row - bh * Hd;
-#pragma unroll
-    for (int ks = 0; ks < 4; ++ks)
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int i = 8 * ks + t + 4 * h;
-        if (ks < KS_X && i < I)
-          asm volatile("prefetch.global.L2 [%0];" ::"l"(x + (((long long)bh * I + i) * Hd + hh) * W + n0));
-      }
-  };
   float zb[ZPT];
   int tile = blockIdx.x;
   if (tile < ntiles) {
@@ -185,13 +190,13 @@ __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __
   int stage = 0;
   for (; tile < ntiles; tile += gridDim.x) {
     const int next = tile + gridDim.x;
+    const int row = tile * RPI + wrow;
     float4 xb[8];
-    load_x(tile, xb);
+    load_x(row, xb);
     if (next < ntiles) {
-      prefetch_x(next);
+      prefetch_x(next * RPI + wrow);
       load_z(next, zb);
     }
-    const int row = tile * RPI + wrow;
     if (row < Bn) {
       float acc[2][4][4];
 #pragma unroll
@@ -200,40 +205,41 @@ __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __
         for (int j = 0; j < 4; ++j)
 #pragma unroll
           for (int c = 0; c < 4; ++c) acc[m][j][c] = 0.f;
-      const float* zh = zring + (size_t)stage * 2 * RPI * RP * F2M_LDA + (size_t)wrow * RP * F2M_LDA;
+      const float* zh = zring + (size_t)stage * 2 * RPI * RP * F2M_LDA + (size_t)wrow * RP * F2M_LDA + a_off;
       const float* zl = zh + RPI * RP * F2M_LDA;
       // spectral rows
-      for (int ks = 0; ks < KS_T; ++ks) {
-        const int r0 = 8 * ks + t;
-        const float4 h0 = *reinterpret_cast<const float4*>(tabH + r0 * LDT + n0 + 4 * pg);
-        const float4 h1 = *reinterpret_cast<const float4*>(tabH + (r0 + 4) * LDT + n0 + 4 * pg);
-        const float4 l0 = *reinterpret_cast<const float4*>(tabL + r0 * LDT + n0 + 4 * pg);
-        const float4 l1 = *reinterpret_cast<const float4*>(tabL + (r0 + 4) * LDT + n0 + 4 * pg);
-        const float bh0[4] = {h0.x, h0.y, h0.z, h0.w}, bh1[4] = {h1.x, h1.y, h1.z, h1.w};
-        const float bl0[4] = {l0.x, l0.y, l0.z, l0.w}, bl1[4] = {l1.x, l1.y, l1.z, l1.w};
 #pragma unroll
-        for (int m = 0; m < 2; ++m) {
-          uint32_t ah[4], al[4];
-          const int o = 16 * m + g;
-          ah[0] = __float_as_uint(zh[r0 * F2M_LDA + o]);
-          ah[1] = __float_as_uint(zh[r0 * F2M_LDA + o + 8]);
-          ah[2] = __float_as_uint(zh[(r0 + 4) * F2M_LDA + o]);
-          ah[3] = __float_as_uint(zh[(r0 + 4) * F2M_LDA + o + 8]);
-          al[0] = __float_as_uint(zl[r0 * F2M_LDA + o]);
-          al[1] = __float_as_uint(zl[r0 * F2M_LDA + o + 8]);
-          al[2] = __float_as_uint(zl[(r0 + 4) * F2M_LDA + o]);
-          al[3] = __float_as_uint(zl[(r0 + 4) * F2M_LDA + o + 8]);
+      for (int ks = 0; ks < 4; ++ks) {
+        if (ks < KS_T) {
+          const float4 h0 = *reinterpret_cast<const float4*>(tabH + tab_off + ks * 4 * LDP);        // points j = 0, 1
+          const float4 h1 = *reinterpret_cast<const float4*>(tabH + tab_off + ks * 4 * LDP + 4);    // points j = 2, 3
+          const float4 l0 = *reinterpret_cast<const float4*>(tabL + tab_off + ks * 4 * LDP);
+          const float4 l1 = *reinterpret_cast<const float4*>(tabL + tab_off + ks * 4 * LDP + 4);
 #pragma unroll
-          for (int j = 0; j < 4; ++j)
-            mma_3xtf32(acc[m][j], ah, al, __float_as_uint(bh0[j]), __float_as_uint(bh1[j]), __float_as_uint(bl0[j]),
-                       __float_as_uint(bl1[j]));
+          for (int m = 0; m < 2; ++m) {
+            uint32_t ah[4], al[4];
+            const int o = ks * 8 * F2M_LDA + 16 * m;
+            ah[0] = __float_as_uint(zh[o]);
+            ah[1] = __float_as_uint(zh[o + 8]);
+            ah[2] = __float_as_uint(zh[o + 4 * F2M_LDA]);
+            ah[3] = __float_as_uint(zh[o + 4 * F2M_LDA + 8]);
+            al[0] = __float_as_uint(zl[o]);
+            al[1] = __float_as_uint(zl[o + 8]);
+            al[2] = __float_as_uint(zl[o + 4 * F2M_LDA]);
+            al[3] = __float_as_uint(zl[o + 4 * F2M_LDA + 8]);
+            mma_3xtf32(acc[m][0], ah, al, __float_as_uint(h0.x), __float_as_uint(h0.y), __float_as_uint(l0.x), __float_as_uint(l0.y));
+            mma_3xtf32(acc[m][1], ah, al, __float_as_uint(h0.z), __float_as_uint(h0.w), __float_as_uint(l0.z), __float_as_uint(l0.w));
+            mma_3xtf32(acc[m][2], ah, al, __float_as_uint(h1.x), __float_as_uint(h1.y), __float_as_uint(l1.x), __float_as_uint(l1.y));
+            mma_3xtf32(acc[m][3], ah, al, __float_as_uint(h1.z), __float_as_uint(h1.w), __float_as_uint(l1.z), __float_as_uint(l1.w));
+          }
         }
       }
       // bypass conv: input channels
+      const float* wh = wbH + a_off;
+      const float* wl = wbL + a_off;
 #pragma unroll
       for (int ks = 0; ks < 4; ++ks) {
         if (ks < KS_X) {
-          const int i0 = 8 * ks + t;
           const float v0[4] = {xb[2 * ks].x, xb[2 * ks].y, xb[2 * ks].z, xb[2 * ks].w};
           const float v1[4] = {xb[2 * ks + 1].x, xb[2 * ks + 1].y, xb[2 * ks + 1].z, xb[2 * ks + 1].w};
           uint32_t bh0[4], bh1[4], bl0[4], bl1[4];
@@ -245,23 +251,25 @@ __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __
 #pragma unroll
           for (int m = 0; m < 2; ++m) {
             uint32_t ah[4], al[4];
-            const int o = 16 * m + g;
-            ah[0] = __float_as_uint(wbH[i0 * F2M_LDA + o]);
-            ah[1] = __float_as_uint(wbH[i0 * F2M_LDA + o + 8]);
-            ah[2] = __float_as_uint(wbH[(i0 + 4) * F2M_LDA + o]);
-            ah[3] = __float_as_uint(wbH[(i0 + 4) * F2M_LDA + o + 8]);
-            al[0] = __float_as_uint(wbL[i0 * F2M_LDA + o]);
-            al[1] = __float_as_uint(wbL[i0 * F2M_LDA + o + 8]);
-            al[2] = __float_as_uint(wbL[(i0 + 4) * F2M_LDA + o]);
-            al[3] = __float_as_uint(wbL[(i0 + 4) * F2M_LDA + o + 8]);
+            const int o = ks * 8 * F2M_LDA + 16 * m;
+            ah[0] = __float_as_uint(wh[o]);
+            ah[1] = __float_as_uint(wh[o + 8]);
+            ah[2] = __float_as_uint(wh[o + 4 * F2M_LDA]);
+            ah[3] = __float_as_uint(wh[o + 4 * F2M_LDA + 8]);
+            al[0] = __float_as_uint(wl[o]);
+            al[1] = __float_as_uint(wl[o + 8]);
+            al[2] = __float_as_uint(wl[o + 4 * F2M_LDA]);
+            al[3] = __float_as_uint(wl[o + 4 * F2M_LDA + 8]);
 #pragma unroll
             for (int j = 0; j < 4; ++j) mma_3xtf32(acc[m][j], ah, al, bh0[j], bh1[j], bl0[j], bl1[j]);
           }
         }
       }
       // epilogue: lane holds, for channels o = 16 m + g (+ 8), the points n0 + 4 t + {0..3} (accumulator columns 2 t of the
-      // four n-tiles) and n0 + 16 + 4 t + {0..3} (columns 2 t + 1)
+      // four n-tiles) and n0 + 16 + 4 t + {0..3} (columns 2 t + 1); the channel pointer advances by eight channels per step
       const int bh = row / Hd, hh = row - bh * Hd;
+      float* yp = y + ((long long)bh * O * Hd + hh) * W + n0 + 4 * t + (long long)g * chan;
+      const long long zd = z ? z - y : 0;
 #pragma unroll
       for (int m = 0; m < 2; ++m) {
 #pragma unroll
@@ -269,7 +277,6 @@ __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __
           const int o = 16 * m + g + 8 * half;
           if (o < O) {
             const float bias = biasS[o];
-            const long long base = (((long long)bh * O + o) * Hd + hh) * W + n0 + 4 * t;
 #pragma unroll
             for (int c = 0; c < 2; ++c) {
               float pre[4], out[4];
@@ -283,10 +290,11 @@ __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __
 #pragma unroll
                 for (int j = 0; j < 4; ++j) out[j] = act_f(act, pre[j]);
               }
-              *reinterpret_cast<float4*>(y + base + 16 * c) = make_float4(out[0], out[1], out[2], out[3]);
-              if (z) *reinterpret_cast<float4*>(z + base + 16 * c) = make_float4(pre[0], pre[1], pre[2], pre[3]);
+              *reinterpret_cast<float4*>(yp + 16 * c) = make_float4(out[0], out[1], out[2], out[3]);
+              if (z) *reinterpret_cast<float4*>(yp + zd + 16 * c) = make_float4(pre[0], pre[1], pre[2], pre[3]);
             }
           }
+          yp += 8 * chan;
         }
       }
     }
