@@ -920,7 +920,7 @@ __global__ void __launch_bounds__(256, KS == 4 ? 2 : 1) mlp_bwd_mma_kernel(const
 // fp32 plane and its fragments are split when they are read.  The output element (row, r) goes to T[row * s_row + r * s_r]:
 // (R, 1) for the 2-D half transform, (1, rows) for the FNO1d spectrum layout [mode][re|im][b][i] (fno_fused.cuh).
 __host__ __device__ constexpr size_t f2m_waxis_smem(int W, int RP, bool presplit) {
-  return (size_t)(presplit ? 2 : 1) * RP * (W + 16) * sizeof(float);
+  return (size_t)(presplit ? 2 : 1) * RP * (W + 4) * sizeof(float);
 }
 
 template <bool PRESPLIT>
@@ -929,7 +929,9 @@ __global__ void __launch_bounds__(256, PRESPLIT ? 2 : 1) fno2d_waxis_mma_kernel(
                                                                  const float* __restrict__ z, int act, float* __restrict__ xout,
                                                                  int kplanes, long long s_row, long long s_r) {
   extern __shared__ __align__(16) float smem[];
-  const int RP = (R + 7) & ~7, NT = RP / 8, LDT = W + 16;     // stride = 16 mod 32: conflict-free float4 B fragments
+  // Table rows keep each 32-point group as [t][j][k = t | k = t + 4]: the lane's eight floats at 8 t are the B operand pairs
+  // of the four k-steps (no register shuffling in front of the MMA); row stride = 4 mod 32: conflict-free float4 loads
+  const int RP = (R + 7) & ~7, NT = RP / 8, LDT = W + 4;
   float* tabH = smem;
   float* tabL = tabH + (PRESPLIT ? RP * LDT : 0);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
@@ -937,13 +939,15 @@ __global__ void __launch_bounds__(256, PRESPLIT ? 2 : 1) fno2d_waxis_mma_kernel(
     const int r = e / W, n = e - r * W;
     const int tr = kplanes ? (r & 1) * kplanes + (r >> 1) : r;
     const float v = r < R ? __ldg(tab + (long long)tr * W + n) : 0.f;
+    // point n = 32 gi + 16 half + 4 tt + j  ->  32 gi + 8 tt + 2 j + half
+    const int off = r * LDT + (n & ~31) + 8 * ((n >> 2) & 3) + 2 * (n & 3) + ((n >> 4) & 1);
     if (PRESPLIT) {
       uint32_t hi, lo;
       tf32_split_rn(v, hi, lo);
-      tabH[r * LDT + n] = __uint_as_float(hi);
-      tabL[r * LDT + n] = __uint_as_float(tf32_hi(__uint_as_float(lo)));
+      tabH[off] = __uint_as_float(hi);
+      tabL[off] = __uint_as_float(tf32_hi(__uint_as_float(lo)));
     } else {
-      tabH[r * LDT + n] = v;
+      tabH[off] = v;
     }
   }
   __syncthreads();
@@ -1026,14 +1030,14 @@ __global__ void __launch_bounds__(256, PRESPLIT ? 2 : 1) fno2d_waxis_mma_kernel(
 #pragma unroll
       for (int nt = 0; nt < 4; ++nt) {
         if (nt < NT) {
-          const float* th = tabH + (8 * nt + g) * LDT + 32 * gi + 4 * t;
-          const float* tl = tabL + (8 * nt + g) * LDT + 32 * gi + 4 * t;
-          const float4 h0 = *reinterpret_cast<const float4*>(th), h1 = *reinterpret_cast<const float4*>(th + 16);
-          const float bv0[4] = {h0.x, h0.y, h0.z, h0.w}, bv1[4] = {h1.x, h1.y, h1.z, h1.w};
+          const float* th = tabH + (8 * nt + g) * LDT + 32 * gi + 8 * t;
+          const float* tl = tabL + (8 * nt + g) * LDT + 32 * gi + 8 * t;
+          const float4 h0 = *reinterpret_cast<const float4*>(th), h1 = *reinterpret_cast<const float4*>(th + 4);
+          const float bv0[4] = {h0.x, h0.z, h1.x, h1.z}, bv1[4] = {h0.y, h0.w, h1.y, h1.w};   // k = t | k = t + 4 of k-steps j = 0..3
           uint32_t bh0[4], bh1[4], bl0[4], bl1[4];
           if (PRESPLIT) {
-            const float4 l0 = *reinterpret_cast<const float4*>(tl), l1 = *reinterpret_cast<const float4*>(tl + 16);
-            const float lv0[4] = {l0.x, l0.y, l0.z, l0.w}, lv1[4] = {l1.x, l1.y, l1.z, l1.w};
+            const float4 l0 = *reinterpret_cast<const float4*>(tl), l1 = *reinterpret_cast<const float4*>(tl + 4);
+            const float lv0[4] = {l0.x, l0.z, l1.x, l1.z}, lv1[4] = {l0.y, l0.w, l1.y, l1.w};
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               bh0[j] = __float_as_uint(bv0[j]); bh1[j] = __float_as_uint(bv1[j]);
