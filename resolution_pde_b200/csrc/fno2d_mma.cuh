@@ -1106,7 +1106,8 @@ __global__ void __launch_bounds__(128) fno2d_expand_mma_kernel(const float* __re
   // rows of the accumulator fragment: g -> table row row_base + g, g + 8 -> row_base + g + 8
   const int tr0 = row_base + g, tr1 = tr0 + 8;
   const int h0 = tr0 >> 1, r0 = tr0 & 1, h1 = tr1 >> 1, r1 = tr1 & 1;
-  for (int c0 = 0; c0 < C; c0 += 8) {
+  // gridDim.z splits the channel tiles (small images have few table rows: more CTAs instead of longer loops)
+  for (int c0 = 8 * blockIdx.z; c0 < C; c0 += 8 * gridDim.z) {
     const int c = c0 + g;                                      // B fragment column (n = g)
     const float* src = in + ((long long)b * C + c) * A * Ky;
     for (int kq = 0; kq < Ky; kq += 4) {

@@ -513,7 +513,10 @@ static int launch_fno2d_expand(const float* in, const float* tab, float* Z, int 
   if (use_mma && A <= 64 && Ky % 4 == 0 && C % 8 == 0 && (reinterpret_cast<uintptr_t>(in) & 15) == 0 &&
       (reinterpret_cast<uintptr_t>(Z) & 7) == 0) {
     // 32 image rows per CTA (four warps x 16 table rows) on the warp-level tensor path (fno2d_mma.cuh)
-    dim3 gm((unsigned)((2 * H + 63) / 64), (unsigned)B);
+    const unsigned mchunks = (unsigned)((2 * H + 63) / 64);
+    unsigned zsplit = 1;                                  // enough CTAs for two waves of four-warp CTAs where the shape allows
+    while (zsplit < (unsigned)(C / 8) && mchunks * (unsigned)B * zsplit < 4 * 148) zsplit *= 2;
+    dim3 gm(mchunks, (unsigned)B, zsplit);
     if (A <= 32) fno2d_expand_mma_kernel<4><<<gm, 128, 0, s>>>(in, tab, Z, B, C, H, Ky, A);
     else if (A <= 48) fno2d_expand_mma_kernel<6><<<gm, 128, 0, s>>>(in, tab, Z, B, C, H, Ky, A);
     else fno2d_expand_mma_kernel<8><<<gm, 128, 0, s>>>(in, tab, Z, B, C, H, Ky, A);
@@ -533,6 +536,25 @@ static int launch_fno2d_expand(const float* in, const float* tab, float* Z, int 
   else if (Ky <= 8) RPDE_EXPAND(8);
   else RPDE_EXPAND(12);
 #undef RPDE_EXPAND
+  RPDE_LAUNCH_CHECK();
+  return RPDE_OK;
+}
+
+// per-mode channel mixing (mode 0) and its adjoint (mode 1): the shared-memory-tiled kernel when the ky row fits its 16 slots
+static int launch_fno2d_mix(const float* in, const float* w1, const float* w2, float* out, int B, int I, int O, int m1, int Ky,
+                            int mode, cudaStream_t s) {
+  const int J = 2 * m1, Co = mode ? I : O;
+  if (Ky <= F2X_KY && (long long)B <= 65535LL * F2X_MB) {
+    dim3 g((unsigned)J, (unsigned)((Co + F2X_OC - 1) / F2X_OC), (unsigned)((B + F2X_MB - 1) / F2X_MB));
+    auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+    if (Ky % 4 == 0 && al16(in) && al16(w1) && al16(w2))
+      fno2d_mix_tiled_kernel<true><<<g, 256, 0, s>>>(in, w1, w2, out, B, I, O, m1, Ky, mode);
+    else
+      fno2d_mix_tiled_kernel<false><<<g, 256, 0, s>>>(in, w1, w2, out, B, I, O, m1, Ky, mode);
+  } else {
+    const long long total = (long long)B * Co * J * Ky;
+    fno2d_mix_kernel<<<grid_for(total), 256, 0, s>>>(in, w1, w2, out, B, I, O, m1, Ky, mode);
+  }
   RPDE_LAUNCH_CHECK();
   return RPDE_OK;
 }
@@ -561,11 +583,8 @@ int rpde_fno_block2d_fwd(const float* x, const float* w1, const float* w2, const
   if (rc) return rc;
   rc = launch_fno2d_rows(T, g2t, spec, (long long)B * I, H, Ky, 2 * J, s);
   if (rc) return rc;
-  {
-    const long long total = (long long)B * O * J * Ky;
-    fno2d_mix_kernel<<<grid_for(total), 256, 0, s>>>(spec, w1, w2, om, B, I, O, m1, Ky, 0);
-    RPDE_LAUNCH_CHECK();
-  }
+  rc = launch_fno2d_mix(spec, w1, w2, om, B, I, O, m1, Ky, 0, s);
+  if (rc) return rc;
   rc = launch_fno2d_expand(om, g3, Z, B, O, H, Ky, 2 * J, s);
   if (rc) return rc;
   return launch_fno1d_synth(x, Z, fs4_y, wb, bb, y, z, B * H, I, O, W, Ky, act, 0, s, H);
@@ -600,14 +619,18 @@ int rpde_fno_block2d_bwd(const float* dy, const float* z, int act, const float* 
   rc = launch_fno2d_rows(T, g3, dom, (long long)B * O, H, Ky, 2 * J, s);
   if (rc) return rc;
   if (dw1 && dw2) {
-    const long long total = (long long)I * O * J * Ky;
-    fno2d_wgrad_kernel<<<grid_for(total), 256, 0, s>>>(spec, dom, dw1, dw2, B, I, O, m1, Ky);
+    if (Ky <= F2X_KY) {
+      dim3 gw((unsigned)J, (unsigned)((I + F2X_OC - 1) / F2X_OC), (unsigned)((O + F2X_OC - 1) / F2X_OC));
+      fno2d_wgrad_tiled_kernel<<<gw, 256, 0, s>>>(spec, dom, dw1, dw2, B, I, O, m1, Ky);
+    } else {
+      const long long total = (long long)I * O * J * Ky;
+      fno2d_wgrad_kernel<<<grid_for(total), 256, 0, s>>>(spec, dom, dw1, dw2, B, I, O, m1, Ky);
+    }
     RPDE_LAUNCH_CHECK();
   }
   if (dx) {
-    const long long total = (long long)B * I * J * Ky;
-    fno2d_mix_kernel<<<grid_for(total), 256, 0, s>>>(dom, w1, w2, dsp, B, I, O, m1, Ky, 1);
-    RPDE_LAUNCH_CHECK();
+    rc = launch_fno2d_mix(dom, w1, w2, dsp, B, I, O, m1, Ky, 1, s);
+    if (rc) return rc;
     // 2'. U[(ky,ri)][(b,h)][i] = sum_(j,ro) g2[(j,ro)][(ri,h)] dspec[(b,i)][(j,ro)][ky]
     rc = launch_fno2d_expand(dsp, g2t, U, B, I, H, Ky, 2 * J, s);
     if (rc) return rc;
