@@ -26,7 +26,7 @@ tot = sum(e.device_time for e in evs)
 print(f"{len(evs)} kernels, {tot / 1e3:.2f} ms device time")
 if os.environ.get("SEQ"):
     for e in evs:
-        if e.device_time > 50: print(f"{e.device_time:9.1f} us  {e.name[:90]}")
+        if e.device_time > float(os.environ.get("SEQ_MIN", "50")): print(f"{e.device_time:9.1f} us  {e.name[:90]}")
 else:
     agg = collections.OrderedDict()
     for e in evs:
