@@ -64,7 +64,7 @@ __device__ __forceinline__ void mma_3xtf32(float (&d)[4], const uint32_t (&ah)[4
 __host__ __device__ constexpr size_t f2m_synth_smem(int W, int RP) {
   return ((size_t)2 * (RP / 2) * (2 * W + 4)            // table hi / lo, rows t and t + 4 of a k-step interleaved per point
           + (size_t)2 * F2M_MAXC * F2M_LDA              // bypass weight hi / lo
-          + (size_t)2 * 2 * (256 / W) * RP * F2M_LDA    // Z ring: 2 stages x hi / lo x rows per iteration
+          + (size_t)2 * 2 * (W >= 256 ? 1 : 256 / W) * RP * F2M_LDA   // Z ring: 2 stages x hi / lo x rows per iteration
           + F2M_MAXC) * sizeof(float);                  // bias
 }
 
@@ -77,13 +77,15 @@ __host__ __device__ constexpr size_t f2m_synth_smem(int W, int RP) {
 __device__ __forceinline__ int f2m_slot(int pg) { return pg < 4 ? (pg & 1) + 4 * (pg >> 1) : ((pg - 4) & 1) + 4 * ((pg - 4) >> 1) + 2; }
 
 template <int W>
-__global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __restrict__ x, const float* __restrict__ Z,
+__global__ void __launch_bounds__(256, W <= 256 ? 2 : 1) fno2d_synth_mma_kernel(const float* __restrict__ x, const float* __restrict__ Z,
                                                                  const float* __restrict__ table, const float* __restrict__ wb,
                                                                  const float* __restrict__ bb, float* __restrict__ y,
                                                                  float* __restrict__ z, int Bn, int I, int O, int K, int act,
                                                                  int adjoint, int Hd) {
-  static_assert(W == 64 || W == 128 || W == 256, "one warp per 32 grid points, eight warps");
-  constexpr int WPR = W / 32;        // warps per image row
+  static_assert(W == 64 || W == 128 || W == 256 || W == 512 || W == 1024, "one warp per 32 grid points, eight warps");
+  constexpr int TW = W > 256 ? 256 : W;   // points per iteration of one image row (longer rows: W / 256 chunks, whole table resident)
+  constexpr int CH = W / TW;
+  constexpr int WPR = TW / 32;       // warps per image row (chunk)
   constexpr int RPI = 8 / WPR;       // image rows per iteration
   constexpr int LDP = 2 * W + 4;     // paired table rows: stride = 4 mod 32
   extern __shared__ __align__(16) float smem[];
@@ -96,7 +98,7 @@ __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __
   float* biasS = zring + 2 * 2 * RPI * RP * F2M_LDA;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
   const int pg = (g >> 1) + 4 * (g & 1);               // pi(g): this lane's float4 group inside the warp's 32 points
-  const int wrow = warp / WPR, n0 = (warp % WPR) * 32;
+  const int wrow = warp / WPR, nw = (warp % WPR) * 32;   // + 256 * chunk = the warp's first point
 
   // ---- resident operands -------------------------------------------------------------------------------------------
   for (int e = tid; e < RP * W; e += 256) {
@@ -121,21 +123,21 @@ __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __
   }
   if (tid < F2M_MAXC) biasS[tid] = (bb && tid < O) ? __ldg(bb + tid) : 0.f;
 
-  const int ntiles = (Bn + RPI - 1) / RPI;
+  const int ntiles = ((Bn + RPI - 1) / RPI) * CH;         // tile = (row group, chunk), chunk fastest
   constexpr int ZPT = (RPI * F2M_MAXR * F2M_MAXC + 255) / 256;   // Z elements per thread and iteration (upper bound)
   const int zcount = RPI * RP * F2M_MAXC;
   const long long chan = (long long)Hd * W;                      // elements between two channels of one image
   // per-lane table fragment base (row t of k-step 0, this lane's point group) and A fragment bases
-  const int tab_off = t * LDP + (n0 >> 5) * 64 + f2m_slot(pg) * 8;
+  const int tab_off0 = t * LDP + (nw >> 5) * 64 + f2m_slot(pg) * 8;
   const int a_off = t * F2M_LDA + g;
 
   // this warp's x rows (two float4 per k-step): the address of channel t, point group pg of image row `row`
-  auto x_ptr = [&](int row) {
+  auto x_ptr = [&](int row, int n0) {
     const int bh = row / Hd, hh = row - bh * Hd;
     return x + ((long long)bh * I * Hd + hh) * W + n0 + 4 * pg + (long long)t * chan;
   };
-  auto load_x = [&](int row, float4 (&xb)[8]) {
-    const float* p = x_ptr(row);
+  auto load_x = [&](int row, int n0, float4 (&xb)[8]) {
+    const float* p = x_ptr(row, n0);
     const bool ok = row < Bn;
 #pragma unroll
     for (int q = 0; q < 8; ++q) {    // channel t + 4 q: k-step q >> 1, fragment row t (+ 4)
@@ -146,9 +148,9 @@ __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __
   };
   // the next iteration's x rows are only pulled into L2 (no registers held across the MMA loop; the eight lanes g = 0..7
   // of equal t share a 128-byte line, lane g = 0 asks for it)
-  auto prefetch_x = [&](int row) {
+  auto prefetch_x = [&](int row, int n0) {
     if (row >= Bn || g != 0) return;
-    const float* p = x_ptr(row);
+    const float* p = x_ptr(row, n0);
 #pragma unroll
     for (int q = 0; q < 8; ++q)
       if ((q >> 1) < KS_X && t + 4 * q < I) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + 4 * q * chan));
@@ -159,7 +161,7 @@ __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __
       const int e = tid + 256 * q;
       const int o = e % F2M_MAXC, rr = e / F2M_MAXC;       // rr = rowslot * RP + r
       const int slot = RPI == 1 ? 0 : rr / RP, r = rr - slot * RP;
-      const int row = tile * RPI + slot;
+      const int row = (tile / CH) * RPI + slot;
       float v = 0.f;
       if (e < zcount && row < Bn && r < R && o < O) v = __ldg(Z + ((long long)r * Bn + row) * O + o);
       zb[q] = v;
@@ -190,11 +192,12 @@ __global__ void __launch_bounds__(256, 2) fno2d_synth_mma_kernel(const float* __
   int stage = 0;
   for (; tile < ntiles; tile += gridDim.x) {
     const int next = tile + gridDim.x;
-    const int row = tile * RPI + wrow;
+    const int row = (tile / CH) * RPI + wrow, n0 = (tile % CH) * TW + nw;
+    const int tab_off = tab_off0 + (tile % CH) * (TW / 32) * 64;
     float4 xb[8];
-    load_x(row, xb);
+    load_x(row, n0, xb);
     if (next < ntiles) {
-      prefetch_x(next * RPI + wrow);
+      prefetch_x((next / CH) * RPI + wrow, (next % CH) * TW + nw);
       load_z(next, zb);
     }
     if (row < Bn) {

@@ -34,7 +34,10 @@ static int fail(int code, const char* fmt, const char* a = "") {
 #define RPDE_CUDA(expr)                                                        \
   do {                                                                         \
     cudaError_t _e = (expr);                                                   \
-    if (_e != cudaSuccess) return fail(RPDE_E_CUDA, "CUDA error: %s", cudaGetErrorString(_e)); \
+    if (_e != cudaSuccess) {                                                   \
+      snprintf(g_err, sizeof(g_err), "CUDA error: %s (rpde.cu:%d)", cudaGetErrorString(_e), __LINE__); \
+      return RPDE_E_CUDA;                                                      \
+    }                                                                          \
   } while (0)
 // launch statistics only (monotonic counter of kernels this library enqueued; read by bench.py)
 static std::atomic<unsigned long long> g_launches{0};
@@ -229,12 +232,15 @@ static int launch_fno1d_synth(const float* x, const float* om, const float* tabl
   static const int tn_sel = getenv("RPDE_FNO_TN") ? atoi(getenv("RPDE_FNO_TN")) : 0;   // bring-up switch: 64 or 128
   static const bool use_mma = !(getenv("RPDE_FNO2D_MMA") && atoi(getenv("RPDE_FNO2D_MMA")) == 0);
   // FNOBlock2d image rows of 64 / 128 / 256 points, at most 32 channels: the tensor-path kernel (fno2d_mma.cuh)
-  if (use_mma && Hd > 1 && (N == 64 || N == 128 || N == 256) && I <= F2M_MAXC && O <= F2M_MAXC && 2 * modes <= F2M_MAXR) {
-    const int RP = (2 * modes + 7) & ~7;
+  const int RPm = (2 * modes + 7) & ~7;
+  if (use_mma && Hd > 1 && (N == 64 || N == 128 || N == 256 || N == 512 || N == 1024) && I <= F2M_MAXC && O <= F2M_MAXC &&
+      2 * modes <= F2M_MAXR && f2m_synth_smem(N, RPm) <= 227 * 1024) {
+    const int RP = RPm;
     const size_t smem = f2m_synth_smem(N, RP);
-    const int rpi = 256 / N;
-    long long tiles = ((long long)B + rpi - 1) / rpi;
-    const unsigned grid = (unsigned)(tiles < 2 * 148 ? tiles : 2 * 148);
+    const int rpi = N >= 256 ? 1 : 256 / N, ch = N > 256 ? N / 256 : 1;
+    long long tiles = (((long long)B + rpi - 1) / rpi) * ch;
+    const long long resident = N <= 256 ? 2 * 148 : 148;
+    const unsigned grid = (unsigned)(tiles < resident ? tiles : resident);
 #define RPDE_SYNTH_MMA(WW)                                                                                                   \
   do {                                                                                                                       \
     RPDE_CUDA(cudaFuncSetAttribute(fno2d_synth_mma_kernel<WW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));     \
@@ -242,7 +248,9 @@ static int launch_fno1d_synth(const float* x, const float* om, const float* tabl
   } while (0)
     if (N == 64) RPDE_SYNTH_MMA(64);
     else if (N == 128) RPDE_SYNTH_MMA(128);
-    else RPDE_SYNTH_MMA(256);
+    else if (N == 256) RPDE_SYNTH_MMA(256);
+    else if (N == 512) RPDE_SYNTH_MMA(512);
+    else RPDE_SYNTH_MMA(1024);
 #undef RPDE_SYNTH_MMA
     RPDE_LAUNCH_CHECK();
     return RPDE_OK;
@@ -463,7 +471,7 @@ static int launch_fno2d_waxis(const float* x, const float* tab, float* T, long l
                               float* xout, int kplanes, cudaStream_t s) {
   static const bool use_mma = !(getenv("RPDE_FNO2D_MMA") && atoi(getenv("RPDE_FNO2D_MMA")) == 0);
   auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
-  if (use_mma && N % 32 == 0 && R <= F2M_MAXR && f2m_waxis_smem(N, (R + 7) & ~7, true) <= 100 * 1024 && al16(x) && al16(z) && al16(xout))
+  if (use_mma && N % 32 == 0 && R <= F2M_MAXR && f2m_waxis_smem(N, (R + 7) & ~7, false) <= 200 * 1024 && al16(x) && al16(z) && al16(xout))
     return launch_waxis_mma(x, tab, T, rows, N, R, z, act, xout, kplanes, R, 1, s);
   const size_t smem = (size_t)((R + 7) & ~7) * N * sizeof(float);
   long long blocks = (rows + 15) / 16;
@@ -1156,7 +1164,9 @@ int rpde_conv1x1_bwd_params(const float* dy, const float* x, float* dw, float* d
     if (db) RPDE_CUDA(cudaMemsetAsync(db, 0, (size_t)O * sizeof(float), s));
     const int nb = ((I + 31) / 32) * ((O + 31) / 32), nstreams = 8 / nb;
     const long long tiles = (long long)B * (S / 32);
-    long long ctas = (tiles + nstreams - 1) / nstreams;
+    // at least four tiles per warp: every CTA ends with one atomic per (o, i) element, so a small problem spread over
+    // hundreds of CTAs is bound by a million contended atomics (19 us for 8 MB of operands at FNO1d batch 16)
+    long long ctas = (tiles + 4 * nstreams - 1) / (4 * nstreams);
     if (ctas > 2 * 148) ctas = 2 * 148;
     conv1x1_wgrad_mma_kernel<<<(unsigned)ctas, 256, 0, s>>>(dy, x, dw, db, B, I, O, (int)S);
     RPDE_LAUNCH_CHECK();

@@ -31,6 +31,8 @@ SHAPES = [  # B, I, O, H, W, m1, m2, bypass, bias, act
     (2, 20, 12, 10, 128, 3, 7, True, False, "none"),      # channels not multiples of 8
     (1, 3, 5, 6, 64, 2, 16, False, False, "none"),        # no bypass, 2*m2 = 32
     (2, 32, 32, 16, 256, 6, 16, True, True, "gelu"),
+    (1, 32, 32, 5, 512, 2, 12, True, True, "gelu"),       # long rows: two 256-point chunks per image row, whole table resident
+    (1, 16, 16, 3, 1024, 1, 5, True, True, "relu"),       # four chunks; W-axis analysis with the fp32 table plane
     (1, 8, 8, 12, 96, 3, 6, True, True, "gelu"),          # W = 96: the fp32-FMA kernels
     (1, 40, 40, 8, 64, 3, 6, True, True, "relu"),         # 40 channels: the fp32-FMA kernels
 ]
