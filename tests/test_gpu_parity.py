@@ -355,5 +355,7 @@ def test_graphed_step_matches_eager(kind):
             torch.cuda.synchronize()
             assert abs(lg.item() - le.item()) <= 1e-6 * max(1.0, abs(le.item()))
             for k, p in m.named_parameters():
-                assert rel(gg[k], p.grad) < 2e-6 or p.grad.abs().max() < 1e-7, (k, rel(gg[k], p.grad))
+                # same kernels in the same order; parameter gradients that leave their CTAs as fp32 atomics (bias / weight sums
+                # of the fused MLP and the 1x1 convs) differ from run to run by the order of those adds: a few 1e-6
+                assert rel(gg[k], p.grad) < 5e-6 or p.grad.abs().max() < 1e-7, (k, rel(gg[k], p.grad))
             m.zero_grad(set_to_none=True)
