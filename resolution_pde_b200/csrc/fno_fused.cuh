@@ -254,4 +254,78 @@ __global__ void __launch_bounds__(256) fno1d_synth_bypass_kernel(const float* __
   }
 }
 
+// ---- backward mode-space kernels of SpectralConv1d (spectral_convolution.py:34-36 compl_mul1d, its two adjoints) ------------
+// Spectra are mode-major, [k][re|im][b][c]; the weights keep the parameter layout (I, O, K) complex.  They replace
+// pack_weights + two batched contractions + memset + unpack (five launches, 26 us per block at batch 16): at these sizes
+// (K x B x C = 16 x 16 x 64) every launch is latency, so fewer and simpler launches win.
+constexpr int M1_IC = 8;     // input channels per CTA
+constexpr int M1_BC = 16;    // batch elements per staging round
+
+// dsp[k][.][b][i] = sum_o dom[k][.][b][o] * conj(w[i,o,k])       grid (K, ceil(I / 8), ceil(B / 16)), 128 threads = (b, i)
+__global__ void __launch_bounds__(128) fno1d_mix_adjoint_kernel(const float* __restrict__ dom, const float* __restrict__ w,
+                                                                float* __restrict__ dsp, int Bn, int I, int O, int K) {
+  extern __shared__ float sm1[];                      // D[2][M1_BC][O + 1] | W[M1_IC][2 O + 2] (padded rows: no bank conflicts over i)
+  float* D = sm1;
+  float* Wc = sm1 + 2 * M1_BC * (O + 1);
+  const int k = blockIdx.x, i0 = blockIdx.y * M1_IC, b0 = blockIdx.z * M1_BC;
+  const int nb = min(M1_BC, Bn - b0);
+  for (int e = threadIdx.x; e < 2 * nb * O; e += 128) {
+    const int o = e % O, rb = e / O, b = rb % nb, ro = rb / nb;
+    D[(ro * M1_BC + b) * (O + 1) + o] = __ldg(dom + ((long long)(k * 2 + ro) * Bn + b0 + b) * O + o);
+  }
+  for (int e = threadIdx.x; e < M1_IC * O; e += 128) {
+    const int o = e % O, il = e / O;
+    float2 v = make_float2(0.f, 0.f);
+    if (i0 + il < I) v = __ldg(reinterpret_cast<const float2*>(w + (((long long)(i0 + il) * O + o) * K + k) * 2));
+    Wc[il * (2 * O + 2) + 2 * o] = v.x;
+    Wc[il * (2 * O + 2) + 2 * o + 1] = v.y;
+  }
+  __syncthreads();
+  const int il = threadIdx.x & 7, b = threadIdx.x >> 3;
+  if (b >= nb || i0 + il >= I) return;
+  const float* dr = D + b * (O + 1);
+  const float* di = D + (M1_BC + b) * (O + 1);
+  const float* wp = Wc + il * (2 * O + 2);
+  float re = 0.f, im = 0.f;
+#pragma unroll 4
+  for (int o = 0; o < O; ++o) {
+    const float wr = wp[2 * o], wi = wp[2 * o + 1], a = dr[o], c = di[o];
+    re = fmaf(a, wr, re); re = fmaf(c, wi, re);
+    im = fmaf(c, wr, im); im = fmaf(-a, wi, im);
+  }
+  dsp[((long long)(k * 2 + 0) * Bn + b0 + b) * I + i0 + il] = re;
+  dsp[((long long)(k * 2 + 1) * Bn + b0 + b) * I + i0 + il] = im;
+}
+
+// dw[i,o,k] = sum_b conj(spec[k][.][b][i]) * dom[k][.][b][o]       grid (K, ceil(I / 8), ceil(O / 32)), 256 threads = (o, i)
+__global__ void __launch_bounds__(256) fno1d_wgrad_kernel(const float* __restrict__ spec, const float* __restrict__ dom,
+                                                          float* __restrict__ dw, int Bn, int I, int O, int K) {
+  __shared__ float S[2][M1_BC][M1_IC];
+  __shared__ float D[2][M1_BC][32];
+  const int k = blockIdx.x, i0 = blockIdx.y * M1_IC, o0 = blockIdx.z * 32;
+  const int ol = threadIdx.x & 31, il = threadIdx.x >> 5;
+  float re = 0.f, im = 0.f;
+  for (int b0 = 0; b0 < Bn; b0 += M1_BC) {
+    const int nb = min(M1_BC, Bn - b0);
+    __syncthreads();
+    for (int e = threadIdx.x; e < 2 * nb * M1_IC; e += 256) {
+      const int i = e % M1_IC, rb = e / M1_IC, b = rb % nb, ri = rb / nb;
+      S[ri][b][i] = i0 + i < I ? __ldg(spec + ((long long)(k * 2 + ri) * Bn + b0 + b) * I + i0 + i) : 0.f;
+    }
+    for (int e = threadIdx.x; e < 2 * nb * 32; e += 256) {
+      const int o = e & 31, rb = e >> 5, b = rb % nb, ro = rb / nb;
+      D[ro][b][o] = o0 + o < O ? __ldg(dom + ((long long)(k * 2 + ro) * Bn + b0 + b) * O + o0 + o) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll 4
+    for (int b = 0; b < nb; ++b) {
+      const float sr = S[0][b][il], si = S[1][b][il], dr = D[0][b][ol], di = D[1][b][ol];
+      re = fmaf(sr, dr, re); re = fmaf(si, di, re);
+      im = fmaf(sr, di, im); im = fmaf(-si, dr, im);
+    }
+  }
+  if (i0 + il < I && o0 + ol < O)
+    *reinterpret_cast<float2*>(dw + (((long long)(i0 + il) * O + o0 + ol) * K + k) * 2) = make_float2(re, im);
+}
+
 }  // namespace rpde

@@ -343,8 +343,17 @@ static int spectral1d_bwd_impl(const float* dy, const float* z, int act, const f
   float* dom = cv.take((size_t)K * B * 2 * O);
   float* dsp = cv.take((size_t)K * B * 2 * I);
   float* P = cv.take((size_t)K * 4 * I * O);
-  int rc = pack_w(w, wp, I, O, modes, K, 1, 1, s);
-  if (rc) return rc;
+  // mode-space FMA kernels (fno_fused.cuh) for the widths the FNO configurations use: two launches instead of
+  // pack + two batched contractions + memset + unpack
+  static const bool use_modespace = !(getenv("RPDE_FNO1D_MODESPACE") && atoi(getenv("RPDE_FNO1D_MODESPACE")) == 0);
+  // (small batches only: from B ~ 100 on the batched contractions of the tensor engine are faster -- measured 38 + 20 us against
+  // 16 + 10 us at B = 256)
+  const bool tiled = use_modespace && I <= 128 && O <= 128 && B <= 64;
+  int rc = RPDE_OK;
+  if (!tiled) {
+    rc = pack_w(w, wp, I, O, modes, K, 1, 1, s);
+    if (rc) return rc;
+  }
   const long long BI = (long long)B * I, BO = (long long)B * O;
   // 3'. dom[(k,ro)][(b,o)] = sum_n dy[(b,o)][n] fs[n][(k,ro)]
   GemmP g = gemm_default();
@@ -362,7 +371,11 @@ static int spectral1d_bwd_impl(const float* dy, const float* z, int act, const f
     g.splitk = 0;
     RPDE_CUDA(gemm(g, s));
   }
-  if (dw) {
+  if (dw && tiled) {
+    dim3 gw((unsigned)K, (unsigned)((I + M1_IC - 1) / M1_IC), (unsigned)((O + 31) / 32));
+    fno1d_wgrad_kernel<<<gw, 256, 0, s>>>(spec, dom, dw, B, I, O, K);
+    RPDE_LAUNCH_CHECK();
+  } else if (dw) {
     // dWp[k] = spec[k]^T dom[k]
     RPDE_CUDA(cudaMemsetAsync(P, 0, (size_t)K * 4 * I * O * sizeof(float), s));
     g = gemm_default();
@@ -377,14 +390,21 @@ static int spectral1d_bwd_impl(const float* dy, const float* z, int act, const f
     if (rc) return rc;
   }
   if (dx) {
-    // 2'. dsp[k] = dom[k] wp[k]^T
-    g = gemm_default();
-    g.A = dom; g.B = wp; g.C = dsp;
-    g.batch = K; g.M = B; g.N = 2 * I; g.K = 2 * O;
-    g.a = MatDesc{lin(2 * BO), lin(O), two(O, BO, 1)};
-    g.b = MatDesc{lin(4LL * I * O), lin(1), lin(2 * O)};
-    g.c = MatDesc{lin(2 * BI), lin(I), two(I, BI, 1)};
-    RPDE_CUDA(gemm(g, s));
+    if (tiled) {
+      dim3 gm((unsigned)K, (unsigned)((I + M1_IC - 1) / M1_IC), (unsigned)((B + M1_BC - 1) / M1_BC));
+      const size_t smem = (size_t)(2 * M1_BC * (O + 1) + M1_IC * (2 * O + 2)) * sizeof(float);
+      fno1d_mix_adjoint_kernel<<<gm, 128, smem, s>>>(dom, w, dsp, B, I, O, K);
+      RPDE_LAUNCH_CHECK();
+    } else {
+      // 2'. dsp[k] = dom[k] wp[k]^T
+      g = gemm_default();
+      g.A = dom; g.B = wp; g.C = dsp;
+      g.batch = K; g.M = B; g.N = 2 * I; g.K = 2 * O;
+      g.a = MatDesc{lin(2 * BO), lin(O), two(O, BO, 1)};
+      g.b = MatDesc{lin(4LL * I * O), lin(1), lin(2 * O)};
+      g.c = MatDesc{lin(2 * BI), lin(I), two(I, BI, 1)};
+      RPDE_CUDA(gemm(g, s));
+    }
     // 1'. dx[(b,i)][n] (+)= sum_(k,ri) dsp[(k,ri)][(b,i)] fa[(k,ri)][n]
     if (fuse_dx && !dx_accumulate)   // (+ the bypass conv's input gradient wb^T dpre in the same kernel; dy == dpre here)
       return launch_fno1d_synth(dy, dsp, fa, wb, nullptr, dx, nullptr, B, /*reduction channels*/ O, /*outputs*/ I, N, K, ACT_NONE, 1, s);
