@@ -1176,12 +1176,17 @@ int rpde_conv1x1_bwd_params(const float* dy, const float* x, float* dw, float* d
   if (!dy || !x || !dw || B <= 0 || I <= 0 || O <= 0 || S <= 0 || S > INT_MAX || (long long)B * S > INT_MAX)
     return fail(RPDE_E_INVALID, "rpde_conv1x1_bwd_params: bad arguments%s");
   cudaStream_t s = (cudaStream_t)stream;
-  RPDE_CUDA(cudaMemsetAsync(dw, 0, (size_t)O * I * sizeof(float), s));
   static const bool use_mma = !(getenv("RPDE_FNO2D_MMA") && atoi(getenv("RPDE_FNO2D_MMA")) == 0);
   auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
-  if (use_mma && S % 32 == 0 && I <= 64 && O <= 64 && al16(dy) && al16(x)) {
+  const bool mma_path = use_mma && S % 32 == 0 && I <= 64 && O <= 64 && al16(dy) && al16(x);
+  if (mma_path && db == dw + (size_t)O * I) {      // dw | db back to back (the Python wrapper): one memset for both
+    RPDE_CUDA(cudaMemsetAsync(dw, 0, ((size_t)O * I + O) * sizeof(float), s));
+  } else {
+    RPDE_CUDA(cudaMemsetAsync(dw, 0, (size_t)O * I * sizeof(float), s));
+    if (mma_path && db) RPDE_CUDA(cudaMemsetAsync(db, 0, (size_t)O * sizeof(float), s));
+  }
+  if (mma_path) {
     // weight and bias gradient in one streaming pass on the warp-level tensor path (fno2d_mma.cuh)
-    if (db) RPDE_CUDA(cudaMemsetAsync(db, 0, (size_t)O * sizeof(float), s));
     const int nb = ((I + 31) / 32) * ((O + 31) / 32), nstreams = 8 / nb;
     const long long tiles = (long long)B * (S / 32);
     // at least four tiles per warp: every CTA ends with one atomic per (o, i) element, so a small problem spread over
@@ -1243,10 +1248,16 @@ int rpde_mlp_bwd(const float* x, const float* dy, const float* w1, const float* 
   if (!x || !dy || !w1 || !w2 || !dw1 || !dw2 || B <= 0) return fail(RPDE_E_INVALID, "rpde_mlp_bwd: bad arguments%s");
   if (!rpde_mlp_supported(I, Hd, O, S)) return fail(RPDE_E_INVALID, "rpde_mlp_bwd: shape outside the fused kernel%s");
   cudaStream_t s = (cudaStream_t)stream;
-  RPDE_CUDA(cudaMemsetAsync(dw1, 0, (size_t)Hd * I * sizeof(float), s));
-  RPDE_CUDA(cudaMemsetAsync(dw2, 0, (size_t)O * Hd * sizeof(float), s));
-  if (db1) RPDE_CUDA(cudaMemsetAsync(db1, 0, (size_t)Hd * sizeof(float), s));
-  if (db2) RPDE_CUDA(cudaMemsetAsync(db2, 0, (size_t)O * sizeof(float), s));
+  // the four gradients are accumulated with atomics: zero-fill them, in one memset when the caller laid them out back to back
+  // (dw1 | db1 | dw2 | db2, as the Python wrapper does: every launch counts on the latency-bound FNO1d step)
+  if (db1 == dw1 + (size_t)Hd * I && dw2 == db1 + Hd && db2 == dw2 + (size_t)O * Hd) {
+    RPDE_CUDA(cudaMemsetAsync(dw1, 0, ((size_t)Hd * I + Hd + (size_t)O * Hd + O) * sizeof(float), s));
+  } else {
+    RPDE_CUDA(cudaMemsetAsync(dw1, 0, (size_t)Hd * I * sizeof(float), s));
+    RPDE_CUDA(cudaMemsetAsync(dw2, 0, (size_t)O * Hd * sizeof(float), s));
+    if (db1) RPDE_CUDA(cudaMemsetAsync(db1, 0, (size_t)Hd * sizeof(float), s));
+    if (db2) RPDE_CUDA(cudaMemsetAsync(db2, 0, (size_t)O * sizeof(float), s));
+  }
   const size_t smem = mlp_bwd_smem(I, Hd);
   const int HP = (Hd + 31) & ~31, PT = 256 / HP;
   const long long tiles = (long long)B * (S / 32);

@@ -183,6 +183,15 @@ def _check_modes(ndim, spatial, modes):
             raise RuntimeError(f"SpectralConv2d: modes {tuple(modes)} exceed the spectrum of a {tuple(spatial)} grid")
 
 
+def _dw_db(w: torch.Tensor, O: int, has_bias: bool):
+    """gradient buffers of a 1x1 conv laid out back to back (dw | db): rpde_conv1x1_bwd_params then zero-fills both with
+    one memset (its streaming kernel accumulates with atomics)"""
+    if not has_bias:
+        return torch.empty_like(w), None
+    flat = torch.empty(w.numel() + O, dtype=torch.float32, device=w.device)
+    return flat[:w.numel()].view_as(w), flat[w.numel():]
+
+
 class _FNOSpectralFn(torch.autograd.Function):
     """y = act(spectral(x; weights) [+ conv1x1(x; wb, bb)])   channels-first, 1-D or 2-D."""
 
@@ -289,8 +298,7 @@ class _FNOSpectralFn(torch.autograd.Function):
                 if dpre is None:
                     dpre = dy
                 if wb is not None:
-                    dwb = torch.empty_like(wb)
-                    dbb = torch.empty(O, dtype=torch.float32, device=x.device) if has_bias else None
+                    dwb, dbb = _dw_db(wb, O, has_bias)
                     _lib.check(c.lib.rpde_conv1x1_bwd_params(_p(dpre), _p(x), _p(dwb), _p(dbb), B, I, O, S, c.stream),
                                "rpde_conv1x1_bwd_params")
             return (dx, torch.view_as_complex(dw1), torch.view_as_complex(dw2), dwb, dbb, None, None, None)
@@ -333,8 +341,7 @@ class _FNOSpectralFn(torch.autograd.Function):
                 if need_x and not (fused and dx_done):
                     _lib.check(c.lib.rpde_conv1x1_bwd_input(_p(dpre), _p(wbc), None, 0, _p(dx), 1, B, I, O, S, c.stream),
                                "rpde_conv1x1_bwd_input")
-                dwb = torch.empty_like(wb)
-                dbb = torch.empty(O, dtype=torch.float32, device=x.device) if has_bias else None
+                dwb, dbb = _dw_db(wb, O, has_bias)
                 _lib.check(c.lib.rpde_conv1x1_bwd_params(_p(dpre), _p(x), _p(dwb), _p(dbb), B, I, O, S, c.stream),
                            "rpde_conv1x1_bwd_params")
         return (dx, torch.view_as_complex(dw1), torch.view_as_complex(dw2) if dw2 is not None else None, dwb, dbb,
@@ -726,8 +733,7 @@ class _Conv1x1Fn(torch.autograd.Function):
                 dx = torch.empty_like(x)
                 _lib.check(c.lib.rpde_conv1x1_bwd_input(_p(dy), _p(w2), None, 0, _p(dx), 0, B, I, O, S, c.stream),
                            "rpde_conv1x1_bwd_input")
-            dw = torch.empty_like(w)
-            db = torch.empty(O, dtype=torch.float32, device=x.device) if has_b else None
+            dw, db = _dw_db(w, O, has_b)
             _lib.check(c.lib.rpde_conv1x1_bwd_params(_p(dy), _p(x), _p(dw), _p(db), B, I, O, S, c.stream),
                        "rpde_conv1x1_bwd_params")
         return dx, dw, db
@@ -784,9 +790,17 @@ class _MLPFn(torch.autograd.Function):
             w1c = w1.detach().reshape(H, I).contiguous()
             w2c = w2.detach().reshape(O, H).contiguous()
             dx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
-            dw1, dw2 = torch.empty_like(w1), torch.empty_like(w2)
-            db1 = torch.empty(H, dtype=torch.float32, device=dev) if hb1 else None
-            db2 = torch.empty(O, dtype=torch.float32, device=dev) if hb2 else None
+            # dw1 | db1 | dw2 | db2 back to back: the kernel accumulates them with atomics and zero-fills them with one memset
+            flat = torch.empty(H * I + H + O * H + O, dtype=torch.float32, device=dev)
+            dw1 = flat[:H * I].view_as(w1)
+            db1f = flat[H * I:H * I + H]
+            dw2 = flat[H * I + H:H * I + H + O * H].view_as(w2)
+            db2f = flat[H * I + H + O * H:]
+            db1, db2 = (db1f if hb1 else None), (db2f if hb2 else None)
+            if not (hb1 and hb2):       # a missing bias breaks the back-to-back layout the C side looks for: separate tensors
+                dw1, dw2 = torch.empty_like(w1), torch.empty_like(w2)
+                db1 = torch.empty(H, dtype=torch.float32, device=dev) if hb1 else None
+                db2 = torch.empty(O, dtype=torch.float32, device=dev) if hb2 else None
             with _Ctx(x) as c:
                 _lib.check(c.lib.rpde_mlp_bwd(_p(x), _p(dy), _p(w1c), _p(b1), _p(w2c), _p(dx), _p(dw1), _p(db1), _p(dw2), _p(db2),
                                               B, I, H, O, S, c.stream), "rpde_mlp_bwd")
