@@ -183,6 +183,46 @@ def _check_modes(ndim, spatial, modes):
             raise RuntimeError(f"SpectralConv2d: modes {tuple(modes)} exceed the spectrum of a {tuple(spatial)} grid")
 
 
+# ---------------------------------------------------------------------------------------------
+# Parameter-gradient side stream.  On the launch-bound FNO steps (FNO1d at batch 16: ~60 kernels of 4-16 us) the kernels
+# that only produce a parameter gradient are off the critical path: nothing in the backward pass reads their result.
+# training.GraphedTrainStep opens `pgrad_side_stream` while it captures; those kernels are then enqueued on a second
+# stream (forked after everything the main stream has enqueued so far, joined once at the end of the backward pass), so the
+# captured graph runs them next to the input-gradient chain.  Outside that context everything stays on one stream.
+# ---------------------------------------------------------------------------------------------
+_pgrad = {}     # device index -> [stream, kept tensors, forked]; autograd runs CUDA nodes on its own per-device threads, so
+                # this is process-wide state keyed by device, not thread-local
+
+
+class pgrad_side_stream:
+    def __init__(self, device):
+        self.dev = torch.device(device)
+        self.idx = self.dev.index if self.dev.index is not None else torch.cuda.current_device()
+        self.stream = torch.cuda.Stream(device=self.dev)
+
+    def __enter__(self):
+        _pgrad[self.idx] = [self.stream, [], False]
+        return self
+
+    def __exit__(self, *a):
+        st = _pgrad.pop(self.idx, None)
+        if st is not None and st[2]:   # a forked stream must rejoin before the capture ends; its inputs were kept alive until here
+            torch.cuda.current_stream(self.dev).wait_stream(self.stream)
+        return False
+
+
+def _pgrad_stream(c: "_Ctx", *reads):
+    """stream handle for a kernel that only writes parameter gradients; `reads`: the tensors it reads (kept alive until the join,
+    so that the allocator cannot hand their memory to later main-stream work)"""
+    st = _pgrad.get(c.dev.index if c.dev.index is not None else torch.cuda.current_device())
+    if st is None:
+        return c.stream
+    st[0].wait_stream(torch.cuda.current_stream(c.dev))
+    st[2] = True
+    st[1].extend(t for t in reads if t is not None)
+    return st[0].cuda_stream
+
+
 def _dw_db(w: torch.Tensor, O: int, has_bias: bool):
     """gradient buffers of a 1x1 conv laid out back to back (dw | db): rpde_conv1x1_bwd_params then zero-fills both with
     one memset (its streaming kernel accumulates with atomics)"""
@@ -299,7 +339,8 @@ class _FNOSpectralFn(torch.autograd.Function):
                     dpre = dy
                 if wb is not None:
                     dwb, dbb = _dw_db(wb, O, has_bias)
-                    _lib.check(c.lib.rpde_conv1x1_bwd_params(_p(dpre), _p(x), _p(dwb), _p(dbb), B, I, O, S, c.stream),
+                    _lib.check(c.lib.rpde_conv1x1_bwd_params(_p(dpre), _p(x), _p(dwb), _p(dbb), B, I, O, S,
+                                                             _pgrad_stream(c, dpre, x) if S % 32 == 0 and max(I, O) <= 64 else c.stream),
                                "rpde_conv1x1_bwd_params")
             return (dx, torch.view_as_complex(dw1), torch.view_as_complex(dw2), dwb, dbb, None, None, None)
         with _Ctx(x) as c:
@@ -342,7 +383,8 @@ class _FNOSpectralFn(torch.autograd.Function):
                     _lib.check(c.lib.rpde_conv1x1_bwd_input(_p(dpre), _p(wbc), None, 0, _p(dx), 1, B, I, O, S, c.stream),
                                "rpde_conv1x1_bwd_input")
                 dwb, dbb = _dw_db(wb, O, has_bias)
-                _lib.check(c.lib.rpde_conv1x1_bwd_params(_p(dpre), _p(x), _p(dwb), _p(dbb), B, I, O, S, c.stream),
+                _lib.check(c.lib.rpde_conv1x1_bwd_params(_p(dpre), _p(x), _p(dwb), _p(dbb), B, I, O, S,
+                                                         _pgrad_stream(c, dpre, x) if S % 32 == 0 and max(I, O) <= 64 else c.stream),
                            "rpde_conv1x1_bwd_params")
         return (dx, torch.view_as_complex(dw1), torch.view_as_complex(dw2) if dw2 is not None else None, dwb, dbb,
                 None, None, None)

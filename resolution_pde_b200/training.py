@@ -17,6 +17,8 @@ from typing import Callable, Dict, Optional, Tuple
 
 import torch
 
+from . import ops
+
 
 class GraphedTrainStep:
     """step(x, y) -> loss (0-dim device tensor).  x, y may live on the device or in pinned host memory."""
@@ -63,7 +65,8 @@ class GraphedTrainStep:
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
             loss = self.loss_fn(self.model(sx), sy)
-            loss.backward()
+            with ops.pgrad_side_stream(dev):       # parameter-gradient-only kernels on a second captured stream (ops.py)
+                loss.backward()
             self._reduce()
         # the gradient tensors written by this graph (its pool owns them); re-attached to the parameters after a replay
         params = [q for q in self.model.parameters() if q.grad is not None]
