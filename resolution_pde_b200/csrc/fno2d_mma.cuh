@@ -934,14 +934,17 @@ __global__ void __launch_bounds__(256, PRESPLIT ? 2 : 1) fno2d_waxis_mma_kernel(
   extern __shared__ __align__(16) float smem[];
   // Table rows keep each 32-point group as [t][j][k = t | k = t + 4]: the lane's eight floats at 8 t are the B operand pairs
   // of the four k-steps (no register shuffling in front of the MMA); row stride = 4 mod 32: conflict-free float4 loads
-  const int RP = (R + 7) & ~7, NT = RP / 8, LDT = W + 4;
+  // gridDim.y > 1 (few rows: FNO1d at batch 16 has 64 row tiles): the CTAs of one blockIdx.y take W / gridDim.y points of
+  // every row, stage only that slice of the table, and add their partial sums into T with atomics (T zero-filled by the host)
+  const int Wc = W / gridDim.y, w0 = blockIdx.y * Wc;
+  const int RP = (R + 7) & ~7, NT = RP / 8, LDT = Wc + 4;
   float* tabH = smem;
   float* tabL = tabH + (PRESPLIT ? RP * LDT : 0);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
-  for (int e = tid; e < RP * W; e += 256) {
-    const int r = e / W, n = e - r * W;
+  for (int e = tid; e < RP * Wc; e += 256) {
+    const int r = e / Wc, n = e - r * Wc;
     const int tr = kplanes ? (r & 1) * kplanes + (r >> 1) : r;
-    const float v = r < R ? __ldg(tab + (long long)tr * W + n) : 0.f;
+    const float v = r < R ? __ldg(tab + (long long)tr * W + w0 + n) : 0.f;
     // point n = 32 gi + 16 half + 4 tt + j  ->  32 gi + 8 tt + 2 j + half
     const int off = r * LDT + (n & ~31) + 8 * ((n >> 2) & 3) + 2 * (n & 3) + ((n >> 4) & 1);
     if (PRESPLIT) {
@@ -954,13 +957,13 @@ __global__ void __launch_bounds__(256, PRESPLIT ? 2 : 1) fno2d_waxis_mma_kernel(
     }
   }
   __syncthreads();
-  const int groups = W / 32;
+  const int groups = Wc / 32;
   const long long mtiles = (rows + 15) / 16;
   for (long long mt = (long long)blockIdx.x * 8 + warp; mt < mtiles; mt += (long long)gridDim.x * 8) {
     const long long row0 = mt * 16 + g, row1 = row0 + 8;
     const bool ok0 = row0 < rows, ok1 = row1 < rows;
-    const float* x0 = x + row0 * W + 4 * t;
-    const float* x1 = x + row1 * W + 4 * t;
+    const float* x0 = x + row0 * W + w0 + 4 * t;
+    const float* x1 = x + row1 * W + w0 + 4 * t;
     float sum[4][4];
 #pragma unroll
     for (int nt = 0; nt < 4; ++nt)
@@ -976,8 +979,8 @@ __global__ void __launch_bounds__(256, PRESPLIT ? 2 : 1) fno2d_waxis_mma_kernel(
       v[2] = ok1 ? __ldg(reinterpret_cast<const float4*>(x1 + p)) : zero;
       v[3] = ok1 ? __ldg(reinterpret_cast<const float4*>(x1 + p + 16)) : zero;
       if (z) {
-        const float* z0 = z + row0 * W + 4 * t + p;
-        const float* z1 = z + row1 * W + 4 * t + p;
+        const float* z0 = z + row0 * W + w0 + 4 * t + p;
+        const float* z1 = z + row1 * W + w0 + 4 * t + p;
         zz[0] = ok0 ? __ldg(reinterpret_cast<const float4*>(z0)) : zero;
         zz[1] = ok0 ? __ldg(reinterpret_cast<const float4*>(z0 + 16)) : zero;
         zz[2] = ok1 ? __ldg(reinterpret_cast<const float4*>(z1)) : zero;
@@ -1004,8 +1007,8 @@ __global__ void __launch_bounds__(256, PRESPLIT ? 2 : 1) fno2d_waxis_mma_kernel(
           cur[q].x *= d0; cur[q].y *= d1; cur[q].z *= d2; cur[q].w *= d3;
         }
         if (xout) {
-          float* o0 = xout + row0 * W + 4 * t + 32 * gi;
-          float* o1 = xout + row1 * W + 4 * t + 32 * gi;
+          float* o0 = xout + row0 * W + w0 + 4 * t + 32 * gi;
+          float* o1 = xout + row1 * W + w0 + 4 * t + 32 * gi;
           if (ok0) {
             *reinterpret_cast<float4*>(o0) = cur[0];
             *reinterpret_cast<float4*>(o0 + 16) = cur[1];
@@ -1065,6 +1068,17 @@ __global__ void __launch_bounds__(256, PRESPLIT ? 2 : 1) fno2d_waxis_mma_kernel(
     for (int nt = 0; nt < 4; ++nt) {
       const int r = 8 * nt + 2 * t;
       if (nt < NT) {
+        if (gridDim.y > 1) {
+          if (ok0) {
+            if (r < R) atomicAdd(T + row0 * s_row + r * s_r, sum[nt][0]);
+            if (r + 1 < R) atomicAdd(T + row0 * s_row + (r + 1) * s_r, sum[nt][1]);
+          }
+          if (ok1) {
+            if (r < R) atomicAdd(T + row1 * s_row + r * s_r, sum[nt][2]);
+            if (r + 1 < R) atomicAdd(T + row1 * s_row + (r + 1) * s_r, sum[nt][3]);
+          }
+          continue;
+        }
         if (ok0) {
           if (r < R) T[row0 * s_row + r * s_r] = sum[nt][0];
           if (r + 1 < R) T[row0 * s_row + (r + 1) * s_r] = sum[nt][1];

@@ -277,13 +277,12 @@ static int launch_waxis_mma(const float* x, const float* tab, float* T, long lon
 static int launch_fno1d_analysis(const float* x, const float* table, float* out, int B, int rows_per_b, int N, int modes,
                                  const float* z, int act, float* xout, int rowmap, cudaStream_t s) {
   {
-    // enough rows to give every SM two 16-row tiles: the tensor-path kernel (the FMA kernel is faster on small batches,
-    // where eight CTAs would each stage the whole table)
+    // the tensor-path kernel (fno2d_mma.cuh); with few rows it splits the points of a row over several CTAs
     static const bool use_mma = !(getenv("RPDE_FNO2D_MMA") && atoi(getenv("RPDE_FNO2D_MMA")) == 0);
     auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
     const long long rows = (long long)B * rows_per_b;
     const int R = 2 * modes;
-    if (use_mma && rows >= 16LL * 2 * 148 && N % 32 == 0 && R <= F2M_MAXR && f2m_waxis_smem(N, (R + 7) & ~7, false) <= 200 * 1024 &&
+    if (use_mma && rows >= 128 && N % 32 == 0 && R <= F2M_MAXR && f2m_waxis_smem(N, (R + 7) & ~7, false) <= 200 * 1024 &&
         al16(x) && al16(z) && al16(xout))
       return launch_waxis_mma(x, table, out, rows, N, R, z, act, xout, rowmap ? modes : 0, 1, rows, s);
   }
@@ -471,17 +470,23 @@ size_t rpde_fno_block2d_workspace_bytes(int B, int I, int O, int H, int W, int m
 static int launch_waxis_mma(const float* x, const float* tab, float* T, long long rows, int N, int R, const float* z, int act,
                             float* xout, int kplanes, long long s_row, long long s_r, cudaStream_t s) {
   const int RP = (R + 7) & ~7;
-  const bool presplit = f2m_waxis_smem(N, RP, true) <= 100 * 1024;
-  const size_t sm = f2m_waxis_smem(N, RP, presplit);
   long long ctas = ((rows + 15) / 16 + 7) / 8;
+  // few row tiles: split the points of a row over gridDim.y CTAs (partial sums meet in T through atomics) until ~128 CTAs exist
+  int split = 1;
+  while (ctas * split < 128 && N % (64 * split) == 0 && N / (2 * split) >= 64) split *= 2;
+  const int Wc = N / split;
+  const bool presplit = f2m_waxis_smem(Wc, RP, true) <= 100 * 1024;
+  const size_t sm = f2m_waxis_smem(Wc, RP, presplit);
   const long long resident = presplit ? 2 * 148 : 148;
   if (ctas > resident) ctas = resident;
+  if (split > 1) RPDE_CUDA(cudaMemsetAsync(T, 0, (size_t)rows * R * sizeof(float), s));   // T is dense: rows x R either way
+  dim3 grid((unsigned)ctas, (unsigned)split);
   if (presplit) {
     RPDE_CUDA(cudaFuncSetAttribute(fno2d_waxis_mma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    fno2d_waxis_mma_kernel<true><<<(unsigned)ctas, 256, sm, s>>>(x, tab, T, rows, N, R, z, act, xout, kplanes, s_row, s_r);
+    fno2d_waxis_mma_kernel<true><<<grid, 256, sm, s>>>(x, tab, T, rows, N, R, z, act, xout, kplanes, s_row, s_r);
   } else {
     RPDE_CUDA(cudaFuncSetAttribute(fno2d_waxis_mma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    fno2d_waxis_mma_kernel<false><<<(unsigned)ctas, 256, sm, s>>>(x, tab, T, rows, N, R, z, act, xout, kplanes, s_row, s_r);
+    fno2d_waxis_mma_kernel<false><<<grid, 256, sm, s>>>(x, tab, T, rows, N, R, z, act, xout, kplanes, s_row, s_r);
   }
   RPDE_LAUNCH_CHECK();
   return RPDE_OK;

@@ -72,7 +72,7 @@ def test_fno_block2d_forward_and_gradients(B, I, O, H, W, m1, m2, bypass, bias, 
 
 
 def test_fno_block2d_inference_matches_training_forward():
-    """no_grad forward (no spectrum, no pre-activation stored) gives the same output bits as the training forward"""
+    """no_grad forward (no spectrum, no pre-activation stored) gives the same output as the training forward"""
     from resolution_pde_b200 import ops
     g = torch.Generator().manual_seed(5)
     x = torch.randn(2, 32, 32, 128, generator=g).to(DEV)
@@ -83,4 +83,4 @@ def test_fno_block2d_inference_matches_training_forward():
     with torch.no_grad():
         y0 = ops.fno_spectral(x, w1, w2, wb, bb, ops.ACT_GELU)
     y1 = ops.fno_spectral(x.clone().requires_grad_(True), w1, w2, wb, bb, ops.ACT_GELU)
-    assert torch.equal(y0, y1.detach())
+    assert rel(y0, y1.detach()) < 1e-6      # bit-equal unless the W-axis analysis split its rows over CTAs (atomics)

@@ -110,7 +110,9 @@ def test_fused_inference_skips_spectrum_and_preactivation():
         y0 = ops.fno_spectral(x, w, None, wb, bb, ops.ACT_GELU)
     xr = x.clone().requires_grad_(True)
     y1 = ops.fno_spectral(xr, w, None, wb, bb, ops.ACT_GELU)
-    assert torch.equal(y0, y1.detach())
+    # same kernels either way; with few rows the analysis splits each row over several CTAs whose partial sums meet through
+    # fp32 atomics, so two runs agree to the order of those adds, not bit for bit
+    assert rel(y0, y1.detach()) < 1e-6
 
 
 def test_composed_path_still_matches_fixture(composed):
