@@ -261,40 +261,53 @@ __global__ void __launch_bounds__(256) fno1d_synth_bypass_kernel(const float* __
 constexpr int M1_IC = 8;     // input channels per CTA
 constexpr int M1_BC = 16;    // batch elements per staging round
 
-// dsp[k][.][b][i] = sum_o dom[k][.][b][o] * conj(w[i,o,k])       grid (K, ceil(I / 8), ceil(B / 16)), 128 threads = (b, i)
-__global__ void __launch_bounds__(128) fno1d_mix_adjoint_kernel(const float* __restrict__ dom, const float* __restrict__ w,
-                                                                float* __restrict__ dsp, int Bn, int I, int O, int K) {
-  extern __shared__ float sm1[];                      // D[2][M1_BC][O + 1] | W[M1_IC][2 O + 2] (padded rows: no bank conflicts over i)
+// adjoint = 1:  out[k][.][b][i] = sum_o in[k][.][b][o] * conj(w[i,o,k])     (mixing adjoint, Co = I, Cl = O)
+// adjoint = 0:  out[k][.][b][o] = sum_i in[k][.][b][i] * w[i,o,k]           (forward mixing,  Co = O, Cl = I)
+// grid (K, ceil(Co / 8), ceil(B / 16)), 128 threads = (b, output channel of 8); smem: D[2][M1_BC][Cl + 1] | W[8][2 Cl + 2]
+__global__ void __launch_bounds__(128) fno1d_mix_modes_kernel(const float* __restrict__ in, const float* __restrict__ w,
+                                                              float* __restrict__ out, int Bn, int I, int O, int K, int adjoint) {
+  extern __shared__ float sm1[];                      // padded rows: no bank conflicts over b / over the output channel
+  const int Co = adjoint ? I : O, Cl = adjoint ? O : I;
   float* D = sm1;
-  float* Wc = sm1 + 2 * M1_BC * (O + 1);
-  const int k = blockIdx.x, i0 = blockIdx.y * M1_IC, b0 = blockIdx.z * M1_BC;
+  float* Wc = sm1 + 2 * M1_BC * (Cl + 1);
+  const int k = blockIdx.x, c0 = blockIdx.y * M1_IC, b0 = blockIdx.z * M1_BC;
   const int nb = min(M1_BC, Bn - b0);
-  for (int e = threadIdx.x; e < 2 * nb * O; e += 128) {
-    const int o = e % O, rb = e / O, b = rb % nb, ro = rb / nb;
-    D[(ro * M1_BC + b) * (O + 1) + o] = __ldg(dom + ((long long)(k * 2 + ro) * Bn + b0 + b) * O + o);
+  for (int e = threadIdx.x; e < 2 * nb * Cl; e += 128) {
+    const int cl = e % Cl, rb = e / Cl, b = rb % nb, ro = rb / nb;
+    D[(ro * M1_BC + b) * (Cl + 1) + cl] = __ldg(in + ((long long)(k * 2 + ro) * Bn + b0 + b) * Cl + cl);
   }
-  for (int e = threadIdx.x; e < M1_IC * O; e += 128) {
-    const int o = e % O, il = e / O;
+  for (int e = threadIdx.x; e < M1_IC * Cl; e += 128) {
+    const int cl = e % Cl, c = e / Cl;
+    const int i = adjoint ? c0 + c : cl, o = adjoint ? cl : c0 + c;
     float2 v = make_float2(0.f, 0.f);
-    if (i0 + il < I) v = __ldg(reinterpret_cast<const float2*>(w + (((long long)(i0 + il) * O + o) * K + k) * 2));
-    Wc[il * (2 * O + 2) + 2 * o] = v.x;
-    Wc[il * (2 * O + 2) + 2 * o + 1] = v.y;
+    if (c0 + c < Co) v = __ldg(reinterpret_cast<const float2*>(w + (((long long)i * O + o) * K + k) * 2));
+    Wc[c * (2 * Cl + 2) + 2 * cl] = v.x;
+    Wc[c * (2 * Cl + 2) + 2 * cl + 1] = v.y;
   }
   __syncthreads();
-  const int il = threadIdx.x & 7, b = threadIdx.x >> 3;
-  if (b >= nb || i0 + il >= I) return;
-  const float* dr = D + b * (O + 1);
-  const float* di = D + (M1_BC + b) * (O + 1);
-  const float* wp = Wc + il * (2 * O + 2);
+  const int c = threadIdx.x & 7, b = threadIdx.x >> 3;
+  if (b >= nb || c0 + c >= Co) return;
+  const float* dr = D + b * (Cl + 1);
+  const float* di = D + (M1_BC + b) * (Cl + 1);
+  const float* wp = Wc + c * (2 * Cl + 2);
   float re = 0.f, im = 0.f;
+  if (adjoint) {
 #pragma unroll 4
-  for (int o = 0; o < O; ++o) {
-    const float wr = wp[2 * o], wi = wp[2 * o + 1], a = dr[o], c = di[o];
-    re = fmaf(a, wr, re); re = fmaf(c, wi, re);
-    im = fmaf(c, wr, im); im = fmaf(-a, wi, im);
+    for (int cl = 0; cl < Cl; ++cl) {
+      const float wr = wp[2 * cl], wi = wp[2 * cl + 1], a = dr[cl], q = di[cl];
+      re = fmaf(a, wr, re); re = fmaf(q, wi, re);
+      im = fmaf(q, wr, im); im = fmaf(-a, wi, im);
+    }
+  } else {
+#pragma unroll 4
+    for (int cl = 0; cl < Cl; ++cl) {
+      const float wr = wp[2 * cl], wi = wp[2 * cl + 1], a = dr[cl], q = di[cl];
+      re = fmaf(a, wr, re); re = fmaf(-q, wi, re);
+      im = fmaf(a, wi, im); im = fmaf(q, wr, im);
+    }
   }
-  dsp[((long long)(k * 2 + 0) * Bn + b0 + b) * I + i0 + il] = re;
-  dsp[((long long)(k * 2 + 1) * Bn + b0 + b) * I + i0 + il] = im;
+  out[((long long)(k * 2 + 0) * Bn + b0 + b) * Co + c0 + c] = re;
+  out[((long long)(k * 2 + 1) * Bn + b0 + b) * Co + c0 + c] = im;
 }
 
 // dw[i,o,k] = sum_b conj(spec[k][.][b][i]) * dom[k][.][b][o]       grid (K, ceil(I / 8), ceil(O / 32)), 256 threads = (o, i)

@@ -316,10 +316,16 @@ int rpde_fno_block1d_fwd(const float* x, const float* w, const float* fa, const 
   if (!spec) spec = (float*)((char*)ws + align_up((size_t)modes * B * 2 * O * 4));   // inference: spectrum stays in the workspace
   int rc1 = launch_fno1d_analysis(x, fa, spec, B, I, N, modes, nullptr, 0, nullptr, 0, s);
   if (rc1) return rc1;
-  if (smem2 > 48 * 1024)
-    RPDE_CUDA(cudaFuncSetAttribute(fno1d_mix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-  dim3 gm((unsigned)((O + FNO_MO - 1) / FNO_MO), (unsigned)B);
-  fno1d_mix_kernel<<<gm, 256, smem2, s>>>(spec, w, om, B, I, O, modes);
+  if (I <= 128 && B <= 64) {     // small batch: one CTA per (mode, 8 output channels), operands staged once (fno_fused.cuh)
+    dim3 gk((unsigned)modes, (unsigned)((O + M1_IC - 1) / M1_IC), (unsigned)((B + M1_BC - 1) / M1_BC));
+    const size_t smk = (size_t)(2 * M1_BC * (I + 1) + M1_IC * (2 * I + 2)) * sizeof(float);
+    fno1d_mix_modes_kernel<<<gk, 128, smk, s>>>(spec, w, om, B, I, O, modes, 0);
+  } else {
+    if (smem2 > 48 * 1024)
+      RPDE_CUDA(cudaFuncSetAttribute(fno1d_mix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+    dim3 gm((unsigned)((O + FNO_MO - 1) / FNO_MO), (unsigned)B);
+    fno1d_mix_kernel<<<gm, 256, smem2, s>>>(spec, w, om, B, I, O, modes);
+  }
   RPDE_LAUNCH_CHECK();
   return launch_fno1d_synth(x, om, fs4, wb, bb, y, z, B, I, O, N, modes, act, 0, s);
 }
@@ -392,7 +398,7 @@ static int spectral1d_bwd_impl(const float* dy, const float* z, int act, const f
     if (tiled) {
       dim3 gm((unsigned)K, (unsigned)((I + M1_IC - 1) / M1_IC), (unsigned)((B + M1_BC - 1) / M1_BC));
       const size_t smem = (size_t)(2 * M1_BC * (O + 1) + M1_IC * (2 * O + 2)) * sizeof(float);
-      fno1d_mix_adjoint_kernel<<<gm, 128, smem, s>>>(dom, w, dsp, B, I, O, K);
+      fno1d_mix_modes_kernel<<<gm, 128, smem, s>>>(dom, w, dsp, B, I, O, K, 1);
       RPDE_LAUNCH_CHECK();
     } else {
       // 2'. dsp[k] = dom[k] wp[k]^T
