@@ -308,6 +308,199 @@ __global__ void __launch_bounds__(256, W <= 256 ? 2 : 1) fno2d_synth_mma_kernel(
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
+// fno1d_synth_mma_kernel: FNOBlock1d synthesis + 1x1 bypass conv + bias + activation (fno_blocks.py:25-33 around
+// spectral_convolution.py:54), and with adjoint = 1 the complete input gradient (analysis adjoint + wb^T dpre), for up to 64
+// channels per side:   y[b,o,:] = act( sum_r Z[r][b][o] * tab[r][:] + sum_i wb[o,i] * x[b,i,:] + bb[o] ).
+// CTA = (b, 128 points): four point segments x two halves of the output channels over its eight warps.  Nothing is resident
+// across tiles (at batch 16 there are as many tiles as SMs): the CTA stages the table slice of its 128 points (paired layout
+// of fno2d_synth_mma_kernel), the row's Z and the bypass weight as TF32 hi / lo planes, while its x fragments are already in
+// flight.  N % 128 == 0, I, O <= 64, 2 K <= 32.
+constexpr int F1M_LDA = 72;    // A-operand planes [k][o], o < 64: stride = 8 mod 32
+__host__ __device__ constexpr size_t f1m_synth_smem(int RP) {
+  return ((size_t)2 * (RP / 2) * (2 * 128 + 4) + (size_t)2 * 64 * F1M_LDA + (size_t)2 * RP * F1M_LDA + 64) * sizeof(float);
+}
+
+__global__ void __launch_bounds__(256, 1) fno1d_synth_mma_kernel(const float* __restrict__ x, const float* __restrict__ Z,
+                                                                 const float* __restrict__ table, const float* __restrict__ wb,
+                                                                 const float* __restrict__ bb, float* __restrict__ y,
+                                                                 float* __restrict__ z, int Bn, int I, int O, int N, int K, int act,
+                                                                 int adjoint) {
+  constexpr int LDP = 2 * 128 + 4;
+  extern __shared__ __align__(16) float smem[];
+  const int R = 2 * K, RP = (R + 7) & ~7, KS_T = RP / 8, KS_X = wb ? (I + 7) / 8 : 0;
+  float* tabH = smem;
+  float* tabL = tabH + (RP / 2) * LDP;
+  float* wbH = tabL + (RP / 2) * LDP;
+  float* wbL = wbH + 64 * F1M_LDA;
+  float* zH = wbL + 64 * F1M_LDA;
+  float* zL = zH + RP * F1M_LDA;
+  float* biasS = zL + RP * F1M_LDA;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  const int pg = (g >> 1) + 4 * (g & 1);
+  const int b = blockIdx.y, nb = blockIdx.x * 128;
+  const int seg = warp & 3, oh = warp >> 2, n0 = nb + 32 * seg;
+  // x fragments first: their latency hides behind the staging below
+  float4 xb[16];
+  {
+    const float* p = x + ((long long)b * I + t) * N + n0 + 4 * pg;
+#pragma unroll
+    for (int q = 0; q < 16; ++q) {      // channel t + 4 q: k-step q >> 1, fragment row t (+ 4)
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if ((q >> 1) < KS_X && t + 4 * q < I) v = __ldg(reinterpret_cast<const float4*>(p + (long long)4 * q * N));
+      xb[q] = v;
+    }
+  }
+  // staging in batches of eight independent loads per thread (one L2 round trip per batch instead of one per element)
+  for (int e0 = tid; e0 < RP * 128; e0 += 8 * 256) {
+    float v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int e = e0 + 256 * u, r = e >> 7, n = e & 127;
+      v[u] = (e < RP * 128 && r < R) ? __ldg(table + (adjoint ? (long long)r : (long long)(r & 1) * K + (r >> 1)) * N + nb + n) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int e = e0 + 256 * u, r = e >> 7, n = e & 127;
+      if (e >= RP * 128) continue;
+      uint32_t hi, lo;
+      tf32_split_rn(v[u], hi, lo);
+      const int ks = r >> 3, tt = r & 3, half = (r >> 2) & 1;
+      const int off = (ks * 4 + tt) * LDP + (n >> 5) * 64 + f2m_slot((n >> 2) & 7) * 8 + (n & 3) * 2 + half;
+      tabH[off] = __uint_as_float(hi);
+      tabL[off] = __uint_as_float(tf32_hi(__uint_as_float(lo)));
+    }
+  }
+  for (int e0 = tid; e0 < 64 * 64; e0 += 8 * 256) {
+    float v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int e = e0 + 256 * u, i = e >> 6, o = e & 63;   // A[o][k = i]
+      v[u] = (wb && i < I && o < O) ? __ldg(adjoint ? wb + (long long)i * O + o : wb + (long long)o * I + i) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int e = e0 + 256 * u, i = e >> 6, o = e & 63;
+      uint32_t hi, lo;
+      tf32_split_rn(v[u], hi, lo);
+      wbH[i * F1M_LDA + o] = __uint_as_float(hi);
+      wbL[i * F1M_LDA + o] = __uint_as_float(tf32_hi(__uint_as_float(lo)));
+    }
+  }
+  {
+    float v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int e = tid + 256 * u, r = e >> 6, o = e & 63;
+      v[u] = (e < RP * 64 && r < R && o < O) ? __ldg(Z + ((long long)r * Bn + b) * O + o) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int e = tid + 256 * u, r = e >> 6, o = e & 63;
+      if (e >= RP * 64) continue;
+      uint32_t hi, lo;
+      tf32_split_rn(v[u], hi, lo);
+      zH[r * F1M_LDA + o] = __uint_as_float(hi);
+      zL[r * F1M_LDA + o] = __uint_as_float(tf32_hi(__uint_as_float(lo)));
+    }
+  }
+  if (tid < 64) biasS[tid] = (bb && tid < O) ? __ldg(bb + tid) : 0.f;
+  __syncthreads();
+
+  float acc[2][4][4];
+#pragma unroll
+  for (int m = 0; m < 2; ++m)
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) acc[m][j][c] = 0.f;
+  const int tab_off = t * LDP + seg * 64 + f2m_slot(pg) * 8;
+  const int a_off = t * F1M_LDA + 32 * oh + g;
+#pragma unroll
+  for (int ks = 0; ks < 4; ++ks) {
+    if (ks < KS_T) {
+      const float4 h0 = *reinterpret_cast<const float4*>(tabH + tab_off + ks * 4 * LDP);
+      const float4 h1 = *reinterpret_cast<const float4*>(tabH + tab_off + ks * 4 * LDP + 4);
+      const float4 l0 = *reinterpret_cast<const float4*>(tabL + tab_off + ks * 4 * LDP);
+      const float4 l1 = *reinterpret_cast<const float4*>(tabL + tab_off + ks * 4 * LDP + 4);
+#pragma unroll
+      for (int m = 0; m < 2; ++m) {
+        uint32_t ah[4], al[4];
+        const int o = a_off + ks * 8 * F1M_LDA + 16 * m;
+        ah[0] = __float_as_uint(zH[o]);
+        ah[1] = __float_as_uint(zH[o + 8]);
+        ah[2] = __float_as_uint(zH[o + 4 * F1M_LDA]);
+        ah[3] = __float_as_uint(zH[o + 4 * F1M_LDA + 8]);
+        al[0] = __float_as_uint(zL[o]);
+        al[1] = __float_as_uint(zL[o + 8]);
+        al[2] = __float_as_uint(zL[o + 4 * F1M_LDA]);
+        al[3] = __float_as_uint(zL[o + 4 * F1M_LDA + 8]);
+        mma_3xtf32(acc[m][0], ah, al, __float_as_uint(h0.x), __float_as_uint(h0.y), __float_as_uint(l0.x), __float_as_uint(l0.y));
+        mma_3xtf32(acc[m][1], ah, al, __float_as_uint(h0.z), __float_as_uint(h0.w), __float_as_uint(l0.z), __float_as_uint(l0.w));
+        mma_3xtf32(acc[m][2], ah, al, __float_as_uint(h1.x), __float_as_uint(h1.y), __float_as_uint(l1.x), __float_as_uint(l1.y));
+        mma_3xtf32(acc[m][3], ah, al, __float_as_uint(h1.z), __float_as_uint(h1.w), __float_as_uint(l1.z), __float_as_uint(l1.w));
+      }
+    }
+  }
+#pragma unroll
+  for (int ks = 0; ks < 8; ++ks) {
+    if (ks < KS_X) {
+      const float v0[4] = {xb[2 * ks].x, xb[2 * ks].y, xb[2 * ks].z, xb[2 * ks].w};
+      const float v1[4] = {xb[2 * ks + 1].x, xb[2 * ks + 1].y, xb[2 * ks + 1].z, xb[2 * ks + 1].w};
+      uint32_t bh0[4], bh1[4], bl0[4], bl1[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        tf32_split(v0[j], bh0[j], bl0[j]);
+        tf32_split(v1[j], bh1[j], bl1[j]);
+      }
+#pragma unroll
+      for (int m = 0; m < 2; ++m) {
+        uint32_t ah[4], al[4];
+        const int o = a_off + ks * 8 * F1M_LDA + 16 * m;
+        ah[0] = __float_as_uint(wbH[o]);
+        ah[1] = __float_as_uint(wbH[o + 8]);
+        ah[2] = __float_as_uint(wbH[o + 4 * F1M_LDA]);
+        ah[3] = __float_as_uint(wbH[o + 4 * F1M_LDA + 8]);
+        al[0] = __float_as_uint(wbL[o]);
+        al[1] = __float_as_uint(wbL[o + 8]);
+        al[2] = __float_as_uint(wbL[o + 4 * F1M_LDA]);
+        al[3] = __float_as_uint(wbL[o + 4 * F1M_LDA + 8]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) mma_3xtf32(acc[m][j], ah, al, bh0[j], bh1[j], bl0[j], bl1[j]);
+      }
+    }
+  }
+  float* yp = y + ((long long)b * O + 32 * oh + g) * N + n0 + 4 * t;
+  const long long zd = z ? z - y : 0;
+#pragma unroll
+  for (int m = 0; m < 2; ++m) {
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const int o = 32 * oh + 16 * m + g + 8 * half;
+      if (o < O) {
+        const float bias = biasS[o];
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          float pre[4], out[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) pre[j] = acc[m][j][2 * half + c] + bias;
+          if (act == ACT_GELU) {
+            float d0, d1;
+            gelu_both2(pre[0], pre[1], out[0], out[1], d0, d1);
+            gelu_both2(pre[2], pre[3], out[2], out[3], d0, d1);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) out[j] = act_f(act, pre[j]);
+          }
+          *reinterpret_cast<float4*>(yp + 16 * c) = make_float4(out[0], out[1], out[2], out[3]);
+          if (z) *reinterpret_cast<float4*>(yp + zd + 16 * c) = make_float4(pre[0], pre[1], pre[2], pre[3]);
+        }
+      }
+      yp += (long long)8 * N;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
 // conv1x1_wgrad_mma_kernel: parameter gradients of a channels-first 1x1 convolution (fno_blocks.py:29,67 bypass conv and
 // the lifting / projection layers),  dw[o][i] = sum_(b,s) dy[b,o,s] x[b,i,s],  db[o] = sum_(b,s) dy[b,o,s],
 // as D[o][i] = A[o][k] B[k][i] with k = grid point.  It replaces a split-K contraction with a 10^6-long reduction

@@ -255,6 +255,15 @@ static int launch_fno1d_synth(const float* x, const float* om, const float* tabl
     RPDE_LAUNCH_CHECK();
     return RPDE_OK;
   }
+  if (use_mma && Hd == 1 && N % 128 == 0 && I <= 64 && O <= 64 && 2 * modes <= F2M_MAXR && B <= 65535 && !tn_sel) {
+    // FNOBlock1d: one CTA per (b, 128 points) on the warp-level tensor path (fno2d_mma.cuh)
+    const size_t smem = f1m_synth_smem(RPm);
+    RPDE_CUDA(cudaFuncSetAttribute(fno1d_synth_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 g1((unsigned)(N / 128), (unsigned)B);
+    fno1d_synth_mma_kernel<<<g1, 256, smem, s>>>(x, om, table, wb, bb, y, z, B, I, O, N, modes, act, adjoint);
+    RPDE_LAUNCH_CHECK();
+    return RPDE_OK;
+  }
   const bool wide = tn_sel ? tn_sel == 128 : (long long)((N + 127) / 128) * B >= 2 * 148;   // enough 128-point tiles to fill the SMs twice
   if (O <= 32 && (wide || Hd > 1)) {     // narrow layers (FNO2d width 32): a 32-channel register tile, no padded FMAs
     dim3 g2((unsigned)((N + 127) / 128), (unsigned)B);

@@ -29,9 +29,16 @@ _fno_fused = os.environ.get("RPDE_FNO_FUSED", "1") != "0"   # fused FNOBlock1d f
 # 0.723 ms composed -> 0.679 ms fused forward -> 0.638 ms with this prologue (profiles/README.md r1i); 0 = composed prologue
 _fno_fused_bwd = os.environ.get("RPDE_FNO_FUSED_BWD", "1") != "0"
 # rpde_fno_block1d_bwd can also produce dx (analysis adjoint + bypass dgrad) in one kernel when it is handed the bypass
-# weight; parity-green on B200 (profiles/r1j_tests.log) but measured slower than the two separate kernels (0.656 vs 0.638
-# ms/step, FNO1d Burgers), so the wrapper only passes the weight when asked to
-_fno_fused_dx = os.environ.get("RPDE_FNO_FUSED_DX", "0") != "0"
+# weight.  With the tensor-path synthesis kernel (csrc/fno2d_mma.cuh: N % 128 == 0, at most 64 channels) that is the faster
+# choice on launch-bound batches (FNO1d Burgers, batch 16: 0.383 against 0.399 ms/step) and the slower one on large ones
+# (batch 256: 3.34 against 2.80 ms), so the default is automatic; RPDE_FNO_FUSED_DX=1 / 0 forces it on / off.
+_fno_fused_dx = {"1": True, "0": False}.get(os.environ.get("RPDE_FNO_FUSED_DX", ""), None)
+
+
+def _use_fused_dx(B: int, I: int, O: int, n: int) -> bool:
+    if _fno_fused_dx is not None:
+        return _fno_fused_dx
+    return B <= 64 and n % 128 == 0 and I <= 64 and O <= 64
 
 
 def set_precision(name: str) -> None:
@@ -352,7 +359,7 @@ class _FNOSpectralFn(torch.autograd.Function):
                 nb = c.lib.rpde_spectral1d_workspace_bytes(B, I, O, n, k)
                 ws = _ws(nb, x.device)
                 wbc = wb.detach().reshape(O, I).contiguous() if wb is not None else None
-                dx_done = bool(_fno_fused_dx and wbc is not None and need_x)   # dx then includes the bypass conv's input gradient
+                dx_done = bool(_use_fused_dx(B, I, O, n) and wbc is not None and need_x)   # dx then includes the bypass conv's input gradient
                 _lib.check(c.lib.rpde_fno_block1d_bwd(_p(dy), _p(z) if dpre is not None else None, act, _p(w1r), _p(tabs[0]), _p(fs4),
                                                       _p(spec), _p(wbc) if dx_done else None, _p(dpre), _p(dx), 0, _p(dw1), B, I, O,
                                                       n, k, _p(ws), nb, c.stream), "rpde_fno_block1d_bwd")

@@ -125,3 +125,31 @@ def test_composed_path_still_matches_fixture(composed):
     with composed:
         out = m(torch.from_numpy(z["x"]).to(DEV))
     assert rel(out, z["out"]) < TOL
+
+
+@pytest.mark.parametrize("force", [True, False])
+@pytest.mark.parametrize("B,I,O,N,K", [(3, 24, 40, 256, 9), (2, 64, 64, 1024, 16)])
+def test_fused_input_gradient_switch(force, B, I, O, N, K):
+    """dx from one kernel (tensor-path synthesis kernel in adjoint mode: analysis adjoint + wb^T dpre) or from the analysis-adjoint
+    contraction plus rpde_conv1x1_bwd_input: the automatic choice (ops._use_fused_dx) may take either, both must match the oracle."""
+    from resolution_pde_b200 import ops
+    g = torch.Generator().manual_seed(N + K)
+    x = torch.randn(B, I, N, generator=g)
+    w = torch.complex(torch.rand(I, O, K, generator=g), torch.rand(I, O, K, generator=g)) / (I * O) ** 0.5
+    wb = torch.randn(O, I, 1, generator=g) / I ** 0.5
+    bb = torch.randn(O, generator=g)
+    gy = torch.randn(B, O, N, generator=g)
+    old, ops._fno_fused_dx = ops._fno_fused_dx, force
+    try:
+        leaves = [t.clone().to(DEV).requires_grad_(True) for t in (x, w, wb, bb)]
+        y = ops.fno_spectral(leaves[0], leaves[1], None, leaves[2], leaves[3], ops.ACT_GELU)
+        y.backward(gy.to(DEV))
+    finally:
+        ops._fno_fused_dx = old
+    lo = [x.double().requires_grad_(True), w.to(torch.complex128).requires_grad_(True), wb.double().requires_grad_(True),
+          bb.double().requires_grad_(True)]
+    yo = _oracle(lo[0], lo[1], lo[2], lo[3], "gelu")
+    yo.backward(gy.double())
+    assert rel(y, yo) < TOL
+    for a, o in zip(leaves, lo):
+        assert rel(a.grad, o.grad) < TOL, rel(a.grad, o.grad)
