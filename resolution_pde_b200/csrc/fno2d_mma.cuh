@@ -647,13 +647,24 @@ __host__ __device__ constexpr size_t mlp_fwd_smem(int I, int Hd) {
 // (A[m = i][k = h]: lanes (g, t) -> row h0 + t, column i0 + g) take a 2-way conflict (cheaper than a second copy).
 __device__ __forceinline__ void mlp_stage_w1(const float* __restrict__ w1, float* w1h, float* w1l, int I, int Hd, int HP, int IP) {
   const int LDW = IP + 4;
-  for (int e = threadIdx.x; e < HP * IP; e += blockDim.x) {
-    const int h = e / IP, i = e - h * IP;
-    const float v = (h < Hd && i < I) ? __ldg(w1 + (long long)h * I + i) : 0.f;
-    uint32_t hi, lo;
-    tf32_split_rn(v, hi, lo);
-    w1h[h * LDW + i] = __uint_as_float(hi);
-    w1l[h * LDW + i] = __uint_as_float(tf32_hi(__uint_as_float(lo)));
+  // eight independent loads per thread and round trip (a plain element loop serialises on L2 latency: 64 round trips for the
+  // 256 x 64 weight of the FNO1d projection, most of the kernel's time on a small batch)
+  for (int e0 = threadIdx.x; e0 < HP * IP; e0 += 8 * blockDim.x) {
+    float v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int e = e0 + u * blockDim.x, h = e / IP, i = e - h * IP;
+      v[u] = (e < HP * IP && h < Hd && i < I) ? __ldg(w1 + (long long)h * I + i) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int e = e0 + u * blockDim.x, h = e / IP, i = e - h * IP;
+      if (e >= HP * IP) continue;
+      uint32_t hi, lo;
+      tf32_split_rn(v[u], hi, lo);
+      w1h[h * LDW + i] = __uint_as_float(hi);
+      w1l[h * LDW + i] = __uint_as_float(tf32_hi(__uint_as_float(lo)));
+    }
   }
 }
 // A fragment of the z orientation at (h0, i0): bz = plane + g * LDW + t

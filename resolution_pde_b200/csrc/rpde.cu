@@ -152,14 +152,24 @@ int rpde_dft_table(float* out, int kind, int n, int k, int m1, double scale, rpd
 
 static int pack_w(const float* w, float* wp, int I, int O, int modes, int keep, int sub, int sub_keep, cudaStream_t s) {
   const long long total = (long long)keep * sub_keep * 4 * I * O;
-  pack_weights_kernel<<<grid_for(total), 256, 0, s>>>(w, wp, I, O, modes, keep, sub, sub_keep);
+  if (sub == 1 && sub_keep == 1 && keep <= 128 && I <= 65535 && (O + 31) / 32 <= 65535) {
+    dim3 g((unsigned)I, (unsigned)((O + 31) / 32));
+    pack_weights_tiled_kernel<<<g, 256, 0, s>>>(w, wp, I, O, modes, keep);
+  } else {
+    pack_weights_kernel<<<grid_for(total), 256, 0, s>>>(w, wp, I, O, modes, keep, sub, sub_keep);
+  }
   RPDE_LAUNCH_CHECK();
   return RPDE_OK;
 }
 static int unpack_g(const float* P, float* dw, int I, int O, int modes, int keep, int sub, int sub_keep, int acc,
                     cudaStream_t s) {
   const long long total = (long long)I * O * modes;
-  unpack_wgrad_kernel<<<grid_for(total), 256, 0, s>>>(P, dw, I, O, modes, keep, sub, sub_keep, acc);
+  if (sub == 1 && sub_keep == 1 && keep <= 128 && I <= 65535 && (O + 31) / 32 <= 65535) {
+    dim3 g((unsigned)I, (unsigned)((O + 31) / 32));
+    unpack_wgrad_tiled_kernel<<<g, 256, 0, s>>>(P, dw, I, O, modes, keep, acc);
+  } else {
+    unpack_wgrad_kernel<<<grid_for(total), 256, 0, s>>>(P, dw, I, O, modes, keep, sub, sub_keep, acc);
+  }
   RPDE_LAUNCH_CHECK();
   return RPDE_OK;
 }
