@@ -337,19 +337,8 @@ __global__ void __launch_bounds__(256, 1) fno1d_synth_mma_kernel(const float* __
   float* biasS = zL + RP * F1M_LDA;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
   const int pg = (g >> 1) + 4 * (g & 1);
-  const int b = blockIdx.y, nb = blockIdx.x * 128;
+  const int nb = blockIdx.x * 128;
   const int seg = warp & 3, oh = warp >> 2, n0 = nb + 32 * seg;
-  // x fragments first: their latency hides behind the staging below
-  float4 xb[16];
-  {
-    const float* p = x + ((long long)b * I + t) * N + n0 + 4 * pg;
-#pragma unroll
-    for (int q = 0; q < 16; ++q) {      // channel t + 4 q: k-step q >> 1, fragment row t (+ 4)
-      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      if ((q >> 1) < KS_X && t + 4 * q < I) v = __ldg(reinterpret_cast<const float4*>(p + (long long)4 * q * N));
-      xb[q] = v;
-    }
-  }
   // staging in batches of eight independent loads per thread (one L2 round trip per batch instead of one per element)
   for (int e0 = tid; e0 < RP * 128; e0 += 8 * 256) {
     float v[8];
@@ -386,6 +375,22 @@ __global__ void __launch_bounds__(256, 1) fno1d_synth_mma_kernel(const float* __
       wbL[i * F1M_LDA + o] = __uint_as_float(tf32_hi(__uint_as_float(lo)));
     }
   }
+  if (tid < 64) biasS[tid] = (bb && tid < O) ? __ldg(bb + tid) : 0.f;
+  // The table slice of this CTA's 128 points, the bypass weight and the bias stay for all of its rows: blockIdx.y strides over b
+  // (one row per CTA at batch 16, ~14 at batch 256); per row only Z is re-staged, between two barriers.
+  for (int b = blockIdx.y; b < Bn; b += gridDim.y) {
+  // x fragments first: their latency hides behind the staging below
+  float4 xb[16];
+  {
+    const float* p = x + ((long long)b * I + t) * N + n0 + 4 * pg;
+#pragma unroll
+    for (int q = 0; q < 16; ++q) {      // channel t + 4 q: k-step q >> 1, fragment row t (+ 4)
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if ((q >> 1) < KS_X && t + 4 * q < I) v = __ldg(reinterpret_cast<const float4*>(p + (long long)4 * q * N));
+      xb[q] = v;
+    }
+  }
+  __syncthreads();      // the previous row's MMAs are done with zH / zL (and the resident operands are staged)
   {
     float v[8];
 #pragma unroll
@@ -403,7 +408,6 @@ __global__ void __launch_bounds__(256, 1) fno1d_synth_mma_kernel(const float* __
       zL[r * F1M_LDA + o] = __uint_as_float(tf32_hi(__uint_as_float(lo)));
     }
   }
-  if (tid < 64) biasS[tid] = (bb && tid < O) ? __ldg(bb + tid) : 0.f;
   __syncthreads();
 
   float acc[2][4][4];
@@ -498,6 +502,7 @@ __global__ void __launch_bounds__(256, 1) fno1d_synth_mma_kernel(const float* __
       yp += (long long)8 * N;
     }
   }
+  }   // rows
 }
 
 // ---------------------------------------------------------------------------------------------------------------------

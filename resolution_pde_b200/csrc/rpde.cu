@@ -265,11 +265,14 @@ static int launch_fno1d_synth(const float* x, const float* om, const float* tabl
     RPDE_LAUNCH_CHECK();
     return RPDE_OK;
   }
-  if (use_mma && Hd == 1 && N % 128 == 0 && I <= 64 && O <= 64 && 2 * modes <= F2M_MAXR && B <= 65535 && !tn_sel) {
+  if (use_mma && Hd == 1 && N % 128 == 0 && I <= 64 && O <= 64 && 2 * modes <= F2M_MAXR && !tn_sel) {
     // FNOBlock1d: one CTA per (b, 128 points) on the warp-level tensor path (fno2d_mma.cuh)
     const size_t smem = f1m_synth_smem(RPm);
     RPDE_CUDA(cudaFuncSetAttribute(fno1d_synth_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    dim3 g1((unsigned)(N / 128), (unsigned)B);
+    const int chunks = N / 128;
+    int by = 148 / chunks > 0 ? 148 / chunks : 1;  // one resident CTA per SM (146 registers); more rows are walked by the CTA
+    if (by > B) by = B;
+    dim3 g1((unsigned)chunks, (unsigned)by);
     fno1d_synth_mma_kernel<<<g1, 256, smem, s>>>(x, om, table, wb, bb, y, z, B, I, O, N, modes, act, adjoint);
     RPDE_LAUNCH_CHECK();
     return RPDE_OK;
