@@ -501,7 +501,9 @@ static int launch_waxis_mma(const float* x, const float* tab, float* T, long lon
   long long ctas = ((rows + 15) / 16 + 7) / 8;
   // few row tiles: split the points of a row over gridDim.y CTAs (partial sums meet in T through atomics) until ~128 CTAs exist
   int split = 1;
-  while (ctas * split < 128 && N % (64 * split) == 0 && N / (2 * split) >= 64) split *= 2;
+  // ... or until both TF32 planes of the table slice fit (two CTAs per SM, no splitting of table fragments in the loop)
+  while ((ctas * split < 128 || f2m_waxis_smem(N / split, RP, true) > 100 * 1024) && N % (64 * split) == 0 && N / (2 * split) >= 64)
+    split *= 2;
   const int Wc = N / split;
   const bool presplit = f2m_waxis_smem(Wc, RP, true) <= 100 * 1024;
   const size_t sm = f2m_waxis_smem(Wc, RP, presplit);
