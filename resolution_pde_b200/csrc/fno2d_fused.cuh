@@ -234,13 +234,14 @@ constexpr int F2X_CL = 32;   // looped channels per staging round
 // smem: S[cl][ri][b][16] | Wt[cl][c][ky][re|im].  VEC: Ky % 4 == 0 and 16-byte aligned operands -> float4 staging
 // (a spectrum row is Ky floats, a weight row Ky complex numbers: 3 and 6 float4 at Ky = 12).
 constexpr int F2X_MB = 8;    // batch elements per CTA of the mixing kernel
-constexpr int F2X_MCL = 16;  // looped channels per staging round of the mixing kernel (32 KB of static shared memory)
+constexpr int F2X_MCL = 32;  // looped channels per staging round of the mixing kernel (64 KB of dynamic shared memory: one round at width 32)
 template <bool VEC>
 __global__ void __launch_bounds__(256) fno2d_mix_tiled_kernel(const float* __restrict__ in, const float* __restrict__ w1,
                                                               const float* __restrict__ w2, float* __restrict__ out, int Bn, int I,
                                                               int O, int m1, int Ky, int mode) {
-  __shared__ __align__(16) float S[F2X_MCL * 2 * F2X_MB * F2X_KY];      // 16 KB
-  __shared__ __align__(16) float Wt[F2X_MCL * F2X_OC * F2X_KY * 2];     // 16 KB
+  extern __shared__ __align__(16) float mixsm[];
+  float* S = mixsm;                                         // F2X_MCL * 2 * F2X_MB * F2X_KY   (32 KB)
+  float* Wt = mixsm + F2X_MCL * 2 * F2X_MB * F2X_KY;        // F2X_MCL * F2X_OC * F2X_KY * 2   (32 KB)
   const int J = 2 * m1;
   const int Co = mode ? I : O, Cl = mode ? O : I;
   const int j = blockIdx.x, co0 = blockIdx.y * F2X_OC, b0 = blockIdx.z * F2X_MB;

@@ -1400,25 +1400,41 @@ __global__ void __launch_bounds__(256) fno2d_rows_mma_kernel(const float* __rest
   // raw operands of one k-step: every global load is issued before the first value is used, and the next k-step's loads go
   // out before the current k-step's MMAs (the loop is a chain of L2 round trips otherwise)
   const int ks_end = min(ksteps, (warp + 1) * per);
+  // per-lane operand bases, so that a load is one multiply-add away (the address arithmetic of 20 predicated scalar loads per
+  // k-step was most of this kernel's instructions):
+  //   B: k = 8 ks + t + 4 q -> row h = 4 ks + 2 q + (t >> 1), r = t & 1; column n = g of tile nt -> plane nt >> 1, ky = 8 (nt & 1) + g
+  //   A: a = 16 m + g + 8 (q & 1), k = 8 ks + t + 4 (q >> 1)
+  const float* Tb[4];
+  bool okb[4];
+#pragma unroll
+  for (int nt = 0; nt < 4; ++nt) {
+    const long long p = p0 + (nt >> 1);
+    const int ky = 8 * (nt & 1) + g;
+    okb[nt] = p < planes && ky < Ky;
+    Tb[nt] = T + (okb[nt] ? (p * H + (t >> 1)) * R + 2 * ky + (t & 1) : 0);
+  }
+  int ao[MT][4];
+  bool oka[MT][2];
+#pragma unroll
+  for (int m = 0; m < MT; ++m) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) ao[m][q] = (t + 4 * (q >> 1)) * A + 16 * m + g + 8 * (q & 1);
+    oka[m][0] = 16 * m + g < A;
+    oka[m][1] = 16 * m + g + 8 < A;
+  }
   auto load = [&](int ks, float (&braw)[4][2], float (&araw)[MT][4]) {
-    // B: k = 8 ks + t (+ 4) -> (h, r) = (k >> 1, k & 1); column n = g of tile nt -> plane nt >> 1, ky = 8 (nt & 1) + g
+    const bool k0 = 8 * ks + t < K, k1 = 8 * ks + t + 4 < K;
+    const long long rb = (long long)(4 * ks) * R;
 #pragma unroll
     for (int nt = 0; nt < 4; ++nt) {
-      const long long p = p0 + (nt >> 1);
-      const int ky = 8 * (nt & 1) + g;
-#pragma unroll
-      for (int q = 0; q < 2; ++q) {
-        const int k = 8 * ks + t + 4 * q;
-        braw[nt][q] = (p < planes && ky < Ky && k < K) ? __ldg(T + (p * H + (k >> 1)) * R + 2 * ky + (k & 1)) : 0.f;
-      }
+      braw[nt][0] = (okb[nt] && k0) ? __ldg(Tb[nt] + rb) : 0.f;
+      braw[nt][1] = (okb[nt] && k1) ? __ldg(Tb[nt] + rb + 2 * R) : 0.f;
     }
+    const float* ta = tab + (long long)(8 * ks) * A;
 #pragma unroll
     for (int m = 0; m < MT; ++m)
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const int a = 16 * m + g + 8 * (q & 1), k = 8 * ks + t + 4 * (q >> 1);
-        araw[m][q] = (a < A && k < K) ? __ldg(tab + (long long)k * A + a) : 0.f;
-      }
+      for (int q = 0; q < 4; ++q) araw[m][q] = (oka[m][q & 1] && ((q >> 1) ? k1 : k0)) ? __ldg(ta + ao[m][q]) : 0.f;
   };
   float bnext[4][2], anext[MT][4];
   if (warp * per < ks_end) load(warp * per, bnext, anext);

@@ -610,10 +610,14 @@ static int launch_fno2d_mix(const float* in, const float* w1, const float* w2, f
   if (Ky <= F2X_KY && (long long)B <= 65535LL * F2X_MB) {
     dim3 g((unsigned)J, (unsigned)((Co + F2X_OC - 1) / F2X_OC), (unsigned)((B + F2X_MB - 1) / F2X_MB));
     auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
-    if (Ky % 4 == 0 && al16(in) && al16(w1) && al16(w2))
-      fno2d_mix_tiled_kernel<true><<<g, 256, 0, s>>>(in, w1, w2, out, B, I, O, m1, Ky, mode);
-    else
-      fno2d_mix_tiled_kernel<false><<<g, 256, 0, s>>>(in, w1, w2, out, B, I, O, m1, Ky, mode);
+    const size_t smem = (size_t)(F2X_MCL * 2 * F2X_MB * F2X_KY + F2X_MCL * F2X_OC * F2X_KY * 2) * sizeof(float);   // 64 KB
+    if (Ky % 4 == 0 && al16(in) && al16(w1) && al16(w2)) {
+      RPDE_CUDA(cudaFuncSetAttribute(fno2d_mix_tiled_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      fno2d_mix_tiled_kernel<true><<<g, 256, smem, s>>>(in, w1, w2, out, B, I, O, m1, Ky, mode);
+    } else {
+      RPDE_CUDA(cudaFuncSetAttribute(fno2d_mix_tiled_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      fno2d_mix_tiled_kernel<false><<<g, 256, smem, s>>>(in, w1, w2, out, B, I, O, m1, Ky, mode);
+    }
   } else {
     const long long total = (long long)B * Co * J * Ky;
     fno2d_mix_kernel<<<grid_for(total), 256, 0, s>>>(in, w1, w2, out, B, I, O, m1, Ky, mode);
